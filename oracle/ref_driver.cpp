@@ -1,0 +1,173 @@
+// TEST INFRASTRUCTURE — not part of the product path.
+//
+// Batch driver over the UNMODIFIED reference core.  This file is ours; it only *calls* the
+// reference (tiny_setup / tiny_set_* / tiny_solve from tinympc/TinyMPC/src/tinympc/tiny_api.hpp)
+// and is compiled together with the reference sources where they lie under /root/reference
+// by oracle/Makefile into oracle/_ref/libtinympc_refbatch.so.  It exists because the
+// reference's own C ABI (src/bindings.cpp) is a process-wide singleton that hides
+// `solution->iter` and cannot run instances on several host threads.
+//
+// One TinySolver per host thread; instances are dealt to threads in contiguous blocks.
+// The per-solve "Solver converged in N iterations" line (admm.cpp:373) is silenced by
+// putting std::cout into a failed state for the duration of the run.
+#include <chrono>
+#include <cstring>
+#include <iostream>
+#include <thread>
+#include <vector>
+
+#include "tinympc/tiny_api.hpp"
+#include "tinympc/types.hpp"
+
+#include "batch_problem.h"
+
+namespace {
+
+using MapMat = Eigen::Map<const Eigen::Matrix<double, Eigen::Dynamic, Eigen::Dynamic>>;
+using MapVec = Eigen::Map<const Eigen::Matrix<double, Eigen::Dynamic, 1>>;
+using MapVecI = Eigen::Map<const Eigen::VectorXi>;
+
+void free_solver(TinySolver *s) {
+    if (!s) return;
+    delete s->solution; delete s->cache; delete s->settings; delete s->work; delete s;
+}
+
+// Build a solver the way bindings.cpp does, then apply constraints/settings from P.
+TinySolver *make_solver(const tmpc_problem *P) {
+    const int nx = P->nx, nu = P->nu, N = P->N;
+    tinyMatrix A = MapMat(P->A, nx, nx), B = MapMat(P->B, nx, nu), f = MapMat(P->f, nx, 1);
+    tinyMatrix Q = MapMat(P->Q, nx, nx), R = MapMat(P->R, nu, nu);
+    TinySolver *s = nullptr;
+    if (tiny_setup(&s, A, B, f, Q, R, P->rho, nx, nu, N, 0) != 0) { free_solver(s); return nullptr; }
+
+    if (P->x_min && !P->bounds_per_instance) {
+        tiny_set_bound_constraints(s, MapMat(P->x_min, nx, N), MapMat(P->x_max, nx, N),
+                                   MapMat(P->u_min, nu, N - 1), MapMat(P->u_max, nu, N - 1));
+    }
+    if (P->num_state_cones > 0 || P->num_input_cones > 0) {
+        // definition order is (state triple, input triple): tiny_api.cpp:166-168
+        Eigen::VectorXi Acx = MapVecI(P->Acx, P->num_state_cones), qcx = MapVecI(P->qcx, P->num_state_cones);
+        Eigen::VectorXi Acu = MapVecI(P->Acu, P->num_input_cones), qcu = MapVecI(P->qcu, P->num_input_cones);
+        tinyVector cx = MapVec(P->cx, P->num_state_cones), cu = MapVec(P->cu, P->num_input_cones);
+        tiny_set_cone_constraints(s, Acx, qcx, cx, Acu, qcu, cu);
+    }
+    if (P->num_state_linear > 0 || P->num_input_linear > 0) {
+        tinyMatrix Ax = MapMat(P->Alin_x, P->num_state_linear, nx), Au = MapMat(P->Alin_u, P->num_input_linear, nu);
+        tinyVector bx = MapVec(P->blin_x, P->num_state_linear), bu = MapVec(P->blin_u, P->num_input_linear);
+        tiny_set_linear_constraints(s, Ax, bx, Au, bu);
+    }
+    if (P->Kinf) {  // set_cache_terms semantics: bindings.cpp:277-280
+        s->cache->Kinf = MapMat(P->Kinf, nu, nx);
+        s->cache->Pinf = MapMat(P->Pinf, nx, nx);
+        s->cache->Quu_inv = MapMat(P->Quu_inv, nu, nu);
+        s->cache->AmBKt = MapMat(P->AmBKt, nx, nx);
+    }
+    TinySettings *st = s->settings;
+    st->abs_pri_tol = P->abs_pri_tol; st->abs_dua_tol = P->abs_dua_tol;
+    st->max_iter = P->max_iter; st->check_termination = P->check_termination;
+    st->en_state_bound = P->en_state_bound; st->en_input_bound = P->en_input_bound;
+    st->en_state_soc = P->en_state_soc; st->en_input_soc = P->en_input_soc;
+    st->en_state_linear = P->en_state_linear; st->en_input_linear = P->en_input_linear;
+    st->adaptive_rho = 0;
+    return s;
+}
+
+// Back to the state tiny_setup leaves (tiny_api.cpp:68-105), without redoing the Riccati cache.
+void zero_workspace(TinySolver *s) {
+    TinyWorkspace *w = s->work;
+    for (tinyMatrix *m : {&w->x, &w->u, &w->q, &w->r, &w->p, &w->d, &w->v, &w->vnew, &w->z, &w->znew, &w->g, &w->y,
+                          &w->vc, &w->vcnew, &w->zc, &w->zcnew, &w->gc, &w->yc, &w->vl, &w->vlnew, &w->zl,
+                          &w->zlnew, &w->gl, &w->yl, &w->Xref, &w->Uref})
+        m->setZero();
+    s->solution->x.setZero(); s->solution->u.setZero();
+    s->solution->iter = 0; s->solution->solved = 0;
+    w->iter = 0; w->status = 0;
+}
+
+}  // namespace
+
+extern "C" int ref_batch_run(const tmpc_problem *P, int B, int nsteps, const double *x0, const double *Xref,
+                             const double *Uref, int ref_mode, int nthreads, int *ret, int *iters, double *Xsol,
+                             double *Usol, double *x_final, double *seconds) {
+    if (!P || B < 0 || nsteps < 1 || !x0) return 1;
+    if (P->check_termination == 0) return 2;  // iter % 0 in admm.cpp:255 is a SIGFPE; refuse instead of crashing
+    const int nx = P->nx, nu = P->nu, N = P->N;
+    if (nthreads < 1) nthreads = 1;
+    if (nthreads > B && B > 0) nthreads = B;
+    const size_t sx = (size_t)nx * N, su = (size_t)nu * (N - 1);
+
+    std::vector<TinySolver *> solvers(nthreads, nullptr);
+    for (int t = 0; t < nthreads; ++t) {
+        solvers[t] = make_solver(P);
+        if (!solvers[t]) { for (auto *s : solvers) free_solver(s); return 3; }
+    }
+    const auto saved = std::cout.rdstate();
+    std::cout.setstate(std::ios_base::failbit);
+
+    auto worker = [&](int t) {
+        TinySolver *s = solvers[t];
+        const int lo = (int)((long long)B * t / nthreads), hi = (int)((long long)B * (t + 1) / nthreads);
+        tinyVector x(nx);
+        for (int b = lo; b < hi; ++b) {
+            zero_workspace(s);
+            if (P->x_min && P->bounds_per_instance) {
+                tiny_set_bound_constraints(s, MapMat(P->x_min + sx * b, nx, N), MapMat(P->x_max + sx * b, nx, N),
+                                           MapMat(P->u_min + su * b, nu, N - 1), MapMat(P->u_max + su * b, nu, N - 1));
+            }
+            x = MapVec(x0 + (size_t)nx * b, nx);
+            if (ref_mode == TMPC_REF_SHARED) {
+                if (Xref) tiny_set_x_ref(s, MapMat(Xref, nx, N));
+                if (Uref) tiny_set_u_ref(s, MapMat(Uref, nu, N - 1));
+            } else if (ref_mode == TMPC_REF_PER_INSTANCE) {
+                if (Xref) tiny_set_x_ref(s, MapMat(Xref + sx * b, nx, N));
+                if (Uref) tiny_set_u_ref(s, MapMat(Uref + su * b, nu, N - 1));
+            } else if (ref_mode == TMPC_REF_SLIDING) {
+                if (Uref) tiny_set_u_ref(s, MapMat(Uref, nu, N - 1));
+            }
+            for (int k = 0; k < nsteps; ++k) {
+                tiny_set_x0(s, x);
+                if (ref_mode == TMPC_REF_SLIDING && Xref) {
+                    const size_t len = (size_t)nx * (N + nsteps - 1);
+                    tiny_set_x_ref(s, MapMat(Xref + len * b + (size_t)nx * k, nx, N));
+                }
+                const int r = tiny_solve(s);
+                if (ret) ret[(size_t)k * B + b] = r;
+                if (iters) iters[(size_t)k * B + b] = s->solution->iter;
+                // Julia convention: apply the clamped first control, solution.u(:,0) (cartpole_example_mpc.jl:44-48)
+                x = s->work->Adyn * x + s->work->Bdyn * s->solution->u.col(0) + s->work->fdyn;
+            }
+            if (Xsol) std::memcpy(Xsol + sx * b, s->solution->x.data(), sx * sizeof(double));
+            if (Usol) std::memcpy(Usol + su * b, s->solution->u.data(), su * sizeof(double));
+            if (x_final) std::memcpy(x_final + (size_t)nx * b, x.data(), nx * sizeof(double));
+        }
+    };
+
+    const auto t0 = std::chrono::steady_clock::now();
+    if (nthreads == 1) {
+        worker(0);
+    } else {
+        std::vector<std::thread> th;
+        for (int t = 0; t < nthreads; ++t) th.emplace_back(worker, t);
+        for (auto &x : th) x.join();
+    }
+    const auto t1 = std::chrono::steady_clock::now();
+    std::cout.clear(saved);
+    if (seconds) *seconds = std::chrono::duration<double>(t1 - t0).count();
+    for (auto *s : solvers) free_solver(s);
+    return 0;
+}
+
+extern "C" int ref_get_cache(const tmpc_problem *P, double *Kinf, double *Pinf, double *Quu_inv, double *AmBKt,
+                             double *APf, double *BPf) {
+    TinySolver *s = make_solver(P);
+    if (!s) return 3;
+    const int nx = P->nx, nu = P->nu;
+    if (Kinf) std::memcpy(Kinf, s->cache->Kinf.data(), sizeof(double) * nu * nx);
+    if (Pinf) std::memcpy(Pinf, s->cache->Pinf.data(), sizeof(double) * nx * nx);
+    if (Quu_inv) std::memcpy(Quu_inv, s->cache->Quu_inv.data(), sizeof(double) * nu * nu);
+    if (AmBKt) std::memcpy(AmBKt, s->cache->AmBKt.data(), sizeof(double) * nx * nx);
+    if (APf) std::memcpy(APf, s->cache->APf.data(), sizeof(double) * nx);
+    if (BPf) std::memcpy(BPf, s->cache->BPf.data(), sizeof(double) * nu);
+    free_solver(s);
+    return 0;
+}
