@@ -1,0 +1,206 @@
+/*
+ * tinympc_b200 — C ABI of the Blackwell-native batched TinyMPC ADMM solver.
+ *
+ * The library is built as  tinympc_julia_b200/lib/libtinympc_jl.so  — the file name and
+ * location the Julia package dlopens (reference: src/TinyMPC.jl:12-14).
+ *
+ * PART 1 re-exports, symbol for symbol and signature for signature, the sixteen `extern "C"`
+ * entry points of the reference glue (reference: src/bindings.cpp) so that the unmodified
+ * `src/TinyMPC.jl` drives the CUDA solver through its existing `ccall`s.  They operate on one
+ * process-wide solver (reference: src/bindings.cpp:15) which here is a batch of B = 1 living
+ * on the current CUDA device.
+ *
+ * PART 2 adds the batched, handle-based variants (B independent problem instances that share
+ * dynamics, cost and cache) and device-pointer variants for callers that keep their data in HBM.
+ *
+ * Conventions (identical to the reference):
+ *   - every matrix is column-major double (Julia `Matrix{Float64}`), passed as pointer + rows/cols;
+ *   - inputs are copied during the call, outputs are caller-allocated;
+ *   - return 0 = success, non-zero = failure; C++ exceptions never cross the boundary (-1);
+ *   - calls are synchronous unless the name ends in `_async`.
+ * Batched arrays carry the instance index as the slowest dimension (Julia `Array{Float64,3}` of
+ * size (nx, N, B)), i.e. each instance's matrix is one contiguous block.
+ *
+ * There is no CPU fallback: every solve runs the CUDA kernels of this library; when no CUDA
+ * device is usable the calls fail with TMPC_ERR_CUDA.
+ */
+#ifndef TINYMPC_B200_H
+#define TINYMPC_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------------------------------
+ * PART 1 — drop-in symbols of the reference library
+ * ------------------------------------------------------------------------------------------ */
+
+/* replaces src/bindings.cpp:21-73 (called from src/TinyMPC.jl:77-83) */
+int setup_solver(double* A_data, int A_rows, int A_cols,
+                 double* B_data, int B_rows, int B_cols,
+                 double* fdyn_data, int fdyn_rows, int fdyn_cols,
+                 double* Q_data, int Q_rows, int Q_cols,
+                 double* R_data, int R_rows, int R_cols,
+                 double rho, int nx, int nu, int N, int verbose);
+/* replaces src/bindings.cpp:75-96 (src/TinyMPC.jl:119-120) */
+int set_x0(double* x0_data, int x0_rows, int x0_cols, int verbose);
+/* replaces src/bindings.cpp:98-119 (src/TinyMPC.jl:128-129) */
+int set_x_ref(double* x_ref_data, int x_ref_rows, int x_ref_cols, int verbose);
+/* replaces src/bindings.cpp:121-142 (src/TinyMPC.jl:137-138) */
+int set_u_ref(double* u_ref_data, int u_ref_rows, int u_ref_cols, int verbose);
+/* replaces src/bindings.cpp:144-159 (src/TinyMPC.jl:146): 0 converged, 1 max_iter reached, -1 error */
+int solve_mpc(int verbose);
+/* replaces src/bindings.cpp:161-181 / :183-203 (src/TinyMPC.jl:165-168) */
+int get_states(double* states_buffer, int* rows, int* cols);
+int get_controls(double* controls_buffer, int* rows, int* cols);
+/* replaces src/bindings.cpp:205-208 (src/TinyMPC.jl:428-429) */
+void cleanup_solver(void);
+/* replaces src/bindings.cpp:210-225 and :298-331 — code generation for MCUs is outside the
+ * accelerated path; the symbols exist and return a non-zero status. */
+int codegen(const char* output_dir, int verbose);
+int codegen_with_sensitivity(const char* output_dir,
+                             double* dK_data, int dK_rows, int dK_cols,
+                             double* dP_data, int dP_rows, int dP_cols,
+                             double* dC1_data, int dC1_rows, int dC1_cols,
+                             double* dC2_data, int dC2_rows, int dC2_cols, int verbose);
+/* replaces src/bindings.cpp:228-259 (src/TinyMPC.jl:273) */
+int print_problem_data(int verbose);
+/* replaces src/bindings.cpp:262-293 (src/TinyMPC.jl:281-286): overrides Kinf, Pinf, Quu_inv, AmBKt only */
+int set_cache_terms(double* Kinf_data, int Kinf_rows, int Kinf_cols,
+                    double* Pinf_data, int Pinf_rows, int Pinf_cols,
+                    double* Quu_inv_data, int Quu_inv_rows, int Quu_inv_cols,
+                    double* AmBKt_data, int AmBKt_rows, int AmBKt_cols, int verbose);
+/* replaces src/bindings.cpp:336-376 (src/TinyMPC.jl:199-207): overwrites ALL settings.
+ * Deviations: check_termination == 0 is rejected (the reference divides by it, admm.cpp:255);
+ * adaptive_rho != 0 is rejected. */
+int update_settings(double abs_pri_tol, double abs_dua_tol, int max_iter, int check_termination,
+                    int en_state_bound, int en_input_bound, int en_state_soc, int en_input_soc,
+                    int en_state_linear, int en_input_linear,
+                    int adaptive_rho, double adaptive_rho_min, double adaptive_rho_max,
+                    int adaptive_rho_enable_clipping, int verbose);
+/* replaces src/bindings.cpp:378-411 (src/TinyMPC.jl:218-223): enables both bound flags on success */
+int set_bound_constraints(double* x_min_data, int x_min_rows, int x_min_cols,
+                          double* x_max_data, int x_max_rows, int x_max_cols,
+                          double* u_min_data, int u_min_rows, int u_min_cols,
+                          double* u_max_data, int u_max_rows, int u_max_cols, int verbose);
+/* replaces src/bindings.cpp:414-450 (src/TinyMPC.jl:233-238) */
+int set_linear_constraints(double* Alin_x_data, int Alin_x_rows, int Alin_x_cols,
+                           double* blin_x_data, int blin_x_len,
+                           double* Alin_u_data, int Alin_u_rows, int Alin_u_cols,
+                           double* blin_u_data, int blin_u_len, int verbose);
+/* replaces src/bindings.cpp:453-490 (src/TinyMPC.jl:248-253).  The reference stores the FIRST
+ * triple in the state-cone slots and the SECOND in the input-cone slots while deriving the
+ * enable flags the other way round; that behaviour is reproduced. */
+int set_cone_constraints(int* Acu_data, int Acu_len, int* qcu_data, int qcu_len, double* cu_data, int cu_len,
+                         int* Acx_data, int Acx_len, int* qcx_data, int qcx_len, double* cx_data, int cx_len,
+                         int verbose);
+
+/* extra accessors on the process-wide solver (the reference exposes iter/solved only through
+ * print_problem_data, src/bindings.cpp:236-237) */
+int get_solve_info(int* iter, int* solved);
+
+/* ------------------------------------------------------------------------------------------
+ * PART 2 — batched variants
+ * ------------------------------------------------------------------------------------------ */
+
+typedef struct tmpc_batch tmpc_batch; /* opaque */
+
+enum {
+    TMPC_OK = 0,
+    TMPC_ERR_DIM = 1,       /* dimension mismatch / null pointer (the reference core's `1`) */
+    TMPC_ERR_STATE = 2,     /* call order / unsupported setting */
+    TMPC_ERR_CUDA = 3,      /* CUDA runtime failure (message on stderr) */
+    TMPC_ERR_EXCEPTION = -1
+};
+
+/* kernel selection */
+enum {
+    TMPC_KERNEL_AUTO = 0,
+    TMPC_KERNEL_THREAD = 1,   /* one thread per instance, state streamed through L2/HBM each iteration; any nx, nu */
+    TMPC_KERNEL_SUBWARP = 2   /* one instance per 4-lane sub-warp, state resident in shared memory (box constraints) */
+};
+
+/* Create a batch of B instances sharing A, B, f, Q, R, rho (same meaning as setup_solver) on
+ * CUDA device `device` (-1 = current).  All instances start from the zero workspace tiny_setup
+ * produces (reference: tiny_api.cpp:68-105); settings start at the Julia defaults
+ * (src/TinyMPC.jl:57-61: tol 1e-3, max_iter 100, check_termination 1, all en_* = 0). */
+int tmpc_batch_create(tmpc_batch** out,
+                      const double* A, const double* Bdyn, const double* f, const double* Q, const double* R,
+                      double rho, int nx, int nu, int N, int B, int device, int verbose);
+int tmpc_batch_destroy(tmpc_batch* h);
+
+int tmpc_batch_update_settings(tmpc_batch* h, double abs_pri_tol, double abs_dua_tol, int max_iter,
+                               int check_termination, int en_state_bound, int en_input_bound,
+                               int en_state_soc, int en_input_soc, int en_state_linear, int en_input_linear,
+                               int adaptive_rho, double adaptive_rho_min, double adaptive_rho_max,
+                               int adaptive_rho_enable_clipping);
+int tmpc_batch_set_kernel(tmpc_batch* h, int kernel);   /* TMPC_KERNEL_*; AUTO picks SUBWARP where it applies */
+int tmpc_batch_get_kernel(tmpc_batch* h);               /* kernel the next solve will run (resolved AUTO) */
+
+/* Host-pointer setters.  `batch` = 1: one matrix shared by all instances; `batch` = B: one per instance. */
+int tmpc_batch_set_x0(tmpc_batch* h, const double* x0, int rows, int batch);                 /* nx x B */
+int tmpc_batch_set_x_ref(tmpc_batch* h, const double* x_ref, int rows, int cols, int batch); /* nx x N [x B] */
+int tmpc_batch_set_u_ref(tmpc_batch* h, const double* u_ref, int rows, int cols, int batch); /* nu x (N-1) [x B] */
+int tmpc_batch_set_bound_constraints(tmpc_batch* h, const double* x_min, const double* x_max,
+                                     const double* u_min, const double* u_max, int batch);
+int tmpc_batch_set_linear_constraints(tmpc_batch* h, const double* Alin_x, int nlx, const double* blin_x,
+                                      const double* Alin_u, int nlu, const double* blin_u);
+/* first triple -> state-cone slots, second triple -> input-cone slots (core order, tiny_api.cpp:166-168);
+ * enable flags are set per non-empty triple of the SAME side.  Cone size must be 3 (admm.cpp:53). */
+int tmpc_batch_set_cone_constraints(tmpc_batch* h, const int* Acx, const int* qcx, const double* cx, int ncx,
+                                    const int* Acu, const int* qcu, const double* cu, int ncu);
+/* Julia argument order (input-cone triple first, as src/TinyMPC.jl:243-256 passes them) WITH the
+ * reference's crossed behaviour: the first triple lands in the state-cone slots,
+ * the second in the input-cone slots, en_state_soc follows the second triple's length and
+ * en_input_soc the first's.  This is what set_cone_constraints (PART 1) does. */
+int tmpc_batch_set_cone_constraints_jl(tmpc_batch* h, const int* Acu, const int* qcu, const double* cu, int ncu_len,
+                                       const int* Acx, const int* qcx, const double* cx, int ncx_len);
+/* tols[2] = {abs_pri_tol, abs_dua_tol}; ints[8] = {max_iter, check_termination, en_state_bound,
+ * en_input_bound, en_state_soc, en_input_soc, en_state_linear, en_input_linear} */
+int tmpc_batch_get_settings(tmpc_batch* h, double* tols, int* ints);
+int tmpc_batch_set_cache_terms(tmpc_batch* h, const double* Kinf, const double* Pinf,
+                               const double* Quu_inv, const double* AmBKt);
+int tmpc_batch_get_cache_terms(tmpc_batch* h, double* Kinf, double* Pinf, double* Quu_inv, double* AmBKt,
+                               double* APf, double* BPf);
+
+/* Back to the zero workspace (cold start): duals, slacks, linear cost terms and solution cleared;
+ * x0, references, constraints and settings kept. */
+int tmpc_batch_reset(tmpc_batch* h);
+
+/* Solve all instances (warm-started from each instance's own carried state).  Returns 0 when every
+ * instance converged, 1 when at least one stopped at max_iter, <0 / >1 on error. */
+int tmpc_batch_solve(tmpc_batch* h);
+int tmpc_batch_solve_async(tmpc_batch* h, void* cuda_stream);   /* enqueue only; no host sync */
+int tmpc_batch_synchronize(tmpc_batch* h);
+
+/* Per-instance results.  status[b] = what solve_mpc would return for that instance (0 / 1). */
+int tmpc_batch_get_status(tmpc_batch* h, int* status, int* iters);
+int tmpc_batch_get_states(tmpc_batch* h, double* buf);     /* nx x N x B */
+int tmpc_batch_get_controls(tmpc_batch* h, double* buf);   /* nu x (N-1) x B */
+
+/* Device-pointer variants: the pointers must be device memory on the batch's device, laid out as
+ * above, and must stay valid until replaced (they are NOT copied).  NULL restores the internal buffer. */
+int tmpc_batch_bind_x0_device(tmpc_batch* h, const double* d_x0);
+int tmpc_batch_bind_x_ref_device(tmpc_batch* h, const double* d_x_ref, int batch);
+int tmpc_batch_bind_u_ref_device(tmpc_batch* h, const double* d_u_ref, int batch);
+/* device addresses of the result buffers: 0 states (nx x N x B), 1 controls, 2 status (int), 3 iters (int), 4 x0 */
+void* tmpc_batch_device_ptr(tmpc_batch* h, int which);
+
+/* Closed-loop MPC on the device (reference pattern: examples/cartpole_example_mpc.jl:35-51):
+ * for k in 0..nsteps-1:  [x_ref <- columns k..k+N-1 of x_ref_long];  solve;  u = controls(:,0);
+ *                        x0 <- A x0 + B u + f.
+ * x_ref_long: device pointer, nx x (N+nsteps-1) x B, or NULL to keep the current references.
+ * iters_out / status_out: optional device int arrays of nsteps x B (step-major). */
+int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_long,
+                             int* d_status_out, int* d_iters_out, void* cuda_stream);
+
+/* Introspection */
+int tmpc_batch_dims(tmpc_batch* h, int* nx, int* nu, int* N, int* B);
+long long tmpc_batch_launch_count(tmpc_batch* h);   /* kernels launched by this handle so far */
+const char* tmpc_last_error(void);
+const char* tmpc_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TINYMPC_B200_H */

@@ -1,0 +1,79 @@
+// Device-side description of one batch of TinyMPC problem instances, shared by the solve kernels.
+//
+// HBM layout
+// ----------
+// * User-facing arrays keep the Julia layout (instance = slowest dimension): x0 is nx x B,
+//   references nx x N [x B], bounds likewise, solutions nx x N x B.  A per-instance array and a
+//   shared one differ only by the instance stride (0 when shared).
+// * Carried ADMM state (what TinyWorkspace keeps between solves, reference types.hpp:86-187:
+//   duals g,y,gc,yc,gl,yl; previous box slacks v,z; linear cost terms q,r and the terminal p)
+//   is stored element-major: entry e of instance b lives at [e * ld + b], ld = B rounded up to 32.
+//   One thread per instance then reads it fully coalesced, and an 8-instance tile of it is a
+//   64-byte-wide 2-D box for the sub-warp kernel.
+#pragma once
+#include <cstdint>
+
+namespace tmpc {
+
+struct AdmmSettings {        // reference: TinySettings, types.hpp:63-80
+    double abs_pri_tol, abs_dua_tol;
+    int max_iter, check_termination;
+    int en_state_bound, en_input_bound;
+    int en_state_soc, en_input_soc;
+    int en_state_linear, en_input_linear;
+};
+
+constexpr int kMaxCones = 4;     // cones per side
+constexpr int kMaxLinear = 16;   // half-spaces per side (runtime-dim kernel reads them from global memory)
+
+struct BatchView {
+    int B, ld;
+    int nx, nu, N;
+    double rho;
+
+    // ---- inputs, Julia layout; stride = elements between consecutive instances (0 = shared)
+    const double* x0;                       // nx x B
+    const double* Xref; long long xref_stride;   // nullptr => zeros
+    const double* Uref; long long uref_stride;
+    const double* x_min; const double* x_max; long long xb_stride;   // nullptr => unbounded
+    const double* u_min; const double* u_max; long long ub_stride;
+
+    // ---- shared problem constants, column-major, device memory
+    const double *A, *Bm, *f, *Kinf, *Pinf, *Quu_inv, *AmBKt, *APf, *BPf, *Qd, *Rd;
+
+    // ---- second-order cones in the slots the reference core stores them in (size-3 blocks)
+    int ncx; int Acx[kMaxCones]; double cx[kMaxCones];
+    int ncu; int Acu[kMaxCones]; double cu[kMaxCones];
+    // ---- half-spaces a_k . z <= b_k, A column-major (rows = constraints)
+    int nlx; const double* Alin_x; const double* blin_x;
+    int nlu; const double* Alin_u; const double* blin_u;
+
+    // ---- carried state, element-major [e][ld]
+    double *g, *y;          // box duals                       nx*N, nu*(N-1)
+    double *v[2], *z[2];    // box slacks, ping-pong: v[0] is the carried "v" between solves
+    double *q, *r, *pN;     // linear cost terms, terminal p    nx*N, nu*(N-1), nx
+    double *d;              // feed-forward scratch             nu*(N-1)
+    double *gc, *yc;        // cone duals   (allocated when a cone flag is on)
+    double *gl, *yl;        // linear duals (allocated when a linear flag is on)
+
+    // ---- results
+    double* Xsol;           // nx x N x B      (Julia layout)  = vnew of the last iteration
+    double* Usol;           // nu x (N-1) x B                  = znew of the last iteration
+    int* status;            // 0 converged / 1 max_iter         (what solve() returns, admm.cpp:375,388)
+    int* iters;
+};
+
+// ---- arithmetic helpers: the elementwise updates are written with explicitly rounded operations
+// so that nvcc cannot contract them differently from one kernel to the next; dot products are
+// ascending-index FMA chains.
+__device__ __forceinline__ double dadd(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ double dsub(double a, double b) { return __dsub_rn(a, b); }
+__device__ __forceinline__ double dmul(double a, double b) { return __dmul_rn(a, b); }
+// min(hi, max(lo, t)) with the comparison semantics of std::max / std::min (Eigen cwiseMax/cwiseMin,
+// reference admm.cpp:92,97): two compares + selects, cheaper than DMNMX on sm_100.
+__device__ __forceinline__ double clampd(double t, double lo, double hi) {
+    const double w = (lo < t) ? t : lo;      // std::max(lo, t)
+    return (w < hi) ? w : hi;                // std::min(hi, w)
+}
+
+}  // namespace tmpc

@@ -1,0 +1,37 @@
+// Host-visible launch interface of the ADMM solve kernels.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <vector>
+
+#include "admm_device.cuh"
+
+namespace tmpc {
+
+constexpr int kThreadKernelBlock = 128;
+constexpr int kThreadKernelMaxNx = 32;   // runtime-dimension path of the thread kernel
+constexpr int kThreadKernelMaxNu = 16;
+
+// Problem constants on the host, column-major (the same numbers the device copies hold).
+struct HostMats {
+    int nx = 0, nu = 0;
+    std::vector<double> A, B, f, Kinf, Pinf, Quu_inv, AmBKt, APf, BPf, Qd, Rd;
+};
+
+// ---- one thread per instance (admm_thread.cu)
+bool thread_kernel_supports(int nx, int nu);
+cudaError_t launch_admm_thread(const BatchView& bv, const AdmmSettings& st, const HostMats& h, cudaStream_t stream);
+
+// ---- one instance per 4-lane sub-warp, shared-memory resident (admm_subwarp.cu)
+// Applies to box-constrained problems (no cone / half-space flags) of a compiled-in shape.
+bool subwarp_kernel_supports(int nx, int nu, int N, const AdmmSettings& st);
+// `cold` = 1: the carried state is known to be all-zero (fresh / reset batch): it is not read.
+// `counter` = device int used as the tile work queue (zeroed by the launcher).
+cudaError_t launch_admm_subwarp(const BatchView& bv, const AdmmSettings& st, const HostMats& h, int cold,
+                                int* counter, int num_sms, cudaStream_t stream);
+
+// ---- closed-loop plant step (rollout.cu): x0 <- A x0 + B Usol(:,0) + f, optional reference slide
+cudaError_t launch_plant_step(const BatchView& bv, double* x0_rw, cudaStream_t stream);
+cudaError_t launch_record_step(const BatchView& bv, int* status_out, int* iters_out, cudaStream_t stream);
+
+}  // namespace tmpc

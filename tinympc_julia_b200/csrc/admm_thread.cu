@@ -1,0 +1,387 @@
+// ADMM solve kernel, mapping "one thread per problem instance".
+//
+// This is the general-purpose kernel of the library: any nx, nu, N, every constraint family
+// (box, second-order cone, half-space), warm start.  An instance's carried state streams through
+// L2/HBM once per ADMM iteration in the element-major layout (fully coalesced across the warp),
+// the per-column vectors live in registers, and for the compiled-in shapes the problem matrices
+// are kernel parameters, i.e. constant-bank operands folded straight into the DFMAs (no operand
+// delivery instructions at all).  Its ceiling is HBM bandwidth (~11-19 KB per instance-iteration);
+// the shared-memory-resident sub-warp kernel (admm_subwarp.cu) removes that traffic for the
+// box-constrained shapes.
+//
+// Algorithm: the ADMM iteration of the reference, restated in SURVEY.md §8a —
+//   backward_pass_grad   reference admm.cpp:13-20
+//   forward_pass         reference admm.cpp:25-32
+//   update_slack         reference admm.cpp:81-175   (project_soc :39-60, project_hyperplane :70-73)
+//   update_dual          reference admm.cpp:181-208
+//   update_linear_cost   reference admm.cpp:214-247
+//   termination_condition reference admm.cpp:253-271
+//   solve                reference admm.cpp:274-389
+// The slack/dual/cost/residual updates are elementwise per knot point, so they are fused into the
+// forward sweep column by column; x, u and p never leave registers.
+#include <cuda_runtime.h>
+
+#include "admm_device.cuh"
+#include "admm_kernels.hpp"
+
+namespace tmpc {
+
+namespace {
+
+// ---------------------------------------------------------------- matrix operand providers
+template <int NX, int NU>
+struct MatsConst {           // by-value kernel parameter -> constant bank
+    static constexpr int kMaxNx = NX, kMaxNu = NU;
+    static constexpr bool kStatic = true;
+    double A_[NX * NX], B_[NX * NU], Kinf_[NU * NX], AmBKt_[NX * NX], Quu_inv_[NU * NU], Pinf_[NX * NX];
+    double f_[NX], APf_[NX], BPf_[NU], Qd_[NX], Rd_[NU];
+    __device__ __forceinline__ int nx() const { return NX; }
+    __device__ __forceinline__ int nu() const { return NU; }
+    __device__ __forceinline__ double A(int i, int k) const { return A_[k * NX + i]; }
+    __device__ __forceinline__ double B(int i, int k) const { return B_[k * NX + i]; }
+    __device__ __forceinline__ double Kinf(int i, int k) const { return Kinf_[k * NU + i]; }
+    __device__ __forceinline__ double AmBKt(int i, int k) const { return AmBKt_[k * NX + i]; }
+    __device__ __forceinline__ double Quu_inv(int i, int k) const { return Quu_inv_[k * NU + i]; }
+    __device__ __forceinline__ double Pinf(int i, int k) const { return Pinf_[k * NX + i]; }
+    __device__ __forceinline__ double f(int i) const { return f_[i]; }
+    __device__ __forceinline__ double APf(int i) const { return APf_[i]; }
+    __device__ __forceinline__ double BPf(int i) const { return BPf_[i]; }
+    __device__ __forceinline__ double Qd(int i) const { return Qd_[i]; }
+    __device__ __forceinline__ double Rd(int i) const { return Rd_[i]; }
+};
+
+struct MatsGlobal {          // runtime dimensions: uniform loads through the read-only path
+    static constexpr int kMaxNx = kThreadKernelMaxNx, kMaxNu = kThreadKernelMaxNu;
+    static constexpr bool kStatic = false;
+    int nx_, nu_;
+    const double *A_, *B_, *Kinf_, *AmBKt_, *Quu_inv_, *Pinf_, *f_, *APf_, *BPf_, *Qd_, *Rd_;
+    __device__ __forceinline__ int nx() const { return nx_; }
+    __device__ __forceinline__ int nu() const { return nu_; }
+    __device__ __forceinline__ double A(int i, int k) const { return __ldg(A_ + k * nx_ + i); }
+    __device__ __forceinline__ double B(int i, int k) const { return __ldg(B_ + k * nx_ + i); }
+    __device__ __forceinline__ double Kinf(int i, int k) const { return __ldg(Kinf_ + k * nu_ + i); }
+    __device__ __forceinline__ double AmBKt(int i, int k) const { return __ldg(AmBKt_ + k * nx_ + i); }
+    __device__ __forceinline__ double Quu_inv(int i, int k) const { return __ldg(Quu_inv_ + k * nu_ + i); }
+    __device__ __forceinline__ double Pinf(int i, int k) const { return __ldg(Pinf_ + k * nx_ + i); }
+    __device__ __forceinline__ double f(int i) const { return __ldg(f_ + i); }
+    __device__ __forceinline__ double APf(int i) const { return __ldg(APf_ + i); }
+    __device__ __forceinline__ double BPf(int i) const { return __ldg(BPf_ + i); }
+    __device__ __forceinline__ double Qd(int i) const { return __ldg(Qd_ + i); }
+    __device__ __forceinline__ double Rd(int i) const { return __ldg(Rd_ + i); }
+};
+
+// Second-order-cone projection of a 3-block, with the reference's mixed precision: mu and the
+// norm are rounded to float (reference admm.cpp:39,42), the last entry comes from a float division (:54).
+__device__ __forceinline__ void project_soc3(double* s, double mu_d) {
+    const float mu = static_cast<float>(mu_d);
+    const double u0 = dmul(s[2], static_cast<double>(mu));
+    const float a = static_cast<float>(sqrt(dadd(dmul(s[0], s[0]), dmul(s[1], s[1]))));
+    const double ad = static_cast<double>(a);
+    if (ad <= -u0) {
+        s[0] = 0.0; s[1] = 0.0; s[2] = 0.0;
+    } else if (ad <= u0) {
+        // inside the cone: unchanged
+    } else {
+        const double scale = dmul(0.5, dadd(1.0, u0 / ad));
+        const double last = static_cast<double>(a / mu);
+        s[0] = dmul(scale, s[0]); s[1] = dmul(scale, s[1]); s[2] = dmul(scale, last);
+    }
+}
+
+// Sequential (Gauss-Seidel) half-space projections, reference admm.cpp:148-173.
+__device__ __forceinline__ void project_halfspaces(double* col, int len, const double* __restrict__ Alin,
+                                                   const double* __restrict__ blin, int nrows) {
+    for (int k = 0; k < nrows; ++k) {
+        double dot = 0.0;
+        for (int j = 0; j < len; ++j) dot = fma(__ldg(Alin + j * nrows + k), col[j], dot);
+        const double bk = __ldg(blin + k);
+        if (dot > bk) {
+            double sq = 0.0;
+            for (int j = 0; j < len; ++j) { const double a = __ldg(Alin + j * nrows + k); sq = fma(a, a, sq); }
+            const double dist = dsub(dot, bk) / sq;
+            for (int j = 0; j < len; ++j) col[j] = dsub(col[j], dmul(dist, __ldg(Alin + j * nrows + k)));
+        }
+    }
+}
+
+template <class M>
+__global__ void __launch_bounds__(kThreadKernelBlock)
+admm_thread_kernel(const __grid_constant__ M mt, const __grid_constant__ BatchView bv,
+                   const __grid_constant__ AdmmSettings st) {
+    constexpr int MX = M::kMaxNx, MU = M::kMaxNu;
+    constexpr int UNR = M::kStatic ? 64 : 1;   // full unroll for compiled-in shapes, rolled loops otherwise
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= bv.B) return;
+    const int nx = mt.nx(), nu = mt.nu(), N = bv.N;
+    const size_t ld = static_cast<size_t>(bv.ld);
+    const double rho = bv.rho;
+#define ST(arr, e) (arr)[static_cast<size_t>(e) * ld + b]
+
+    if (st.max_iter <= 0) {   // the reference's loop does not run: solution keeps the previous slacks
+        bv.status[b] = 1; bv.iters[b] = 0;
+        return;
+    }
+
+    const bool box_x = st.en_state_bound && bv.x_min != nullptr;
+    const bool box_u = st.en_input_bound && bv.u_min != nullptr;
+    const bool soc_x = st.en_state_soc && bv.ncx > 0;
+    const bool soc_u = st.en_input_soc && bv.ncu > 0;
+    const bool lin_x = st.en_state_linear != 0;
+    const bool lin_u = st.en_input_linear != 0;
+
+    const double* xref = bv.Xref ? bv.Xref + static_cast<size_t>(b) * bv.xref_stride : nullptr;
+    const double* uref = bv.Uref ? bv.Uref + static_cast<size_t>(b) * bv.uref_stride : nullptr;
+    const double* xmin = box_x ? bv.x_min + static_cast<size_t>(b) * bv.xb_stride : nullptr;
+    const double* xmax = box_x ? bv.x_max + static_cast<size_t>(b) * bv.xb_stride : nullptr;
+    const double* umin = box_u ? bv.u_min + static_cast<size_t>(b) * bv.ub_stride : nullptr;
+    const double* umax = box_u ? bv.u_max + static_cast<size_t>(b) * bv.ub_stride : nullptr;
+
+    double p[MX], x[MX], tmp[MX], acc[MX], u[MU], t[MU], rr[MU];
+    double vc[MX];   // cone / half-space slack column (state or input)
+
+#pragma unroll UNR
+    for (int j = 0; j < MX; ++j) if (j < nx) p[j] = ST(bv.pN, j);
+
+    int cur = 0;          // bv.v[cur] / bv.z[cur] hold the previous slacks, the new ones go to [cur ^ 1]
+    int iter = 0;
+    bool converged = false;
+
+    for (int it = 0; it < st.max_iter; ++it) {
+        double* __restrict__ v_old = bv.v[cur];
+        double* __restrict__ v_new = bv.v[cur ^ 1];
+        double* __restrict__ z_old = bv.z[cur];
+        double* __restrict__ z_new = bv.z[cur ^ 1];
+
+        // ---------------- backward pass: d_i, p_i for i = N-2 .. 0
+        for (int i = N - 2; i >= 0; --i) {
+#pragma unroll UNR
+            for (int j = 0; j < MU; ++j) if (j < nu) rr[j] = ST(bv.r, i * nu + j);
+#pragma unroll UNR
+            for (int j = 0; j < MU; ++j) if (j < nu) {
+                double s = 0.0;
+#pragma unroll UNR
+                for (int k = 0; k < MX; ++k) if (k < nx) s = fma(mt.B(k, j), p[k], s);
+                t[j] = dadd(dadd(s, rr[j]), mt.BPf(j));
+            }
+#pragma unroll UNR
+            for (int j = 0; j < MU; ++j) if (j < nu) {
+                double s = 0.0;
+#pragma unroll UNR
+                for (int k = 0; k < MU; ++k) if (k < nu) s = fma(mt.Quu_inv(j, k), t[k], s);
+                ST(bv.d, i * nu + j) = s;
+            }
+#pragma unroll UNR
+            for (int j = 0; j < MX; ++j) if (j < nx) {
+                double s1 = 0.0, s2 = 0.0;
+#pragma unroll UNR
+                for (int k = 0; k < MX; ++k) if (k < nx) s1 = fma(mt.AmBKt(j, k), p[k], s1);
+#pragma unroll UNR
+                for (int k = 0; k < MU; ++k) if (k < nu) s2 = fma(mt.Kinf(k, j), rr[k], s2);
+                tmp[j] = dadd(dsub(dadd(ST(bv.q, i * nx + j), s1), s2), mt.APf(j));
+            }
+#pragma unroll UNR
+            for (int j = 0; j < MX; ++j) if (j < nx) p[j] = tmp[j];
+        }
+
+        // ---------------- forward pass fused with slack / dual / linear-cost / residual updates
+#pragma unroll UNR
+        for (int j = 0; j < MX; ++j) if (j < nx) x[j] = bv.x0[static_cast<size_t>(b) * nx + j];
+        double pri_x = 0.0, dua_x = 0.0, pri_u = 0.0, dua_u = 0.0;
+
+        for (int i = 0; i < N; ++i) {
+            const bool terminal = (i == N - 1);
+            if (!terminal) {
+                // u_i = -Kinf x_i - d_i
+#pragma unroll UNR
+                for (int j = 0; j < MU; ++j) if (j < nu) {
+                    double s = 0.0;
+#pragma unroll UNR
+                    for (int k = 0; k < MX; ++k) if (k < nx) s = fma(mt.Kinf(j, k), x[k], s);
+                    u[j] = dsub(-s, ST(bv.d, i * nu + j));
+                }
+                // ---- input column i
+#pragma unroll UNR
+                for (int j = 0; j < MU; ++j) if (j < nu) {
+                    const int e = i * nu + j;
+                    const double yj = ST(bv.y, e);
+                    double znew = dadd(u[j], yj);
+                    if (box_u) znew = clampd(znew, umin[e], umax[e]);
+                    const double ynew = dsub(dadd(yj, u[j]), znew);
+                    pri_u = fmax(pri_u, fabs(dsub(u[j], znew)));
+                    dua_u = fmax(dua_u, fabs(dsub(ST(z_old, e), znew)));
+                    double racc = -dmul(uref ? uref[e] : 0.0, mt.Rd(j));
+                    racc = dsub(racc, dmul(rho, dsub(znew, ynew)));
+                    ST(bv.y, e) = ynew;
+                    ST(z_new, e) = znew;
+                    t[j] = racc;
+                }
+                if (soc_u) {
+#pragma unroll UNR
+                    for (int j = 0; j < MU; ++j) if (j < nu) vc[j] = dadd(u[j], ST(bv.yc, i * nu + j));
+                    if (st.en_input_soc)
+                        for (int k = 0; k < bv.ncu; ++k) project_soc3(vc + bv.Acu[k], bv.cu[k]);
+#pragma unroll UNR
+                    for (int j = 0; j < MU; ++j) if (j < nu) {
+                        const int e = i * nu + j;
+                        const double ycn = dsub(dadd(ST(bv.yc, e), u[j]), vc[j]);
+                        t[j] = dsub(t[j], dmul(rho, dsub(vc[j], ycn)));
+                        ST(bv.yc, e) = ycn;
+                    }
+                }
+                if (lin_u) {
+#pragma unroll UNR
+                    for (int j = 0; j < MU; ++j) if (j < nu) vc[j] = dadd(u[j], ST(bv.yl, i * nu + j));
+                    project_halfspaces(vc, nu, bv.Alin_u, bv.blin_u, bv.nlu);
+#pragma unroll UNR
+                    for (int j = 0; j < MU; ++j) if (j < nu) {
+                        const int e = i * nu + j;
+                        const double yln = dsub(dadd(ST(bv.yl, e), u[j]), vc[j]);
+                        t[j] = dsub(t[j], dmul(rho, dsub(vc[j], yln)));
+                        ST(bv.yl, e) = yln;
+                    }
+                }
+#pragma unroll UNR
+                for (int j = 0; j < MU; ++j) if (j < nu) ST(bv.r, i * nu + j) = t[j];
+            }
+
+            // ---- state column i
+#pragma unroll UNR
+            for (int j = 0; j < MX; ++j) if (j < nx) {
+                const int e = i * nx + j;
+                const double gj = ST(bv.g, e);
+                double vnew = dadd(x[j], gj);
+                if (box_x) vnew = clampd(vnew, xmin[e], xmax[e]);
+                const double gnew = dsub(dadd(gj, x[j]), vnew);
+                pri_x = fmax(pri_x, fabs(dsub(x[j], vnew)));
+                dua_x = fmax(dua_x, fabs(dsub(ST(v_old, e), vnew)));
+                ST(bv.g, e) = gnew;
+                ST(v_new, e) = vnew;
+                acc[j] = dmul(rho, dsub(vnew, gnew));       // rho * (vnew - g)
+            }
+            // linear cost: q_i = -(Xref_i .* Qd) - rho (vnew - g) [- cone] [- half-space];
+            // terminal column: p_{N-1} = -(Xref_{N-1}' Pinf)' - ...   (reference admm.cpp:238-246)
+            if (!terminal) {
+#pragma unroll UNR
+                for (int j = 0; j < MX; ++j) if (j < nx)
+                    acc[j] = dsub(-dmul(xref ? xref[i * nx + j] : 0.0, mt.Qd(j)), acc[j]);
+            } else {
+#pragma unroll UNR
+                for (int j = 0; j < MX; ++j) if (j < nx) {
+                    double s = 0.0;
+                    if (xref) {
+#pragma unroll UNR
+                        for (int k = 0; k < MX; ++k) if (k < nx) s = fma(xref[i * nx + k], mt.Pinf(k, j), s);
+                    }
+                    acc[j] = dsub(-s, acc[j]);
+                }
+            }
+            if (soc_x) {
+#pragma unroll UNR
+                for (int j = 0; j < MX; ++j) if (j < nx) vc[j] = dadd(x[j], ST(bv.gc, i * nx + j));
+                if (st.en_state_soc)
+                    for (int k = 0; k < bv.ncx; ++k) project_soc3(vc + bv.Acx[k], bv.cx[k]);
+#pragma unroll UNR
+                for (int j = 0; j < MX; ++j) if (j < nx) {
+                    const int e = i * nx + j;
+                    const double gcn = dsub(dadd(ST(bv.gc, e), x[j]), vc[j]);
+                    acc[j] = dsub(acc[j], dmul(rho, dsub(vc[j], gcn)));
+                    ST(bv.gc, e) = gcn;
+                }
+            }
+            if (lin_x) {
+#pragma unroll UNR
+                for (int j = 0; j < MX; ++j) if (j < nx) vc[j] = dadd(x[j], ST(bv.gl, i * nx + j));
+                project_halfspaces(vc, nx, bv.Alin_x, bv.blin_x, bv.nlx);
+#pragma unroll UNR
+                for (int j = 0; j < MX; ++j) if (j < nx) {
+                    const int e = i * nx + j;
+                    const double gln = dsub(dadd(ST(bv.gl, e), x[j]), vc[j]);
+                    acc[j] = dsub(acc[j], dmul(rho, dsub(vc[j], gln)));
+                    ST(bv.gl, e) = gln;
+                }
+            }
+            if (!terminal) {
+#pragma unroll UNR
+                for (int j = 0; j < MX; ++j) if (j < nx) ST(bv.q, i * nx + j) = acc[j];
+                // x_{i+1} = A x_i + B u_i + f
+#pragma unroll UNR
+                for (int j = 0; j < MX; ++j) if (j < nx) {
+                    double s1 = 0.0, s2 = 0.0;
+#pragma unroll UNR
+                    for (int k = 0; k < MX; ++k) if (k < nx) s1 = fma(mt.A(j, k), x[k], s1);
+#pragma unroll UNR
+                    for (int k = 0; k < MU; ++k) if (k < nu) s2 = fma(mt.B(j, k), u[k], s2);
+                    tmp[j] = dadd(dadd(s1, s2), mt.f(j));
+                }
+#pragma unroll UNR
+                for (int j = 0; j < MX; ++j) if (j < nx) x[j] = tmp[j];
+            } else {
+#pragma unroll UNR
+                for (int j = 0; j < MX; ++j) if (j < nx) p[j] = acc[j];
+            }
+        }
+
+        iter += 1;
+        if (iter % st.check_termination == 0) {
+            converged = pri_x < st.abs_pri_tol && pri_u < st.abs_pri_tol &&
+                        dmul(dua_x, rho) < st.abs_dua_tol && dmul(dua_u, rho) < st.abs_dua_tol;
+        }
+        if (converged) break;     // v, z deliberately NOT advanced (reference admm.cpp:375 precedes :379-380)
+        cur ^= 1;
+    }
+
+    // ---------------- results and carried state
+    const int sol = converged ? (cur ^ 1) : cur;     // buffer holding vnew / znew of the last iteration
+    const int nxN = nx * N, nuN = nu * (N - 1);
+    double* Xs = bv.Xsol + static_cast<size_t>(b) * nxN;
+    double* Us = bv.Usol + static_cast<size_t>(b) * nuN;
+    for (int e = 0; e < nxN; ++e) Xs[e] = ST(bv.v[sol], e);
+    for (int e = 0; e < nuN; ++e) Us[e] = ST(bv.z[sol], e);
+    if (cur == 1) {   // the carried previous-slack pair must end up in buffer 0
+        for (int e = 0; e < nxN; ++e) ST(bv.v[0], e) = ST(bv.v[1], e);
+        for (int e = 0; e < nuN; ++e) ST(bv.z[0], e) = ST(bv.z[1], e);
+    }
+#pragma unroll UNR
+    for (int j = 0; j < MX; ++j) if (j < nx) ST(bv.pN, j) = p[j];
+    bv.status[b] = converged ? 0 : 1;
+    bv.iters[b] = iter;
+#undef ST
+}
+
+template <int NX, int NU>
+void fill_const(MatsConst<NX, NU>& m, const HostMats& h) {
+    auto cp = [](double* dst, const std::vector<double>& src) { for (size_t i = 0; i < src.size(); ++i) dst[i] = src[i]; };
+    cp(m.A_, h.A); cp(m.B_, h.B); cp(m.Kinf_, h.Kinf); cp(m.AmBKt_, h.AmBKt); cp(m.Quu_inv_, h.Quu_inv);
+    cp(m.Pinf_, h.Pinf); cp(m.f_, h.f); cp(m.APf_, h.APf); cp(m.BPf_, h.BPf); cp(m.Qd_, h.Qd); cp(m.Rd_, h.Rd);
+}
+
+template <int NX, int NU>
+cudaError_t launch_const(const BatchView& bv, const AdmmSettings& st, const HostMats& h, cudaStream_t stream) {
+    MatsConst<NX, NU> m;
+    fill_const(m, h);
+    const int grid = (bv.B + kThreadKernelBlock - 1) / kThreadKernelBlock;
+    admm_thread_kernel<MatsConst<NX, NU>><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+bool thread_kernel_supports(int nx, int nu) {
+    return nx >= 1 && nu >= 1 && nx <= kThreadKernelMaxNx && nu <= kThreadKernelMaxNu;
+}
+
+cudaError_t launch_admm_thread(const BatchView& bv, const AdmmSettings& st, const HostMats& h, cudaStream_t stream) {
+    if (bv.B <= 0) return cudaSuccess;
+    if (bv.nx == 12 && bv.nu == 4) return launch_const<12, 4>(bv, st, h, stream);
+    if (bv.nx == 4 && bv.nu == 1) return launch_const<4, 1>(bv, st, h, stream);
+    if (bv.nx == 6 && bv.nu == 3) return launch_const<6, 3>(bv, st, h, stream);
+    MatsGlobal m;
+    m.nx_ = bv.nx; m.nu_ = bv.nu;
+    m.A_ = bv.A; m.B_ = bv.Bm; m.Kinf_ = bv.Kinf; m.AmBKt_ = bv.AmBKt; m.Quu_inv_ = bv.Quu_inv; m.Pinf_ = bv.Pinf;
+    m.f_ = bv.f; m.APf_ = bv.APf; m.BPf_ = bv.BPf; m.Qd_ = bv.Qd; m.Rd_ = bv.Rd;
+    const int grid = (bv.B + kThreadKernelBlock - 1) / kThreadKernelBlock;
+    admm_thread_kernel<MatsGlobal><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
+    return cudaGetLastError();
+}
+
+}  // namespace tmpc

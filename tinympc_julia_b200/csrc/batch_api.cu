@@ -1,0 +1,596 @@
+// Handle-based batched C ABI (include/tinympc_b200.h, PART 2).
+//
+// Host-side runtime of the library: owns the device buffers of one batch, mirrors the reference's
+// setter semantics (reference: tinympc/TinyMPC/src/tinympc/tiny_api.cpp:139-242, 375-409 and the
+// flag handling of src/bindings.cpp:336-490), picks the solve kernel and launches it.  Nothing here
+// computes an ADMM iteration on the host: without a usable CUDA device every call fails.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/tinympc_b200.h"
+#include "admm_device.cuh"
+#include "admm_kernels.hpp"
+#include "lqr_cache.hpp"
+
+namespace {
+
+thread_local std::string g_last_error;
+
+void set_error(const std::string& s) {
+    g_last_error = s;
+    std::fprintf(stderr, "tinympc_b200: %s\n", s.c_str());
+}
+
+struct CudaFail { cudaError_t e; const char* what; };
+
+#define CUDA_TRY(expr)                                                       \
+    do {                                                                     \
+        cudaError_t e__ = (expr);                                            \
+        if (e__ != cudaSuccess) throw CudaFail{e__, #expr};                  \
+    } while (0)
+
+template <class T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    void alloc(size_t count) {
+        release();
+        n = count;
+        if (count) CUDA_TRY(cudaMalloc(reinterpret_cast<void**>(&p), count * sizeof(T)));
+    }
+    void zero(cudaStream_t s) { if (p) CUDA_TRY(cudaMemsetAsync(p, 0, n * sizeof(T), s)); }
+    void upload(const T* src, size_t count, cudaStream_t s) {
+        if (count > n) alloc(count);
+        if (count) CUDA_TRY(cudaMemcpyAsync(p, src, count * sizeof(T), cudaMemcpyHostToDevice, s));
+    }
+    void release() { if (p) { cudaFree(p); p = nullptr; } n = 0; }
+    ~DevBuf() { release(); }
+    DevBuf() = default;
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+};
+
+}  // namespace
+
+struct tmpc_batch {
+    int device = 0;
+    int nx = 0, nu = 0, N = 0, B = 0, ld = 0;
+    double rho = 0.0;
+    int num_sms = 148;
+    tmpc::HostMats hm;
+    tmpc::AdmmSettings st{};
+    int kernel_pref = TMPC_KERNEL_AUTO;
+    cudaStream_t stream = nullptr;
+    long long launches = 0;
+    bool state_zero = true;   // carried state is identically zero (fresh or reset)
+
+    // problem constants
+    DevBuf<double> dA, dB, df, dKinf, dPinf, dQuu, dAmBKt, dAPf, dBPf, dQd, dRd;
+    // inputs
+    DevBuf<double> x0, Xref, Uref, xmin, xmax, umin, umax;
+    int xref_batch = 0, uref_batch = 0, bounds_batch = 0;      // 0 = never set
+    const double *ext_x0 = nullptr, *ext_xref = nullptr, *ext_uref = nullptr;
+    int ext_xref_batch = 0, ext_uref_batch = 0;
+    // constraints
+    int ncx = 0, ncu = 0, nlx = 0, nlu = 0;
+    int Acx[tmpc::kMaxCones]{}, Acu[tmpc::kMaxCones]{};
+    double cx[tmpc::kMaxCones]{}, cu[tmpc::kMaxCones]{};
+    DevBuf<double> Alin_x, blin_x, Alin_u, blin_u;
+    // carried state + scratch
+    DevBuf<double> g, y, v0, v1, z0, z1, q, r, pN, d, gc, yc, gl, yl;
+    // results
+    DevBuf<double> Xsol, Usol;
+    DevBuf<int> status, iters, counter;
+
+    void use_device() const { CUDA_TRY(cudaSetDevice(device)); }
+};
+
+namespace {
+
+using tmpc::Mat;
+
+void upload_mats(tmpc_batch* h) {
+    auto up = [&](DevBuf<double>& b, const std::vector<double>& v) { b.upload(v.data(), v.size(), h->stream); };
+    up(h->dA, h->hm.A); up(h->dB, h->hm.B); up(h->df, h->hm.f); up(h->dKinf, h->hm.Kinf); up(h->dPinf, h->hm.Pinf);
+    up(h->dQuu, h->hm.Quu_inv); up(h->dAmBKt, h->hm.AmBKt); up(h->dAPf, h->hm.APf); up(h->dBPf, h->hm.BPf);
+    up(h->dQd, h->hm.Qd); up(h->dRd, h->hm.Rd);
+    CUDA_TRY(cudaStreamSynchronize(h->stream));   // sources are host vectors that may change
+}
+
+void ensure_aux_state(tmpc_batch* h) {
+    const size_t sx = static_cast<size_t>(h->nx) * h->N * h->ld, su = static_cast<size_t>(h->nu) * (h->N - 1) * h->ld;
+    if ((h->st.en_state_soc || h->st.en_input_soc) && !h->gc.p) {
+        h->gc.alloc(sx); h->yc.alloc(su); h->gc.zero(h->stream); h->yc.zero(h->stream);
+    }
+    if ((h->st.en_state_linear || h->st.en_input_linear) && !h->gl.p) {
+        h->gl.alloc(sx); h->yl.alloc(su); h->gl.zero(h->stream); h->yl.zero(h->stream);
+    }
+}
+
+tmpc::BatchView make_view(tmpc_batch* h) {
+    tmpc::BatchView v{};
+    v.B = h->B; v.ld = h->ld; v.nx = h->nx; v.nu = h->nu; v.N = h->N; v.rho = h->rho;
+    const long long sxN = static_cast<long long>(h->nx) * h->N, suN = static_cast<long long>(h->nu) * (h->N - 1);
+    v.x0 = h->ext_x0 ? h->ext_x0 : h->x0.p;
+    if (h->ext_xref) { v.Xref = h->ext_xref; v.xref_stride = h->ext_xref_batch > 1 ? sxN : 0; }
+    else if (h->xref_batch) { v.Xref = h->Xref.p; v.xref_stride = h->xref_batch > 1 ? sxN : 0; }
+    if (h->ext_uref) { v.Uref = h->ext_uref; v.uref_stride = h->ext_uref_batch > 1 ? suN : 0; }
+    else if (h->uref_batch) { v.Uref = h->Uref.p; v.uref_stride = h->uref_batch > 1 ? suN : 0; }
+    if (h->bounds_batch) {
+        v.x_min = h->xmin.p; v.x_max = h->xmax.p; v.xb_stride = h->bounds_batch > 1 ? sxN : 0;
+        v.u_min = h->umin.p; v.u_max = h->umax.p; v.ub_stride = h->bounds_batch > 1 ? suN : 0;
+    }
+    v.A = h->dA.p; v.Bm = h->dB.p; v.f = h->df.p; v.Kinf = h->dKinf.p; v.Pinf = h->dPinf.p; v.Quu_inv = h->dQuu.p;
+    v.AmBKt = h->dAmBKt.p; v.APf = h->dAPf.p; v.BPf = h->dBPf.p; v.Qd = h->dQd.p; v.Rd = h->dRd.p;
+    v.ncx = h->ncx; v.ncu = h->ncu;
+    for (int k = 0; k < tmpc::kMaxCones; ++k) { v.Acx[k] = h->Acx[k]; v.cx[k] = h->cx[k]; v.Acu[k] = h->Acu[k]; v.cu[k] = h->cu[k]; }
+    v.nlx = h->nlx; v.Alin_x = h->Alin_x.p; v.blin_x = h->blin_x.p;
+    v.nlu = h->nlu; v.Alin_u = h->Alin_u.p; v.blin_u = h->blin_u.p;
+    v.g = h->g.p; v.y = h->y.p; v.v[0] = h->v0.p; v.v[1] = h->v1.p; v.z[0] = h->z0.p; v.z[1] = h->z1.p;
+    v.q = h->q.p; v.r = h->r.p; v.pN = h->pN.p; v.d = h->d.p;
+    v.gc = h->gc.p; v.yc = h->yc.p; v.gl = h->gl.p; v.yl = h->yl.p;
+    v.Xsol = h->Xsol.p; v.Usol = h->Usol.p; v.status = h->status.p; v.iters = h->iters.p;
+    return v;
+}
+
+int resolve_kernel(const tmpc_batch* h) {
+    const bool sub_ok = tmpc::subwarp_kernel_supports(h->nx, h->nu, h->N, h->st);
+    if (h->kernel_pref == TMPC_KERNEL_SUBWARP) return sub_ok ? TMPC_KERNEL_SUBWARP : -1;
+    if (h->kernel_pref == TMPC_KERNEL_THREAD) return TMPC_KERNEL_THREAD;
+    return sub_ok ? TMPC_KERNEL_SUBWARP : TMPC_KERNEL_THREAD;
+}
+
+void zero_state(tmpc_batch* h) {
+    cudaStream_t s = h->stream;
+    h->g.zero(s); h->y.zero(s); h->v0.zero(s); h->v1.zero(s); h->z0.zero(s); h->z1.zero(s);
+    h->q.zero(s); h->r.zero(s); h->pN.zero(s); h->d.zero(s);
+    h->gc.zero(s); h->yc.zero(s); h->gl.zero(s); h->yl.zero(s);
+    h->Xsol.zero(s); h->Usol.zero(s); h->status.zero(s); h->iters.zero(s);
+    h->state_zero = true;
+}
+
+// Enqueue one batched solve on `s` (ordered after everything already queued on the handle's own
+// stream when s is that stream; callers passing another stream order it themselves).
+int enqueue_solve(tmpc_batch* h, cudaStream_t s) {
+    if (h->st.check_termination == 0) { set_error("check_termination = 0 is not supported (the reference divides by it)"); return TMPC_ERR_STATE; }
+    ensure_aux_state(h);
+    const int k = resolve_kernel(h);
+    if (k < 0) { set_error("sub-warp kernel requested but it does not support this problem (shape or constraint flags)"); return TMPC_ERR_STATE; }
+    tmpc::BatchView v = make_view(h);
+    cudaError_t e;
+    if (k == TMPC_KERNEL_SUBWARP) {
+        e = tmpc::launch_admm_subwarp(v, h->st, h->hm, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
+        h->launches += 1;
+    } else {
+        e = tmpc::launch_admm_thread(v, h->st, h->hm, s);
+        h->launches += 1;
+    }
+    if (e != cudaSuccess) throw CudaFail{e, "solve kernel launch"};
+    if (h->st.max_iter > 0) h->state_zero = false;
+    return TMPC_OK;
+}
+
+template <class F>
+int guarded(F&& body) {
+    try {
+        return body();
+    } catch (const CudaFail& f) {
+        set_error(std::string("CUDA error: ") + cudaGetErrorString(f.e) + " in " + f.what);
+        return TMPC_ERR_CUDA;
+    } catch (const std::bad_alloc&) {
+        set_error("out of host memory");
+        return TMPC_ERR_EXCEPTION;
+    } catch (const std::exception& e) {
+        set_error(std::string("exception: ") + e.what());
+        return TMPC_ERR_EXCEPTION;
+    } catch (...) {
+        set_error("unknown exception");
+        return TMPC_ERR_EXCEPTION;
+    }
+}
+
+bool finite_all(const double* p, size_t n) {
+    for (size_t i = 0; i < n; ++i) if (!std::isfinite(p[i])) return false;
+    return true;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* tmpc_last_error(void) { return g_last_error.c_str(); }
+const char* tmpc_version(void) { return "tinympc_b200 0.1 (sm_100a)"; }
+
+int tmpc_batch_create(tmpc_batch** out, const double* A, const double* Bdyn, const double* f, const double* Q,
+                      const double* R, double rho, int nx, int nu, int N, int B, int device, int verbose) {
+    if (out) *out = nullptr;
+    return guarded([&]() -> int {
+        if (!out || !A || !Bdyn || !f || !Q || !R) { set_error("tmpc_batch_create: null argument"); return TMPC_ERR_DIM; }
+        if (nx < 1 || nu < 1 || N < 2 || B < 1) { set_error("tmpc_batch_create: need nx >= 1, nu >= 1, N >= 2, B >= 1"); return TMPC_ERR_DIM; }
+        if (!tmpc::thread_kernel_supports(nx, nu)) {
+            set_error("tmpc_batch_create: nx/nu beyond the compiled limits (nx <= 32, nu <= 16)");
+            return TMPC_ERR_DIM;
+        }
+        if (!finite_all(A, static_cast<size_t>(nx) * nx) || !finite_all(Bdyn, static_cast<size_t>(nx) * nu) ||
+            !finite_all(f, nx) || !std::isfinite(rho)) { set_error("tmpc_batch_create: non-finite problem data"); return TMPC_ERR_DIM; }
+        int ndev = 0;
+        if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) {
+            set_error("no CUDA device available: this library has no CPU path");
+            return TMPC_ERR_CUDA;
+        }
+        std::unique_ptr<tmpc_batch> h(new tmpc_batch());
+        if (device < 0) CUDA_TRY(cudaGetDevice(&device));
+        h->device = device;
+        h->use_device();
+        cudaDeviceProp prop{};
+        CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+        h->num_sms = prop.multiProcessorCount;
+        h->nx = nx; h->nu = nu; h->N = N; h->B = B; h->rho = rho;
+        h->ld = (B + 31) / 32 * 32;
+
+        tmpc::LqrCache c;
+        Mat mA(nx, nx, A), mB(nx, nu, Bdyn), mf(nx, 1, f), mQ(nx, nx, Q), mR(nu, nu, R);
+        if (tmpc::compute_lqr_cache(mA, mB, mf, mQ, mR, rho, c) != 0) {
+            set_error("tmpc_batch_create: singular matrix in the Riccati recursion");
+            return TMPC_ERR_DIM;
+        }
+        if (verbose) std::printf("tinympc_b200: Kinf converged after %d Riccati sweeps (nx=%d nu=%d N=%d B=%d)\n",
+                                 c.riccati_sweeps, nx, nu, N, B);
+        h->hm.nx = nx; h->hm.nu = nu;
+        h->hm.A = mA.a; h->hm.B = mB.a; h->hm.f = mf.a; h->hm.Kinf = c.Kinf.a; h->hm.Pinf = c.Pinf.a;
+        h->hm.Quu_inv = c.Quu_inv.a; h->hm.AmBKt = c.AmBKt.a; h->hm.APf = c.APf.a; h->hm.BPf = c.BPf.a;
+        h->hm.Qd = c.Qd; h->hm.Rd = c.Rd;
+
+        // Julia-side defaults (src/TinyMPC.jl:57-61, :94-99)
+        h->st.abs_pri_tol = 1e-3; h->st.abs_dua_tol = 1e-3; h->st.max_iter = 100; h->st.check_termination = 1;
+
+        CUDA_TRY(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+        upload_mats(h.get());
+        const size_t sx = static_cast<size_t>(nx) * N * h->ld, su = static_cast<size_t>(nu) * (N - 1) * h->ld;
+        h->g.alloc(sx); h->v0.alloc(sx); h->v1.alloc(sx); h->q.alloc(sx);
+        h->y.alloc(su); h->z0.alloc(su); h->z1.alloc(su); h->r.alloc(su); h->d.alloc(su);
+        h->pN.alloc(static_cast<size_t>(nx) * h->ld);
+        h->x0.alloc(static_cast<size_t>(nx) * B); h->x0.zero(h->stream);
+        h->Xsol.alloc(static_cast<size_t>(nx) * N * B); h->Usol.alloc(static_cast<size_t>(nu) * (N - 1) * B);
+        h->status.alloc(B); h->iters.alloc(B); h->counter.alloc(8); h->counter.zero(h->stream);
+        zero_state(h.get());
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        *out = h.release();
+        return TMPC_OK;
+    });
+}
+
+int tmpc_batch_destroy(tmpc_batch* h) {
+    if (!h) return TMPC_OK;
+    return guarded([&]() -> int {
+        cudaSetDevice(h->device);
+        if (h->stream) { cudaStreamSynchronize(h->stream); cudaStreamDestroy(h->stream); }
+        delete h;
+        return TMPC_OK;
+    });
+}
+
+int tmpc_batch_update_settings(tmpc_batch* h, double abs_pri_tol, double abs_dua_tol, int max_iter,
+                               int check_termination, int en_state_bound, int en_input_bound, int en_state_soc,
+                               int en_input_soc, int en_state_linear, int en_input_linear, int adaptive_rho,
+                               double adaptive_rho_min, double adaptive_rho_max, int adaptive_rho_enable_clipping) {
+    (void)adaptive_rho_min; (void)adaptive_rho_max; (void)adaptive_rho_enable_clipping;
+    return guarded([&]() -> int {
+        if (!h) { set_error("update_settings: null handle"); return TMPC_ERR_DIM; }
+        if (check_termination == 0) { set_error("update_settings: check_termination = 0 rejected (reference computes iter % 0)"); return TMPC_ERR_STATE; }
+        if (adaptive_rho) { set_error("update_settings: adaptive_rho is not implemented on the device path"); return TMPC_ERR_STATE; }
+        h->st.abs_pri_tol = abs_pri_tol; h->st.abs_dua_tol = abs_dua_tol;
+        h->st.max_iter = max_iter; h->st.check_termination = check_termination;
+        h->st.en_state_bound = en_state_bound != 0; h->st.en_input_bound = en_input_bound != 0;
+        h->st.en_state_soc = en_state_soc != 0; h->st.en_input_soc = en_input_soc != 0;
+        h->st.en_state_linear = en_state_linear != 0; h->st.en_input_linear = en_input_linear != 0;
+        return TMPC_OK;
+    });
+}
+
+int tmpc_batch_set_kernel(tmpc_batch* h, int kernel) {
+    if (!h || kernel < TMPC_KERNEL_AUTO || kernel > TMPC_KERNEL_SUBWARP) return TMPC_ERR_DIM;
+    h->kernel_pref = kernel;
+    return TMPC_OK;
+}
+
+int tmpc_batch_get_kernel(tmpc_batch* h) { return h ? resolve_kernel(h) : -1; }
+
+int tmpc_batch_set_x0(tmpc_batch* h, const double* x0, int rows, int batch) {
+    return guarded([&]() -> int {
+        if (!h || !x0) { set_error("set_x0: null argument"); return TMPC_ERR_DIM; }
+        if (rows != h->nx || batch != h->B) { set_error("set_x0: expected nx x B"); return TMPC_ERR_DIM; }
+        h->use_device();
+        h->ext_x0 = nullptr;
+        h->x0.upload(x0, static_cast<size_t>(h->nx) * h->B, h->stream);
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        return TMPC_OK;
+    });
+}
+
+int tmpc_batch_set_x_ref(tmpc_batch* h, const double* x_ref, int rows, int cols, int batch) {
+    return guarded([&]() -> int {
+        if (!h || !x_ref) { set_error("set_x_ref: null argument"); return TMPC_ERR_DIM; }
+        if (rows != h->nx || cols != h->N || (batch != 1 && batch != h->B)) { set_error("set_x_ref: expected nx x N [x B]"); return TMPC_ERR_DIM; }
+        h->use_device();
+        h->ext_xref = nullptr;
+        h->Xref.upload(x_ref, static_cast<size_t>(rows) * cols * batch, h->stream);
+        h->xref_batch = batch;
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        return TMPC_OK;
+    });
+}
+
+int tmpc_batch_set_u_ref(tmpc_batch* h, const double* u_ref, int rows, int cols, int batch) {
+    return guarded([&]() -> int {
+        if (!h || !u_ref) { set_error("set_u_ref: null argument"); return TMPC_ERR_DIM; }
+        if (rows != h->nu || cols != h->N - 1 || (batch != 1 && batch != h->B)) { set_error("set_u_ref: expected nu x (N-1) [x B]"); return TMPC_ERR_DIM; }
+        h->use_device();
+        h->ext_uref = nullptr;
+        h->Uref.upload(u_ref, static_cast<size_t>(rows) * cols * batch, h->stream);
+        h->uref_batch = batch;
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        return TMPC_OK;
+    });
+}
+
+int tmpc_batch_set_bound_constraints(tmpc_batch* h, const double* x_min, const double* x_max, const double* u_min,
+                                     const double* u_max, int batch) {
+    return guarded([&]() -> int {
+        if (!h || !x_min || !x_max || !u_min || !u_max) { set_error("set_bound_constraints: null argument"); return TMPC_ERR_DIM; }
+        if (batch != 1 && batch != h->B) { set_error("set_bound_constraints: batch must be 1 or B"); return TMPC_ERR_DIM; }
+        h->use_device();
+        const size_t sx = static_cast<size_t>(h->nx) * h->N * batch, su = static_cast<size_t>(h->nu) * (h->N - 1) * batch;
+        h->xmin.upload(x_min, sx, h->stream); h->xmax.upload(x_max, sx, h->stream);
+        h->umin.upload(u_min, su, h->stream); h->umax.upload(u_max, su, h->stream);
+        h->bounds_batch = batch;
+        h->st.en_state_bound = 1; h->st.en_input_bound = 1;     // src/bindings.cpp:400-404
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        return TMPC_OK;
+    });
+}
+
+int tmpc_batch_set_linear_constraints(tmpc_batch* h, const double* Alin_x, int nlx, const double* blin_x,
+                                      const double* Alin_u, int nlu, const double* blin_u) {
+    return guarded([&]() -> int {
+        if (!h || nlx < 0 || nlu < 0) { set_error("set_linear_constraints: bad argument"); return TMPC_ERR_DIM; }
+        if ((nlx > 0 && (!Alin_x || !blin_x)) || (nlu > 0 && (!Alin_u || !blin_u))) { set_error("set_linear_constraints: null matrix"); return TMPC_ERR_DIM; }
+        h->use_device();
+        h->nlx = nlx; h->nlu = nlu;
+        if (nlx) { h->Alin_x.upload(Alin_x, static_cast<size_t>(nlx) * h->nx, h->stream); h->blin_x.upload(blin_x, nlx, h->stream); }
+        if (nlu) { h->Alin_u.upload(Alin_u, static_cast<size_t>(nlu) * h->nu, h->stream); h->blin_u.upload(blin_u, nlu, h->stream); }
+        if (nlx > 0) h->st.en_state_linear = 1;                 // src/bindings.cpp:438-443
+        if (nlu > 0) h->st.en_input_linear = 1;
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        return TMPC_OK;
+    });
+}
+
+int tmpc_batch_set_cone_constraints(tmpc_batch* h, const int* Acx, const int* qcx, const double* cx, int ncx,
+                                    const int* Acu, const int* qcu, const double* cu, int ncu) {
+    return guarded([&]() -> int {
+        if (!h || ncx < 0 || ncu < 0 || ncx > tmpc::kMaxCones || ncu > tmpc::kMaxCones) {
+            set_error("set_cone_constraints: at most 4 cones per side"); return TMPC_ERR_DIM;
+        }
+        for (int k = 0; k < ncx; ++k)
+            if (qcx[k] != 3 || Acx[k] < 0 || Acx[k] + 3 > h->nx) { set_error("set_cone_constraints: state cone must be a 3-block inside the state"); return TMPC_ERR_DIM; }
+        for (int k = 0; k < ncu; ++k)
+            if (qcu[k] != 3 || Acu[k] < 0 || Acu[k] + 3 > h->nu) { set_error("set_cone_constraints: input cone must be a 3-block inside the input"); return TMPC_ERR_DIM; }
+        h->ncx = ncx; h->ncu = ncu;
+        for (int k = 0; k < ncx; ++k) { h->Acx[k] = Acx[k]; h->cx[k] = cx[k]; }
+        for (int k = 0; k < ncu; ++k) { h->Acu[k] = Acu[k]; h->cu[k] = cu[k]; }
+        if (ncx > 0) h->st.en_state_soc = 1;
+        if (ncu > 0) h->st.en_input_soc = 1;
+        return TMPC_OK;
+    });
+}
+
+int tmpc_batch_set_cone_constraints_jl(tmpc_batch* h, const int* Acu, const int* qcu, const double* cu, int ncu_len,
+                                       const int* Acx, const int* qcx, const double* cx, int ncx_len) {
+    return guarded([&]() -> int {
+        if (!h) return TMPC_ERR_DIM;
+        const tmpc::AdmmSettings before = h->st;
+        // first triple -> state-cone slots, second -> input-cone slots (src/bindings.cpp:472-475 calling
+        // tiny_api.cpp:166-168) ...
+        const int rc = tmpc_batch_set_cone_constraints(h, Acu, qcu, cu, ncu_len, Acx, qcx, cx, ncx_len);
+        if (rc != TMPC_OK) return rc;
+        // ... while the flags follow the caller's naming and are only ever switched on (src/bindings.cpp:478-483)
+        h->st.en_state_soc = before.en_state_soc || (ncx_len > 0);
+        h->st.en_input_soc = before.en_input_soc || (ncu_len > 0);
+        return TMPC_OK;
+    });
+}
+
+int tmpc_batch_get_settings(tmpc_batch* h, double* tols, int* ints) {
+    if (!h) return TMPC_ERR_DIM;
+    if (tols) { tols[0] = h->st.abs_pri_tol; tols[1] = h->st.abs_dua_tol; }
+    if (ints) {
+        ints[0] = h->st.max_iter; ints[1] = h->st.check_termination; ints[2] = h->st.en_state_bound; ints[3] = h->st.en_input_bound;
+        ints[4] = h->st.en_state_soc; ints[5] = h->st.en_input_soc; ints[6] = h->st.en_state_linear; ints[7] = h->st.en_input_linear;
+    }
+    return TMPC_OK;
+}
+
+int tmpc_batch_set_cache_terms(tmpc_batch* h, const double* Kinf, const double* Pinf, const double* Quu_inv,
+                               const double* AmBKt) {
+    return guarded([&]() -> int {
+        if (!h || !Kinf || !Pinf || !Quu_inv || !AmBKt) { set_error("set_cache_terms: null argument"); return TMPC_ERR_DIM; }
+        h->use_device();
+        const int n = h->nx, m = h->nu;
+        h->hm.Kinf.assign(Kinf, Kinf + static_cast<size_t>(m) * n);
+        h->hm.Pinf.assign(Pinf, Pinf + static_cast<size_t>(n) * n);
+        h->hm.Quu_inv.assign(Quu_inv, Quu_inv + static_cast<size_t>(m) * m);
+        h->hm.AmBKt.assign(AmBKt, AmBKt + static_cast<size_t>(n) * n);
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        upload_mats(h);      // APf, BPf, rho deliberately untouched
+        return TMPC_OK;
+    });
+}
+
+int tmpc_batch_get_cache_terms(tmpc_batch* h, double* Kinf, double* Pinf, double* Quu_inv, double* AmBKt, double* APf,
+                               double* BPf) {
+    if (!h) return TMPC_ERR_DIM;
+    auto cp = [](double* dst, const std::vector<double>& v) { if (dst) std::memcpy(dst, v.data(), v.size() * sizeof(double)); };
+    cp(Kinf, h->hm.Kinf); cp(Pinf, h->hm.Pinf); cp(Quu_inv, h->hm.Quu_inv); cp(AmBKt, h->hm.AmBKt);
+    cp(APf, h->hm.APf); cp(BPf, h->hm.BPf);
+    return TMPC_OK;
+}
+
+int tmpc_batch_reset(tmpc_batch* h) {
+    return guarded([&]() -> int {
+        if (!h) return TMPC_ERR_DIM;
+        h->use_device();
+        zero_state(h);
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        return TMPC_OK;
+    });
+}
+
+int tmpc_batch_solve_async(tmpc_batch* h, void* cuda_stream) {
+    return guarded([&]() -> int {
+        if (!h) return TMPC_ERR_DIM;
+        h->use_device();
+        return enqueue_solve(h, cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : h->stream);
+    });
+}
+
+int tmpc_batch_synchronize(tmpc_batch* h) {
+    return guarded([&]() -> int {
+        if (!h) return TMPC_ERR_DIM;
+        h->use_device();
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        return TMPC_OK;
+    });
+}
+
+int tmpc_batch_solve(tmpc_batch* h) {
+    return guarded([&]() -> int {
+        if (!h) return TMPC_ERR_DIM;
+        h->use_device();
+        const int rc = enqueue_solve(h, h->stream);
+        if (rc != TMPC_OK) return rc < 0 ? rc : 100 + rc;
+        std::vector<int> st(h->B);
+        CUDA_TRY(cudaMemcpyAsync(st.data(), h->status.p, sizeof(int) * h->B, cudaMemcpyDeviceToHost, h->stream));
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        for (int s : st) if (s != 0) return 1;
+        return 0;
+    });
+}
+
+int tmpc_batch_get_status(tmpc_batch* h, int* status, int* iters) {
+    return guarded([&]() -> int {
+        if (!h) return TMPC_ERR_DIM;
+        h->use_device();
+        if (status) CUDA_TRY(cudaMemcpyAsync(status, h->status.p, sizeof(int) * h->B, cudaMemcpyDeviceToHost, h->stream));
+        if (iters) CUDA_TRY(cudaMemcpyAsync(iters, h->iters.p, sizeof(int) * h->B, cudaMemcpyDeviceToHost, h->stream));
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        return TMPC_OK;
+    });
+}
+
+int tmpc_batch_get_states(tmpc_batch* h, double* buf) {
+    return guarded([&]() -> int {
+        if (!h || !buf) return TMPC_ERR_DIM;
+        h->use_device();
+        CUDA_TRY(cudaMemcpyAsync(buf, h->Xsol.p, sizeof(double) * h->nx * h->N * h->B, cudaMemcpyDeviceToHost, h->stream));
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        return TMPC_OK;
+    });
+}
+
+int tmpc_batch_get_controls(tmpc_batch* h, double* buf) {
+    return guarded([&]() -> int {
+        if (!h || !buf) return TMPC_ERR_DIM;
+        h->use_device();
+        CUDA_TRY(cudaMemcpyAsync(buf, h->Usol.p, sizeof(double) * h->nu * (h->N - 1) * h->B, cudaMemcpyDeviceToHost, h->stream));
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        return TMPC_OK;
+    });
+}
+
+int tmpc_batch_bind_x0_device(tmpc_batch* h, const double* d_x0) {
+    if (!h) return TMPC_ERR_DIM;
+    h->ext_x0 = d_x0;
+    return TMPC_OK;
+}
+
+int tmpc_batch_bind_x_ref_device(tmpc_batch* h, const double* d_x_ref, int batch) {
+    if (!h || (d_x_ref && batch != 1 && batch != h->B)) return TMPC_ERR_DIM;
+    h->ext_xref = d_x_ref; h->ext_xref_batch = batch;
+    return TMPC_OK;
+}
+
+int tmpc_batch_bind_u_ref_device(tmpc_batch* h, const double* d_u_ref, int batch) {
+    if (!h || (d_u_ref && batch != 1 && batch != h->B)) return TMPC_ERR_DIM;
+    h->ext_uref = d_u_ref; h->ext_uref_batch = batch;
+    return TMPC_OK;
+}
+
+void* tmpc_batch_device_ptr(tmpc_batch* h, int which) {
+    if (!h) return nullptr;
+    switch (which) {
+        case 0: return h->Xsol.p;
+        case 1: return h->Usol.p;
+        case 2: return h->status.p;
+        case 3: return h->iters.p;
+        case 4: return h->x0.p;
+        default: return nullptr;
+    }
+}
+
+int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_long, int* d_status_out, int* d_iters_out,
+                             void* cuda_stream) {
+    return guarded([&]() -> int {
+        if (!h || nsteps < 1) return TMPC_ERR_DIM;
+        h->use_device();
+        cudaStream_t s = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : h->stream;
+        if (h->ext_x0) {   // the plant state is advanced in place: work on the internal copy
+            CUDA_TRY(cudaMemcpyAsync(h->x0.p, h->ext_x0, sizeof(double) * h->nx * h->B, cudaMemcpyDeviceToDevice, s));
+            h->ext_x0 = nullptr;
+        }
+        if (h->st.check_termination == 0) { set_error("check_termination = 0 is not supported"); return TMPC_ERR_STATE; }
+        ensure_aux_state(h);
+        const int k = resolve_kernel(h);
+        if (k < 0) { set_error("sub-warp kernel requested but unsupported for this problem"); return TMPC_ERR_STATE; }
+        const long long ref_len = static_cast<long long>(h->nx) * (h->N + nsteps - 1);
+        for (int step = 0; step < nsteps; ++step) {
+            tmpc::BatchView v = make_view(h);
+            if (d_x_ref_long) { v.Xref = d_x_ref_long + static_cast<size_t>(h->nx) * step; v.xref_stride = ref_len; }
+            cudaError_t e = (k == TMPC_KERNEL_SUBWARP)
+                ? tmpc::launch_admm_subwarp(v, h->st, h->hm, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s)
+                : tmpc::launch_admm_thread(v, h->st, h->hm, s);
+            if (e != cudaSuccess) throw CudaFail{e, "rollout solve launch"};
+            if (h->st.max_iter > 0) h->state_zero = false;
+            if (d_status_out || d_iters_out) {
+                e = tmpc::launch_record_step(v, d_status_out ? d_status_out + static_cast<size_t>(step) * h->B : nullptr,
+                                             d_iters_out ? d_iters_out + static_cast<size_t>(step) * h->B : nullptr, s);
+                if (e != cudaSuccess) throw CudaFail{e, "rollout record launch"};
+                h->launches += 1;
+            }
+            e = tmpc::launch_plant_step(v, h->x0.p, s);
+            if (e != cudaSuccess) throw CudaFail{e, "rollout plant-step launch"};
+            h->launches += 2;
+        }
+        return TMPC_OK;
+    });
+}
+
+int tmpc_batch_dims(tmpc_batch* h, int* nx, int* nu, int* N, int* B) {
+    if (!h) return TMPC_ERR_DIM;
+    if (nx) *nx = h->nx;
+    if (nu) *nu = h->nu;
+    if (N) *N = h->N;
+    if (B) *B = h->B;
+    return TMPC_OK;
+}
+
+long long tmpc_batch_launch_count(tmpc_batch* h) { return h ? h->launches : 0; }
+
+}  // extern "C"
