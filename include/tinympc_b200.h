@@ -120,6 +120,13 @@ enum {
     TMPC_KERNEL_SUBWARP = 2   /* one instance per 4-lane sub-warp, state resident in shared memory (box constraints) */
 };
 
+/* Host-only: the infinite-horizon LQR cache the solve loop reads (replaces tiny_precompute_and_set_cache,
+ * tiny_api.cpp:244-318, fed as tiny_setup feeds it, :107-108,:126).  Column-major outputs, any may be NULL:
+ * Kinf nu x nx, Pinf nx x nx, Quu_inv nu x nu, AmBKt nx x nx, APf nx, BPf nu, Qd = diag(Q)+rho, Rd = diag(R)+rho. */
+int tmpc_compute_cache(const double* A, const double* Bdyn, const double* f, const double* Q, const double* R, double rho,
+                       int nx, int nu, double* Kinf, double* Pinf, double* Quu_inv, double* AmBKt, double* APf,
+                       double* BPf, double* Qd, double* Rd);
+
 /* Create a batch of B instances sharing A, B, f, Q, R, rho (same meaning as setup_solver) on
  * CUDA device `device` (-1 = current).  All instances start from the zero workspace tiny_setup
  * produces (reference: tiny_api.cpp:68-105); settings start at the Julia defaults

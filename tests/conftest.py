@@ -1,0 +1,26 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.dirname(os.path.abspath(__file__))):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+@pytest.fixture(scope="session")
+def orc():
+    import oracle
+    return oracle.load_oracle()
+
+
+@pytest.fixture(scope="session")
+def ref():
+    """The compiled, unmodified reference core — None where oracle/_ref has not been built."""
+    import oracle
+    return oracle.load_ref()

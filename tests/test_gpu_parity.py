@@ -1,0 +1,148 @@
+"""Parity of the CUDA solve path against the oracle and the reference's golden fixtures — GPU only.
+
+Every call goes through the C ABI (ctypes -> lib/libtinympc_jl.so).  Bar (BASELINE.json north_star):
+identical solve status and iteration count per instance; states and controls within 1e-5 relative /
+1e-6 absolute (tinytype = double).
+"""
+import numpy as np
+import pytest
+
+import cases
+import tinympc_julia_b200 as t
+
+pytestmark = pytest.mark.gpu
+
+THREAD, SUBWARP = t.KERNEL_THREAD, t.KERNEL_SUBWARP
+
+
+def kernels_for(c):
+    """Kernels able to run a case: the thread kernel always; the sub-warp kernel where it applies."""
+    ks = [THREAD]
+    sol = cases.make_cuda_solver(c, kernel=t.KERNEL_AUTO)
+    if sol.kernel == SUBWARP:
+        ks.append(SUBWARP)
+    del sol
+    return ks
+
+
+@pytest.mark.parametrize("name", sorted(cases.GOLDEN_CASES))
+def test_cuda_matches_golden_fixture(name):
+    c = cases.GOLDEN_CASES[name]()
+    want = cases.load_golden(name)
+    for k in kernels_for(c):
+        got = cases.run_cuda(c, kernel=k)
+        cases.compare(got, want, what=f"cuda[kernel {k}] vs golden[{name}]")
+        np.testing.assert_allclose(got["x_final"], want["x_final"], rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("make,B", [(cases.cartpole_batch, 2000), (cases.quadrotor_batch, 1500),
+                                    (lambda B: cases.quadrotor_batch(B, hard=True), 1000),
+                                    (cases.quadrotor_per_instance, 500), (lambda B: cases.rocket(B, N=50), 200),
+                                    (lambda B: cases.random_system(7, 3, 15, B, seed=21), 300)])
+def test_cuda_matches_oracle_seeded(orc, make, B):
+    c = make(B)
+    want = cases.run_checker(c, orc, nthreads=8)
+    for k in kernels_for(c):
+        got = cases.run_cuda(c, kernel=k)
+        cases.compare(got, want, what=f"cuda[kernel {k}] vs oracle")
+
+
+def test_cuda_ragged_batch_sizes(orc):
+    """B not a multiple of the tile (8) / warp (32) / block: tail lanes must stay inert."""
+    for B in (1, 2, 7, 9, 31, 33, 130):
+        c = cases.quadrotor_batch(B, hard=True, seed=100 + B, max_iter=40)
+        want = cases.run_checker(c, orc)
+        for k in kernels_for(c):
+            cases.compare(cases.run_cuda(c, kernel=k), want, what=f"B={B} kernel {k}")
+
+
+def test_cuda_closed_loop_warm_start(orc):
+    """config 5 pattern: carried duals/slacks/cost terms must reproduce the reference's iteration counts."""
+    c = cases.quadrotor_closed_loop(64, 60)
+    want = cases.run_checker(c, orc, nthreads=8)
+    for k in kernels_for(c):
+        got = cases.run_cuda(c, kernel=k)
+        cases.compare(got, want, what=f"closed loop kernel {k}")
+        np.testing.assert_allclose(got["x_final"], want["x_final"], rtol=1e-5, atol=1e-6)
+
+
+def test_kernels_interchangeable_mid_rollout(orc):
+    """The carried state has one HBM format: switching kernels between solves must not change results."""
+    c = cases.quadrotor_closed_loop(24, 12)
+    want = cases.run_checker(c, orc)
+    sol = cases.make_cuda_solver(c)
+    if sol.kernel != SUBWARP:
+        pytest.skip("sub-warp kernel not available for this shape")
+    import oracle
+    x = np.asfortranarray(c["x0"]).copy(order="F")
+    s, N = c["sys"], c["N"]
+    iters = np.zeros((c["nsteps"], x.shape[1]), dtype=np.int32)
+    for k in range(c["nsteps"]):
+        sol.set_kernel(SUBWARP if k % 2 == 0 else THREAD)
+        t.set_x0(sol, x)
+        t.set_x_ref(sol, np.asfortranarray(c["Xref"][:, k:k + N, :]))
+        t.solve(sol)
+        iters[k] = sol.status()[1]
+        U = t.get_solution(sol).controls
+        x = np.asfortranarray(cases._plant(s.A, s.B, s.f, x, U[:, 0, :]))
+    assert np.array_equal(iters, want["iters"])
+
+
+def test_cuda_check_termination_and_max_iter(orc):
+    c = cases.quadrotor_batch(100, hard=True)
+    for chk, mi in ((3, 50), (1, 1), (7, 20)):
+        c["check_termination"], c["max_iter"] = chk, mi
+        want = cases.run_checker(c, orc)
+        for k in kernels_for(c):
+            cases.compare(cases.run_cuda(c, kernel=k), want, what=f"check={chk} max_iter={mi} kernel {k}")
+
+
+def test_cuda_unconstrained_and_flag_subsets(orc):
+    """Q3 of SURVEY.md: with the box flags off the primal state residual is identically zero."""
+    c = cases.quadrotor_batch(64)
+    c["bounds"] = None
+    want = cases.run_checker(c, orc)
+    for k in kernels_for(c):
+        cases.compare(cases.run_cuda(c, kernel=k), want, what=f"unconstrained kernel {k}")
+    # input bounds only (state bounds infinite), as tests/test_basic.jl:47-70 does
+    c = cases.quadrotor_batch(64, hard=True)
+    xm, xM, um, uM = c["bounds"]
+    c["bounds"] = (np.full_like(xm, -np.inf), np.full_like(xM, np.inf), um, uM)
+    want = cases.run_checker(c, orc)
+    for k in kernels_for(c):
+        cases.compare(cases.run_cuda(c, kernel=k), want, what=f"input-bounds-only kernel {k}")
+
+
+def test_cuda_set_cache_terms_override(orc):
+    """set_cache_terms replaces Kinf/Pinf/Quu_inv/AmBKt only."""
+    c = cases.cartpole_batch(32)
+    p = cases.to_oracle_problem(c)
+    k0 = orc.get_cache(p)
+    c["cache"] = {k: k0[k] * (1.0 + 1e-3) for k in ("Kinf", "Pinf", "Quu_inv", "AmBKt")}
+    want = cases.run_checker(c, orc)
+    for k in kernels_for(c):
+        cases.compare(cases.run_cuda(c, kernel=k), want, what=f"cache override kernel {k}")
+
+
+def test_full_size_batch_properties():
+    """BASELINE.json config 3 at full size (B = 65,536): properties that do not need the oracle —
+    bounds respected exactly by the returned slacks (Q4), x(:,0) = clamp(x0), determinism across
+    kernels, iteration counts within [1, max_iter], converged instances report status 0."""
+    B = 65536
+    c = cases.quadrotor_batch(B)
+    res = {}
+    for k in kernels_for(c):
+        got = cases.run_cuda(c, kernel=k)
+        X, U = got["X"], got["U"]
+        assert np.all(U <= 0.5) and np.all(U >= -0.5) and np.all(np.abs(X) <= 5.0)
+        assert np.array_equal(X[:, 0, :], np.clip(c["x0"], -5, 5))
+        it, st = got["iters"][0], got["ret"][0]
+        assert it.min() >= 1 and it.max() <= 100
+        assert np.all((st == 0) | (it == 100))
+        assert (st == 0).mean() > 0.99
+        res[k] = got
+    if len(res) == 2:
+        a, b = res[THREAD], res[SUBWARP]
+        assert np.array_equal(a["iters"], b["iters"]) and np.array_equal(a["ret"], b["ret"])
+        np.testing.assert_allclose(a["X"], b["X"], rtol=1e-5, atol=1e-6)
+        np.testing.assert_allclose(a["U"], b["U"], rtol=1e-5, atol=1e-6)

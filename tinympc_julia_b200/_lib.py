@@ -40,6 +40,7 @@ SIGNATURES = {
     "set_cone_constraints": (_I, [_IP, _I, _IP, _I, _P, _I, _IP, _I, _IP, _I, _P, _I, _I]),
     "get_solve_info": (_I, [_IP, _IP]),
     # PART 2: batched variants
+    "tmpc_compute_cache": (_I, [_P, _P, _P, _P, _P, _D, _I, _I] + [_P] * 8),
     "tmpc_batch_create": (_I, [C.POINTER(_V), _P, _P, _P, _P, _P, _D, _I, _I, _I, _I, _I, _I]),
     "tmpc_batch_destroy": (_I, [_V]),
     "tmpc_batch_update_settings": (_I, [_V, _D, _D, _I, _I, _I, _I, _I, _I, _I, _I, _I, _D, _D, _I]),

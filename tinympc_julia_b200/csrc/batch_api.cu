@@ -208,6 +208,21 @@ extern "C" {
 const char* tmpc_last_error(void) { return g_last_error.c_str(); }
 const char* tmpc_version(void) { return "tinympc_b200 0.1 (sm_100a)"; }
 
+int tmpc_compute_cache(const double* A, const double* Bdyn, const double* f, const double* Q, const double* R, double rho,
+                       int nx, int nu, double* Kinf, double* Pinf, double* Quu_inv, double* AmBKt, double* APf,
+                       double* BPf, double* Qd, double* Rd) {
+    return guarded([&]() -> int {
+        if (!A || !Bdyn || !f || !Q || !R || nx < 1 || nu < 1) { set_error("tmpc_compute_cache: bad argument"); return TMPC_ERR_DIM; }
+        tmpc::LqrCache c;
+        Mat mA(nx, nx, A), mB(nx, nu, Bdyn), mf(nx, 1, f), mQ(nx, nx, Q), mR(nu, nu, R);
+        if (tmpc::compute_lqr_cache(mA, mB, mf, mQ, mR, rho, c) != 0) { set_error("tmpc_compute_cache: singular matrix"); return TMPC_ERR_DIM; }
+        auto cp = [](double* dst, const std::vector<double>& v) { if (dst) std::memcpy(dst, v.data(), v.size() * sizeof(double)); };
+        cp(Kinf, c.Kinf.a); cp(Pinf, c.Pinf.a); cp(Quu_inv, c.Quu_inv.a); cp(AmBKt, c.AmBKt.a); cp(APf, c.APf.a); cp(BPf, c.BPf.a);
+        cp(Qd, c.Qd); cp(Rd, c.Rd);
+        return c.riccati_sweeps > 0 ? TMPC_OK : TMPC_ERR_DIM;
+    });
+}
+
 int tmpc_batch_create(tmpc_batch** out, const double* A, const double* Bdyn, const double* f, const double* Q,
                       const double* R, double rho, int nx, int nu, int N, int B, int device, int verbose) {
     if (out) *out = nullptr;

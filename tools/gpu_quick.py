@@ -1,0 +1,44 @@
+"""Quick GPU sanity + timing driver used during development (not a test, not the bench)."""
+import sys, time, os
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests"))
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+import numpy as np
+import cases, oracle
+import tinympc_julia_b200 as t
+
+orc = oracle.load_oracle()
+for name in ("cartpole_one_solve", "quadrotor_easy_64", "quadrotor_hard_64", "rocket_julia_example", "random_5x2_16"):
+    c = cases.GOLDEN_CASES[name]()
+    want = cases.load_golden(name)
+    for k in (1, 2):
+        sol = cases.make_cuda_solver(c, kernel=0)
+        if k == 2 and sol.kernel != 2:
+            continue
+        got = cases.run_cuda(c, kernel=k)
+        print(name, "kernel", k, "iter mismatches", int((got["iters"] != want["iters"]).sum()), "of", want["iters"].size,
+              "max|dX|", float(np.abs(got["X"] - want["X"]).max()), "max|dU|", float(np.abs(got["U"] - want["U"]).max()), flush=True)
+
+import torch
+B = int(os.environ.get("QB", 65536))
+for hard in (False, True):
+    c = cases.quadrotor_batch(B, hard=hard)
+    for k in (1, 2):
+        sol = cases.make_cuda_solver(c, kernel=0)
+        if k == 2 and sol.kernel != 2:
+            continue
+        sol.set_kernel(k)
+        t.set_x0(sol, c["x0"])
+        ts = []
+        for rep in range(4):
+            sol.reset()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            sol.solve_async(0)
+            sol.synchronize()
+            torch.cuda.synchronize()
+            ts.append(time.perf_counter() - t0)
+        st, it = sol.status()
+        F = 24612
+        best = min(ts)
+        print(f"quad hard={hard} kernel={k} B={B} best {best*1e3:.3f} ms  solves/s {B/best:.3e} iters/s {it.sum()/best:.3e} "
+              f"TFLOP/s {it.sum()*F/best/1e12:.2f} mean iters {it.mean():.2f} solved {(st==0).mean():.3f}", flush=True)
