@@ -186,6 +186,15 @@ def make_cuda_solver(c, kernel=0, device=-1):
         t.set_cone_constraints(sol, k["Acu"], k["qcu"], k["cu"], k["Acx"], k["qcx"], k["cx"])
     if c["linear"] is not None:
         t.set_linear_constraints(sol, *c["linear"])
+    if c["check_termination"] not in (0, 1):
+        # the Julia API only carries a Bool (src/TinyMPC.jl:185); integer periods go through the C ABI directly
+        import ctypes as C
+        from tinympc_julia_b200 import _lib
+        lib = _lib.load()
+        tols, ints = (C.c_double * 2)(), (C.c_int * 8)()
+        assert lib.tmpc_batch_get_settings(sol._h, tols, ints) == 0
+        assert lib.tmpc_batch_update_settings(sol._h, tols[0], tols[1], ints[0], int(c["check_termination"]), ints[2], ints[3],
+                                              ints[4], ints[5], ints[6], ints[7], 0, 0.1, 10.0, 1) == 0
     sol.set_kernel(kernel)
     return sol
 
