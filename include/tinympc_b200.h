@@ -204,6 +204,10 @@ int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_lo
 /* Introspection */
 int tmpc_batch_dims(tmpc_batch* h, int* nx, int* nu, int* N, int* B);
 long long tmpc_batch_launch_count(tmpc_batch* h);   /* kernels launched by this handle so far */
+/* Measurement aid (not on the solve path): best-of-`reps` FMA throughput of register-resident,
+ * dependency-free chains on `device` (-1 = current), in TFLOP/s (2 flop per FMA).  fp64 != 0: DFMA
+ * (the reference's tinytype, types.hpp:15); fp64 == 0: FFMA.  The roofline denominator of bench.py. */
+int tmpc_measure_fma_peak(int device, int fp64, int reps, double* tflops);
 const char* tmpc_last_error(void);
 const char* tmpc_version(void);
 

@@ -70,6 +70,7 @@ SIGNATURES = {
     "tmpc_batch_rollout_async": (_I, [_V, _I, _V, _V, _V, _V]),
     "tmpc_batch_dims": (_I, [_V, _IP, _IP, _IP, _IP]),
     "tmpc_batch_launch_count": (C.c_longlong, [_V]),
+    "tmpc_measure_fma_peak": (_I, [_I, _I, _I, _P]),
     "tmpc_last_error": (C.c_char_p, []),
     "tmpc_version": (C.c_char_p, []),
 }

@@ -69,7 +69,10 @@ struct tmpc_batch {
     int kernel_pref = TMPC_KERNEL_AUTO;
     cudaStream_t stream = nullptr;
     long long launches = 0;
-    bool state_zero = true;   // carried state is identically zero (fresh or reset)
+    bool state_zero = true;   // carried state is LOGICALLY zero (fresh or reset) ...
+    bool mem_zero = true;     // ... and the device buffers physically hold those zeros.  tmpc_batch_reset only flips
+                              // state_zero: the sub-warp kernel never reads a cold state and rewrites all of it, so
+                              // the ~0.9 GB of memsets (quadrotor, B = 65,536) happen only for readers that need them.
 
     // problem constants
     DevBuf<double> dA, dB, df, dKinf, dPinf, dQuu, dAmBKt, dAPf, dBPf, dQd, dRd;
@@ -154,6 +157,34 @@ void zero_state(tmpc_batch* h) {
     h->gc.zero(s); h->yc.zero(s); h->gl.zero(s); h->yl.zero(s);
     h->Xsol.zero(s); h->Usol.zero(s); h->status.zero(s); h->iters.zero(s);
     h->state_zero = true;
+    h->mem_zero = true;
+}
+
+// Make a logically-zero state physically zero before something reads it (thread kernel, result getters).
+// `s` must be ordered with the handle's stream by the caller.
+void materialize_zero(tmpc_batch* h) {
+    if (h->state_zero && !h->mem_zero) zero_state(h);
+}
+
+// One solve kernel on `s`.  A cold (reset) state is passed to the sub-warp kernel as a flag; every other
+// reader gets physically zeroed buffers first (memsets on the handle's stream, joined into `s` by an event).
+cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v, cudaStream_t s) {
+    const bool sub = (k == TMPC_KERNEL_SUBWARP) && h->st.max_iter > 0 && h->rho > 0.0;
+    if (!sub && h->state_zero && !h->mem_zero) {
+        zero_state(h);
+        if (s != h->stream) {
+            cudaEvent_t ev;
+            CUDA_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+            CUDA_TRY(cudaEventRecord(ev, h->stream));
+            CUDA_TRY(cudaStreamWaitEvent(s, ev, 0));
+            CUDA_TRY(cudaEventDestroy(ev));
+        }
+    }
+    cudaError_t e = sub ? tmpc::launch_admm_subwarp(v, h->st, h->hm, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s)
+                        : tmpc::launch_admm_thread(v, h->st, h->hm, s);
+    h->launches += 1;
+    if (h->st.max_iter > 0) { h->state_zero = false; h->mem_zero = false; }
+    return e;
 }
 
 // Enqueue one batched solve on `s` (ordered after everything already queued on the handle's own
@@ -165,15 +196,8 @@ int enqueue_solve(tmpc_batch* h, cudaStream_t s) {
     if (k < 0) { set_error("sub-warp kernel requested but it does not support this problem (shape or constraint flags)"); return TMPC_ERR_STATE; }
     tmpc::BatchView v = make_view(h);
     cudaError_t e;
-    if (k == TMPC_KERNEL_SUBWARP) {
-        e = tmpc::launch_admm_subwarp(v, h->st, h->hm, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
-        h->launches += 1;
-    } else {
-        e = tmpc::launch_admm_thread(v, h->st, h->hm, s);
-        h->launches += 1;
-    }
+    e = launch_solve(h, k, v, s);
     if (e != cudaSuccess) throw CudaFail{e, "solve kernel launch"};
-    if (h->st.max_iter > 0) h->state_zero = false;
     return TMPC_OK;
 }
 
@@ -462,8 +486,8 @@ int tmpc_batch_reset(tmpc_batch* h) {
     return guarded([&]() -> int {
         if (!h) return TMPC_ERR_DIM;
         h->use_device();
-        zero_state(h);
         CUDA_TRY(cudaStreamSynchronize(h->stream));
+        h->state_zero = true;            // physical zeroing is deferred to the first reader that needs it
         return TMPC_OK;
     });
 }
@@ -503,6 +527,7 @@ int tmpc_batch_get_status(tmpc_batch* h, int* status, int* iters) {
     return guarded([&]() -> int {
         if (!h) return TMPC_ERR_DIM;
         h->use_device();
+        materialize_zero(h);
         if (status) CUDA_TRY(cudaMemcpyAsync(status, h->status.p, sizeof(int) * h->B, cudaMemcpyDeviceToHost, h->stream));
         if (iters) CUDA_TRY(cudaMemcpyAsync(iters, h->iters.p, sizeof(int) * h->B, cudaMemcpyDeviceToHost, h->stream));
         CUDA_TRY(cudaStreamSynchronize(h->stream));
@@ -514,6 +539,7 @@ int tmpc_batch_get_states(tmpc_batch* h, double* buf) {
     return guarded([&]() -> int {
         if (!h || !buf) return TMPC_ERR_DIM;
         h->use_device();
+        materialize_zero(h);
         CUDA_TRY(cudaMemcpyAsync(buf, h->Xsol.p, sizeof(double) * h->nx * h->N * h->B, cudaMemcpyDeviceToHost, h->stream));
         CUDA_TRY(cudaStreamSynchronize(h->stream));
         return TMPC_OK;
@@ -524,6 +550,7 @@ int tmpc_batch_get_controls(tmpc_batch* h, double* buf) {
     return guarded([&]() -> int {
         if (!h || !buf) return TMPC_ERR_DIM;
         h->use_device();
+        materialize_zero(h);
         CUDA_TRY(cudaMemcpyAsync(buf, h->Usol.p, sizeof(double) * h->nu * (h->N - 1) * h->B, cudaMemcpyDeviceToHost, h->stream));
         CUDA_TRY(cudaStreamSynchronize(h->stream));
         return TMPC_OK;
@@ -578,11 +605,8 @@ int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_lo
         for (int step = 0; step < nsteps; ++step) {
             tmpc::BatchView v = make_view(h);
             if (d_x_ref_long) { v.Xref = d_x_ref_long + static_cast<size_t>(h->nx) * step; v.xref_stride = ref_len; }
-            cudaError_t e = (k == TMPC_KERNEL_SUBWARP)
-                ? tmpc::launch_admm_subwarp(v, h->st, h->hm, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s)
-                : tmpc::launch_admm_thread(v, h->st, h->hm, s);
+            cudaError_t e = launch_solve(h, k, v, s);
             if (e != cudaSuccess) throw CudaFail{e, "rollout solve launch"};
-            if (h->st.max_iter > 0) h->state_zero = false;
             if (d_status_out || d_iters_out) {
                 e = tmpc::launch_record_step(v, d_status_out ? d_status_out + static_cast<size_t>(step) * h->B : nullptr,
                                              d_iters_out ? d_iters_out + static_cast<size_t>(step) * h->B : nullptr, s);
@@ -591,7 +615,7 @@ int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_lo
             }
             e = tmpc::launch_plant_step(v, h->x0.p, s);
             if (e != cudaSuccess) throw CudaFail{e, "rollout plant-step launch"};
-            h->launches += 2;
+            h->launches += 1;
         }
         return TMPC_OK;
     });
