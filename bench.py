@@ -275,8 +275,12 @@ def run_gpu(args, rank, local_rank, world):
     x0_dev = x0_pinned.to(dev)
     sol.bind_x0_device(x0_dev.data_ptr())
     flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
-    stream = torch.cuda.current_stream()
+    # a real (non-default) stream: the library treats a NULL stream argument as "use the handle's own stream",
+    # which CUDA events recorded on torch's default stream would not see
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
     sptr = stream.cuda_stream
+    assert sptr != 0
 
     def barrier():
         if world > 1:
