@@ -355,7 +355,7 @@ def run_gpu(args, rank, local_rank, world):
         "admm_iters_per_s": iters_per_s,
         "mean_iters_per_solve": all_iters_step / (B * world), "solved_fraction": all_solved / (B * world),
         "config": {"workload": workload_name(args), "nx": NX, "nu": NU, "N": NH, "batch_per_gpu": B,
-                   "kernel": {1: "thread", 2: "subwarp"}.get(sol.kernel, str(sol.kernel)),
+                   "kernel": {1: "thread", 2: "subwarp", 3: "tmem"}.get(sol.kernel, str(sol.kernel)),
                    "l2": "flushed between timed steps (256 MiB write, outside the event pair)",
                    "timing": "CUDA events on the launch stream per step, summed, max over ranks",
                    "parallelism": f"instances sharded over {world} GPU(s), no collective inside the solve"},
@@ -441,7 +441,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=65536)
     ap.add_argument("--workload", default="quadrotor_easy", choices=["quadrotor_easy", "quadrotor_hard"])
-    ap.add_argument("--kernel", type=int, default=0, help="0 auto, 1 thread-per-instance, 2 sub-warp")
+    ap.add_argument("--kernel", type=int, default=0, help="0 auto, 1 thread-per-instance, 2 sub-warp (shared memory), 3 sub-warp (TMEM + shared memory)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline / single_solve legs")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

@@ -117,7 +117,9 @@ enum {
 enum {
     TMPC_KERNEL_AUTO = 0,
     TMPC_KERNEL_THREAD = 1,   /* one thread per instance, state streamed through L2/HBM each iteration; any nx, nu */
-    TMPC_KERNEL_SUBWARP = 2   /* one instance per 4-lane sub-warp, state resident in shared memory (box constraints) */
+    TMPC_KERNEL_SUBWARP = 2,  /* one instance per 4-lane sub-warp, state resident in shared memory (box constraints) */
+    TMPC_KERNEL_TMEM = 3      /* 4-lane sub-warp, state rows in Tensor Memory + input rows in shared memory, 8 warps/SM,
+                                 per-instance refill (box constraints with shared bounds, nx=12 nu=4, N <= 21) */
 };
 
 /* Host-only: the infinite-horizon LQR cache the solve loop reads (replaces tiny_precompute_and_set_cache,
@@ -141,7 +143,7 @@ int tmpc_batch_update_settings(tmpc_batch* h, double abs_pri_tol, double abs_dua
                                int en_state_soc, int en_input_soc, int en_state_linear, int en_input_linear,
                                int adaptive_rho, double adaptive_rho_min, double adaptive_rho_max,
                                int adaptive_rho_enable_clipping);
-int tmpc_batch_set_kernel(tmpc_batch* h, int kernel);   /* TMPC_KERNEL_*; AUTO picks SUBWARP where it applies */
+int tmpc_batch_set_kernel(tmpc_batch* h, int kernel);   /* TMPC_KERNEL_*; AUTO picks TMEM, then SUBWARP, where they apply */
 int tmpc_batch_get_kernel(tmpc_batch* h);               /* kernel the next solve will run (resolved AUTO) */
 
 /* Host-pointer setters.  `batch` = 1: one matrix shared by all instances; `batch` = B: one per instance. */

@@ -12,15 +12,17 @@ import tinympc_julia_b200 as t
 
 pytestmark = pytest.mark.gpu
 
-THREAD, SUBWARP = t.KERNEL_THREAD, t.KERNEL_SUBWARP
+THREAD, SUBWARP, TMEM = t.KERNEL_THREAD, t.KERNEL_SUBWARP, t.KERNEL_TMEM
 
 
 def kernels_for(c):
-    """Kernels able to run a case: the thread kernel always; the sub-warp kernel where it applies."""
+    """Kernels able to run a case: the thread kernel always; the on-chip kernels where they apply."""
     ks = [THREAD]
     sol = cases.make_cuda_solver(c, kernel=t.KERNEL_AUTO)
-    if sol.kernel == SUBWARP:
-        ks.append(SUBWARP)
+    for k in (SUBWARP, TMEM):
+        sol.set_kernel(k)
+        if sol.kernel == k:
+            ks.append(k)
     del sol
     return ks
 
@@ -71,14 +73,15 @@ def test_kernels_interchangeable_mid_rollout(orc):
     c = cases.quadrotor_closed_loop(24, 12)
     want = cases.run_checker(c, orc)
     sol = cases.make_cuda_solver(c)
-    if sol.kernel != SUBWARP:
-        pytest.skip("sub-warp kernel not available for this shape")
+    order = kernels_for(c)
+    if len(order) < 2:
+        pytest.skip("only one kernel available for this shape")
     import oracle
     x = np.asfortranarray(c["x0"]).copy(order="F")
     s, N = c["sys"], c["N"]
     iters = np.zeros((c["nsteps"], x.shape[1]), dtype=np.int32)
     for k in range(c["nsteps"]):
-        sol.set_kernel(SUBWARP if k % 2 == 0 else THREAD)
+        sol.set_kernel(order[k % len(order)])
         t.set_x0(sol, x)
         t.set_x_ref(sol, np.asfortranarray(c["Xref"][:, k:k + N, :]))
         t.solve(sol)
@@ -141,8 +144,8 @@ def test_full_size_batch_properties():
         assert np.all((st == 0) | (it == 100))
         assert (st == 0).mean() > 0.99
         res[k] = got
-    if len(res) == 2:
-        a, b = res[THREAD], res[SUBWARP]
-        assert np.array_equal(a["iters"], b["iters"]) and np.array_equal(a["ret"], b["ret"])
+    a = res[THREAD]
+    for k, b in res.items():
+        assert np.array_equal(a["iters"], b["iters"]) and np.array_equal(a["ret"], b["ret"]), f"kernel {k}"
         np.testing.assert_allclose(a["X"], b["X"], rtol=1e-5, atol=1e-6)
         np.testing.assert_allclose(a["U"], b["U"], rtol=1e-5, atol=1e-6)

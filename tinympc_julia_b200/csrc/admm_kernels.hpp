@@ -30,6 +30,12 @@ bool subwarp_kernel_supports(int nx, int nu, int N, const AdmmSettings& st);
 cudaError_t launch_admm_subwarp(const BatchView& bv, const AdmmSettings& st, const HostMats& h, int cold,
                                 int* counter, int num_sms, cudaStream_t stream);
 
+// ---- one instance per 4-lane sub-warp, state rows in Tensor Memory + input rows in shared memory, per-instance
+// refill from a global queue (admm_tmem.cu).  Box-constrained (or unconstrained) problems with shared bounds.
+bool tmem_kernel_supports(const BatchView& bv, const AdmmSettings& st);
+cudaError_t launch_admm_tmem(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms,
+                             cudaStream_t stream);
+
 // ---- closed-loop plant step (rollout.cu): x0 <- A x0 + B Usol(:,0) + f, optional reference slide
 cudaError_t launch_plant_step(const BatchView& bv, double* x0_rw, cudaStream_t stream);
 cudaError_t launch_record_step(const BatchView& bv, int* status_out, int* iters_out, cudaStream_t stream);

@@ -1,0 +1,670 @@
+// ADMM solve kernel v2: "one instance per 4-lane sub-warp, duals and slacks split between Tensor Memory and
+// shared memory, per-instance refill".
+//
+// Why it exists (measured, profiles/r01_a_*): the shared-memory-only sub-warp kernel (admm_subwarp.cu) holds 708
+// doubles per instance in shared memory, which caps an SM at 32 resident instances = 4 warps = ONE warp per
+// scheduler; every DFMA dependency chain is then exposed (issue active 22 %, FP64 pipe 11.6 %).  Blackwell's
+// 256 KB of Tensor Memory per SM is idle in a kernel without MMAs, and tcgen05.ld/st give every lane private
+// access to its own TMEM row (measured: 200-256 B/clk/SM loads, 177-212 B/clk/SM stores, st->ld round trip
+// 34 cycles, profiles/r01_tmem_probe.jsonl).  This kernel keeps the state-row duals and slacks (g, v: 480 of the
+// 708 doubles) in TMEM and only the input-row arrays (y, z, r/t) in shared memory, which doubles the residency to
+// 8 warps per SM = two warps per scheduler, and it
+//   * refills a sub-warp with the next instance the moment its instance finishes (global instance queue), so a
+//     warp never idles on the slowest of its 8 instances (iteration counts are bimodal on the hard workload);
+//   * moves the Quu_inv mat-vec into the forward sweep (the backward sweep leaves t = B'p + r + BPf in shared
+//     memory, the forward sweep reads the 4-vector back and forms d), and lets the forward sweep leave the new
+//     r in the same slot, so the backward sweep needs no warp shuffles at all;
+//   * drops all "finished instance" predication from the sweeps: a finished instance is written out and replaced.
+//
+// Lane map: lane = sub * 8 + inst; lane `sub` of instance `inst` owns state rows {4 r + sub} and input row `sub`.
+// TMEM map: warp w uses TMEM lanes 32 (w % 4) .. +31 (the only ones it may touch) and columns 256 (w / 4) .. +255;
+// lane-private column 12 i + {0..5} = g(i, rows), {6..11} = v(i, rows) as 32-bit halves of the doubles.
+//
+// Arithmetic is the same sequence of correctly rounded operations as admm_subwarp.cu / admm_thread.cu, so all
+// kernels agree bit for bit on the carried state (tests switch kernels in the middle of a closed loop).
+//
+// Reference being reproduced: tinympc/TinyMPC/src/tinympc/admm.cpp:13-32 (Riccati sweeps), :81-98 (box slack),
+// :181-187 (dual), :214-247 (linear cost), :253-271 (termination), :274-389 (solve).
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdint>
+
+#include "admm_device.cuh"
+#include "admm_kernels.hpp"
+
+namespace tmpc {
+namespace {
+
+constexpr int kQWarps = 8;           // warps per CTA (one CTA per SM): two per scheduler
+constexpr int kQInst = 8;            // instances per warp
+constexpr unsigned kAll = 0xffffffffu;
+constexpr int kTmemColsPerWarp = 256;
+
+struct QuadParams {
+    double pri_thresh;      // primal residual passes  <=>  |x - vnew| <  pri_thresh
+    double dua_thresh;      // dual residual passes    <=>  |v - vnew| <= dua_thresh  (largest a with fl(rho a) < tol)
+    int* counter;           // instance queue
+    int off_consts, off_bounds, off_refs, off_warp0, warp_stride;   // shared-memory carve-up, in doubles
+};
+
+template <int NX>
+struct QPad {   // pitch of one instance's broadcast slot: an odd number of 16-byte chunks
+    static constexpr int value = ((NX / 2) % 2 == 1) ? NX : NX + 2;
+};
+
+template <int NX, int NU>
+struct QConst {      // shared staging of the problem constants (doubles)
+    static constexpr int A_rm = 0;                       // A(row, k) row-major
+    static constexpr int AmBKt_rm = A_rm + NX * NX;      // AmBKt(row, k) row-major
+    static constexpr int B_rm = AmBKt_rm + NX * NX;      // B(row, k) row-major  (NX x NU)
+    static constexpr int B_cm = B_rm + NX * NU;          // B(k, j) column-major: column j = row j of B'
+    static constexpr int Kinf_rm = B_cm + NX * NU;       // Kinf(j, k) row-major (NU x NX)
+    static constexpr int Kinf_cm = Kinf_rm + NX * NU;    // Kinf(k, row): column `row` = row of Kinf'
+    static constexpr int Quu_rm = Kinf_cm + NX * NU;     // Quu_inv(j, k) row-major
+    static constexpr int Pinf_cm = Quu_rm + NU * NU;     // Pinf(k, row): column `row`
+    static constexpr int f = Pinf_cm + NX * NX;
+    static constexpr int APf = f + NX;
+    static constexpr int BPf = APf + NX;
+    static constexpr int Qd = BPf + NU;
+    static constexpr int Rd = Qd + NX;
+    static constexpr int size = ((Rd + NU) + 1) / 2 * 2;
+};
+
+// ---------------------------------------------------------------- Tensor Memory as lane-private scratch
+struct TmRow { uint32_t w[12]; };     // one knot point of a lane: g(3 rows), v(3 rows) as 32-bit halves
+
+__device__ __forceinline__ void tm_ld4(uint32_t taddr, uint32_t* r) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(taddr));
+}
+__device__ __forceinline__ void tm_st4(uint32_t taddr, const uint32_t* r) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};"
+                 :: "r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]) : "memory");
+}
+template <int WORDS>
+__device__ __forceinline__ void tm_load(uint32_t taddr, uint32_t* w) {
+#pragma unroll
+    for (int k = 0; k < WORDS; k += 4) tm_ld4(taddr + k, w + k);
+}
+template <int WORDS>
+__device__ __forceinline__ void tm_store(uint32_t taddr, const uint32_t* w) {
+#pragma unroll
+    for (int k = 0; k < WORDS; k += 4) tm_st4(taddr + k, w + k);
+}
+// tcgen05.ld is asynchronous and NOT covered by the register scoreboard: the destination registers are valid
+// only after tcgen05.wait::ld.  Passing them through the wait as in/out operands makes every later use depend
+// on it, so the compiler cannot hoist a consumer above the wait.
+__device__ __forceinline__ void tm_wait_ld12(uint32_t* w) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(w[0]), "+r"(w[1]), "+r"(w[2]), "+r"(w[3]), "+r"(w[4]), "+r"(w[5]),
+                   "+r"(w[6]), "+r"(w[7]), "+r"(w[8]), "+r"(w[9]), "+r"(w[10]), "+r"(w[11]) :: "memory");
+}
+__device__ __forceinline__ void tm_wait_ld4(uint32_t* w) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(w[0]), "+r"(w[1]), "+r"(w[2]), "+r"(w[3]) :: "memory");
+}
+__device__ __forceinline__ void tm_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+__device__ __forceinline__ double mk_double(uint32_t lo, uint32_t hi) { return __hiloint2double(static_cast<int>(hi), static_cast<int>(lo)); }
+__device__ __forceinline__ uint32_t lo32(double d) { return static_cast<uint32_t>(__double2loint(d)); }
+__device__ __forceinline__ uint32_t hi32(double d) { return static_cast<uint32_t>(__double2hiint(d)); }
+
+__device__ __forceinline__ void ld2(const double* p, double& a, double& b) {
+    const double2 t = *reinterpret_cast<const double2*>(p);
+    a = t.x; b = t.y;
+}
+__device__ __forceinline__ void st2(double* p, double a, double b) { *reinterpret_cast<double2*>(p) = make_double2(a, b); }
+__device__ __forceinline__ double shfl_dq(double v, int src_lane) { return __shfl_sync(kAll, v, src_lane); }
+
+template <int W> __device__ __forceinline__ void tm_wait_ld(uint32_t* w);
+template <> __device__ __forceinline__ void tm_wait_ld<12>(uint32_t* w) { tm_wait_ld12(w); }
+template <> __device__ __forceinline__ void tm_wait_ld<4>(uint32_t* w) { tm_wait_ld4(w); }
+
+// REFS: 0 = no references (Xref = Uref = 0), 1 = references shared by all instances (staged in shared memory as
+// the products the linear cost needs), 2 = per-instance references read through the read-only path.
+template <int NX, int NU, bool COLD, int REFS>
+__global__ void __launch_bounds__(kQWarps * 32, 1)
+admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ AdmmSettings st,
+                 const __grid_constant__ QuadParams qp) {
+    static_assert(NX % 4 == 0 && NX >= 4, "state rows are dealt 4 lanes x RX rows");
+    static_assert(NU >= 1 && NU <= 4, "one input row per lane");
+    constexpr int RX = NX / 4;
+    constexpr int XP = QPad<NX>::value;
+    constexpr int W = 4 * RX;                         // 32-bit TMEM words per knot point per lane: g(RX), v(RX)
+    static_assert(W == 12 || W == 4, "tm_wait_ld is specialised for 3 or 1 state rows per lane");
+    using CL = QConst<NX, NU>;
+
+    extern __shared__ __align__(16) double smem[];
+    __shared__ uint32_t s_tmem_base;
+    const int N = bv.N;
+    const int nxN = NX * N, nuN = NU * (N - 1);
+    const size_t ld = static_cast<size_t>(bv.ld);
+    const double rho = bv.rho, nrho = -bv.rho;
+
+    // ---------------- Tensor Memory: the whole 512-column file of this SM (one CTA per SM)
+    if (threadIdx.x < 32) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;"
+                     :: "l"(static_cast<uint64_t>(__cvta_generic_to_shared(&s_tmem_base))) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+
+    // ---------------- stage the shared constants once per CTA
+    double* sc = smem + qp.off_consts;
+    for (int idx = threadIdx.x; idx < NX * NX; idx += blockDim.x) {
+        const int row = idx / NX, k = idx % NX;
+        sc[CL::A_rm + idx] = bv.A[k * NX + row];
+        sc[CL::AmBKt_rm + idx] = bv.AmBKt[k * NX + row];
+        sc[CL::Pinf_cm + idx] = bv.Pinf[idx];
+    }
+    for (int idx = threadIdx.x; idx < NX * NU; idx += blockDim.x) {
+        const int row = idx / NU, k = idx % NU;          // B(row, k)
+        sc[CL::B_rm + idx] = bv.Bm[k * NX + row];
+        sc[CL::B_cm + idx] = bv.Bm[idx];
+        const int j = idx / NX, kk = idx % NX;           // Kinf(j, kk)
+        sc[CL::Kinf_rm + idx] = bv.Kinf[kk * NU + j];
+        sc[CL::Kinf_cm + idx] = bv.Kinf[idx];
+    }
+    for (int idx = threadIdx.x; idx < NU * NU; idx += blockDim.x)
+        sc[CL::Quu_rm + idx] = bv.Quu_inv[(idx % NU) * NU + idx / NU];
+    for (int idx = threadIdx.x; idx < NX; idx += blockDim.x) {
+        sc[CL::f + idx] = bv.f[idx]; sc[CL::APf + idx] = bv.APf[idx]; sc[CL::Qd + idx] = bv.Qd[idx];
+    }
+    for (int idx = threadIdx.x; idx < NU; idx += blockDim.x) { sc[CL::BPf + idx] = bv.BPf[idx]; sc[CL::Rd + idx] = bv.Rd[idx]; }
+
+    // box bounds as (lo, hi) pairs; a disabled side is (-inf, +inf), for which the clamp is the identity
+    double* s_xb = smem + qp.off_bounds;              // [N][NX][2]
+    double* s_ub = s_xb + 2 * nxN;                    // [N-1][NU][2]
+    {
+        const bool bx = st.en_state_bound && bv.x_min != nullptr, bu = st.en_input_bound && bv.u_min != nullptr;
+        for (int e = threadIdx.x; e < nxN; e += blockDim.x) {
+            s_xb[2 * e] = bx ? bv.x_min[e] : -INFINITY; s_xb[2 * e + 1] = bx ? bv.x_max[e] : INFINITY;
+        }
+        for (int e = threadIdx.x; e < nuN; e += blockDim.x) {
+            s_ub[2 * e] = bu ? bv.u_min[e] : -INFINITY; s_ub[2 * e + 1] = bu ? bv.u_max[e] : INFINITY;
+        }
+    }
+    // shared references, stored as the terms the linear cost uses: cq = -(Xref .* Qd), cr = -(Uref .* Rd),
+    // tq = -(Xref_{N-1}' Pinf)'   (reference admm.cpp:218, :228, :238)
+    double* s_cq = smem + qp.off_refs;                // [N][NX]
+    double* s_cr = s_cq + nxN;                        // [N-1][NU]
+    double* s_tq = s_cr + nuN;                        // [NX]
+    if (REFS == 1) {
+        for (int e = threadIdx.x; e < nxN; e += blockDim.x) s_cq[e] = -dmul(bv.Xref ? bv.Xref[e] : 0.0, bv.Qd[e % NX]);
+        for (int e = threadIdx.x; e < nuN; e += blockDim.x) s_cr[e] = -dmul(bv.Uref ? bv.Uref[e] : 0.0, bv.Rd[e % NU]);
+        for (int row = threadIdx.x; row < NX; row += blockDim.x) {
+            double s = 0.0;
+            if (bv.Xref) for (int k = 0; k < NX; ++k) s = fma(bv.Xref[(N - 1) * NX + k], bv.Pinf[row * NX + k], s);
+            s_tq[row] = -s;
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;");
+
+    // ---------------- per-warp carve-up
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int inst = lane & 7, sub = lane >> 3;
+    const bool urow = (NU == 4) || (sub < NU);        // this lane owns an input row
+    const uint32_t tbase = s_tmem_base + (static_cast<uint32_t>((warp & 3) * 32) << 16) +
+                           static_cast<uint32_t>((warp >> 2) * kTmemColsPerWarp);
+    double* wbase = smem + qp.off_warp0 + static_cast<size_t>(warp) * qp.warp_stride;
+    double* s_yz = wbase;                             // [N-1][32 lanes][2] : (y, z) of the lane's input row
+    double* s_rt = s_yz + (N - 1) * 64;               // [N-1][8 inst][4]   : r_i (after a forward sweep) / t_i (after a backward sweep)
+    double* s_bc = s_rt + (N - 1) * 32;               // 2 x 8 x XP broadcast slots
+    double* my_rt = s_rt + inst * 4 + sub;            // + i * 32
+    const double* my_rt4 = s_rt + inst * 4;
+
+    const double fr_BPf = urow ? sc[CL::BPf + (urow ? sub : 0)] : 0.0;
+    const double fr_Rd = urow ? sc[CL::Rd + (urow ? sub : 0)] : 0.0;
+    double fr_f[RX], fr_APf[RX], fr_Qd[RX];
+#pragma unroll
+    for (int r = 0; r < RX; ++r) { fr_f[r] = sc[CL::f + r * 4 + sub]; fr_APf[r] = sc[CL::APf + r * 4 + sub]; fr_Qd[r] = sc[CL::Qd + r * 4 + sub]; }
+
+    // ---------------- per-lane instance state
+    int b = 0, iter = 0, status = 1;
+    bool valid = false, first = true, fin = true;     // fin = true: the sub-warp wants a (new) instance
+    double x0r[RX], p_term[RX];
+#pragma unroll
+    for (int r = 0; r < RX; ++r) { x0r[r] = 0.0; p_term[r] = 0.0; }
+    int bcast_phase = 0;
+    const double* xref_g = nullptr;                   // REFS == 2 only
+    const double* uref_g = nullptr;
+
+    for (;;) {
+        // =====================================================================================================
+        // write-out of finished instances + refill from the queue.  Warp-uniform (tcgen05.ld/st are .aligned):
+        // every lane walks the knot points, lanes whose instance is not finished store back what they loaded.
+        // =====================================================================================================
+        if (__any_sync(kAll, fin)) {
+            const bool wr = fin && valid;                 // results to write
+            const bool unconv = (status != 0);
+            const size_t bb = wr ? static_cast<size_t>(b) : 0;
+            if (wr && urow) {
+                double* Us = bv.Usol + bb * nuN;
+                for (int i = 0; i < N - 1; ++i) {
+                    const int e = i * NU + sub;
+                    const size_t ge = static_cast<size_t>(e) * ld + bb;
+                    double yy, zz;
+                    ld2(s_yz + (i * 32 + lane) * 2, yy, zz);
+                    Us[e] = zz;                                   // solution = znew of the last iteration (admm.cpp:371,387)
+                    bv.y[ge] = yy;
+                    if (unconv) bv.z[0][ge] = zz;                 // z = znew happened (admm.cpp:380); else the lagging copy is there
+                    bv.r[ge] = my_rt[i * 32];                     // r as update_linear_cost left it (admm.cpp:228-233)
+                }
+            }
+            if (wr) {
+#pragma unroll
+                for (int r = 0; r < RX; ++r) bv.pN[(r * 4 + sub) * ld + bb] = p_term[r];
+                if (sub == 0) { bv.status[b] = status; bv.iters[b] = iter; }
+            }
+            // next instance for every finished sub-warp
+            int nb = 0x7fffffff;
+            if (fin && sub == 0) nb = atomicAdd(qp.counter, 1);
+            nb = __shfl_sync(kAll, nb, inst);
+            const bool nvalid = fin && nb < bv.B;
+            const size_t nbb = nvalid ? static_cast<size_t>(nb) : 0;
+
+            double* Xs = bv.Xsol + bb * nxN;
+            const double* xr_old = (REFS == 2 && bv.Xref) ? bv.Xref + bb * bv.xref_stride : nullptr;
+            for (int i = 0; i < N; ++i) {
+                uint32_t w[W];
+                tm_load<W>(tbase + i * W, w);
+                tm_wait_ld<W>(w);
+#pragma unroll
+                for (int r = 0; r < RX; ++r) {
+                    const int e = i * NX + r * 4 + sub;
+                    if (wr) {
+                        const double gg = mk_double(w[2 * r], w[2 * r + 1]);
+                        const double vv = mk_double(w[2 * (RX + r)], w[2 * (RX + r) + 1]);
+                        const size_t ge = static_cast<size_t>(e) * ld + bb;
+                        Xs[e] = vv;                               // solution = vnew of the last iteration (admm.cpp:370,386)
+                        bv.g[ge] = gg;
+                        if (unconv) bv.v[0][ge] = vv;
+                        if (i < N - 1) {                          // q as update_linear_cost left it (admm.cpp:218-219)
+                            double q;
+                            if (REFS == 0) q = dmul(nrho, dsub(vv, gg));
+                            else {
+                                const double cq = (REFS == 1) ? s_cq[e] : -dmul(xr_old ? __ldg(xr_old + e) : 0.0, fr_Qd[r]);
+                                q = dsub(cq, dmul(rho, dsub(vv, gg)));
+                            }
+                            bv.q[ge] = q;
+                        }
+                    }
+                    if (fin) {
+                        double gg = 0.0, vv = 0.0;
+                        if (!COLD && nvalid) {
+                            const size_t ge = static_cast<size_t>(e) * ld + nbb;
+                            gg = bv.g[ge]; vv = bv.v[0][ge];
+                        }
+                        w[2 * r] = lo32(gg); w[2 * r + 1] = hi32(gg);
+                        w[2 * (RX + r)] = lo32(vv); w[2 * (RX + r) + 1] = hi32(vv);
+                    }
+                }
+                tm_store<W>(tbase + i * W, w);
+            }
+            if (fin) {
+                if (urow) {
+                    for (int i = 0; i < N - 1; ++i) {
+                        double yy = 0.0, zz = 0.0, rr = 0.0;
+                        if (!COLD && nvalid) {
+                            const size_t ge = static_cast<size_t>(i * NU + sub) * ld + nbb;
+                            yy = bv.y[ge]; zz = bv.z[0][ge]; rr = bv.r[ge];
+                        }
+                        st2(s_yz + (i * 32 + lane) * 2, yy, zz);
+                        my_rt[i * 32] = rr;
+                    }
+                } else {
+                    for (int i = 0; i < N - 1; ++i) { st2(s_yz + (i * 32 + lane) * 2, 0.0, 0.0); my_rt[i * 32] = 0.0; }
+                }
+#pragma unroll
+                for (int r = 0; r < RX; ++r) {
+                    x0r[r] = nvalid ? bv.x0[nbb * NX + r * 4 + sub] : 0.0;
+                    p_term[r] = (!COLD && nvalid) ? bv.pN[(r * 4 + sub) * ld + nbb] : 0.0;
+                }
+                b = nvalid ? nb : 0;
+                valid = nvalid; iter = 0; first = true; status = 1; fin = false;
+                if (REFS == 2) {
+                    xref_g = bv.Xref ? bv.Xref + nbb * bv.xref_stride : nullptr;
+                    uref_g = bv.Uref ? bv.Uref + nbb * bv.uref_stride : nullptr;
+                }
+            }
+            tm_wait_st();
+            __syncwarp();
+        }
+        if (!__any_sync(kAll, valid)) break;
+
+        const size_t bb = static_cast<size_t>(b);
+
+        // =====================================================================================================
+        // backward sweep: p_i for i = N-2 .. 0, leaving t_i = B' p_{i+1} + r_i + BPf for the forward sweep
+        // (reference admm.cpp:13-20; d_i = Quu_inv t_i is formed where it is consumed)
+        // =====================================================================================================
+        {
+            double Mab[RX][NX], Mkt[RX][NU], Mbt[NX];
+#pragma unroll
+            for (int r = 0; r < RX; ++r) {
+#pragma unroll
+                for (int k = 0; k < NX; k += 2) ld2(sc + CL::AmBKt_rm + (r * 4 + sub) * NX + k, Mab[r][k], Mab[r][k + 1]);
+#pragma unroll
+                for (int k = 0; k < NU; ++k) Mkt[r][k] = sc[CL::Kinf_cm + (r * 4 + sub) * NU + k];
+            }
+#pragma unroll
+            for (int k = 0; k < NX; ++k) Mbt[k] = urow ? sc[CL::B_cm + (urow ? sub : 0) * NX + k] : 0.0;
+
+            double p[RX];
+#pragma unroll
+            for (int r = 0; r < RX; ++r) p[r] = p_term[r];
+
+            uint32_t w[W];
+            tm_load<W>(tbase + (N - 2) * W, w);
+            double qcar[RX];                              // carried q of the first sweep of a warm-started solve
+#pragma unroll
+            for (int r = 0; r < RX; ++r) qcar[r] = 0.0;
+            const bool ldq = !COLD && first && valid;
+            if (ldq) {
+#pragma unroll
+                for (int r = 0; r < RX; ++r) qcar[r] = bv.q[static_cast<size_t>((N - 2) * NX + r * 4 + sub) * ld + bb];
+            }
+            double t_def = 0.0;
+
+            for (int i = N - 2; i >= 0; --i) {
+                double cq[RX];
+                if (REFS == 2) {
+#pragma unroll
+                    for (int r = 0; r < RX; ++r) cq[r] = -dmul(xref_g ? __ldg(xref_g + i * NX + r * 4 + sub) : 0.0, fr_Qd[r]);
+                }
+                // broadcast p_{i+1} to the 4 lanes of the instance
+                double* slot = s_bc + (bcast_phase & 1) * (kQInst * XP) + inst * XP;
+                ++bcast_phase;
+#pragma unroll
+                for (int r = 0; r < RX; ++r) slot[r * 4 + sub] = p[r];
+                __syncwarp();
+                if (i < N - 2 && urow) my_rt[(i + 1) * 32] = t_def;      // every lane has read r_{i+1} by now
+                double pb[NX];
+#pragma unroll
+                for (int k = 0; k < NX; k += 2) ld2(slot + k, pb[k], pb[k + 1]);
+                double rr[4];
+                ld2(my_rt4 + i * 32, rr[0], rr[1]);
+                ld2(my_rt4 + i * 32 + 2, rr[2], rr[3]);
+                const double r_own = my_rt[i * 32];
+
+                // q_i (own rows): carried on the first sweep of a solve, otherwise rebuilt from slacks and duals
+                tm_wait_ld<W>(w);
+                double q_own[RX];
+#pragma unroll
+                for (int r = 0; r < RX; ++r) {
+                    const double gg = mk_double(w[2 * r], w[2 * r + 1]);
+                    const double vv = mk_double(w[2 * (RX + r)], w[2 * (RX + r) + 1]);
+                    double q;
+                    if (REFS == 0) q = dmul(nrho, dsub(vv, gg));
+                    else q = dsub(REFS == 1 ? s_cq[i * NX + r * 4 + sub] : cq[r], dmul(rho, dsub(vv, gg)));
+                    q_own[r] = first ? qcar[r] : q;
+                }
+                if (i > 0) {
+                    tm_load<W>(tbase + (i - 1) * W, w);
+                    if (ldq) {
+#pragma unroll
+                        for (int r = 0; r < RX; ++r) qcar[r] = bv.q[static_cast<size_t>((i - 1) * NX + r * 4 + sub) * ld + bb];
+                    }
+                }
+
+                // t_i = B' p_{i+1} + r_i + BPf   (own input row)
+                double s = 0.0;
+#pragma unroll
+                for (int k = 0; k < NX; ++k) s = fma(Mbt[k], pb[k], s);
+                t_def = dadd(dadd(s, r_own), fr_BPf);
+
+                // p_i = q_i + AmBKt p_{i+1} - Kinf' r_i + APf
+#pragma unroll
+                for (int r = 0; r < RX; ++r) {
+                    double s1 = 0.0, s2 = 0.0;
+#pragma unroll
+                    for (int k = 0; k < NX; ++k) s1 = fma(Mab[r][k], pb[k], s1);
+#pragma unroll
+                    for (int k = 0; k < NU; ++k) s2 = fma(Mkt[r][k], rr[k], s2);
+                    p[r] = dadd(dsub(dadd(q_own[r], s1), s2), fr_APf[r]);
+                }
+            }
+            __syncwarp();
+            if (urow) my_rt[0] = t_def;
+        }
+
+        // =====================================================================================================
+        // forward sweep fused with slack / dual / linear-cost / residual updates
+        // (reference admm.cpp:25-32, :84-98, :184-187, :218-239, :257-265)
+        // =====================================================================================================
+        bool ok = true;              // every residual this lane has seen in this sweep is under its tolerance
+        {
+            double Ma[RX][NX], Mb[RX][NU], Mk[NX], Mq[NU];
+#pragma unroll
+            for (int r = 0; r < RX; ++r) {
+#pragma unroll
+                for (int k = 0; k < NX; k += 2) ld2(sc + CL::A_rm + (r * 4 + sub) * NX + k, Ma[r][k], Ma[r][k + 1]);
+#pragma unroll
+                for (int k = 0; k < NU; ++k) Mb[r][k] = sc[CL::B_rm + (r * 4 + sub) * NU + k];
+            }
+#pragma unroll
+            for (int k = 0; k < NX; ++k) Mk[k] = urow ? sc[CL::Kinf_rm + (urow ? sub : 0) * NX + k] : 0.0;
+#pragma unroll
+            for (int k = 0; k < NU; ++k) Mq[k] = urow ? sc[CL::Quu_rm + (urow ? sub : 0) * NU + k] : 0.0;
+
+            double x[RX];
+#pragma unroll
+            for (int r = 0; r < RX; ++r) x[r] = x0r[r];
+            uint32_t w[W];
+            tm_load<W>(tbase, w);
+            // the carried "previous slacks" must lag the solution by one iteration when the solve converges
+            // (admm.cpp:375 returns before :379-380): while this sweep can still end in convergence, park them in HBM
+            const bool lag = valid && ((iter + 1) % st.check_termination == 0);
+            double* vlag = bv.v[0] + static_cast<size_t>(sub) * ld + bb;      // + (i NX + 4 r) ld
+            double* zlag = bv.z[0] + static_cast<size_t>(sub) * ld + bb;      // + (i NU) ld
+            double r_def = 0.0;
+
+            for (int i = 0; i < N; ++i) {
+                const bool terminal = (i == N - 1);
+                double xb[NX], ub[NU];
+                if (!terminal) {
+                    double cr = 0.0;
+                    if (REFS == 2) cr = -dmul((uref_g && urow) ? __ldg(uref_g + i * NU + sub) : 0.0, fr_Rd);
+                    double* slot = s_bc + (bcast_phase & 1) * (kQInst * XP) + inst * XP;
+                    ++bcast_phase;
+#pragma unroll
+                    for (int r = 0; r < RX; ++r) slot[r * 4 + sub] = x[r];
+                    __syncwarp();
+                    if (i > 0 && urow) my_rt[(i - 1) * 32] = r_def;          // every lane has read t_{i-1} by now
+#pragma unroll
+                    for (int k = 0; k < NX; k += 2) ld2(slot + k, xb[k], xb[k + 1]);
+                    double tt[4];
+                    ld2(my_rt4 + i * 32, tt[0], tt[1]);
+                    ld2(my_rt4 + i * 32 + 2, tt[2], tt[3]);
+
+                    // d_i = Quu_inv t_i ; u_i = -Kinf x_i - d_i
+                    double d = 0.0;
+#pragma unroll
+                    for (int k = 0; k < NU; ++k) d = fma(Mq[k], tt[k], d);
+                    double s = 0.0;
+#pragma unroll
+                    for (int k = 0; k < NX; ++k) s = fma(Mk[k], xb[k], s);
+                    double u_own = 0.0;
+                    if (urow) {
+                        u_own = dsub(-s, d);
+                        double yj, zold, lo, hi;
+                        ld2(s_yz + (i * 32 + lane) * 2, yj, zold);
+                        ld2(s_ub + (i * NU + sub) * 2, lo, hi);
+                        const double t = dadd(u_own, yj);
+                        const double znew = clampd(t, lo, hi);
+                        const double ynew = dsub(t, znew);                  // y + u - znew
+                        ok = ok && (fabs(dsub(u_own, znew)) < qp.pri_thresh) && (fabs(dsub(zold, znew)) <= qp.dua_thresh);
+                        if (lag && ok) zlag[static_cast<size_t>(i * NU) * ld] = zold;
+                        st2(s_yz + (i * 32 + lane) * 2, ynew, znew);
+                        // r_i = -(Uref .* Rd) - rho (znew - y)    (admm.cpp:228-229)
+                        if (REFS == 0) r_def = dmul(nrho, dsub(znew, ynew));
+                        else r_def = dsub(REFS == 1 ? s_cr[i * NU + sub] : cr, dmul(rho, dsub(znew, ynew)));
+                    }
+#pragma unroll
+                    for (int k = 0; k < NU; ++k) ub[k] = shfl_dq(u_own, k * kQInst + inst);
+                }
+
+                // state column i: slack, dual, residuals
+                tm_wait_ld<W>(w);
+                double gold[RX], vold[RX];
+#pragma unroll
+                for (int r = 0; r < RX; ++r) {
+                    gold[r] = mk_double(w[2 * r], w[2 * r + 1]);
+                    vold[r] = mk_double(w[2 * (RX + r)], w[2 * (RX + r) + 1]);
+                }
+                if (!terminal) tm_load<W>(tbase + (i + 1) * W, w);
+                uint32_t wn[W];
+                double vg[RX];
+#pragma unroll
+                for (int r = 0; r < RX; ++r) {
+                    double lo, hi;
+                    ld2(s_xb + (i * NX + r * 4 + sub) * 2, lo, hi);
+                    const double t = dadd(x[r], gold[r]);
+                    const double vnew = clampd(t, lo, hi);
+                    const double gnew = dsub(t, vnew);
+                    ok = ok && (fabs(dsub(x[r], vnew)) < qp.pri_thresh) && (fabs(dsub(vold[r], vnew)) <= qp.dua_thresh);
+                    if (lag && ok) vlag[static_cast<size_t>(i * NX + r * 4) * ld] = vold[r];
+                    wn[2 * r] = lo32(gnew); wn[2 * r + 1] = hi32(gnew);
+                    wn[2 * (RX + r)] = lo32(vnew); wn[2 * (RX + r) + 1] = hi32(vnew);
+                    vg[r] = dsub(vnew, gnew);
+                }
+                tm_store<W>(tbase + i * W, wn);
+
+                if (!terminal) {
+                    // x_{i+1} = A x_i + B u_i + f
+#pragma unroll
+                    for (int r = 0; r < RX; ++r) {
+                        double s1 = 0.0, s2 = 0.0;
+#pragma unroll
+                        for (int k = 0; k < NX; ++k) s1 = fma(Ma[r][k], xb[k], s1);
+#pragma unroll
+                        for (int k = 0; k < NU; ++k) s2 = fma(Mb[r][k], ub[k], s2);
+                        x[r] = dadd(dadd(s1, s2), fr_f[r]);
+                    }
+                } else {
+                    // p_{N-1} = -(Xref_{N-1}' Pinf)' - rho (vnew - g)   (admm.cpp:238-239)
+#pragma unroll
+                    for (int r = 0; r < RX; ++r) {
+                        if (REFS == 0) p_term[r] = dmul(nrho, vg[r]);
+                        else if (REFS == 1) p_term[r] = dsub(s_tq[r * 4 + sub], dmul(rho, vg[r]));
+                        else {
+                            double s = 0.0;
+                            if (xref_g) for (int k = 0; k < NX; ++k) s = fma(__ldg(xref_g + i * NX + k), sc[CL::Pinf_cm + (r * 4 + sub) * NX + k], s);
+                            p_term[r] = dsub(-s, dmul(rho, vg[r]));
+                        }
+                    }
+                }
+            }
+            tm_wait_st();
+            __syncwarp();
+            if (urow) my_rt[(N - 2) * 32] = r_def;
+        }
+
+        // =====================================================================================================
+        // termination (admm.cpp:253-271, :364-388), per instance
+        // =====================================================================================================
+        iter += 1;
+        first = false;
+        const unsigned votes = __ballot_sync(kAll, ok);
+        const unsigned mine = 0x01010101u << inst;
+        const bool conv = valid && (iter % st.check_termination == 0) && ((votes & mine) == mine);
+        status = conv ? 0 : 1;
+        fin = valid && (conv || iter >= st.max_iter);
+    }
+
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" :: "r"(s_tmem_base));
+    }
+}
+
+// Largest a >= 0 with fl(rho * a) < tol, so that  rho * max|.| < tol  <=>  every |.| <= a.
+double dual_threshold_q(double rho, double tol) {
+    if (!(tol > 0.0) || !(rho > 0.0)) return -1.0;
+    double a = tol / rho;
+    while (rho * a < tol) a = std::nextafter(a, INFINITY);
+    while (!(rho * a < tol)) a = std::nextafter(a, -INFINITY);
+    return a;
+}
+
+struct QPlan { size_t smem_bytes; QuadParams qp; };
+
+template <int NX, int NU>
+bool make_qplan(int N, int refs, QPlan& pl) {
+    constexpr int XP = QPad<NX>::value;
+    constexpr int W = 4 * (NX / 4);
+    if (N < 2 || N * W > kTmemColsPerWarp) return false;           // g, v of a lane must fit its 256 TMEM columns
+    const int nxN = NX * N, nuN = NU * (N - 1);
+    QuadParams qp{};
+    int off = 0;
+    qp.off_consts = off; off += QConst<NX, NU>::size;
+    qp.off_bounds = off; off += 2 * (nxN + nuN);
+    qp.off_refs = off; if (refs == 1) off += nxN + nuN + NX;
+    off = (off + 1) / 2 * 2;
+    qp.off_warp0 = off;
+    int per_warp = (N - 1) * 96 + 2 * kQInst * XP;
+    per_warp = (per_warp + 1) / 2 * 2;
+    qp.warp_stride = per_warp;
+    pl.smem_bytes = (static_cast<size_t>(off) + static_cast<size_t>(per_warp) * kQWarps) * sizeof(double);
+    pl.qp = qp;
+    return pl.smem_bytes <= 227 * 1024;
+}
+
+int refs_mode(const BatchView& bv) {
+    if (bv.Xref == nullptr && bv.Uref == nullptr) return 0;
+    const bool xs = bv.Xref == nullptr || bv.xref_stride == 0, us = bv.Uref == nullptr || bv.uref_stride == 0;
+    return (xs && us) ? 1 : 2;
+}
+
+template <int NX, int NU, bool COLD, int REFS>
+cudaError_t launch_q(const BatchView& bv, const AdmmSettings& st, const QPlan& pl, int num_sms, cudaStream_t stream) {
+    auto kern = admm_tmem_kernel<NX, NU, COLD, REFS>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(pl.smem_bytes));
+    if (e != cudaSuccess) return e;
+    const int per_cta = kQWarps * kQInst;
+    int grid = (bv.B + per_cta - 1) / per_cta;
+    if (grid > num_sms) grid = num_sms;            // persistent: one CTA per SM, sub-warps pull instances from the queue
+    kern<<<grid, kQWarps * 32, pl.smem_bytes, stream>>>(bv, st, pl.qp);
+    return cudaGetLastError();
+}
+
+template <int NX, int NU>
+cudaError_t launch_shape(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms, cudaStream_t stream) {
+    QPlan pl;
+    const int refs = refs_mode(bv);
+    if (!make_qplan<NX, NU>(bv.N, refs, pl)) return cudaErrorInvalidConfiguration;
+    pl.qp.counter = counter;
+    pl.qp.pri_thresh = st.abs_pri_tol;
+    pl.qp.dua_thresh = dual_threshold_q(bv.rho, st.abs_dua_tol);
+    cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(int), stream);
+    if (e != cudaSuccess) return e;
+    if (cold) {
+        if (refs == 0) return launch_q<NX, NU, true, 0>(bv, st, pl, num_sms, stream);
+        if (refs == 1) return launch_q<NX, NU, true, 1>(bv, st, pl, num_sms, stream);
+        return launch_q<NX, NU, true, 2>(bv, st, pl, num_sms, stream);
+    }
+    if (refs == 0) return launch_q<NX, NU, false, 0>(bv, st, pl, num_sms, stream);
+    if (refs == 1) return launch_q<NX, NU, false, 1>(bv, st, pl, num_sms, stream);
+    return launch_q<NX, NU, false, 2>(bv, st, pl, num_sms, stream);
+}
+
+}  // namespace
+
+bool tmem_kernel_supports(const BatchView& bv, const AdmmSettings& st) {
+    if (st.en_state_soc || st.en_input_soc || st.en_state_linear || st.en_input_linear) return false;
+    if (st.max_iter <= 0 || !(bv.rho > 0.0)) return false;
+    if (bv.x_min != nullptr && (bv.xb_stride != 0 || bv.ub_stride != 0)) return false;   // per-instance bounds: other kernels
+    QPlan pl;
+    if (bv.nx == 12 && bv.nu == 4) return make_qplan<12, 4>(bv.N, refs_mode(bv), pl);
+    return false;
+}
+
+cudaError_t launch_admm_tmem(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms,
+                             cudaStream_t stream) {
+    if (bv.B <= 0) return cudaSuccess;
+    if (bv.nx == 12 && bv.nu == 4) return launch_shape<12, 4>(bv, st, cold, counter, num_sms, stream);
+    return cudaErrorNotSupported;
+}
+
+}  // namespace tmpc

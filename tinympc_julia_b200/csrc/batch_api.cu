@@ -143,11 +143,13 @@ tmpc::BatchView make_view(tmpc_batch* h) {
     return v;
 }
 
-int resolve_kernel(const tmpc_batch* h) {
+int resolve_kernel(tmpc_batch* h) {
     const bool sub_ok = tmpc::subwarp_kernel_supports(h->nx, h->nu, h->N, h->st);
+    const bool tm_ok = tmpc::tmem_kernel_supports(make_view(h), h->st);
+    if (h->kernel_pref == TMPC_KERNEL_TMEM) return tm_ok ? TMPC_KERNEL_TMEM : -1;
     if (h->kernel_pref == TMPC_KERNEL_SUBWARP) return sub_ok ? TMPC_KERNEL_SUBWARP : -1;
     if (h->kernel_pref == TMPC_KERNEL_THREAD) return TMPC_KERNEL_THREAD;
-    return sub_ok ? TMPC_KERNEL_SUBWARP : TMPC_KERNEL_THREAD;
+    return tm_ok ? TMPC_KERNEL_TMEM : (sub_ok ? TMPC_KERNEL_SUBWARP : TMPC_KERNEL_THREAD);
 }
 
 void zero_state(tmpc_batch* h) {
@@ -169,7 +171,7 @@ void materialize_zero(tmpc_batch* h) {
 // One solve kernel on `s`.  A cold (reset) state is passed to the sub-warp kernel as a flag; every other
 // reader gets physically zeroed buffers first (memsets on the handle's stream, joined into `s` by an event).
 cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v, cudaStream_t s) {
-    const bool sub = (k == TMPC_KERNEL_SUBWARP) && h->st.max_iter > 0 && h->rho > 0.0;
+    const bool sub = (k == TMPC_KERNEL_SUBWARP || k == TMPC_KERNEL_TMEM) && h->st.max_iter > 0 && h->rho > 0.0;
     if (!sub && h->state_zero && !h->mem_zero) {
         zero_state(h);
         if (s != h->stream) {
@@ -180,8 +182,10 @@ cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v, cudaStr
             CUDA_TRY(cudaEventDestroy(ev));
         }
     }
-    cudaError_t e = sub ? tmpc::launch_admm_subwarp(v, h->st, h->hm, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s)
-                        : tmpc::launch_admm_thread(v, h->st, h->hm, s);
+    cudaError_t e;
+    if (sub && k == TMPC_KERNEL_TMEM) e = tmpc::launch_admm_tmem(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
+    else if (sub) e = tmpc::launch_admm_subwarp(v, h->st, h->hm, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
+    else e = tmpc::launch_admm_thread(v, h->st, h->hm, s);
     h->launches += 1;
     if (h->st.max_iter > 0) { h->state_zero = false; h->mem_zero = false; }
     return e;
@@ -193,7 +197,7 @@ int enqueue_solve(tmpc_batch* h, cudaStream_t s) {
     if (h->st.check_termination == 0) { set_error("check_termination = 0 is not supported (the reference divides by it)"); return TMPC_ERR_STATE; }
     ensure_aux_state(h);
     const int k = resolve_kernel(h);
-    if (k < 0) { set_error("sub-warp kernel requested but it does not support this problem (shape or constraint flags)"); return TMPC_ERR_STATE; }
+    if (k < 0) { set_error("requested kernel does not support this problem (shape, constraint flags or per-instance bounds)"); return TMPC_ERR_STATE; }
     tmpc::BatchView v = make_view(h);
     cudaError_t e;
     e = launch_solve(h, k, v, s);
@@ -335,7 +339,7 @@ int tmpc_batch_update_settings(tmpc_batch* h, double abs_pri_tol, double abs_dua
 }
 
 int tmpc_batch_set_kernel(tmpc_batch* h, int kernel) {
-    if (!h || kernel < TMPC_KERNEL_AUTO || kernel > TMPC_KERNEL_SUBWARP) return TMPC_ERR_DIM;
+    if (!h || kernel < TMPC_KERNEL_AUTO || kernel > TMPC_KERNEL_TMEM) return TMPC_ERR_DIM;
     h->kernel_pref = kernel;
     return TMPC_OK;
 }
@@ -600,7 +604,7 @@ int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_lo
         if (h->st.check_termination == 0) { set_error("check_termination = 0 is not supported"); return TMPC_ERR_STATE; }
         ensure_aux_state(h);
         const int k = resolve_kernel(h);
-        if (k < 0) { set_error("sub-warp kernel requested but unsupported for this problem"); return TMPC_ERR_STATE; }
+        if (k < 0) { set_error("requested kernel does not support this problem"); return TMPC_ERR_STATE; }
         const long long ref_len = static_cast<long long>(h->nx) * (h->N + nsteps - 1);
         for (int step = 0; step < nsteps; ++step) {
             tmpc::BatchView v = make_view(h);

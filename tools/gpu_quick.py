@@ -7,12 +7,13 @@ import cases, oracle
 import tinympc_julia_b200 as t
 
 orc = oracle.load_oracle()
-for name in ("cartpole_one_solve", "quadrotor_easy_64", "quadrotor_hard_64", "rocket_julia_example", "random_5x2_16"):
+for name in ("cartpole_one_solve", "quadrotor_easy_64", "quadrotor_hard_64", "quadrotor_hover", "quadrotor_per_instance_32", "quadrotor_closed_loop_16x40", "rocket_julia_example", "random_5x2_16"):
     c = cases.GOLDEN_CASES[name]()
     want = cases.load_golden(name)
-    for k in (1, 2):
+    for k in (1, 2, 3):
         sol = cases.make_cuda_solver(c, kernel=0)
-        if k == 2 and sol.kernel != 2:
+        sol.set_kernel(k)
+        if sol.kernel != k:
             continue
         got = cases.run_cuda(c, kernel=k)
         print(name, "kernel", k, "iter mismatches", int((got["iters"] != want["iters"]).sum()), "of", want["iters"].size,
@@ -22,11 +23,11 @@ import torch
 B = int(os.environ.get("QB", 65536))
 for hard in (False, True):
     c = cases.quadrotor_batch(B, hard=hard)
-    for k in (1, 2):
+    for k in (1, 2, 3):
         sol = cases.make_cuda_solver(c, kernel=0)
-        if k == 2 and sol.kernel != 2:
-            continue
         sol.set_kernel(k)
+        if sol.kernel != k:
+            continue
         t.set_x0(sol, c["x0"])
         ts = []
         for rep in range(4):
