@@ -209,10 +209,12 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                            static_cast<uint32_t>((warp >> 2) * kTmemColsPerWarp);
     double* wbase = smem + qp.off_warp0 + static_cast<size_t>(warp) * qp.warp_stride;
     double* s_yz = wbase;                             // [N-1][32 lanes][2] : (y, z) of the lane's input row
-    double* s_rt = s_yz + (N - 1) * 64;               // [N-1][8 inst][4]   : r_i (after a forward sweep) / t_i (after a backward sweep)
+    double* s_rt = s_yz + (N - 1) * 64;               // [N-1][2 halves][8 inst][2] : r_i (after a forward sweep) / t_i (after a
+                                                      // backward sweep); rows (0,1) and (2,3) of the 8 instances are each 128
+                                                      // contiguous bytes, so the 4-vector comes back in two conflict-free LDS.128
     double* s_bc = s_rt + (N - 1) * 32;               // 2 x 8 x XP broadcast slots
-    double* my_rt = s_rt + inst * 4 + sub;            // + i * 32
-    const double* my_rt4 = s_rt + inst * 4;
+    double* my_rt = s_rt + (sub >> 1) * 16 + inst * 2 + (sub & 1);   // + i * 32 : own row
+    const double* my_rt4 = s_rt + inst * 2;                          // + i * 32 (+ 16 for rows 2, 3)
 
     const double fr_BPf = urow ? sc[CL::BPf + (urow ? sub : 0)] : 0.0;
     const double fr_Rd = urow ? sc[CL::Rd + (urow ? sub : 0)] : 0.0;
@@ -279,7 +281,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                         const size_t ge = static_cast<size_t>(e) * ld + bb;
                         Xs[e] = vv;                               // solution = vnew of the last iteration (admm.cpp:370,386)
                         bv.g[ge] = gg;
-                        if (unconv) bv.v[0][ge] = vv;
+                        if (unconv) bv.v[0][ge] = vv;             // v = vnew happened (admm.cpp:379); else the lagging copy is there
                         if (i < N - 1) {                          // q as update_linear_cost left it (admm.cpp:218-219)
                             double q;
                             if (REFS == 0) q = dmul(nrho, dsub(vv, gg));
@@ -385,7 +387,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 for (int k = 0; k < NX; k += 2) ld2(slot + k, pb[k], pb[k + 1]);
                 double rr[4];
                 ld2(my_rt4 + i * 32, rr[0], rr[1]);
-                ld2(my_rt4 + i * 32 + 2, rr[2], rr[3]);
+                ld2(my_rt4 + i * 32 + 16, rr[2], rr[3]);
                 const double r_own = my_rt[i * 32];
 
                 // q_i (own rows): carried on the first sweep of a solve, otherwise rebuilt from slacks and duals
@@ -435,18 +437,19 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
         // =====================================================================================================
         bool ok = true;              // every residual this lane has seen in this sweep is under its tolerance
         {
-            double Ma[RX][NX], Mb[RX][NU], Mk[NX], Mq[NU];
+            // register-resident: the lane's rows of A and Kinf (48 doubles).  B and Quu_inv rows are re-read from
+            // shared memory every knot point (8 broadcast LDS.128 off the critical path): keeping them in registers
+            // too pushed the sweep over the register file and the compiler into rematerialising addresses.
+            double Ma[RX][NX], Mk[NX];
 #pragma unroll
             for (int r = 0; r < RX; ++r) {
 #pragma unroll
                 for (int k = 0; k < NX; k += 2) ld2(sc + CL::A_rm + (r * 4 + sub) * NX + k, Ma[r][k], Ma[r][k + 1]);
-#pragma unroll
-                for (int k = 0; k < NU; ++k) Mb[r][k] = sc[CL::B_rm + (r * 4 + sub) * NU + k];
             }
 #pragma unroll
             for (int k = 0; k < NX; ++k) Mk[k] = urow ? sc[CL::Kinf_rm + (urow ? sub : 0) * NX + k] : 0.0;
-#pragma unroll
-            for (int k = 0; k < NU; ++k) Mq[k] = urow ? sc[CL::Quu_rm + (urow ? sub : 0) * NU + k] : 0.0;
+            const double* sMb = sc + CL::B_rm + sub * NU;                 // + r * 4 * NU : row r*4+sub of B
+            const double* sMq = sc + CL::Quu_rm + (urow ? sub : 0) * NU;
 
             double x[RX];
 #pragma unroll
@@ -454,15 +457,18 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             uint32_t w[W];
             tm_load<W>(tbase, w);
             // the carried "previous slacks" must lag the solution by one iteration when the solve converges
-            // (admm.cpp:375 returns before :379-380): while this sweep can still end in convergence, park them in HBM
+            // (admm.cpp:375 returns before :379-380): while this sweep can still end in convergence the lane parks
+            // them in the carried-state arrays in HBM (running pointers: no address arithmetic per store)
             const bool lag = valid && ((iter + 1) % st.check_termination == 0);
-            double* vlag = bv.v[0] + static_cast<size_t>(sub) * ld + bb;      // + (i NX + 4 r) ld
-            double* zlag = bv.z[0] + static_cast<size_t>(sub) * ld + bb;      // + (i NU) ld
+            double* vlag = bv.v[0] + static_cast<size_t>(sub) * ld + bb;      // row r of knot i: + (i NX + 4 r) ld
+            double* zlag = bv.z[0] + static_cast<size_t>(sub) * ld + bb;      // knot i: + (i NU) ld
+            const size_t ld4 = 4 * ld, ldx = static_cast<size_t>(NX) * ld, ldu = static_cast<size_t>(NU) * ld;
             double r_def = 0.0;
 
             for (int i = 0; i < N; ++i) {
                 const bool terminal = (i == N - 1);
-                double xb[NX], ub[NU];
+                double s1[RX];
+                double ub[NU];
                 if (!terminal) {
                     double cr = 0.0;
                     if (REFS == 2) cr = -dmul((uref_g && urow) ? __ldg(uref_g + i * NU + sub) : 0.0, fr_Rd);
@@ -472,30 +478,45 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                     for (int r = 0; r < RX; ++r) slot[r * 4 + sub] = x[r];
                     __syncwarp();
                     if (i > 0 && urow) my_rt[(i - 1) * 32] = r_def;          // every lane has read t_{i-1} by now
+                    double xb[NX];
 #pragma unroll
                     for (int k = 0; k < NX; k += 2) ld2(slot + k, xb[k], xb[k + 1]);
-                    double tt[4];
+                    double tt[4], mq[4];
                     ld2(my_rt4 + i * 32, tt[0], tt[1]);
-                    ld2(my_rt4 + i * 32 + 2, tt[2], tt[3]);
+                    ld2(my_rt4 + i * 32 + 16, tt[2], tt[3]);
+#pragma unroll
+                    for (int k = 0; k < NU; k += 2) {
+                        if (k + 1 < NU) ld2(sMq + k, mq[k], mq[k + 1]); else mq[k] = sMq[k];
+                    }
+                    double yj = 0.0, zold = 0.0, ulo = 0.0, uhi = 0.0;
+                    if (urow) {
+                        ld2(s_yz + (i * 32 + lane) * 2, yj, zold);
+                        ld2(s_ub + (i * NU + sub) * 2, ulo, uhi);
+                    }
 
-                    // d_i = Quu_inv t_i ; u_i = -Kinf x_i - d_i
+                    // d_i = Quu_inv t_i ;  -u_i - d_i = Kinf x_i ;  A x_i  — five independent chains, interleaved
                     double d = 0.0;
 #pragma unroll
-                    for (int k = 0; k < NU; ++k) d = fma(Mq[k], tt[k], d);
+                    for (int k = 0; k < NU; ++k) d = fma(mq[k], tt[k], d);
                     double s = 0.0;
 #pragma unroll
-                    for (int k = 0; k < NX; ++k) s = fma(Mk[k], xb[k], s);
+                    for (int r = 0; r < RX; ++r) s1[r] = 0.0;
+#pragma unroll
+                    for (int k = 0; k < NX; ++k) {
+                        s = fma(Mk[k], xb[k], s);
+#pragma unroll
+                        for (int r = 0; r < RX; ++r) s1[r] = fma(Ma[r][k], xb[k], s1[r]);
+                    }
                     double u_own = 0.0;
                     if (urow) {
                         u_own = dsub(-s, d);
-                        double yj, zold, lo, hi;
-                        ld2(s_yz + (i * 32 + lane) * 2, yj, zold);
-                        ld2(s_ub + (i * NU + sub) * 2, lo, hi);
                         const double t = dadd(u_own, yj);
-                        const double znew = clampd(t, lo, hi);
+                        const double znew = clampd(t, ulo, uhi);
                         const double ynew = dsub(t, znew);                  // y + u - znew
-                        ok = ok && (fabs(dsub(u_own, znew)) < qp.pri_thresh) && (fabs(dsub(zold, znew)) <= qp.dua_thresh);
-                        if (lag && ok) zlag[static_cast<size_t>(i * NU) * ld] = zold;
+                        const bool p1 = fabs(dsub(u_own, znew)) < qp.pri_thresh;
+                        const bool p2 = fabs(dsub(zold, znew)) <= qp.dua_thresh;
+                        ok = ok & p1 & p2;
+                        if (lag & ok) *zlag = zold;
                         st2(s_yz + (i * 32 + lane) * 2, ynew, znew);
                         // r_i = -(Uref .* Rd) - rho (znew - y)    (admm.cpp:228-229)
                         if (REFS == 0) r_def = dmul(nrho, dsub(znew, ynew));
@@ -505,42 +526,44 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                     for (int k = 0; k < NU; ++k) ub[k] = shfl_dq(u_own, k * kQInst + inst);
                 }
 
-                // state column i: slack, dual, residuals
+                // state column i: slack, dual, residuals (independent of u_i: overlaps the shuffles)
                 tm_wait_ld<W>(w);
-                double gold[RX], vold[RX];
-#pragma unroll
-                for (int r = 0; r < RX; ++r) {
-                    gold[r] = mk_double(w[2 * r], w[2 * r + 1]);
-                    vold[r] = mk_double(w[2 * (RX + r)], w[2 * (RX + r) + 1]);
-                }
-                if (!terminal) tm_load<W>(tbase + (i + 1) * W, w);
                 uint32_t wn[W];
                 double vg[RX];
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
+                    const double gold = mk_double(w[2 * r], w[2 * r + 1]);
+                    const double vold = mk_double(w[2 * (RX + r)], w[2 * (RX + r) + 1]);
                     double lo, hi;
                     ld2(s_xb + (i * NX + r * 4 + sub) * 2, lo, hi);
-                    const double t = dadd(x[r], gold[r]);
+                    const double t = dadd(x[r], gold);
                     const double vnew = clampd(t, lo, hi);
                     const double gnew = dsub(t, vnew);
-                    ok = ok && (fabs(dsub(x[r], vnew)) < qp.pri_thresh) && (fabs(dsub(vold[r], vnew)) <= qp.dua_thresh);
-                    if (lag && ok) vlag[static_cast<size_t>(i * NX + r * 4) * ld] = vold[r];
+                    const bool p1 = fabs(dsub(x[r], vnew)) < qp.pri_thresh;
+                    const bool p2 = fabs(dsub(vold, vnew)) <= qp.dua_thresh;
+                    ok = ok & p1 & p2;
+                    if (lag & ok) vlag[r * ld4] = vold;
                     wn[2 * r] = lo32(gnew); wn[2 * r + 1] = hi32(gnew);
                     wn[2 * (RX + r)] = lo32(vnew); wn[2 * (RX + r) + 1] = hi32(vnew);
                     vg[r] = dsub(vnew, gnew);
                 }
                 tm_store<W>(tbase + i * W, wn);
+                vlag += ldx; zlag += ldu;
 
                 if (!terminal) {
+                    tm_load<W>(tbase + (i + 1) * W, w);          // next knot point; consumed after the next broadcast
                     // x_{i+1} = A x_i + B u_i + f
 #pragma unroll
                     for (int r = 0; r < RX; ++r) {
-                        double s1 = 0.0, s2 = 0.0;
+                        double mb[4];
 #pragma unroll
-                        for (int k = 0; k < NX; ++k) s1 = fma(Ma[r][k], xb[k], s1);
+                        for (int k = 0; k < NU; k += 2) {
+                            if (k + 1 < NU) ld2(sMb + r * 4 * NU + k, mb[k], mb[k + 1]); else mb[k] = sMb[r * 4 * NU + k];
+                        }
+                        double s2 = 0.0;
 #pragma unroll
-                        for (int k = 0; k < NU; ++k) s2 = fma(Mb[r][k], ub[k], s2);
-                        x[r] = dadd(dadd(s1, s2), fr_f[r]);
+                        for (int k = 0; k < NU; ++k) s2 = fma(mb[k], ub[k], s2);
+                        x[r] = dadd(dadd(s1[r], s2), fr_f[r]);
                     }
                 } else {
                     // p_{N-1} = -(Xref_{N-1}' Pinf)' - rho (vnew - g)   (admm.cpp:238-239)
@@ -630,7 +653,8 @@ cudaError_t launch_q(const BatchView& bv, const AdmmSettings& st, const QPlan& p
 }
 
 template <int NX, int NU>
-cudaError_t launch_shape(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms, cudaStream_t stream) {
+cudaError_t launch_shape(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms,
+                         cudaStream_t stream) {
     QPlan pl;
     const int refs = refs_mode(bv);
     if (!make_qplan<NX, NU>(bv.N, refs, pl)) return cudaErrorInvalidConfiguration;
