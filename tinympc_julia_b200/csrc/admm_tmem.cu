@@ -116,6 +116,30 @@ __device__ __forceinline__ void ld2(const double* p, double& a, double& b) {
 __device__ __forceinline__ void st2(double* p, double a, double b) { *reinterpret_cast<double2*>(p) = make_double2(a, b); }
 __device__ __forceinline__ double shfl_dq(double v, int src_lane) { return __shfl_sync(kAll, v, src_lane); }
 
+// ---------------------------------------------------------------- shared memory by 32-bit address
+// The sweeps address shared memory through explicit .shared instructions on 32-bit addresses computed once per
+// kernel: with generic pointers the compiler rebuilt the shared window base (S2UR SR_CgaCtaId + ULEA, ~20 cycles of
+// scoreboard wait) twice per knot point.  OFF is a byte offset folded into the instruction.
+template <int OFF = 0>
+__device__ __forceinline__ void lds2(uint32_t a, double& x, double& y) {
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2+%3];" : "=d"(x), "=d"(y) : "r"(a), "n"(OFF));
+}
+template <int OFF = 0>
+__device__ __forceinline__ double lds1(uint32_t a) {
+    double x;
+    asm volatile("ld.shared.f64 %0, [%1+%2];" : "=d"(x) : "r"(a), "n"(OFF));
+    return x;
+}
+template <int OFF = 0>
+__device__ __forceinline__ void sts1(uint32_t a, double x) {
+    asm volatile("st.shared.f64 [%0+%1], %2;" :: "r"(a), "n"(OFF), "d"(x) : "memory");
+}
+template <int OFF = 0>
+__device__ __forceinline__ void sts2(uint32_t a, double x, double y) {
+    asm volatile("st.shared.v2.f64 [%0+%1], {%2, %3};" :: "r"(a), "n"(OFF), "d"(x), "d"(y) : "memory");
+}
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+
 template <int W> __device__ __forceinline__ void tm_wait_ld(uint32_t* w);
 template <> __device__ __forceinline__ void tm_wait_ld<12>(uint32_t* w) { tm_wait_ld12(w); }
 template <> __device__ __forceinline__ void tm_wait_ld<4>(uint32_t* w) { tm_wait_ld4(w); }
@@ -205,6 +229,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int inst = lane & 7, sub = lane >> 3;
     const bool urow = (NU == 4) || (sub < NU);        // this lane owns an input row
+    const int usub = urow ? sub : 0;
     const uint32_t tbase = s_tmem_base + (static_cast<uint32_t>((warp & 3) * 32) << 16) +
                            static_cast<uint32_t>((warp >> 2) * kTmemColsPerWarp);
     double* wbase = smem + qp.off_warp0 + static_cast<size_t>(warp) * qp.warp_stride;
@@ -214,13 +239,28 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                                                       // contiguous bytes, so the 4-vector comes back in two conflict-free LDS.128
     double* s_bc = s_rt + (N - 1) * 32;               // 2 x 8 x XP broadcast slots
     double* my_rt = s_rt + (sub >> 1) * 16 + inst * 2 + (sub & 1);   // + i * 32 : own row
-    const double* my_rt4 = s_rt + inst * 2;                          // + i * 32 (+ 16 for rows 2, 3)
 
-    const double fr_BPf = urow ? sc[CL::BPf + (urow ? sub : 0)] : 0.0;
-    const double fr_Rd = urow ? sc[CL::Rd + (urow ? sub : 0)] : 0.0;
+    // 32-bit shared addresses of everything the sweeps touch (byte strides per knot point in the comments)
+    const uint32_t a_yz = smem_addr(s_yz) + lane * 16;                               // + i * 512
+    const uint32_t a_rt4 = smem_addr(s_rt) + inst * 16;                              // + i * 256 ; rows 2,3: + 128
+    const uint32_t a_myrt = smem_addr(my_rt);                                        // + i * 256
+    const uint32_t a_slotA = smem_addr(s_bc) + inst * XP * 8;
+    const uint32_t a_slot_sum = 2 * a_slotA + kQInst * XP * 8;                       // slot B = sum - slot A
+    const uint32_t a_ub = smem_addr(s_ub) + usub * 16;                               // + i * NU * 16
+    const uint32_t a_xb = smem_addr(s_xb) + sub * 16;                                // + i * NX * 16 ; row r: + r * 64
+    const uint32_t a_sc = smem_addr(sc);
+    const uint32_t a_Mb = a_sc + (CL::B_rm + sub * NU) * 8;                          // row r: + r * 4 * NU * 8
+    const uint32_t a_Mq = a_sc + (CL::Quu_rm + usub * NU) * 8;
+    const uint32_t a_cq = smem_addr(s_cq) + sub * 8;                                 // + i * NX * 8 ; row r: + r * 32
+    const uint32_t a_cr = smem_addr(s_cr) + usub * 8;                                // + i * NU * 8
+    uint32_t a_slot = a_slotA;
+
+    const double fr_BPf = urow ? sc[CL::BPf + usub] : 0.0;
+    const double fr_Rd = urow ? sc[CL::Rd + usub] : 0.0;
     double fr_f[RX], fr_APf[RX], fr_Qd[RX];
 #pragma unroll
     for (int r = 0; r < RX; ++r) { fr_f[r] = sc[CL::f + r * 4 + sub]; fr_APf[r] = sc[CL::APf + r * 4 + sub]; fr_Qd[r] = sc[CL::Qd + r * 4 + sub]; }
+    const size_t ld4 = 4 * ld, ldx = static_cast<size_t>(NX) * ld, ldu = static_cast<size_t>(NU) * ld;
 
     // ---------------- per-lane instance state
     int b = 0, iter = 0, status = 1;
@@ -228,7 +268,6 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     double x0r[RX], p_term[RX];
 #pragma unroll
     for (int r = 0; r < RX; ++r) { x0r[r] = 0.0; p_term[r] = 0.0; }
-    int bcast_phase = 0;
     const double* xref_g = nullptr;                   // REFS == 2 only
     const double* uref_g = nullptr;
 
@@ -236,22 +275,23 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
         // =====================================================================================================
         // write-out of finished instances + refill from the queue.  Warp-uniform (tcgen05.ld/st are .aligned):
         // every lane walks the knot points, lanes whose instance is not finished store back what they loaded.
+        // Global addresses advance by running offsets (one add per knot point instead of a multiply per store).
         // =====================================================================================================
         if (__any_sync(kAll, fin)) {
             const bool wr = fin && valid;                 // results to write
             const bool unconv = (status != 0);
             const size_t bb = wr ? static_cast<size_t>(b) : 0;
             if (wr && urow) {
-                double* Us = bv.Usol + bb * nuN;
+                double* Us = bv.Usol + bb * nuN + sub;
+                size_t off = static_cast<size_t>(sub) * ld + bb;
                 for (int i = 0; i < N - 1; ++i) {
-                    const int e = i * NU + sub;
-                    const size_t ge = static_cast<size_t>(e) * ld + bb;
                     double yy, zz;
                     ld2(s_yz + (i * 32 + lane) * 2, yy, zz);
-                    Us[e] = zz;                                   // solution = znew of the last iteration (admm.cpp:371,387)
-                    bv.y[ge] = yy;
-                    if (unconv) bv.z[0][ge] = zz;                 // z = znew happened (admm.cpp:380); else the lagging copy is there
-                    bv.r[ge] = my_rt[i * 32];                     // r as update_linear_cost left it (admm.cpp:228-233)
+                    *Us = zz;                                     // solution = znew of the last iteration (admm.cpp:371,387)
+                    bv.y[off] = yy;
+                    if (unconv) bv.z[0][off] = zz;                // z = znew happened (admm.cpp:380); else the lagging copy is there
+                    bv.r[off] = my_rt[i * 32];                    // r as update_linear_cost left it (admm.cpp:228-233)
+                    Us += NU; off += ldu;
                 }
             }
             if (wr) {
@@ -265,69 +305,70 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             nb = __shfl_sync(kAll, nb, inst);
             const bool nvalid = fin && nb < bv.B;
             const size_t nbb = nvalid ? static_cast<size_t>(nb) : 0;
+            const bool warm = !COLD && nvalid;
 
-            double* Xs = bv.Xsol + bb * nxN;
-            const double* xr_old = (REFS == 2 && bv.Xref) ? bv.Xref + bb * bv.xref_stride : nullptr;
+            double* Xs = bv.Xsol + bb * nxN + sub;
+            const double* xr_old = (REFS == 2 && bv.Xref) ? bv.Xref + bb * bv.xref_stride + sub : nullptr;
+            size_t off = static_cast<size_t>(sub) * ld + bb;          // old instance, element (i NX + sub)
+            size_t noff = static_cast<size_t>(sub) * ld + nbb;        // new instance
             for (int i = 0; i < N; ++i) {
                 uint32_t w[W];
                 tm_load<W>(tbase + i * W, w);
+                double gn[RX], vn[RX];
+#pragma unroll
+                for (int r = 0; r < RX; ++r) { gn[r] = 0.0; vn[r] = 0.0; }
+                if (warm) {
+#pragma unroll
+                    for (int r = 0; r < RX; ++r) { gn[r] = bv.g[noff + r * ld4]; vn[r] = bv.v[0][noff + r * ld4]; }
+                }
                 tm_wait_ld<W>(w);
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
-                    const int e = i * NX + r * 4 + sub;
                     if (wr) {
                         const double gg = mk_double(w[2 * r], w[2 * r + 1]);
                         const double vv = mk_double(w[2 * (RX + r)], w[2 * (RX + r) + 1]);
-                        const size_t ge = static_cast<size_t>(e) * ld + bb;
-                        Xs[e] = vv;                               // solution = vnew of the last iteration (admm.cpp:370,386)
+                        const size_t ge = off + r * ld4;
+                        Xs[r * 4] = vv;                           // solution = vnew of the last iteration (admm.cpp:370,386)
                         bv.g[ge] = gg;
                         if (unconv) bv.v[0][ge] = vv;             // v = vnew happened (admm.cpp:379); else the lagging copy is there
                         if (i < N - 1) {                          // q as update_linear_cost left it (admm.cpp:218-219)
                             double q;
                             if (REFS == 0) q = dmul(nrho, dsub(vv, gg));
                             else {
-                                const double cq = (REFS == 1) ? s_cq[e] : -dmul(xr_old ? __ldg(xr_old + e) : 0.0, fr_Qd[r]);
+                                const double cq = (REFS == 1) ? s_cq[i * NX + r * 4 + sub]
+                                                              : -dmul(xr_old ? __ldg(xr_old + i * NX + r * 4) : 0.0, fr_Qd[r]);
                                 q = dsub(cq, dmul(rho, dsub(vv, gg)));
                             }
                             bv.q[ge] = q;
                         }
                     }
                     if (fin) {
-                        double gg = 0.0, vv = 0.0;
-                        if (!COLD && nvalid) {
-                            const size_t ge = static_cast<size_t>(e) * ld + nbb;
-                            gg = bv.g[ge]; vv = bv.v[0][ge];
-                        }
-                        w[2 * r] = lo32(gg); w[2 * r + 1] = hi32(gg);
-                        w[2 * (RX + r)] = lo32(vv); w[2 * (RX + r) + 1] = hi32(vv);
+                        w[2 * r] = lo32(gn[r]); w[2 * r + 1] = hi32(gn[r]);
+                        w[2 * (RX + r)] = lo32(vn[r]); w[2 * (RX + r) + 1] = hi32(vn[r]);
                     }
                 }
                 tm_store<W>(tbase + i * W, w);
+                Xs += NX; off += ldx; noff += ldx;
             }
             if (fin) {
-                if (urow) {
-                    for (int i = 0; i < N - 1; ++i) {
-                        double yy = 0.0, zz = 0.0, rr = 0.0;
-                        if (!COLD && nvalid) {
-                            const size_t ge = static_cast<size_t>(i * NU + sub) * ld + nbb;
-                            yy = bv.y[ge]; zz = bv.z[0][ge]; rr = bv.r[ge];
-                        }
-                        st2(s_yz + (i * 32 + lane) * 2, yy, zz);
-                        my_rt[i * 32] = rr;
-                    }
-                } else {
-                    for (int i = 0; i < N - 1; ++i) { st2(s_yz + (i * 32 + lane) * 2, 0.0, 0.0); my_rt[i * 32] = 0.0; }
+                size_t uo = static_cast<size_t>(sub) * ld + nbb;
+                for (int i = 0; i < N - 1; ++i) {
+                    double yy = 0.0, zz = 0.0, rr = 0.0;
+                    if (warm && urow) { yy = bv.y[uo]; zz = bv.z[0][uo]; rr = bv.r[uo]; }
+                    st2(s_yz + (i * 32 + lane) * 2, yy, zz);
+                    my_rt[i * 32] = rr;
+                    uo += ldu;
                 }
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
                     x0r[r] = nvalid ? bv.x0[nbb * NX + r * 4 + sub] : 0.0;
-                    p_term[r] = (!COLD && nvalid) ? bv.pN[(r * 4 + sub) * ld + nbb] : 0.0;
+                    p_term[r] = warm ? bv.pN[(r * 4 + sub) * ld + nbb] : 0.0;
                 }
                 b = nvalid ? nb : 0;
                 valid = nvalid; iter = 0; first = true; status = 1; fin = false;
                 if (REFS == 2) {
-                    xref_g = bv.Xref ? bv.Xref + nbb * bv.xref_stride : nullptr;
-                    uref_g = bv.Uref ? bv.Uref + nbb * bv.uref_stride : nullptr;
+                    xref_g = bv.Xref ? bv.Xref + nbb * bv.xref_stride + sub : nullptr;      // + i NX + 4 r
+                    uref_g = (bv.Uref && urow) ? bv.Uref + nbb * bv.uref_stride + sub : nullptr;   // + i NU
                 }
             }
             tm_wait_st();
@@ -351,7 +392,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 for (int k = 0; k < NU; ++k) Mkt[r][k] = sc[CL::Kinf_cm + (r * 4 + sub) * NU + k];
             }
 #pragma unroll
-            for (int k = 0; k < NX; ++k) Mbt[k] = urow ? sc[CL::B_cm + (urow ? sub : 0) * NX + k] : 0.0;
+            for (int k = 0; k < NX; ++k) Mbt[k] = urow ? sc[CL::B_cm + usub * NX + k] : 0.0;
 
             double p[RX];
 #pragma unroll
@@ -363,32 +404,45 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
 #pragma unroll
             for (int r = 0; r < RX; ++r) qcar[r] = 0.0;
             const bool ldq = !COLD && first && valid;
+            const double* qp_g = bv.q + static_cast<size_t>(sub) * ld + bb + static_cast<size_t>(N - 2) * ldx;   // row r: + r ld4
             if (ldq) {
 #pragma unroll
-                for (int r = 0; r < RX; ++r) qcar[r] = bv.q[static_cast<size_t>((N - 2) * NX + r * 4 + sub) * ld + bb];
+                for (int r = 0; r < RX; ++r) qcar[r] = qp_g[r * ld4];
             }
             double t_def = 0.0;
+            uint32_t o_rt = (N - 2) * 256;                // byte offset of knot i in the r/t array
+            uint32_t o_cq = (N - 2) * NX * 8;
 
             for (int i = N - 2; i >= 0; --i) {
                 double cq[RX];
                 if (REFS == 2) {
 #pragma unroll
-                    for (int r = 0; r < RX; ++r) cq[r] = -dmul(xref_g ? __ldg(xref_g + i * NX + r * 4 + sub) : 0.0, fr_Qd[r]);
+                    for (int r = 0; r < RX; ++r) cq[r] = -dmul(xref_g ? __ldg(xref_g + i * NX + r * 4) : 0.0, fr_Qd[r]);
                 }
                 // broadcast p_{i+1} to the 4 lanes of the instance
-                double* slot = s_bc + (bcast_phase & 1) * (kQInst * XP) + inst * XP;
-                ++bcast_phase;
+                a_slot = a_slot_sum - a_slot;
 #pragma unroll
-                for (int r = 0; r < RX; ++r) slot[r * 4 + sub] = p[r];
+                for (int r = 0; r < RX; ++r) {
+                    if (r == 0) sts1<0>(a_slot + sub * 8, p[r]);
+                    else if (r == 1) sts1<32>(a_slot + sub * 8, p[r]);
+                    else sts1<64>(a_slot + sub * 8, p[r]);
+                }
                 __syncwarp();
-                if (i < N - 2 && urow) my_rt[(i + 1) * 32] = t_def;      // every lane has read r_{i+1} by now
+                if (i < N - 2 && urow) sts1<256>(a_myrt + o_rt, t_def);    // t_{i+1}: every lane has read r_{i+1} by now
                 double pb[NX];
-#pragma unroll
-                for (int k = 0; k < NX; k += 2) ld2(slot + k, pb[k], pb[k + 1]);
+                lds2<0>(a_slot, pb[0], pb[1]);
+                if (NX > 2) lds2<16>(a_slot, pb[2], pb[3]);
+                if (NX > 4) { lds2<32>(a_slot, pb[4], pb[5]); lds2<48>(a_slot, pb[6], pb[7]); }
+                if (NX > 8) { lds2<64>(a_slot, pb[8], pb[9]); lds2<80>(a_slot, pb[10], pb[11]); }
                 double rr[4];
-                ld2(my_rt4 + i * 32, rr[0], rr[1]);
-                ld2(my_rt4 + i * 32 + 16, rr[2], rr[3]);
-                const double r_own = my_rt[i * 32];
+                lds2<0>(a_rt4 + o_rt, rr[0], rr[1]);
+                lds2<128>(a_rt4 + o_rt, rr[2], rr[3]);
+                const double r_own = lds1<0>(a_myrt + o_rt);
+                double cqs[RX];
+                if (REFS == 1) {
+#pragma unroll
+                    for (int r = 0; r < RX; ++r) cqs[r] = (r == 0) ? lds1<0>(a_cq + o_cq) : (r == 1) ? lds1<32>(a_cq + o_cq) : lds1<64>(a_cq + o_cq);
+                }
 
                 // q_i (own rows): carried on the first sweep of a solve, otherwise rebuilt from slacks and duals
                 tm_wait_ld<W>(w);
@@ -399,36 +453,42 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                     const double vv = mk_double(w[2 * (RX + r)], w[2 * (RX + r) + 1]);
                     double q;
                     if (REFS == 0) q = dmul(nrho, dsub(vv, gg));
-                    else q = dsub(REFS == 1 ? s_cq[i * NX + r * 4 + sub] : cq[r], dmul(rho, dsub(vv, gg)));
+                    else q = dsub(REFS == 1 ? cqs[r] : cq[r], dmul(rho, dsub(vv, gg)));
                     q_own[r] = first ? qcar[r] : q;
                 }
                 if (i > 0) {
                     tm_load<W>(tbase + (i - 1) * W, w);
                     if (ldq) {
+                        qp_g -= ldx;
 #pragma unroll
-                        for (int r = 0; r < RX; ++r) qcar[r] = bv.q[static_cast<size_t>((i - 1) * NX + r * 4 + sub) * ld + bb];
+                        for (int r = 0; r < RX; ++r) qcar[r] = qp_g[r * ld4];
                     }
                 }
 
-                // t_i = B' p_{i+1} + r_i + BPf   (own input row)
-                double s = 0.0;
+                // own row of B' p_{i+1} and the lane's rows of AmBKt p_{i+1}: RX + 1 independent chains, interleaved
+                double s = 0.0, s1[RX];
 #pragma unroll
-                for (int k = 0; k < NX; ++k) s = fma(Mbt[k], pb[k], s);
-                t_def = dadd(dadd(s, r_own), fr_BPf);
+                for (int r = 0; r < RX; ++r) s1[r] = 0.0;
+#pragma unroll
+                for (int k = 0; k < NX; ++k) {
+                    s = fma(Mbt[k], pb[k], s);
+#pragma unroll
+                    for (int r = 0; r < RX; ++r) s1[r] = fma(Mab[r][k], pb[k], s1[r]);
+                }
+                t_def = dadd(dadd(s, r_own), fr_BPf);     // t_i = B' p_{i+1} + r_i + BPf
 
                 // p_i = q_i + AmBKt p_{i+1} - Kinf' r_i + APf
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
-                    double s1 = 0.0, s2 = 0.0;
-#pragma unroll
-                    for (int k = 0; k < NX; ++k) s1 = fma(Mab[r][k], pb[k], s1);
+                    double s2 = 0.0;
 #pragma unroll
                     for (int k = 0; k < NU; ++k) s2 = fma(Mkt[r][k], rr[k], s2);
-                    p[r] = dadd(dsub(dadd(q_own[r], s1), s2), fr_APf[r]);
+                    p[r] = dadd(dsub(dadd(q_own[r], s1[r]), s2), fr_APf[r]);
                 }
+                o_rt -= 256; o_cq -= NX * 8;
             }
             __syncwarp();
-            if (urow) my_rt[0] = t_def;
+            if (urow) sts1<0>(a_myrt, t_def);
         }
 
         // =====================================================================================================
@@ -447,9 +507,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 for (int k = 0; k < NX; k += 2) ld2(sc + CL::A_rm + (r * 4 + sub) * NX + k, Ma[r][k], Ma[r][k + 1]);
             }
 #pragma unroll
-            for (int k = 0; k < NX; ++k) Mk[k] = urow ? sc[CL::Kinf_rm + (urow ? sub : 0) * NX + k] : 0.0;
-            const double* sMb = sc + CL::B_rm + sub * NU;                 // + r * 4 * NU : row r*4+sub of B
-            const double* sMq = sc + CL::Quu_rm + (urow ? sub : 0) * NU;
+            for (int k = 0; k < NX; ++k) Mk[k] = urow ? sc[CL::Kinf_rm + usub * NX + k] : 0.0;
 
             double x[RX];
 #pragma unroll
@@ -462,82 +520,28 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             const bool lag = valid && ((iter + 1) % st.check_termination == 0);
             double* vlag = bv.v[0] + static_cast<size_t>(sub) * ld + bb;      // row r of knot i: + (i NX + 4 r) ld
             double* zlag = bv.z[0] + static_cast<size_t>(sub) * ld + bb;      // knot i: + (i NU) ld
-            const size_t ld4 = 4 * ld, ldx = static_cast<size_t>(NX) * ld, ldu = static_cast<size_t>(NU) * ld;
             double r_def = 0.0;
+            double vg[RX];
+            uint32_t o_xb = 0;                                                // byte offset of knot i in the state-bound table
+            uint32_t tcol = tbase;
 
-            for (int i = 0; i < N; ++i) {
-                const bool terminal = (i == N - 1);
-                double s1[RX];
-                double ub[NU];
-                if (!terminal) {
-                    double cr = 0.0;
-                    if (REFS == 2) cr = -dmul((uref_g && urow) ? __ldg(uref_g + i * NU + sub) : 0.0, fr_Rd);
-                    double* slot = s_bc + (bcast_phase & 1) * (kQInst * XP) + inst * XP;
-                    ++bcast_phase;
+            // state column i: slack, dual, residuals; new (g, v) back to Tensor Memory
+            auto state_column = [&]() {
+                double lo[RX], hi[RX];
 #pragma unroll
-                    for (int r = 0; r < RX; ++r) slot[r * 4 + sub] = x[r];
-                    __syncwarp();
-                    if (i > 0 && urow) my_rt[(i - 1) * 32] = r_def;          // every lane has read t_{i-1} by now
-                    double xb[NX];
-#pragma unroll
-                    for (int k = 0; k < NX; k += 2) ld2(slot + k, xb[k], xb[k + 1]);
-                    double tt[4], mq[4];
-                    ld2(my_rt4 + i * 32, tt[0], tt[1]);
-                    ld2(my_rt4 + i * 32 + 16, tt[2], tt[3]);
-#pragma unroll
-                    for (int k = 0; k < NU; k += 2) {
-                        if (k + 1 < NU) ld2(sMq + k, mq[k], mq[k + 1]); else mq[k] = sMq[k];
-                    }
-                    double yj = 0.0, zold = 0.0, ulo = 0.0, uhi = 0.0;
-                    if (urow) {
-                        ld2(s_yz + (i * 32 + lane) * 2, yj, zold);
-                        ld2(s_ub + (i * NU + sub) * 2, ulo, uhi);
-                    }
-
-                    // d_i = Quu_inv t_i ;  -u_i - d_i = Kinf x_i ;  A x_i  — five independent chains, interleaved
-                    double d = 0.0;
-#pragma unroll
-                    for (int k = 0; k < NU; ++k) d = fma(mq[k], tt[k], d);
-                    double s = 0.0;
-#pragma unroll
-                    for (int r = 0; r < RX; ++r) s1[r] = 0.0;
-#pragma unroll
-                    for (int k = 0; k < NX; ++k) {
-                        s = fma(Mk[k], xb[k], s);
-#pragma unroll
-                        for (int r = 0; r < RX; ++r) s1[r] = fma(Ma[r][k], xb[k], s1[r]);
-                    }
-                    double u_own = 0.0;
-                    if (urow) {
-                        u_own = dsub(-s, d);
-                        const double t = dadd(u_own, yj);
-                        const double znew = clampd(t, ulo, uhi);
-                        const double ynew = dsub(t, znew);                  // y + u - znew
-                        const bool p1 = fabs(dsub(u_own, znew)) < qp.pri_thresh;
-                        const bool p2 = fabs(dsub(zold, znew)) <= qp.dua_thresh;
-                        ok = ok & p1 & p2;
-                        if (lag & ok) *zlag = zold;
-                        st2(s_yz + (i * 32 + lane) * 2, ynew, znew);
-                        // r_i = -(Uref .* Rd) - rho (znew - y)    (admm.cpp:228-229)
-                        if (REFS == 0) r_def = dmul(nrho, dsub(znew, ynew));
-                        else r_def = dsub(REFS == 1 ? s_cr[i * NU + sub] : cr, dmul(rho, dsub(znew, ynew)));
-                    }
-#pragma unroll
-                    for (int k = 0; k < NU; ++k) ub[k] = shfl_dq(u_own, k * kQInst + inst);
+                for (int r = 0; r < RX; ++r) {
+                    if (r == 0) lds2<0>(a_xb + o_xb, lo[r], hi[r]);
+                    else if (r == 1) lds2<64>(a_xb + o_xb, lo[r], hi[r]);
+                    else lds2<128>(a_xb + o_xb, lo[r], hi[r]);
                 }
-
-                // state column i: slack, dual, residuals (independent of u_i: overlaps the shuffles)
                 tm_wait_ld<W>(w);
                 uint32_t wn[W];
-                double vg[RX];
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
                     const double gold = mk_double(w[2 * r], w[2 * r + 1]);
                     const double vold = mk_double(w[2 * (RX + r)], w[2 * (RX + r) + 1]);
-                    double lo, hi;
-                    ld2(s_xb + (i * NX + r * 4 + sub) * 2, lo, hi);
                     const double t = dadd(x[r], gold);
-                    const double vnew = clampd(t, lo, hi);
+                    const double vnew = clampd(t, lo[r], hi[r]);
                     const double gnew = dsub(t, vnew);
                     const bool p1 = fabs(dsub(x[r], vnew)) < qp.pri_thresh;
                     const bool p2 = fabs(dsub(vold, vnew)) <= qp.dua_thresh;
@@ -547,41 +551,119 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                     wn[2 * (RX + r)] = lo32(vnew); wn[2 * (RX + r) + 1] = hi32(vnew);
                     vg[r] = dsub(vnew, gnew);
                 }
-                tm_store<W>(tbase + i * W, wn);
-                vlag += ldx; zlag += ldu;
+                tm_store<W>(tcol, wn);
+            };
 
-                if (!terminal) {
-                    tm_load<W>(tbase + (i + 1) * W, w);          // next knot point; consumed after the next broadcast
-                    // x_{i+1} = A x_i + B u_i + f
+            uint32_t o_rt = 0, o_yz = 0, o_ub = 0, o_cr = 0;
+            for (int i = 0; i < N - 1; ++i) {
+                double cr = 0.0;
+                if (REFS == 2) cr = -dmul(uref_g ? __ldg(uref_g + i * NU) : 0.0, fr_Rd);
+                a_slot = a_slot_sum - a_slot;
 #pragma unroll
-                    for (int r = 0; r < RX; ++r) {
-                        double mb[4];
+                for (int r = 0; r < RX; ++r) {
+                    if (r == 0) sts1<0>(a_slot + sub * 8, x[r]);
+                    else if (r == 1) sts1<32>(a_slot + sub * 8, x[r]);
+                    else sts1<64>(a_slot + sub * 8, x[r]);
+                }
+                __syncwarp();
+                if (i > 0 && urow) sts1<-256>(a_myrt + o_rt, r_def);         // r_{i-1}: every lane has read t_{i-1} by now
+                double xb[NX];
+                lds2<0>(a_slot, xb[0], xb[1]);
+                if (NX > 2) lds2<16>(a_slot, xb[2], xb[3]);
+                if (NX > 4) { lds2<32>(a_slot, xb[4], xb[5]); lds2<48>(a_slot, xb[6], xb[7]); }
+                if (NX > 8) { lds2<64>(a_slot, xb[8], xb[9]); lds2<80>(a_slot, xb[10], xb[11]); }
+                double tt[4], mq[4];
+                lds2<0>(a_rt4 + o_rt, tt[0], tt[1]);
+                lds2<128>(a_rt4 + o_rt, tt[2], tt[3]);
+                if (NU == 4) { lds2<0>(a_Mq, mq[0], mq[1]); lds2<16>(a_Mq, mq[2], mq[3]); }
+                else {
 #pragma unroll
-                        for (int k = 0; k < NU; k += 2) {
-                            if (k + 1 < NU) ld2(sMb + r * 4 * NU + k, mb[k], mb[k + 1]); else mb[k] = sMb[r * 4 * NU + k];
-                        }
-                        double s2 = 0.0;
+                    for (int k = 0; k < NU; ++k) mq[k] = sc[CL::Quu_rm + usub * NU + k];
+                }
+                double yj = 0.0, zold = 0.0, ulo = 0.0, uhi = 0.0, crs = 0.0;
+                if (urow) {
+                    lds2<0>(a_yz + o_yz, yj, zold);
+                    lds2<0>(a_ub + o_ub, ulo, uhi);
+                    if (REFS == 1) crs = lds1<0>(a_cr + o_cr);
+                }
+
+                // d_i = Quu_inv t_i ;  Kinf x_i (own row) ;  A x_i (own rows): RX + 2 independent chains, interleaved
+                double d = 0.0;
 #pragma unroll
-                        for (int k = 0; k < NU; ++k) s2 = fma(mb[k], ub[k], s2);
-                        x[r] = dadd(dadd(s1[r], s2), fr_f[r]);
+                for (int k = 0; k < NU; ++k) d = fma(mq[k], tt[k], d);
+                double s = 0.0, s1[RX];
+#pragma unroll
+                for (int r = 0; r < RX; ++r) s1[r] = 0.0;
+#pragma unroll
+                for (int k = 0; k < NX; ++k) {
+                    s = fma(Mk[k], xb[k], s);
+#pragma unroll
+                    for (int r = 0; r < RX; ++r) s1[r] = fma(Ma[r][k], xb[k], s1[r]);
+                }
+                // rows of B for the tail of this knot point: issued now, consumed after the shuffles
+                double mb[RX][4];
+#pragma unroll
+                for (int r = 0; r < RX; ++r) {
+                    if (NU == 4) {
+                        if (r == 0) { lds2<0>(a_Mb, mb[r][0], mb[r][1]); lds2<16>(a_Mb, mb[r][2], mb[r][3]); }
+                        else if (r == 1) { lds2<4 * NU * 8>(a_Mb, mb[r][0], mb[r][1]); lds2<4 * NU * 8 + 16>(a_Mb, mb[r][2], mb[r][3]); }
+                        else { lds2<8 * NU * 8>(a_Mb, mb[r][0], mb[r][1]); lds2<8 * NU * 8 + 16>(a_Mb, mb[r][2], mb[r][3]); }
+                    } else {
+#pragma unroll
+                        for (int k = 0; k < NU; ++k) mb[r][k] = sc[CL::B_rm + (r * 4 + sub) * NU + k];
                     }
-                } else {
-                    // p_{N-1} = -(Xref_{N-1}' Pinf)' - rho (vnew - g)   (admm.cpp:238-239)
+                }
+
+                // u_i = -Kinf x_i - d_i ; input slack, dual, residuals (admm.cpp:28, :87, :97, :187, :259-260)
+                double u_own = 0.0;
+                if (urow) {
+                    u_own = dsub(-s, d);
+                    const double t = dadd(u_own, yj);
+                    const double znew = clampd(t, ulo, uhi);
+                    const double ynew = dsub(t, znew);                  // y + u - znew
+                    const bool p1 = fabs(dsub(u_own, znew)) < qp.pri_thresh;
+                    const bool p2 = fabs(dsub(zold, znew)) <= qp.dua_thresh;
+                    ok = ok & p1 & p2;
+                    if (lag & ok) *zlag = zold;
+                    sts2<0>(a_yz + o_yz, ynew, znew);
+                    // r_i = -(Uref .* Rd) - rho (znew - y)    (admm.cpp:228-229)
+                    if (REFS == 0) r_def = dmul(nrho, dsub(znew, ynew));
+                    else r_def = dsub(REFS == 1 ? crs : cr, dmul(rho, dsub(znew, ynew)));
+                }
+                double ub[NU];
 #pragma unroll
-                    for (int r = 0; r < RX; ++r) {
-                        if (REFS == 0) p_term[r] = dmul(nrho, vg[r]);
-                        else if (REFS == 1) p_term[r] = dsub(s_tq[r * 4 + sub], dmul(rho, vg[r]));
-                        else {
-                            double s = 0.0;
-                            if (xref_g) for (int k = 0; k < NX; ++k) s = fma(__ldg(xref_g + i * NX + k), sc[CL::Pinf_cm + (r * 4 + sub) * NX + k], s);
-                            p_term[r] = dsub(-s, dmul(rho, vg[r]));
-                        }
-                    }
+                for (int k = 0; k < NU; ++k) ub[k] = shfl_dq(u_own, k * kQInst + inst);
+
+                state_column();                               // independent of u_i: overlaps the shuffles
+                tcol += W;
+                tm_load<W>(tcol, w);                          // next knot point; consumed after the next broadcast
+
+                // x_{i+1} = A x_i + B u_i + f
+#pragma unroll
+                for (int r = 0; r < RX; ++r) {
+                    double s2 = 0.0;
+#pragma unroll
+                    for (int k = 0; k < NU; ++k) s2 = fma(mb[r][k], ub[k], s2);
+                    x[r] = dadd(dadd(s1[r], s2), fr_f[r]);
+                }
+                vlag += ldx; zlag += ldu;
+                o_rt += 256; o_yz += 512; o_ub += NU * 16; o_cr += NU * 8; o_xb += NX * 16;
+            }
+            // terminal knot point: p_{N-1} = -(Xref_{N-1}' Pinf)' - rho (vnew - g)   (admm.cpp:238-239)
+            state_column();
+#pragma unroll
+            for (int r = 0; r < RX; ++r) {
+                if (REFS == 0) p_term[r] = dmul(nrho, vg[r]);
+                else if (REFS == 1) p_term[r] = dsub(s_tq[r * 4 + sub], dmul(rho, vg[r]));
+                else {
+                    double s = 0.0;
+                    if (xref_g) for (int k = 0; k < NX; ++k) s = fma(__ldg(xref_g - sub + (N - 1) * NX + k), sc[CL::Pinf_cm + (r * 4 + sub) * NX + k], s);
+                    p_term[r] = dsub(-s, dmul(rho, vg[r]));
                 }
             }
             tm_wait_st();
             __syncwarp();
-            if (urow) my_rt[(N - 2) * 32] = r_def;
+            if (urow) sts1<-256>(a_myrt + o_rt, r_def);       // r_{N-2}
         }
 
         // =====================================================================================================
