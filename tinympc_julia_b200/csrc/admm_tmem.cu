@@ -29,6 +29,7 @@
 
 #include <cmath>
 #include <cstdint>
+#include <type_traits>
 
 #include "admm_device.cuh"
 #include "admm_kernels.hpp"
@@ -82,15 +83,31 @@ __device__ __forceinline__ void tm_st4(uint32_t taddr, const uint32_t* r) {
     asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};"
                  :: "r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]) : "memory");
 }
+__device__ __forceinline__ void tm_ld8(uint32_t taddr, uint32_t* r) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]) : "r"(taddr));
+}
+__device__ __forceinline__ void tm_st8(uint32_t taddr, const uint32_t* r) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                 :: "r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]) : "memory");
+}
+// a knot point of a lane is WORDS 32-bit columns: 12 (x8 + x4: each tcgen05 instruction needs its address in a
+// uniform register, so fewer, wider instructions also mean fewer R2UR) or 4
 template <int WORDS>
 __device__ __forceinline__ void tm_load(uint32_t taddr, uint32_t* w) {
+    if (WORDS == 12) { tm_ld8(taddr, w); tm_ld4(taddr + 8, w + 8); }
+    else {
 #pragma unroll
-    for (int k = 0; k < WORDS; k += 4) tm_ld4(taddr + k, w + k);
+        for (int k = 0; k < WORDS; k += 4) tm_ld4(taddr + k, w + k);
+    }
 }
 template <int WORDS>
 __device__ __forceinline__ void tm_store(uint32_t taddr, const uint32_t* w) {
+    if (WORDS == 12) { tm_st8(taddr, w); tm_st4(taddr + 8, w + 8); }
+    else {
 #pragma unroll
-    for (int k = 0; k < WORDS; k += 4) tm_st4(taddr + k, w + k);
+        for (int k = 0; k < WORDS; k += 4) tm_st4(taddr + k, w + k);
+    }
 }
 // tcgen05.ld is asynchronous and NOT covered by the register scoreboard: the destination registers are valid
 // only after tcgen05.wait::ld.  Passing them through the wait as in/out operands makes every later use depend
@@ -114,7 +131,14 @@ __device__ __forceinline__ void ld2(const double* p, double& a, double& b) {
     a = t.x; b = t.y;
 }
 __device__ __forceinline__ void st2(double* p, double a, double b) { *reinterpret_cast<double2*>(p) = make_double2(a, b); }
-__device__ __forceinline__ double shfl_dq(double v, int src_lane) { return __shfl_sync(kAll, v, src_lane); }
+// 64-bit shuffle as two pinned shfl.sync: issued where written (right after the value exists), so their latency
+// overlaps the work that follows instead of being scheduled late by the compiler
+__device__ __forceinline__ double shfl_dq(double v, int src_lane) {
+    uint32_t lo = lo32(v), hi = hi32(v), rlo, rhi;
+    asm volatile("shfl.sync.idx.b32 %0, %1, %2, 0x1f, 0xffffffff;" : "=r"(rlo) : "r"(lo), "r"(src_lane));
+    asm volatile("shfl.sync.idx.b32 %0, %1, %2, 0x1f, 0xffffffff;" : "=r"(rhi) : "r"(hi), "r"(src_lane));
+    return mk_double(rlo, rhi);
+}
 
 // ---------------------------------------------------------------- shared memory by 32-bit address
 // The sweeps address shared memory through explicit .shared instructions on 32-bit addresses computed once per
@@ -525,8 +549,14 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             uint32_t o_xb = 0;                                                // byte offset of knot i in the state-bound table
             uint32_t tcol = tbase;
 
-            // state column i: slack, dual, residuals; new (g, v) back to Tensor Memory
-            auto state_column = [&]() {
+            // Residual tests are evaluated lazily: as soon as every instance of the warp has failed one test of
+            // this sweep (warp vote after each knot point), or when this iteration cannot terminate the solve
+            // (check_termination), the rest of the sweep runs the variant without tests and without lag stores.
+            // The decision per instance is unchanged: a failed lane keeps ok = false.
+
+            // state column: slack, dual, [residuals]; new (g, v) back to Tensor Memory
+            auto state_column = [&](auto chk) {
+                constexpr bool CHK = decltype(chk)::value;
                 double lo[RX], hi[RX];
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
@@ -539,14 +569,16 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
                     const double gold = mk_double(w[2 * r], w[2 * r + 1]);
-                    const double vold = mk_double(w[2 * (RX + r)], w[2 * (RX + r) + 1]);
                     const double t = dadd(x[r], gold);
                     const double vnew = clampd(t, lo[r], hi[r]);
                     const double gnew = dsub(t, vnew);
-                    const bool p1 = fabs(dsub(x[r], vnew)) < qp.pri_thresh;
-                    const bool p2 = fabs(dsub(vold, vnew)) <= qp.dua_thresh;
-                    ok = ok & p1 & p2;
-                    if (lag & ok) vlag[r * ld4] = vold;
+                    if (CHK) {
+                        const double vold = mk_double(w[2 * (RX + r)], w[2 * (RX + r) + 1]);
+                        const bool p1 = fabs(dsub(x[r], vnew)) < qp.pri_thresh;
+                        const bool p2 = fabs(dsub(vold, vnew)) <= qp.dua_thresh;
+                        ok = ok & p1 & p2;
+                        if (lag & ok) vlag[r * ld4] = vold;
+                    }
                     wn[2 * r] = lo32(gnew); wn[2 * r + 1] = hi32(gnew);
                     wn[2 * (RX + r)] = lo32(vnew); wn[2 * (RX + r) + 1] = hi32(vnew);
                     vg[r] = dsub(vnew, gnew);
@@ -555,7 +587,10 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             };
 
             uint32_t o_rt = 0, o_yz = 0, o_ub = 0, o_cr = 0;
-            for (int i = 0; i < N - 1; ++i) {
+            int i = 0;
+            // one non-terminal knot point
+            auto knot = [&](auto chk) {
+                constexpr bool CHK = decltype(chk)::value;
                 double cr = 0.0;
                 if (REFS == 2) cr = -dmul(uref_g ? __ldg(uref_g + i * NU) : 0.0, fr_Rd);
                 a_slot = a_slot_sum - a_slot;
@@ -600,7 +635,14 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
 #pragma unroll
                     for (int r = 0; r < RX; ++r) s1[r] = fma(Ma[r][k], xb[k], s1[r]);
                 }
-                // rows of B for the tail of this knot point: issued now, consumed after the shuffles
+
+                // u_i = -Kinf x_i - d_i, broadcast at once; then input slack, dual, [residuals]
+                // (admm.cpp:28, :87, :97, :187, :259-260)
+                const double u_own = urow ? dsub(-s, d) : 0.0;
+                double ub[NU];
+#pragma unroll
+                for (int k = 0; k < NU; ++k) ub[k] = shfl_dq(u_own, k * kQInst + inst);
+                // rows of B for the tail of this knot point: issued now, consumed after the state column
                 double mb[RX][4];
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
@@ -613,28 +655,23 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                         for (int k = 0; k < NU; ++k) mb[r][k] = sc[CL::B_rm + (r * 4 + sub) * NU + k];
                     }
                 }
-
-                // u_i = -Kinf x_i - d_i ; input slack, dual, residuals (admm.cpp:28, :87, :97, :187, :259-260)
-                double u_own = 0.0;
                 if (urow) {
-                    u_own = dsub(-s, d);
                     const double t = dadd(u_own, yj);
                     const double znew = clampd(t, ulo, uhi);
                     const double ynew = dsub(t, znew);                  // y + u - znew
-                    const bool p1 = fabs(dsub(u_own, znew)) < qp.pri_thresh;
-                    const bool p2 = fabs(dsub(zold, znew)) <= qp.dua_thresh;
-                    ok = ok & p1 & p2;
-                    if (lag & ok) *zlag = zold;
+                    if (CHK) {
+                        const bool p1 = fabs(dsub(u_own, znew)) < qp.pri_thresh;
+                        const bool p2 = fabs(dsub(zold, znew)) <= qp.dua_thresh;
+                        ok = ok & p1 & p2;
+                        if (lag & ok) *zlag = zold;
+                    }
                     sts2<0>(a_yz + o_yz, ynew, znew);
                     // r_i = -(Uref .* Rd) - rho (znew - y)    (admm.cpp:228-229)
                     if (REFS == 0) r_def = dmul(nrho, dsub(znew, ynew));
                     else r_def = dsub(REFS == 1 ? crs : cr, dmul(rho, dsub(znew, ynew)));
                 }
-                double ub[NU];
-#pragma unroll
-                for (int k = 0; k < NU; ++k) ub[k] = shfl_dq(u_own, k * kQInst + inst);
 
-                state_column();                               // independent of u_i: overlaps the shuffles
+                state_column(chk);                            // independent of u_i: overlaps the shuffles
                 tcol += W;
                 tm_load<W>(tcol, w);                          // next knot point; consumed after the next broadcast
 
@@ -648,9 +685,19 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 }
                 vlag += ldx; zlag += ldu;
                 o_rt += 256; o_yz += 512; o_ub += NU * 16; o_cr += NU * 8; o_xb += NX * 16;
+            };
+
+            bool checking = __any_sync(kAll, lag);            // no instance of the warp can terminate: no tests at all
+            if (!checking) ok = false;
+            while (checking && i < N - 1) {
+                knot(std::true_type{});
+                ++i;
+                const unsigned v = __ballot_sync(kAll, ok && lag);
+                checking = (v & (v >> 8) & (v >> 16) & (v >> 24) & 0xffu) != 0;   // some instance has all 4 lanes ok
             }
+            for (; i < N - 1; ++i) knot(std::false_type{});
             // terminal knot point: p_{N-1} = -(Xref_{N-1}' Pinf)' - rho (vnew - g)   (admm.cpp:238-239)
-            state_column();
+            if (checking) state_column(std::true_type{}); else state_column(std::false_type{});
 #pragma unroll
             for (int r = 0; r < RX; ++r) {
                 if (REFS == 0) p_term[r] = dmul(nrho, vg[r]);
