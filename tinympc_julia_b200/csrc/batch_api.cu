@@ -152,8 +152,7 @@ int resolve_kernel(tmpc_batch* h) {
     return tm_ok ? TMPC_KERNEL_TMEM : (sub_ok ? TMPC_KERNEL_SUBWARP : TMPC_KERNEL_THREAD);
 }
 
-void zero_state(tmpc_batch* h) {
-    cudaStream_t s = h->stream;
+void zero_state(tmpc_batch* h, cudaStream_t s) {
     h->g.zero(s); h->y.zero(s); h->v0.zero(s); h->v1.zero(s); h->z0.zero(s); h->z1.zero(s);
     h->q.zero(s); h->r.zero(s); h->pN.zero(s); h->d.zero(s);
     h->gc.zero(s); h->yc.zero(s); h->gl.zero(s); h->yl.zero(s);
@@ -163,24 +162,17 @@ void zero_state(tmpc_batch* h) {
 }
 
 // Make a logically-zero state physically zero before something reads it (thread kernel, result getters).
-// `s` must be ordered with the handle's stream by the caller.
 void materialize_zero(tmpc_batch* h) {
-    if (h->state_zero && !h->mem_zero) zero_state(h);
+    if (h->state_zero && !h->mem_zero) zero_state(h, h->stream);
 }
 
 // One solve kernel on `s`.  A cold (reset) state is passed to the sub-warp kernel as a flag; every other
-// reader gets physically zeroed buffers first (memsets on the handle's stream, joined into `s` by an event).
+// reader gets physically zeroed buffers first, on the SAME stream as the solve: an earlier solve enqueued on a
+// caller stream may still be running, and memsets on another stream would race with it.
 cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v, cudaStream_t s) {
     const bool sub = (k == TMPC_KERNEL_SUBWARP || k == TMPC_KERNEL_TMEM) && h->st.max_iter > 0 && h->rho > 0.0;
     if (!sub && h->state_zero && !h->mem_zero) {
-        zero_state(h);
-        if (s != h->stream) {
-            cudaEvent_t ev;
-            CUDA_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-            CUDA_TRY(cudaEventRecord(ev, h->stream));
-            CUDA_TRY(cudaStreamWaitEvent(s, ev, 0));
-            CUDA_TRY(cudaEventDestroy(ev));
-        }
+        zero_state(h, s);
     }
     cudaError_t e;
     if (sub && k == TMPC_KERNEL_TMEM) e = tmpc::launch_admm_tmem(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
@@ -303,7 +295,7 @@ int tmpc_batch_create(tmpc_batch** out, const double* A, const double* Bdyn, con
         h->x0.alloc(static_cast<size_t>(nx) * B); h->x0.zero(h->stream);
         h->Xsol.alloc(static_cast<size_t>(nx) * N * B); h->Usol.alloc(static_cast<size_t>(nu) * (N - 1) * B);
         h->status.alloc(B); h->iters.alloc(B); h->counter.alloc(8); h->counter.zero(h->stream);
-        zero_state(h.get());
+        zero_state(h.get(), h->stream);
         CUDA_TRY(cudaStreamSynchronize(h->stream));
         *out = h.release();
         return TMPC_OK;

@@ -5,16 +5,15 @@ nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gp
 nproc > gpurun_out/nproc.txt
 timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"
 tail -5 gpurun_out/pytest_gpu.log
-timeout 120 tools/microbench > gpurun_out/microbench.jsonl 2> gpurun_out/microbench.err; echo "microbench rc=$?"
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -3 gpurun_out/smoke.log
 timeout 600 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"; cat gpurun_out/bench.json; tail -5 gpurun_out/bench.err
 timeout 300 python bench.py --workload quadrotor_hard --no-cpu > gpurun_out/bench_hard.json 2> gpurun_out/bench_hard.err; echo "bench hard rc=$?"; cat gpurun_out/bench_hard.json
-timeout 300 python bench.py --kernel 1 --no-cpu --steps 10 > gpurun_out/bench_thread.json 2> gpurun_out/bench_thread.err; echo "bench thread rc=$?"; cat gpurun_out/bench_thread.json
+timeout 300 python bench.py --kernel 2 --no-cpu --steps 10 > gpurun_out/bench_subwarp.json 2> gpurun_out/bench_subwarp.err; echo "bench subwarp rc=$?"; timeout 300 python bench.py --kernel 1 --no-cpu --steps 10 > gpurun_out/bench_thread.json 2> gpurun_out/bench_thread.err; echo "bench thread rc=$?"
 timeout 600 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "bench ref rc=$?"; cat gpurun_out/bench_ref.json
 timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/plain.log 2>&1 && \
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_launch.log 2>&1
 echo "ncu launches rc=$?"
 timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/plain2.log 2>&1 && \
-timeout 1200 ncu --set full --clock-control none --import-source on -k regex:admm_subwarp -s 3 -c 2 -o gpurun_out/prof_subwarp -f python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_full.log 2>&1
+timeout 1200 ncu --set full --clock-control none --import-source on -k regex:admm_tmem -s 3 -c 2 -o gpurun_out/prof_tmem -f python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_full.log 2>&1
 echo "ncu full rc=$?"
 ls -la gpurun_out
