@@ -7,7 +7,9 @@ iS, iE, iSamp = hdr.index("Source"), hdr.index("Instructions Executed"), hdr.ind
 ops = collections.Counter(); samp = collections.Counter()
 recs = []
 for r in rows[2:]:
-    if len(r) <= iE: continue
+    if len(r) <= iE or r[0] in ("Kernel Name", "Address"): 
+        if r and r[0] == "Kernel Name": break          # first launch only
+        continue
     src = r[iS].strip()
     m = re.match(r"(@!?U?P\d+\s+)?([A-Z0-9_]+)", src)
     op = m.group(2) if m else src.split()[0]
