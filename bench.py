@@ -348,6 +348,14 @@ def run_gpu(args, rank, local_rank, world):
     hbm_bytes = B * (bytes_in + bytes_out + bytes_state)
     hbm_gbs = hbm_bytes / (kern_ms * 1e-3) / 1e9
 
+    kname = {1: "thread", 2: "subwarp", 3: "tmem"}.get(sol.kernel, str(sol.kernel))
+    traffic = None
+    try:
+        rec = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(kname)
+        if rec and rec.get("workload") == args.workload and rec.get("B") == B:
+            traffic = rec["dram_read_bytes"] + rec["dram_write_bytes"]
+    except Exception:
+        pass
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(W, 3),
         "ms_per_step": float(tot_ms.item()) / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -355,7 +363,7 @@ def run_gpu(args, rank, local_rank, world):
         "admm_iters_per_s": iters_per_s,
         "mean_iters_per_solve": all_iters_step / (B * world), "solved_fraction": all_solved / (B * world),
         "config": {"workload": workload_name(args), "nx": NX, "nu": NU, "N": NH, "batch_per_gpu": B,
-                   "kernel": {1: "thread", 2: "subwarp", 3: "tmem"}.get(sol.kernel, str(sol.kernel)),
+                   "kernel": kname,
                    "l2": "flushed between timed steps (256 MiB write, outside the event pair)",
                    "timing": "CUDA events on the launch stream per step, summed, max over ranks",
                    "parallelism": f"instances sharded over {world} GPU(s), no collective inside the solve"},
@@ -363,12 +371,14 @@ def run_gpu(args, rank, local_rank, world):
         "wall_ms_per_step_incl_flush": 1e3 * (w1 - w0) / K,
         "clocks": clocks,
         "roofline": {"bound": "fp64_fma", "achieved": achieved_tf, "peak": fma_peak, "unit": "TFLOP/s",
-                     "frac": (achieved_tf / fma_peak) if fma_peak else None, "traffic": None,
+                     "frac": (achieved_tf / fma_peak) if fma_peak else None, "traffic": traffic,
+                     "traffic_note": "DRAM bytes per launch from the ncu --set full capture recorded in profiles/traffic.json (null when none matches this kernel/workload)",
                      "flop_per_iter": F, "kernel_ms": kern_ms,
                      "peak_source": "DFMA chains measured live on this GPU by tmpc_measure_fma_peak (MEASURED_PEAKS.json has no CUDA-core peak)",
                      "fp32_fma_peak_tflops": pk32.value},
         "roofline_hbm": {"bound": "hbm", "achieved": hbm_gbs, "peak": peaks_json.get("hbm_gbs"), "unit": "GB/s",
                          "frac": hbm_gbs / peaks_json.get("hbm_gbs", 6650.0), "peak_source": peaks_kind,
+                         "algorithmic_bytes": hbm_bytes, "traffic": traffic,
                          "bytes_per_instance": {"in": bytes_in, "out": bytes_out, "carried_state_out": bytes_state}},
     }
 
