@@ -315,19 +315,14 @@ def run_gpu(args, rank, local_rank, world):
     st, it = sol.status()
     iters_step = int(it.sum())
 
-    tot_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
-    agg = torch.tensor([float(iters_step), float((st == 0).sum()), float(launches)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(tot_ms, op=dist.ReduceOp.MAX)
-        dist.all_reduce(agg, op=dist.ReduceOp.SUM)
-        # the one collective of the path: gather per-instance (status, iterations) over NCCL, outside the solve
-        mine = torch.from_numpy(np.stack([st, it]).astype(np.int32)).to(dev)
-        allst = torch.empty((world,) + tuple(mine.shape), dtype=torch.int32, device=dev)
-        dist.all_gather_into_tensor(allst, mine)
-        gathered = allst.cpu().numpy()
-        assert gathered.shape == (world, 2, B)
-    total_s = float(tot_ms.item()) * 1e-3
-    all_iters_step, all_solved, all_launches = (float(v) for v in agg.tolist())
+    # multi-GPU plumbing (tinympc_julia_b200/sharding.py): device time = max over ranks; counts = sum over ranks; the one
+    # collective of the path gathers the per-instance (status, iterations) over NCCL, outside the solve
+    from tinympc_julia_b200 import sharding
+    tot_ms_max = sharding.max_over_ranks(sum(step_ms), dev)
+    all_iters_step, all_solved, all_launches = sharding.sum_over_ranks([iters_step, int((st == 0).sum()), launches], dev)
+    st_all, it_all = sharding.gather_status(st, it, dev)
+    assert st_all.size == B * world and int(it_all.sum()) == int(all_iters_step)
+    total_s = tot_ms_max * 1e-3
     value = B * world * K / total_s
     iters_per_s = all_iters_step * K / total_s
 
@@ -358,7 +353,7 @@ def run_gpu(args, rank, local_rank, world):
         pass
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(W, 3),
-        "ms_per_step": float(tot_ms.item()) / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": tot_ms_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
         "admm_iters_per_s": iters_per_s,
         "mean_iters_per_solve": all_iters_step / (B * world), "solved_fraction": all_solved / (B * world),
@@ -408,14 +403,12 @@ def run_gpu(args, rank, local_rank, world):
         e2e_step()
     barrier()
     e1 = time.perf_counter()
-    e2e_s = torch.tensor([e1 - e0], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_s = sharding.max_over_ranks(e1 - e0, dev)
     assert int(it_host.sum()) == iters_step, "e2e path solved a different problem than the device-resident path"
-    line["e2e"] = {"value": B * world * K / float(e2e_s.item()), "unit": UNIT,
+    line["e2e"] = {"value": B * world * K / e2e_s, "unit": UNIT,
                    "h2d_bytes_per_step": int(x0_pinned.numel() * 8),
                    "d2h_bytes_per_step": int(X_host.numel() * 8 + U_host.numel() * 8 + 2 * 4 * B),
-                   "ms_per_step": 1e3 * float(e2e_s.item()) / K,
+                   "ms_per_step": 1e3 * e2e_s / K,
                    "path": "tmpc_batch_set_x0 / reset / solve / get_states / get_controls / get_status on pinned host buffers"}
 
     # ---- CPU baseline + single-solve latency: N=1, rank 0 only
