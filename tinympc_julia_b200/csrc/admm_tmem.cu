@@ -810,6 +810,7 @@ bool tmem_kernel_supports(const BatchView& bv, const AdmmSettings& st) {
     if (bv.x_min != nullptr && (bv.xb_stride != 0 || bv.ub_stride != 0)) return false;   // per-instance bounds: other kernels
     QPlan pl;
     if (bv.nx == 12 && bv.nu == 4) return make_qplan<12, 4>(bv.N, refs_mode(bv), pl);
+    if (bv.nx == 4 && bv.nu == 1) return make_qplan<4, 1>(bv.N, refs_mode(bv), pl);
     return false;
 }
 
@@ -817,6 +818,7 @@ cudaError_t launch_admm_tmem(const BatchView& bv, const AdmmSettings& st, int co
                              cudaStream_t stream) {
     if (bv.B <= 0) return cudaSuccess;
     if (bv.nx == 12 && bv.nu == 4) return launch_shape<12, 4>(bv, st, cold, counter, num_sms, stream);
+    if (bv.nx == 4 && bv.nu == 1) return launch_shape<4, 1>(bv, st, cold, counter, num_sms, stream);
     return cudaErrorNotSupported;
 }
 

@@ -7,7 +7,7 @@ import cases, oracle
 import tinympc_julia_b200 as t
 
 orc = oracle.load_oracle()
-for name in ("cartpole_one_solve", "quadrotor_easy_64", "quadrotor_hard_64", "quadrotor_hover", "quadrotor_per_instance_32", "quadrotor_closed_loop_16x40", "rocket_julia_example", "random_5x2_16"):
+for name in ("cartpole_one_solve", "cartpole_test_basic_bounds", "cartpole_batch_64", "quadrotor_easy_64", "quadrotor_hard_64", "quadrotor_hover", "quadrotor_per_instance_32", "quadrotor_closed_loop_16x40", "rocket_julia_example", "random_5x2_16"):
     c = cases.GOLDEN_CASES[name]()
     want = cases.load_golden(name)
     for k in (1, 2, 3):
@@ -43,3 +43,26 @@ for hard in (False, True):
         best = min(ts)
         print(f"quad hard={hard} kernel={k} B={B} best {best*1e3:.3f} ms  solves/s {B/best:.3e} iters/s {it.sum()/best:.3e} "
               f"TFLOP/s {it.sum()*F/best/1e12:.2f} mean iters {it.mean():.2f} solved {(st==0).mean():.3f}", flush=True)
+
+# config 2: batched cartpole, B = 65,536
+from tinympc_julia_b200 import problems
+Fc = problems.flops_per_iteration(4, 1, 20)["F"]
+c = cases.cartpole_batch(B)
+for k in (1, 2, 3):
+    sol = cases.make_cuda_solver(c, kernel=0)
+    sol.set_kernel(k)
+    if sol.kernel != k:
+        continue
+    t.set_x0(sol, c["x0"])
+    ts = []
+    for rep in range(4):
+        sol.reset()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        sol.solve_async(0)
+        sol.synchronize()
+        ts.append(time.perf_counter() - t0)
+    st, it = sol.status()
+    best = min(ts)
+    print(f"cartpole kernel={k} B={B} best {best*1e3:.3f} ms  solves/s {B/best:.3e} iters/s {it.sum()/best:.3e} "
+          f"TFLOP/s {it.sum()*Fc/best/1e12:.2f} mean iters {it.mean():.2f} solved {(st==0).mean():.3f}", flush=True)
