@@ -5,7 +5,7 @@
 // * User-facing arrays keep the Julia layout (instance = slowest dimension): x0 is nx x B,
 //   references nx x N [x B], bounds likewise, solutions nx x N x B.  A per-instance array and a
 //   shared one differ only by the instance stride (0 when shared).
-// * Carried ADMM state (what TinyWorkspace keeps between solves, reference types.hpp:86-187:
+// * (element-major format, thread and shared-memory sub-warp kernels)  Carried ADMM state (what TinyWorkspace keeps between solves, reference types.hpp:86-187:
 //   duals g,y,gc,yc,gl,yl; previous box slacks v,z; linear cost terms q,r and the terminal p)
 //   is stored element-major: entry e of instance b lives at [e * ld + b], ld = B rounded up to 32.
 //   One thread per instance then reads it fully coalesced, and an 8-instance tile of it is a
@@ -55,6 +55,12 @@ struct BatchView {
     double *d;              // feed-forward scratch             nu*(N-1)
     double *gc, *yc;        // cone duals   (allocated when a cone flag is on)
     double *gl, *yl;        // linear duals (allocated when a linear flag is on)
+
+    // ---- carried state, instance-major twin used by the on-chip TMEM kernel: one contiguous block per instance,
+    //      knot i < N: [3 nx i] g(nx) v(nx) q(nx);  knot i < N-1: [3 nx N + 3 nu i] y(nu) z(nu) r(nu);  then p_N (nx).
+    //      The host runtime converts between the two formats when consecutive solves use kernels of different
+    //      families (state_layout.cu); exactly one of them is current at any time.
+    double* state_im; long long state_im_stride;
 
     // ---- results
     double* Xsol;           // nx x N x B      (Julia layout)  = vnew of the last iteration

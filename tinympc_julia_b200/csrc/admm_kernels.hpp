@@ -36,6 +36,10 @@ bool tmem_kernel_supports(const BatchView& bv, const AdmmSettings& st);
 cudaError_t launch_admm_tmem(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms,
                              cudaStream_t stream);
 
+// ---- carried-state formats (state_layout.cu): element-major [e][ld] arrays <-> instance-major blocks
+inline long long state_im_doubles(int nx, int nu, int N) { return 3LL * nx * N + 3LL * nu * (N - 1) + nx; }
+cudaError_t launch_state_convert(const BatchView& bv, bool to_instance_major, cudaStream_t stream);
+
 // ---- closed-loop plant step (rollout.cu): x0 <- A x0 + B Usol(:,0) + f, optional reference slide
 cudaError_t launch_plant_step(const BatchView& bv, double* x0_rw, cudaStream_t stream);
 cudaError_t launch_record_step(const BatchView& bv, int* status_out, int* iters_out, cudaStream_t stream);

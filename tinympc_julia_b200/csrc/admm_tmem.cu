@@ -284,7 +284,6 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     double fr_f[RX], fr_APf[RX], fr_Qd[RX];
 #pragma unroll
     for (int r = 0; r < RX; ++r) { fr_f[r] = sc[CL::f + r * 4 + sub]; fr_APf[r] = sc[CL::APf + r * 4 + sub]; fr_Qd[r] = sc[CL::Qd + r * 4 + sub]; }
-    const size_t ld4 = 4 * ld, ldx = static_cast<size_t>(NX) * ld, ldu = static_cast<size_t>(NU) * ld;
 
     // ---------------- per-lane instance state
     int b = 0, iter = 0, status = 1;
@@ -292,6 +291,11 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     double x0r[RX], p_term[RX];
 #pragma unroll
     for (int r = 0; r < RX; ++r) { x0r[r] = 0.0; p_term[r] = 0.0; }
+    // carried state of an instance: one contiguous block (instance-major):
+    //   knot i < N    : + 3 NX i : g(NX), v(NX), q(NX)
+    //   knot i < N - 1: IB + 3 NU i : y(NU), z(NU), r(NU)          PB: terminal p (NX)
+    const int IB = 3 * NX * N, PB = IB + 3 * NU * (N - 1);
+    double* sblk = bv.state_im + sub;                 // block of the lane's instance, + sub
     const double* xref_g = nullptr;                   // REFS == 2 only
     const double* uref_g = nullptr;
 
@@ -305,22 +309,23 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             const bool wr = fin && valid;                 // results to write
             const bool unconv = (status != 0);
             const size_t bb = wr ? static_cast<size_t>(b) : 0;
+            double* const ob = sblk;                      // block of the finished instance (+ sub)
             if (wr && urow) {
                 double* Us = bv.Usol + bb * nuN + sub;
-                size_t off = static_cast<size_t>(sub) * ld + bb;
+                double* ou = ob + IB;                     // knot i: + 3 NU i ; y +0, z +NU, r +2 NU
                 for (int i = 0; i < N - 1; ++i) {
                     double yy, zz;
                     ld2(s_yz + (i * 32 + lane) * 2, yy, zz);
                     *Us = zz;                                     // solution = znew of the last iteration (admm.cpp:371,387)
-                    bv.y[off] = yy;
-                    if (unconv) bv.z[0][off] = zz;                // z = znew happened (admm.cpp:380); else the lagging copy is there
-                    bv.r[off] = my_rt[i * 32];                    // r as update_linear_cost left it (admm.cpp:228-233)
-                    Us += NU; off += ldu;
+                    ou[0] = yy;
+                    if (unconv) ou[NU] = zz;                      // z = znew happened (admm.cpp:380); else the lagging copy is there
+                    ou[2 * NU] = my_rt[i * 32];                   // r as update_linear_cost left it (admm.cpp:228-233)
+                    Us += NU; ou += 3 * NU;
                 }
             }
             if (wr) {
 #pragma unroll
-                for (int r = 0; r < RX; ++r) bv.pN[(r * 4 + sub) * ld + bb] = p_term[r];
+                for (int r = 0; r < RX; ++r) ob[PB + r * 4] = p_term[r];
                 if (sub == 0) { bv.status[b] = status; bv.iters[b] = iter; }
             }
             // next instance for every finished sub-warp
@@ -330,11 +335,12 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             const bool nvalid = fin && nb < bv.B;
             const size_t nbb = nvalid ? static_cast<size_t>(nb) : 0;
             const bool warm = !COLD && nvalid;
+            double* const nblk = bv.state_im + nbb * static_cast<size_t>(bv.state_im_stride) + sub;
 
             double* Xs = bv.Xsol + bb * nxN + sub;
             const double* xr_old = (REFS == 2 && bv.Xref) ? bv.Xref + bb * bv.xref_stride + sub : nullptr;
-            size_t off = static_cast<size_t>(sub) * ld + bb;          // old instance, element (i NX + sub)
-            size_t noff = static_cast<size_t>(sub) * ld + nbb;        // new instance
+            double* op = ob;                              // knot i of the old / new instance: + 3 NX i ; g +0, v +NX, q +2 NX
+            const double* np = nblk;
             for (int i = 0; i < N; ++i) {
                 uint32_t w[W];
                 tm_load<W>(tbase + i * W, w);
@@ -343,7 +349,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 for (int r = 0; r < RX; ++r) { gn[r] = 0.0; vn[r] = 0.0; }
                 if (warm) {
 #pragma unroll
-                    for (int r = 0; r < RX; ++r) { gn[r] = bv.g[noff + r * ld4]; vn[r] = bv.v[0][noff + r * ld4]; }
+                    for (int r = 0; r < RX; ++r) { gn[r] = np[r * 4]; vn[r] = np[NX + r * 4]; }
                 }
                 tm_wait_ld<W>(w);
 #pragma unroll
@@ -351,10 +357,9 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                     if (wr) {
                         const double gg = mk_double(w[2 * r], w[2 * r + 1]);
                         const double vv = mk_double(w[2 * (RX + r)], w[2 * (RX + r) + 1]);
-                        const size_t ge = off + r * ld4;
                         Xs[r * 4] = vv;                           // solution = vnew of the last iteration (admm.cpp:370,386)
-                        bv.g[ge] = gg;
-                        if (unconv) bv.v[0][ge] = vv;             // v = vnew happened (admm.cpp:379); else the lagging copy is there
+                        op[r * 4] = gg;
+                        if (unconv) op[NX + r * 4] = vv;          // v = vnew happened (admm.cpp:379); else the lagging copy is there
                         if (i < N - 1) {                          // q as update_linear_cost left it (admm.cpp:218-219)
                             double q;
                             if (REFS == 0) q = dmul(nrho, dsub(vv, gg));
@@ -363,7 +368,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                                                               : -dmul(xr_old ? __ldg(xr_old + i * NX + r * 4) : 0.0, fr_Qd[r]);
                                 q = dsub(cq, dmul(rho, dsub(vv, gg)));
                             }
-                            bv.q[ge] = q;
+                            op[2 * NX + r * 4] = q;
                         }
                     }
                     if (fin) {
@@ -372,23 +377,24 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                     }
                 }
                 tm_store<W>(tbase + i * W, w);
-                Xs += NX; off += ldx; noff += ldx;
+                Xs += NX; op += 3 * NX; np += 3 * NX;
             }
             if (fin) {
-                size_t uo = static_cast<size_t>(sub) * ld + nbb;
+                const double* nu_p = nblk + IB;
                 for (int i = 0; i < N - 1; ++i) {
                     double yy = 0.0, zz = 0.0, rr = 0.0;
-                    if (warm && urow) { yy = bv.y[uo]; zz = bv.z[0][uo]; rr = bv.r[uo]; }
+                    if (warm && urow) { yy = nu_p[0]; zz = nu_p[NU]; rr = nu_p[2 * NU]; }
                     st2(s_yz + (i * 32 + lane) * 2, yy, zz);
                     my_rt[i * 32] = rr;
-                    uo += ldu;
+                    nu_p += 3 * NU;
                 }
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
                     x0r[r] = nvalid ? bv.x0[nbb * NX + r * 4 + sub] : 0.0;
-                    p_term[r] = warm ? bv.pN[(r * 4 + sub) * ld + nbb] : 0.0;
+                    p_term[r] = warm ? nblk[PB + r * 4] : 0.0;
                 }
                 b = nvalid ? nb : 0;
+                sblk = nblk;
                 valid = nvalid; iter = 0; first = true; status = 1; fin = false;
                 if (REFS == 2) {
                     xref_g = bv.Xref ? bv.Xref + nbb * bv.xref_stride + sub : nullptr;      // + i NX + 4 r
@@ -428,10 +434,10 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
 #pragma unroll
             for (int r = 0; r < RX; ++r) qcar[r] = 0.0;
             const bool ldq = !COLD && first && valid;
-            const double* qp_g = bv.q + static_cast<size_t>(sub) * ld + bb + static_cast<size_t>(N - 2) * ldx;   // row r: + r ld4
+            const double* qp_g = sblk + 2 * NX + (N - 2) * 3 * NX;          // q of knot N-2; row r: + 4 r
             if (ldq) {
 #pragma unroll
-                for (int r = 0; r < RX; ++r) qcar[r] = qp_g[r * ld4];
+                for (int r = 0; r < RX; ++r) qcar[r] = qp_g[r * 4];
             }
             double t_def = 0.0;
             uint32_t o_rt = (N - 2) * 256;                // byte offset of knot i in the r/t array
@@ -483,9 +489,9 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 if (i > 0) {
                     tm_load<W>(tbase + (i - 1) * W, w);
                     if (ldq) {
-                        qp_g -= ldx;
+                        qp_g -= 3 * NX;
 #pragma unroll
-                        for (int r = 0; r < RX; ++r) qcar[r] = qp_g[r * ld4];
+                        for (int r = 0; r < RX; ++r) qcar[r] = qp_g[r * 4];
                     }
                 }
 
@@ -540,10 +546,10 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             tm_load<W>(tbase, w);
             // the carried "previous slacks" must lag the solution by one iteration when the solve converges
             // (admm.cpp:375 returns before :379-380): while this sweep can still end in convergence the lane parks
-            // them in the carried-state arrays in HBM (running pointers: no address arithmetic per store)
+            // them in the instance's carried-state block in HBM ([pointer + immediate] stores, whole 32-byte sectors)
             const bool lag = valid && ((iter + 1) % st.check_termination == 0);
-            double* vlag = bv.v[0] + static_cast<size_t>(sub) * ld + bb;      // row r of knot i: + (i NX + 4 r) ld
-            double* zlag = bv.z[0] + static_cast<size_t>(sub) * ld + bb;      // knot i: + (i NU) ld
+            double* vlag = sblk + NX;                                         // v of knot i: + 3 NX i ; row r: + 4 r
+            double* zlag = sblk + IB + NU;                                    // z of knot i: + 3 NU i
             double r_def = 0.0;
             double vg[RX];
             uint32_t o_xb = 0;                                                // byte offset of knot i in the state-bound table
@@ -577,7 +583,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                         const bool p1 = fabs(dsub(x[r], vnew)) < qp.pri_thresh;
                         const bool p2 = fabs(dsub(vold, vnew)) <= qp.dua_thresh;
                         ok = ok & p1 & p2;
-                        if (lag & ok) vlag[r * ld4] = vold;
+                        if (lag & ok) vlag[r * 4] = vold;
                     }
                     wn[2 * r] = lo32(gnew); wn[2 * r + 1] = hi32(gnew);
                     wn[2 * (RX + r)] = lo32(vnew); wn[2 * (RX + r) + 1] = hi32(vnew);
@@ -683,7 +689,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                     for (int k = 0; k < NU; ++k) s2 = fma(mb[r][k], ub[k], s2);
                     x[r] = dadd(dadd(s1[r], s2), fr_f[r]);
                 }
-                vlag += ldx; zlag += ldu;
+                vlag += 3 * NX; zlag += 3 * NU;
                 o_rt += 256; o_yz += 512; o_ub += NU * 16; o_cr += NU * 8; o_xb += NX * 16;
             };
 

@@ -91,6 +91,8 @@ struct tmpc_batch {
     // results
     DevBuf<double> Xsol, Usol;
     DevBuf<int> status, iters, counter;
+    DevBuf<double> state_im;  // instance-major twin of the carried state (TMEM kernel), allocated on first use
+    bool state_in_im = false; // which format holds the current carried state (meaningless while state_zero)
 
     void use_device() const { CUDA_TRY(cudaSetDevice(device)); }
 };
@@ -140,6 +142,7 @@ tmpc::BatchView make_view(tmpc_batch* h) {
     v.q = h->q.p; v.r = h->r.p; v.pN = h->pN.p; v.d = h->d.p;
     v.gc = h->gc.p; v.yc = h->yc.p; v.gl = h->gl.p; v.yl = h->yl.p;
     v.Xsol = h->Xsol.p; v.Usol = h->Usol.p; v.status = h->status.p; v.iters = h->iters.p;
+    v.state_im = h->state_im.p; v.state_im_stride = tmpc::state_im_doubles(h->nx, h->nu, h->N);
     return v;
 }
 
@@ -169,8 +172,20 @@ void materialize_zero(tmpc_batch* h) {
 // One solve kernel on `s`.  A cold (reset) state is passed to the sub-warp kernel as a flag; every other
 // reader gets physically zeroed buffers first, on the SAME stream as the solve: an earlier solve enqueued on a
 // caller stream may still be running, and memsets on another stream would race with it.
-cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v, cudaStream_t s) {
+cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v_in, cudaStream_t s) {
     const bool sub = (k == TMPC_KERNEL_SUBWARP || k == TMPC_KERNEL_TMEM) && h->st.max_iter > 0 && h->rho > 0.0;
+    tmpc::BatchView v = v_in;
+    const bool wants_im = sub && k == TMPC_KERNEL_TMEM;
+    if (wants_im && !h->state_im.p) {
+        h->state_im.alloc(static_cast<size_t>(v.state_im_stride) * h->B);
+        v.state_im = h->state_im.p;
+    }
+    if (!h->state_zero && wants_im != h->state_in_im) {      // the previous solve left the other format: convert on `s`
+        if (!v.state_im) return cudaErrorInvalidValue;
+        cudaError_t ce = tmpc::launch_state_convert(v, wants_im, s);
+        if (ce != cudaSuccess) return ce;
+        h->launches += 1;
+    }
     if (!sub && h->state_zero && !h->mem_zero) {
         zero_state(h, s);
     }
@@ -179,7 +194,7 @@ cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v, cudaStr
     else if (sub) e = tmpc::launch_admm_subwarp(v, h->st, h->hm, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
     else e = tmpc::launch_admm_thread(v, h->st, h->hm, s);
     h->launches += 1;
-    if (h->st.max_iter > 0) { h->state_zero = false; h->mem_zero = false; }
+    if (h->st.max_iter > 0) { h->state_zero = false; h->mem_zero = false; h->state_in_im = wants_im; }
     return e;
 }
 

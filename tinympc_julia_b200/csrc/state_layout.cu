@@ -1,0 +1,55 @@
+// Conversion between the two HBM formats of the carried ADMM state (admm_device.cuh):
+//   element-major  g, v, q, y, z, r, pN as [element][ld] arrays  (coalesced for one thread per instance)
+//   instance-major one contiguous block per instance               (whole sectors for one sub-warp per instance)
+// Runs only when consecutive warm-started solves of a batch use kernels of different families, which the library
+// never does on its own (tests do, to prove the formats carry the same state).
+#include <cuda_runtime.h>
+
+#include "admm_device.cuh"
+#include "admm_kernels.hpp"
+
+namespace tmpc {
+namespace {
+
+__global__ void state_convert_kernel(const __grid_constant__ BatchView bv, int to_im) {
+    const int nx = bv.nx, nu = bv.nu, N = bv.N;
+    const int nxN = nx * N, nuN = nu * (N - 1);
+    const int per = 3 * nxN + 3 * nuN + nx;              // scalars per instance
+    const long long total = static_cast<long long>(per) * bv.B;
+    const size_t ld = static_cast<size_t>(bv.ld);
+    for (long long idx = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; idx < total;
+         idx += static_cast<long long>(gridDim.x) * blockDim.x) {
+        // idx enumerates (field element, instance) with the instance fastest: coalesced on the element-major side
+        const int b = static_cast<int>(idx % bv.B);
+        int e = static_cast<int>(idx / bv.B);
+        double* em;      // element-major address
+        int im;          // offset in the instance block
+        if (e < 3 * nxN) {
+            const int f = e / nxN, k = e % nxN, i = k / nx, row = k % nx;       // f: 0 g, 1 v, 2 q
+            em = (f == 0 ? bv.g : f == 1 ? bv.v[0] : bv.q) + static_cast<size_t>(k) * ld + b;
+            im = 3 * nx * i + f * nx + row;
+        } else if (e < 3 * nxN + 3 * nuN) {
+            e -= 3 * nxN;
+            const int f = e / nuN, k = e % nuN, i = k / nu, row = k % nu;       // f: 0 y, 1 z, 2 r
+            em = (f == 0 ? bv.y : f == 1 ? bv.z[0] : bv.r) + static_cast<size_t>(k) * ld + b;
+            im = 3 * nxN + 3 * nu * i + f * nu + row;
+        } else {
+            e -= 3 * nxN + 3 * nuN;
+            em = bv.pN + static_cast<size_t>(e) * ld + b;
+            im = 3 * nxN + 3 * nuN + e;
+        }
+        double* blk = bv.state_im + static_cast<size_t>(b) * bv.state_im_stride + im;
+        if (to_im) *blk = *em; else *em = *blk;
+    }
+}
+
+}  // namespace
+
+cudaError_t launch_state_convert(const BatchView& bv, bool to_instance_major, cudaStream_t stream) {
+    if (bv.B <= 0) return cudaSuccess;
+    if (!bv.state_im) return cudaErrorInvalidValue;
+    state_convert_kernel<<<148 * 8, 256, 0, stream>>>(bv, to_instance_major ? 1 : 0);
+    return cudaGetLastError();
+}
+
+}  // namespace tmpc
