@@ -203,6 +203,10 @@ void* tmpc_batch_device_ptr(tmpc_batch* h, int which);
 int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_long,
                              int* d_status_out, int* d_iters_out, void* cuda_stream);
 
+/* Current x0 of every instance (after a rollout: the plant state reached), nx x B.  `device_dst` != 0: dst is a device
+ * pointer on the batch's device (device-to-device copy), else a host buffer. */
+int tmpc_batch_get_x0(tmpc_batch* h, void* dst, int device_dst);
+
 /* Introspection */
 int tmpc_batch_dims(tmpc_batch* h, int* nx, int* nu, int* N, int* B);
 long long tmpc_batch_launch_count(tmpc_batch* h);   /* kernels launched by this handle so far */

@@ -149,3 +149,35 @@ def test_full_size_batch_properties():
         assert np.array_equal(a["iters"], b["iters"]) and np.array_equal(a["ret"], b["ret"]), f"kernel {k}"
         np.testing.assert_allclose(a["X"], b["X"], rtol=1e-5, atol=1e-6)
         np.testing.assert_allclose(a["U"], b["U"], rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("B,nsteps", [(48, 30), (9, 7)])
+def test_device_rollout_matches_oracle(orc, B, nsteps):
+    """tmpc_batch_rollout_async (config 5 on the device: solve -> apply u0 -> plant step -> slide the reference window,
+    nothing leaves the GPU between steps) against the oracle's closed loop: per-step iteration counts and status,
+    final plant state, last solution."""
+    import torch
+    c = cases.quadrotor_closed_loop(B, nsteps)
+    want = cases.run_checker(c, orc, nthreads=4)
+    s, N = c["sys"], c["N"]
+    for k in kernels_for(c):
+        sol = cases.make_cuda_solver(c, kernel=k)
+        t.set_x0(sol, c["x0"])
+        # (nx, N+nsteps-1, B) Fortran == (B, N+nsteps-1, nx) C-contiguous
+        xlong = torch.from_numpy(np.ascontiguousarray(np.asfortranarray(c["Xref"]).transpose(2, 1, 0))).cuda()
+        st_out = torch.full((nsteps, B), -1, dtype=torch.int32, device="cuda")
+        it_out = torch.full((nsteps, B), -1, dtype=torch.int32, device="cuda")
+        torch.cuda.synchronize()
+        sol.rollout_async(nsteps, xlong.data_ptr(), st_out.data_ptr(), it_out.data_ptr(), 0)
+        sol.synchronize()
+        assert np.array_equal(it_out.cpu().numpy(), want["iters"]), f"kernel {k}: per-step iteration counts"
+        assert np.array_equal(st_out.cpu().numpy(), want["ret"]), f"kernel {k}: per-step status"
+        X, U = t.get_solution(sol)
+        np.testing.assert_allclose(X, want["X"], rtol=1e-5, atol=1e-6)
+        np.testing.assert_allclose(U, want["U"], rtol=1e-5, atol=1e-6)
+        xf = torch.empty((B, s.nx), dtype=torch.float64, device="cuda")
+        import ctypes as C
+        from tinympc_julia_b200 import _lib
+        rc = _lib.load().tmpc_batch_get_x0(sol._h, C.cast(xf.data_ptr(), C.c_void_p), 1)
+        assert rc == 0
+        np.testing.assert_allclose(xf.cpu().numpy().T, want["x_final"], rtol=1e-5, atol=1e-6)

@@ -68,6 +68,7 @@ SIGNATURES = {
     "tmpc_batch_bind_u_ref_device": (_I, [_V, _V, _I]),
     "tmpc_batch_device_ptr": (_V, [_V, _I]),
     "tmpc_batch_rollout_async": (_I, [_V, _I, _V, _V, _V, _V]),
+    "tmpc_batch_get_x0": (_I, [_V, _V, _I]),
     "tmpc_batch_dims": (_I, [_V, _IP, _IP, _IP, _IP]),
     "tmpc_batch_launch_count": (C.c_longlong, [_V]),
     "tmpc_measure_fma_peak": (_I, [_I, _I, _I, _P]),

@@ -632,6 +632,18 @@ int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_lo
     });
 }
 
+int tmpc_batch_get_x0(tmpc_batch* h, void* dst, int device_dst) {
+    return guarded([&]() -> int {
+        if (!h || !dst) return TMPC_ERR_DIM;
+        h->use_device();
+        const double* src = h->ext_x0 ? h->ext_x0 : h->x0.p;
+        CUDA_TRY(cudaMemcpyAsync(dst, src, sizeof(double) * h->nx * h->B,
+                                 device_dst ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, h->stream));
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        return TMPC_OK;
+    });
+}
+
 int tmpc_batch_dims(tmpc_batch* h, int* nx, int* nu, int* N, int* B) {
     if (!h) return TMPC_ERR_DIM;
     if (nx) *nx = h->nx;
