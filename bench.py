@@ -343,7 +343,7 @@ def run_gpu(args, rank, local_rank, world):
     hbm_bytes = B * (bytes_in + bytes_out + bytes_state)
     hbm_gbs = hbm_bytes / (kern_ms * 1e-3) / 1e9
 
-    kname = {1: "thread", 2: "subwarp", 3: "tmem"}.get(sol.kernel, str(sol.kernel))
+    kname = {1: "thread", 2: "subwarp", 3: "tmem", 4: "tmem2"}.get(sol.kernel, str(sol.kernel))
     traffic = None
     try:
         rec = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(kname)
@@ -444,7 +444,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=65536)
     ap.add_argument("--workload", default="quadrotor_easy", choices=["quadrotor_easy", "quadrotor_hard"])
-    ap.add_argument("--kernel", type=int, default=0, help="0 auto, 1 thread-per-instance, 2 sub-warp (shared memory), 3 sub-warp (TMEM + shared memory)")
+    ap.add_argument("--kernel", type=int, default=0, help="0 auto, 1 thread-per-instance, 2 sub-warp (shared memory), 3 sub-warp (TMEM + shared memory), 4 the same with two instances per lane")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline / single_solve legs")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

@@ -12,14 +12,14 @@ import tinympc_julia_b200 as t
 
 pytestmark = pytest.mark.gpu
 
-THREAD, SUBWARP, TMEM = t.KERNEL_THREAD, t.KERNEL_SUBWARP, t.KERNEL_TMEM
+THREAD, SUBWARP, TMEM, TMEM2 = t.KERNEL_THREAD, t.KERNEL_SUBWARP, t.KERNEL_TMEM, t.KERNEL_TMEM2
 
 
 def kernels_for(c):
     """Kernels able to run a case: the thread kernel always; the on-chip kernels where they apply."""
     ks = [THREAD]
     sol = cases.make_cuda_solver(c, kernel=t.KERNEL_AUTO)
-    for k in (SUBWARP, TMEM):
+    for k in (SUBWARP, TMEM, TMEM2):
         sol.set_kernel(k)
         if sol.kernel == k:
             ks.append(k)

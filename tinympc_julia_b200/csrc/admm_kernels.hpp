@@ -36,6 +36,12 @@ bool tmem_kernel_supports(const BatchView& bv, const AdmmSettings& st);
 cudaError_t launch_admm_tmem(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms,
                              cudaStream_t stream);
 
+// ---- the same design with TWO instances per lane and one resident double per element (admm_tmem2.cu): 16 instances
+// per warp, 128 per SM.  Same applicability as the TMEM kernel; N is limited to 21 for nx = 12.
+bool tmem2_kernel_supports(const BatchView& bv, const AdmmSettings& st);
+cudaError_t launch_admm_tmem2(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms,
+                              cudaStream_t stream);
+
 // ---- carried-state formats (state_layout.cu): element-major [e][ld] arrays <-> instance-major blocks
 inline long long state_im_doubles(int nx, int nu, int N) { return 3LL * nx * N + 3LL * nu * (N - 1) + nx; }
 cudaError_t launch_state_convert(const BatchView& bv, bool to_instance_major, cudaStream_t stream);

@@ -149,6 +149,8 @@ tmpc::BatchView make_view(tmpc_batch* h) {
 int resolve_kernel(tmpc_batch* h) {
     const bool sub_ok = tmpc::subwarp_kernel_supports(h->nx, h->nu, h->N, h->st);
     const bool tm_ok = tmpc::tmem_kernel_supports(make_view(h), h->st);
+    const bool tm2_ok = tmpc::tmem2_kernel_supports(make_view(h), h->st);
+    if (h->kernel_pref == TMPC_KERNEL_TMEM2) return tm2_ok ? TMPC_KERNEL_TMEM2 : -1;
     if (h->kernel_pref == TMPC_KERNEL_TMEM) return tm_ok ? TMPC_KERNEL_TMEM : -1;
     if (h->kernel_pref == TMPC_KERNEL_SUBWARP) return sub_ok ? TMPC_KERNEL_SUBWARP : -1;
     if (h->kernel_pref == TMPC_KERNEL_THREAD) return TMPC_KERNEL_THREAD;
@@ -173,9 +175,10 @@ void materialize_zero(tmpc_batch* h) {
 // reader gets physically zeroed buffers first, on the SAME stream as the solve: an earlier solve enqueued on a
 // caller stream may still be running, and memsets on another stream would race with it.
 cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v_in, cudaStream_t s) {
-    const bool sub = (k == TMPC_KERNEL_SUBWARP || k == TMPC_KERNEL_TMEM) && h->st.max_iter > 0 && h->rho > 0.0;
+    const bool tm = (k == TMPC_KERNEL_TMEM || k == TMPC_KERNEL_TMEM2);
+    const bool sub = (k == TMPC_KERNEL_SUBWARP || tm) && h->st.max_iter > 0 && h->rho > 0.0;
     tmpc::BatchView v = v_in;
-    const bool wants_im = sub && k == TMPC_KERNEL_TMEM;
+    const bool wants_im = sub && tm;
     if (wants_im && !h->state_im.p) {
         h->state_im.alloc(static_cast<size_t>(v.state_im_stride) * h->B);
         v.state_im = h->state_im.p;
@@ -190,7 +193,8 @@ cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v_in, cuda
         zero_state(h, s);
     }
     cudaError_t e;
-    if (sub && k == TMPC_KERNEL_TMEM) e = tmpc::launch_admm_tmem(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
+    if (sub && k == TMPC_KERNEL_TMEM2) e = tmpc::launch_admm_tmem2(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
+    else if (sub && k == TMPC_KERNEL_TMEM) e = tmpc::launch_admm_tmem(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
     else if (sub) e = tmpc::launch_admm_subwarp(v, h->st, h->hm, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
     else e = tmpc::launch_admm_thread(v, h->st, h->hm, s);
     h->launches += 1;
@@ -346,7 +350,7 @@ int tmpc_batch_update_settings(tmpc_batch* h, double abs_pri_tol, double abs_dua
 }
 
 int tmpc_batch_set_kernel(tmpc_batch* h, int kernel) {
-    if (!h || kernel < TMPC_KERNEL_AUTO || kernel > TMPC_KERNEL_TMEM) return TMPC_ERR_DIM;
+    if (!h || kernel < TMPC_KERNEL_AUTO || kernel > TMPC_KERNEL_TMEM2) return TMPC_ERR_DIM;
     h->kernel_pref = kernel;
     return TMPC_OK;
 }
