@@ -388,6 +388,11 @@ def run_gpu(args, rank, local_rank, world):
     lib.tmpc_batch_bind_x0_device(h, None)
 
     def e2e_step():
+        # one call: x0 up, solve cut into instance chunks, each chunk's solution crossing PCIe while the next one solves
+        assert lib.tmpc_batch_solve_host(h, dp(x0_pinned), 1, dp(X_host), dp(U_host), ip(st_host), ip(it_host), 0) in (0, 1)
+
+    def e2e_step_calls():
+        # the same through the five reference-style calls (no overlap): reported next to the pipelined number
         assert lib.tmpc_batch_set_x0(h, dp(x0_pinned), NX, B) == 0
         assert lib.tmpc_batch_reset(h) == 0
         assert lib.tmpc_batch_solve(h) in (0, 1)
@@ -395,6 +400,15 @@ def run_gpu(args, rank, local_rank, world):
         assert lib.tmpc_batch_get_controls(h, dp(U_host)) == 0
         assert lib.tmpc_batch_get_status(h, ip(st_host), ip(it_host)) == 0
 
+    for _ in range(2):
+        e2e_step_calls()
+    barrier()
+    c0 = time.perf_counter()
+    for _ in range(max(3, K // 5)):
+        e2e_step_calls()
+    barrier()
+    calls_s = sharding.max_over_ranks((time.perf_counter() - c0) / max(3, K // 5), dev)
+    X_chk = X_host[:64].clone(); U_chk = U_host[:64].clone()
     for _ in range(3):
         e2e_step()
     barrier()
@@ -409,7 +423,10 @@ def run_gpu(args, rank, local_rank, world):
                    "h2d_bytes_per_step": int(x0_pinned.numel() * 8),
                    "d2h_bytes_per_step": int(X_host.numel() * 8 + U_host.numel() * 8 + 2 * 4 * B),
                    "ms_per_step": 1e3 * e2e_s / K,
-                   "path": "tmpc_batch_set_x0 / reset / solve / get_states / get_controls / get_status on pinned host buffers"}
+                   "path": "tmpc_batch_solve_host on pinned host buffers (x0 up, chunked solve overlapped with the D2H of the previous chunk's solution)",
+                   "unpipelined_ms_per_step": 1e3 * calls_s,
+                   "unpipelined_path": "tmpc_batch_set_x0 / reset / solve / get_states / get_controls / get_status"}
+    assert torch.equal(X_chk, X_host[:64]) and torch.equal(U_chk, U_host[:64]), "pipelined e2e path returned a different solution"
 
     # ---- CPU baseline + single-solve latency: N=1, rank 0 only
     if world == 1 and rank == 0 and not args.no_cpu:

@@ -182,6 +182,12 @@ int tmpc_batch_reset(tmpc_batch* h);
  * instance converged, 1 when at least one stopped at max_iter, <0 / >1 on error. */
 int tmpc_batch_solve(tmpc_batch* h);
 int tmpc_batch_solve_async(tmpc_batch* h, void* cuda_stream);   /* enqueue only; no host sync */
+/* set_x0 (+ reset when cold != 0) + solve + get_states / get_controls / get_status in ONE call on host buffers, the
+ * batch cut into `chunks` (0 = default) so that the solution of one chunk crosses PCIe while the next chunk solves.
+ * x0 nx x B or NULL (keep the current one); X nx x N x B, U nu x (N-1) x B, status, iters: B each, any may be NULL.
+ * Pinned host buffers make the copies truly asynchronous.  Returns like tmpc_batch_solve (0 / 1 / 100 + error). */
+int tmpc_batch_solve_host(tmpc_batch* h, const double* x0, int cold, double* X, double* U, int* status, int* iters,
+                          int chunks);
 int tmpc_batch_synchronize(tmpc_batch* h);
 
 /* Per-instance results.  status[b] = what solve_mpc would return for that instance (0 / 1). */

@@ -181,3 +181,36 @@ def test_device_rollout_matches_oracle(orc, B, nsteps):
         rc = _lib.load().tmpc_batch_get_x0(sol._h, C.cast(xf.data_ptr(), C.c_void_p), 1)
         assert rc == 0
         np.testing.assert_allclose(xf.cpu().numpy().T, want["x_final"], rtol=1e-5, atol=1e-6)
+
+
+def test_solve_host_pipelined_matches_stepwise(orc):
+    """tmpc_batch_solve_host (x0 up, chunked solve, solution down in one call) == set_x0 / reset / solve / get_*:
+    bit-identical results cold and warm, with the batch large enough to be cut into chunks."""
+    B = 148 * 64 * 3 + 37
+    c = cases.quadrotor_batch(B, hard=True, max_iter=25)
+    ref = cases.make_cuda_solver(c)
+    pip = cases.make_cuda_solver(c)
+    rng = np.random.default_rng(5)
+    for step, cold in enumerate((True, False, False)):
+        x0 = np.asfortranarray(c["x0"] * (1.0 + 0.1 * step) + 0.01 * rng.standard_normal(c["x0"].shape))
+        t.set_x0(ref, x0)
+        if cold:
+            ref.reset()
+        r0 = t.solve(ref)
+        sol0 = t.get_solution(ref)
+        st0, it0 = ref.status()
+        r1, sol1, st1, it1 = pip.solve_host(x0, cold=cold, chunks=0 if step < 2 else 3)
+        assert r0 == r1
+        assert np.array_equal(st0, st1) and np.array_equal(it0, it1)
+        assert np.array_equal(sol0.states, sol1.states) and np.array_equal(sol0.controls, sol1.controls)
+    # small batch / other kernels: single chunk path
+    c = cases.rocket(40, N=50)
+    want = cases.run_checker(c, orc)
+    sol = cases.make_cuda_solver(c)
+    if c["Xref"] is not None:
+        t.set_x_ref(sol, c["Xref"])
+    if c["Uref"] is not None:
+        t.set_u_ref(sol, c["Uref"])
+    r, s1, st1, it1 = sol.solve_host(c["x0"], cold=True)
+    assert np.array_equal(it1, want["iters"][0]) and np.array_equal(st1, want["ret"][0])
+    np.testing.assert_allclose(s1.controls, want["U"], rtol=1e-5, atol=1e-6)

@@ -6,6 +6,8 @@
 // computes an ADMM iteration on the host: without a usable CUDA device every call fails.
 #include <cuda_runtime.h>
 
+#include <algorithm>
+
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -68,6 +70,8 @@ struct tmpc_batch {
     tmpc::AdmmSettings st{};
     int kernel_pref = TMPC_KERNEL_AUTO;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;       // tmpc_batch_solve_host: result chunks go home while the next chunk solves
+    std::vector<cudaEvent_t> chunk_done;
     long long launches = 0;
     bool state_zero = true;   // carried state is LOGICALLY zero (fresh or reset) ...
     bool mem_zero = true;     // ... and the device buffers physically hold those zeros.  tmpc_batch_reset only flips
@@ -326,6 +330,8 @@ int tmpc_batch_destroy(tmpc_batch* h) {
     return guarded([&]() -> int {
         cudaSetDevice(h->device);
         if (h->stream) { cudaStreamSynchronize(h->stream); cudaStreamDestroy(h->stream); }
+        if (h->copy_stream) { cudaStreamSynchronize(h->copy_stream); cudaStreamDestroy(h->copy_stream); }
+        for (cudaEvent_t e : h->chunk_done) cudaEventDestroy(e);
         delete h;
         return TMPC_OK;
     });
@@ -534,6 +540,94 @@ int tmpc_batch_solve(tmpc_batch* h) {
         CUDA_TRY(cudaMemcpyAsync(st.data(), h->status.p, sizeof(int) * h->B, cudaMemcpyDeviceToHost, h->stream));
         CUDA_TRY(cudaStreamSynchronize(h->stream));
         for (int s : st) if (s != 0) return 1;
+        return 0;
+    });
+}
+
+/* One call, host buffers in and out: x0 up, solve, solution + status down.  The batch is cut into chunks of whole
+ * instances (the on-chip kernels own an instance per sub-warp and the carried state is one block per instance, so a
+ * chunk is just an offset view); chunk c solves on the handle's stream while chunk c-1 travels home on a second
+ * stream, which hides the solve behind the PCIe transfer of the solution (166 MB for the quadrotor at B = 65,536). */
+int tmpc_batch_solve_host(tmpc_batch* h, const double* x0, int cold, double* X, double* U, int* status, int* iters,
+                          int chunks) {
+    return guarded([&]() -> int {
+        if (!h) return TMPC_ERR_DIM;
+        h->use_device();
+        if (h->st.check_termination == 0) { set_error("check_termination = 0 is not supported (the reference divides by it)"); return 100 + TMPC_ERR_STATE; }
+        if (x0) {
+            h->ext_x0 = nullptr;
+            h->x0.upload(x0, static_cast<size_t>(h->nx) * h->B, h->stream);
+        }
+        if (cold) h->state_zero = true;
+        ensure_aux_state(h);
+        const int k = resolve_kernel(h);
+        if (k < 0) { set_error("requested kernel does not support this problem"); return 100 + TMPC_ERR_STATE; }
+        const bool tm = (k == TMPC_KERNEL_TMEM || k == TMPC_KERNEL_TMEM2) && h->st.max_iter > 0 && h->rho > 0.0;
+        // chunks are whole waves of the persistent grid (one CTA per SM, 64 resident instances each), at least two
+        // waves each, so that a chunk runs at the efficiency of the full batch
+        const int wave = h->num_sms * 64;
+        int nch = chunks > 0 ? chunks : 4;
+        if (!tm || h->B < 3 * wave) nch = 1;
+        int chunk_size = h->B;
+        if (nch > 1) {
+            chunk_size = ((h->B + nch - 1) / nch + wave - 1) / wave * wave;
+            if (chunk_size < 2 * wave) chunk_size = 2 * wave;
+            nch = (h->B + chunk_size - 1) / chunk_size;
+        }
+        if (!h->copy_stream) CUDA_TRY(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+        while (static_cast<int>(h->chunk_done.size()) < nch) {
+            cudaEvent_t e; CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); h->chunk_done.push_back(e);
+        }
+        std::vector<int> st_tmp;
+        if (!status) { st_tmp.resize(h->B); status = st_tmp.data(); }
+        tmpc::BatchView v = make_view(h);
+        const size_t sxN = static_cast<size_t>(h->nx) * h->N, suN = static_cast<size_t>(h->nu) * (h->N - 1);
+        if (nch > 1) {
+            const bool was_cold = h->state_zero;
+            if (!h->state_im.p) { h->state_im.alloc(static_cast<size_t>(v.state_im_stride) * h->B); v.state_im = h->state_im.p; }
+            if (!was_cold && !h->state_in_im) {
+                cudaError_t ce = tmpc::launch_state_convert(v, true, h->stream);
+                if (ce != cudaSuccess) throw CudaFail{ce, "state conversion"};
+                h->launches += 1;
+            }
+            for (int c = 0; c < nch; ++c) {
+                const int b0 = c * chunk_size;
+                const int b1 = std::min(h->B, b0 + chunk_size);
+                tmpc::BatchView vc = v;
+                vc.B = b1 - b0;
+                vc.x0 = v.x0 + static_cast<size_t>(b0) * h->nx;
+                if (v.Xref && v.xref_stride) vc.Xref = v.Xref + static_cast<size_t>(b0) * v.xref_stride;
+                if (v.Uref && v.uref_stride) vc.Uref = v.Uref + static_cast<size_t>(b0) * v.uref_stride;
+                vc.state_im = v.state_im + static_cast<size_t>(b0) * v.state_im_stride;
+                vc.Xsol = v.Xsol + b0 * sxN; vc.Usol = v.Usol + b0 * suN;
+                vc.status = v.status + b0; vc.iters = v.iters + b0;
+                cudaError_t e = (k == TMPC_KERNEL_TMEM2)
+                    ? tmpc::launch_admm_tmem2(vc, h->st, was_cold ? 1 : 0, h->counter.p, h->num_sms, h->stream)
+                    : tmpc::launch_admm_tmem(vc, h->st, was_cold ? 1 : 0, h->counter.p, h->num_sms, h->stream);
+                if (e != cudaSuccess) throw CudaFail{e, "solve kernel launch"};
+                h->launches += 1;
+                CUDA_TRY(cudaEventRecord(h->chunk_done[c], h->stream));
+                CUDA_TRY(cudaStreamWaitEvent(h->copy_stream, h->chunk_done[c], 0));
+                const size_t nb = static_cast<size_t>(b1 - b0);
+                if (X) CUDA_TRY(cudaMemcpyAsync(X + b0 * sxN, v.Xsol + b0 * sxN, sizeof(double) * sxN * nb, cudaMemcpyDeviceToHost, h->copy_stream));
+                if (U) CUDA_TRY(cudaMemcpyAsync(U + b0 * suN, v.Usol + b0 * suN, sizeof(double) * suN * nb, cudaMemcpyDeviceToHost, h->copy_stream));
+                CUDA_TRY(cudaMemcpyAsync(status + b0, v.status + b0, sizeof(int) * nb, cudaMemcpyDeviceToHost, h->copy_stream));
+                if (iters) CUDA_TRY(cudaMemcpyAsync(iters + b0, v.iters + b0, sizeof(int) * nb, cudaMemcpyDeviceToHost, h->copy_stream));
+            }
+            h->state_zero = false; h->mem_zero = false; h->state_in_im = true;
+            CUDA_TRY(cudaStreamSynchronize(h->copy_stream));
+            CUDA_TRY(cudaStreamSynchronize(h->stream));
+        } else {
+            cudaError_t e = launch_solve(h, k, v, h->stream);
+            if (e != cudaSuccess) throw CudaFail{e, "solve kernel launch"};
+            const size_t nb = static_cast<size_t>(h->B);
+            if (X) CUDA_TRY(cudaMemcpyAsync(X, h->Xsol.p, sizeof(double) * sxN * nb, cudaMemcpyDeviceToHost, h->stream));
+            if (U) CUDA_TRY(cudaMemcpyAsync(U, h->Usol.p, sizeof(double) * suN * nb, cudaMemcpyDeviceToHost, h->stream));
+            CUDA_TRY(cudaMemcpyAsync(status, h->status.p, sizeof(int) * nb, cudaMemcpyDeviceToHost, h->stream));
+            if (iters) CUDA_TRY(cudaMemcpyAsync(iters, h->iters.p, sizeof(int) * nb, cudaMemcpyDeviceToHost, h->stream));
+            CUDA_TRY(cudaStreamSynchronize(h->stream));
+        }
+        for (int b = 0; b < h->B; ++b) if (status[b] != 0) return 1;
         return 0;
     });
 }

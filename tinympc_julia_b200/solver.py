@@ -141,6 +141,24 @@ class TinyMPCBatchSolver:
     def synchronize(self):
         _chk(_lib.load().tmpc_batch_synchronize(self._h), "synchronize failed")
 
+    def solve_host(self, x0=None, *, cold: bool = False, chunks: int = 0, want_states: bool = True):
+        """set_x0 (+ reset) + solve + get_solution + status in one call, pipelined over instance chunks
+        (tmpc_batch_solve_host).  Returns (ret, Solution, status[B], iters[B]); ret as ``solve``."""
+        n, m, N, B = self.nx, self.nu, self.N, self.B
+        x0p = None
+        if x0 is not None:
+            x0a = _mat(x0, (n, B))
+            x0p = _dp(x0a)
+        X = np.empty((n, N, B), order="F") if want_states else None
+        U = np.empty((m, N - 1, B), order="F")
+        st = np.zeros(B, dtype=np.int32)
+        it = np.zeros(B, dtype=np.int32)
+        ret = _lib.load().tmpc_batch_solve_host(self._h, x0p, int(bool(cold)), _dp(X) if X is not None else None, _dp(U),
+                                                st.ctypes.data_as(_IP), it.ctypes.data_as(_IP), int(chunks))
+        if ret not in (0, 1):
+            raise TinyMPCError(f"solve_host failed with status {ret}: {_lib.last_error()}")
+        return ret, Solution(states=X, controls=U), st, it
+
     def rollout_async(self, nsteps: int, x_ref_long_ptr: int = 0, status_out_ptr: int = 0, iters_out_ptr: int = 0, stream: int = 0):
         _chk(_lib.load().tmpc_batch_rollout_async(self._h, int(nsteps), C.c_void_p(x_ref_long_ptr), C.c_void_p(status_out_ptr),
                                                   C.c_void_p(iters_out_ptr), C.c_void_p(stream)), "rollout failed")
