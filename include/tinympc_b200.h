@@ -210,6 +210,9 @@ void* tmpc_batch_device_ptr(tmpc_batch* h, int which);
  * iters_out / status_out: optional device int arrays of nsteps x B (step-major). */
 int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_long,
                              int* d_status_out, int* d_iters_out, void* cuda_stream);
+/* 1 (default): where the TMEM kernel applies, tmpc_batch_rollout_async is ONE launch that keeps each instance's ADMM
+ * state on chip across its MPC steps; 0: one solve + record + plant-step launch per step (any kernel). */
+int tmpc_batch_set_rollout_fused(tmpc_batch* h, int fused);
 
 /* Current x0 of every instance (after a rollout: the plant state reached), nx x B.  `device_dst` != 0: dst is a device
  * pointer on the batch's device (device-to-device copy), else a host buffer. */

@@ -36,6 +36,20 @@ bool tmem_kernel_supports(const BatchView& bv, const AdmmSettings& st);
 cudaError_t launch_admm_tmem(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms,
                              cudaStream_t stream);
 
+// Fused closed loop on the TMEM kernel: every instance runs `nsteps` MPC steps (solve -> apply znew(:,0) -> plant step ->
+// slide the reference window -> next solve) on the sub-warp that owns it, its ADMM state staying on chip between steps.
+// bv.Xref / bv.xref_stride describe the LONG per-instance reference (nx x (N + nsteps - 1)) when `slide` is set.
+struct RolloutArgs {
+    int nsteps;
+    int cold;               // carried state is logically zero (fresh / reset batch)
+    int slide;
+    double* x0_rw;          // plant state nx x B (the same memory as bv.x0)
+    int* status_out;        // [nsteps][B], may be null
+    int* iters_out;
+};
+cudaError_t launch_admm_tmem_rollout(const BatchView& bv, const AdmmSettings& st, const RolloutArgs& ra, int* counter,
+                                     int num_sms, cudaStream_t stream);
+
 // ---- the same design with TWO instances per lane and one resident double per element (admm_tmem2.cu): 16 instances
 // per warp, 128 per SM.  Same applicability as the TMEM kernel; N is limited to 21 for nx = 12.
 bool tmem2_kernel_supports(const BatchView& bv, const AdmmSettings& st);

@@ -56,6 +56,13 @@ struct QuadParams {
     double dua_thresh;      // dual residual passes    <=>  |v - vnew| <= dua_thresh  (largest a with fl(rho a) < tol)
     int* counter;           // instance queue
     int off_consts, off_bounds, off_refs, off_warp0, warp_stride;   // shared-memory carve-up, in doubles
+    // fused closed loop (ROLL): every instance runs `nsteps` MPC steps on the sub-warp that owns it
+    int nsteps;             // MPC steps per instance
+    int cold_install;       // the batch was reset: instances start from zeros instead of their carried block
+    int slide;              // the reference window (per-instance Xref, REFS = 2) moves one column per step
+    double* x0_rw;          // plant state, nx x B: read at install, written back after the last step
+    int* status_out;        // [nsteps][B] per-step solve status / iteration count (may be null)
+    int* iters_out;
 };
 
 
@@ -66,7 +73,7 @@ struct QuadParams {
 
 // REFS: 0 = no references (Xref = Uref = 0), 1 = references shared by all instances (staged in shared memory as
 // the products the linear cost needs), 2 = per-instance references read through the read-only path.
-template <int NX, int NU, bool COLD, int REFS>
+template <int NX, int NU, bool COLD, int REFS, bool ROLL = false>
 __global__ void __launch_bounds__(kQWarps * 32, 1)
 admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ AdmmSettings st,
                  const __grid_constant__ QuadParams qp) {
@@ -194,8 +201,56 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     double* sblk = bv.state_im + sub;                 // block of the lane's instance, + sub
     const double* xref_g = nullptr;                   // REFS == 2 only
     const double* uref_g = nullptr;
+    // fused closed loop (ROLL): MPC step of the lane's instance; cont = the instance carries on from its previous
+    // step with its state on chip; fix = that step converged, so the carried previous slacks are the lagging copies
+    // parked in the instance's block, to be put in place after the first backward sweep (which needs vnew, via q)
+    int step = 0;
+    bool cont = false, fix = false;
+    static_assert(!ROLL || !COLD, "the fused closed loop takes the cold start as a run-time flag");
 
     for (;;) {
+        // =====================================================================================================
+        // ROLL: step transition of finished solves (examples/cartpole_example_mpc.jl:35-51): record the step, drive the
+        // plant with the first control of the solution, x <- (A x + B znew(:,0)) + f, and either start the next
+        // solve on the state left on chip or fall through to the write-out below after the last step.
+        // Warp-uniform because of the shuffles; lanes whose solve is not finished ignore the results.
+        // =====================================================================================================
+        if (ROLL && __any_sync(kAll, fin && valid)) {
+            const bool tr = fin && valid;
+            if (tr && sub == 0) {
+                const size_t o = static_cast<size_t>(step) * bv.B + b;
+                if (qp.status_out) qp.status_out[o] = status;
+                if (qp.iters_out) qp.iters_out[o] = iter;
+            }
+            double zz0 = 0.0;
+            if (urow) zz0 = s_yz[lane * 2 + 1];           // znew of knot 0, own input row
+            double xs[NX], u0[NU];
+#pragma unroll
+            for (int k = 0; k < NX; ++k) xs[k] = shfl_dq(x0r[k / 4], (k % 4) * kQInst + inst);
+#pragma unroll
+            for (int k = 0; k < NU; ++k) u0[k] = shfl_dq(zz0, k * kQInst + inst);
+#pragma unroll
+            for (int r = 0; r < RX; ++r) {
+                double s1 = 0.0, s2 = 0.0;
+#pragma unroll
+                for (int k = 0; k < NX; ++k) s1 = fma(sc[CL::A_rm + (r * 4 + sub) * NX + k], xs[k], s1);
+#pragma unroll
+                for (int k = 0; k < NU; ++k) s2 = fma(sc[CL::B_rm + (r * 4 + sub) * NU + k], u0[k], s2);
+                const double xn = dadd(dadd(s1, s2), fr_f[r]);
+                if (tr) x0r[r] = xn;
+            }
+            if (tr) {
+                step += 1;
+                if (step < qp.nsteps) {
+                    fix = (status == 0);
+                    cont = true; fin = false; iter = 0; first = true; status = 1;
+                    if (REFS == 2 && qp.slide && xref_g) xref_g += NX;
+                } else {
+#pragma unroll
+                    for (int r = 0; r < RX; ++r) qp.x0_rw[static_cast<size_t>(b) * NX + r * 4 + sub] = x0r[r];
+                }
+            }
+        }
         // =====================================================================================================
         // write-out of finished instances + refill from the queue.  Warp-uniform (tcgen05.ld/st are .aligned):
         // every lane walks the knot points, lanes whose instance is not finished store back what they loaded.
@@ -230,11 +285,11 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             nb = __shfl_sync(kAll, nb, inst);
             const bool nvalid = fin && nb < bv.B;
             const size_t nbb = nvalid ? static_cast<size_t>(nb) : 0;
-            const bool warm = !COLD && nvalid;
+            const bool warm = !COLD && nvalid && !(ROLL && qp.cold_install);
             double* const nblk = bv.state_im + nbb * static_cast<size_t>(bv.state_im_stride) + sub;
 
             double* Xs = bv.Xsol + bb * nxN + sub;
-            const double* xr_old = (REFS == 2 && bv.Xref) ? bv.Xref + bb * bv.xref_stride + sub : nullptr;
+            const double* xr_old = ROLL ? xref_g : ((REFS == 2 && bv.Xref) ? bv.Xref + bb * bv.xref_stride + sub : nullptr);
             double* op = ob;                              // knot i of the old / new instance: + 3 NX i ; g +0, v +NX, q +2 NX
             const double* np = nblk;
             const bool wr_v = wr && unconv;
@@ -289,6 +344,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 b = nvalid ? nb : 0;
                 sblk = nblk;
                 valid = nvalid; iter = 0; first = true; status = 1; fin = false;
+                step = 0; cont = false; fix = false;
                 if (REFS == 2) {
                     xref_g = bv.Xref ? bv.Xref + nbb * bv.xref_stride + sub : nullptr;      // + i NX + 4 r
                     uref_g = (bv.Uref && urow) ? bv.Uref + nbb * bv.uref_stride + sub : nullptr;   // + i NU
@@ -326,7 +382,11 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             double qcar[RX];                              // carried q of the first sweep of a warm-started solve
 #pragma unroll
             for (int r = 0; r < RX; ++r) qcar[r] = 0.0;
-            const bool ldq = !COLD && first && valid;
+            const bool ldq = !COLD && first && valid && !(ROLL && (cont || qp.cold_install));
+            // ROLL, first sweep of a solve that continues on chip: q is what update_linear_cost left at the end of the
+            // previous step, i.e. built from the slacks and duals in Tensor Memory and the PREVIOUS reference window
+            const bool usecar = first && !(ROLL && cont);
+            const double* xref_b = (ROLL && REFS == 2 && cont && first && qp.slide && xref_g) ? xref_g - NX : xref_g;
             const double* qp_g = sblk + 2 * NX + (N - 2) * 3 * NX;          // q of knot N-2; row r: + 4 r
             if (ldq) {
 #pragma unroll
@@ -340,7 +400,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 double cq[RX];
                 if (REFS == 2) {
 #pragma unroll
-                    for (int r = 0; r < RX; ++r) cq[r] = -dmul(xref_g ? __ldg(xref_g + i * NX + r * 4) : 0.0, fr_Qd[r]);
+                    for (int r = 0; r < RX; ++r) cq[r] = -dmul(xref_b ? __ldg(xref_b + i * NX + r * 4) : 0.0, fr_Qd[r]);
                 }
                 // all-gather p_{i+1} among the 4 lanes of the instance
                 double pb[NX];
@@ -384,7 +444,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                     double q;
                     if (REFS == 0) q = dmul(nrho, dsub(vv, gg));
                     else q = dsub(REFS == 1 ? cqs[r] : cq[r], dmul(rho, dsub(vv, gg)));
-                    q_own[r] = first ? qcar[r] : q;
+                    q_own[r] = usecar ? qcar[r] : q;
                 }
                 if (i > 0) {
                     tm_load<W>(tbase + (i - 1) * W, w);
@@ -419,6 +479,35 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             }
             __syncwarp();
             if (urow) sts1<0>(a_myrt, t_def);
+        }
+
+        // ROLL: the previous step of some instance converged, so its carried previous slacks are the lagging copies
+        // the last sweep parked in its block (admm.cpp:375 returns before :379-380).  The backward sweep above
+        // was the last reader of vnew; put v_old / z_old in place for the dual residual of this solve's first iteration.
+        if (ROLL && __any_sync(kAll, fix)) {
+            const double* vl = sblk + NX;                 // v of knot i: + 3 NX i ; row r: + 4 r
+            for (int i = 0; i < N; ++i) {
+                uint32_t w[W];
+                tm_load<W>(tbase + i * W, w);
+                double vo[RX];
+#pragma unroll
+                for (int r = 0; r < RX; ++r) vo[r] = fix ? vl[r * 4] : 0.0;
+                tm_wait_ld<W>(w);
+#pragma unroll
+                for (int r = 0; r < RX; ++r) {
+                    w[2 * (RX + r)] = fix ? lo32(vo[r]) : w[2 * (RX + r)];
+                    w[2 * (RX + r) + 1] = fix ? hi32(vo[r]) : w[2 * (RX + r) + 1];
+                }
+                tm_store<W>(tbase + i * W, w);
+                vl += 3 * NX;
+            }
+            if (fix && urow) {
+                const double* zl = sblk + IB + NU;        // z of knot i: + 3 NU i
+                for (int i = 0; i < N - 1; ++i) { s_yz[(i * 32 + lane) * 2 + 1] = *zl; zl += 3 * NU; }
+            }
+            fix = false;
+            tm_wait_st();
+            __syncwarp();
         }
 
         // =====================================================================================================
@@ -677,9 +766,9 @@ int refs_mode(const BatchView& bv) {
     return (xs && us) ? 1 : 2;
 }
 
-template <int NX, int NU, bool COLD, int REFS>
+template <int NX, int NU, bool COLD, int REFS, bool ROLL = false>
 cudaError_t launch_q(const BatchView& bv, const AdmmSettings& st, const QPlan& pl, int num_sms, cudaStream_t stream) {
-    auto kern = admm_tmem_kernel<NX, NU, COLD, REFS>;
+    auto kern = admm_tmem_kernel<NX, NU, COLD, REFS, ROLL>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(pl.smem_bytes));
     if (e != cudaSuccess) return e;
     const int per_cta = kQWarps * kQInst;
@@ -710,7 +799,33 @@ cudaError_t launch_shape(const BatchView& bv, const AdmmSettings& st, int cold, 
     return launch_q<NX, NU, false, 2>(bv, st, pl, num_sms, stream);
 }
 
+template <int NX, int NU>
+cudaError_t launch_shape_roll(const BatchView& bv, const AdmmSettings& st, const RolloutArgs& ra, int* counter,
+                              int num_sms, cudaStream_t stream) {
+    QPlan pl;
+    const int refs = refs_mode(bv);
+    if (!make_qplan<NX, NU>(bv.N, refs, pl)) return cudaErrorInvalidConfiguration;
+    pl.qp.counter = counter;
+    pl.qp.pri_thresh = st.abs_pri_tol;
+    pl.qp.dua_thresh = dual_threshold_q(bv.rho, st.abs_dua_tol);
+    pl.qp.nsteps = ra.nsteps; pl.qp.cold_install = ra.cold; pl.qp.slide = ra.slide;
+    pl.qp.x0_rw = ra.x0_rw; pl.qp.status_out = ra.status_out; pl.qp.iters_out = ra.iters_out;
+    cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(int), stream);
+    if (e != cudaSuccess) return e;
+    if (refs == 0) return launch_q<NX, NU, false, 0, true>(bv, st, pl, num_sms, stream);
+    if (refs == 1) return launch_q<NX, NU, false, 1, true>(bv, st, pl, num_sms, stream);
+    return launch_q<NX, NU, false, 2, true>(bv, st, pl, num_sms, stream);
+}
+
 }  // namespace
+
+cudaError_t launch_admm_tmem_rollout(const BatchView& bv, const AdmmSettings& st, const RolloutArgs& ra, int* counter,
+                                     int num_sms, cudaStream_t stream) {
+    if (bv.B <= 0 || ra.nsteps <= 0) return cudaSuccess;
+    if (bv.nx == 12 && bv.nu == 4) return launch_shape_roll<12, 4>(bv, st, ra, counter, num_sms, stream);
+    if (bv.nx == 4 && bv.nu == 1) return launch_shape_roll<4, 1>(bv, st, ra, counter, num_sms, stream);
+    return cudaErrorNotSupported;
+}
 
 bool tmem_kernel_supports(const BatchView& bv, const AdmmSettings& st) {
     if (st.en_state_soc || st.en_input_soc || st.en_state_linear || st.en_input_linear) return false;

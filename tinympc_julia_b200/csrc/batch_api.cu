@@ -69,6 +69,7 @@ struct tmpc_batch {
     tmpc::HostMats hm;
     tmpc::AdmmSettings st{};
     int kernel_pref = TMPC_KERNEL_AUTO;
+    bool rollout_fused = true;                // tmpc_batch_rollout_async: one fused launch where the TMEM kernel applies
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr;       // tmpc_batch_solve_host: result chunks go home while the next chunk solves
     std::vector<cudaEvent_t> chunk_done;
@@ -711,6 +712,25 @@ int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_lo
         const int k = resolve_kernel(h);
         if (k < 0) { set_error("requested kernel does not support this problem"); return TMPC_ERR_STATE; }
         const long long ref_len = static_cast<long long>(h->nx) * (h->N + nsteps - 1);
+        if (k == TMPC_KERNEL_TMEM && h->st.max_iter > 0 && h->rho > 0.0 && h->rollout_fused) {
+            // one launch: every instance runs all its steps on the sub-warp that owns it (admm_tmem.cu, ROLL)
+            tmpc::BatchView v = make_view(h);
+            if (d_x_ref_long) { v.Xref = d_x_ref_long; v.xref_stride = ref_len; }
+            if (tmpc::tmem_kernel_supports(v, h->st)) {
+                if (!h->state_im.p) { h->state_im.alloc(static_cast<size_t>(v.state_im_stride) * h->B); v.state_im = h->state_im.p; }
+                if (!h->state_zero && !h->state_in_im) {
+                    cudaError_t ce = tmpc::launch_state_convert(v, true, s);
+                    if (ce != cudaSuccess) throw CudaFail{ce, "state conversion"};
+                    h->launches += 1;
+                }
+                tmpc::RolloutArgs ra{nsteps, h->state_zero ? 1 : 0, d_x_ref_long ? 1 : 0, h->x0.p, d_status_out, d_iters_out};
+                cudaError_t e = tmpc::launch_admm_tmem_rollout(v, h->st, ra, h->counter.p, h->num_sms, s);
+                if (e != cudaSuccess) throw CudaFail{e, "fused rollout launch"};
+                h->launches += 1;
+                h->state_zero = false; h->mem_zero = false; h->state_in_im = true;
+                return TMPC_OK;
+            }
+        }
         for (int step = 0; step < nsteps; ++step) {
             tmpc::BatchView v = make_view(h);
             if (d_x_ref_long) { v.Xref = d_x_ref_long + static_cast<size_t>(h->nx) * step; v.xref_stride = ref_len; }
@@ -728,6 +748,12 @@ int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_lo
         }
         return TMPC_OK;
     });
+}
+
+int tmpc_batch_set_rollout_fused(tmpc_batch* h, int fused) {
+    if (!h) return TMPC_ERR_DIM;
+    h->rollout_fused = fused != 0;
+    return TMPC_OK;
 }
 
 int tmpc_batch_get_x0(tmpc_batch* h, void* dst, int device_dst) {
