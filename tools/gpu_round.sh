@@ -9,6 +9,9 @@ timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smok
 timeout 600 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"; cat gpurun_out/bench.json; tail -5 gpurun_out/bench.err
 timeout 300 python bench.py --workload quadrotor_hard --no-cpu > gpurun_out/bench_hard.json 2> gpurun_out/bench_hard.err; echo "bench hard rc=$?"; cat gpurun_out/bench_hard.json
 timeout 300 python bench.py --kernel 2 --no-cpu --steps 10 > gpurun_out/bench_subwarp.json 2> gpurun_out/bench_subwarp.err; echo "bench subwarp rc=$?"; timeout 300 python bench.py --kernel 1 --no-cpu --steps 10 > gpurun_out/bench_thread.json 2> gpurun_out/bench_thread.err; echo "bench thread rc=$?"
+timeout 300 python bench.py --kernel 4 --no-cpu --steps 20 > gpurun_out/bench_tmem2.json 2> gpurun_out/bench_tmem2.err; echo "bench tmem2 rc=$?"
+timeout 300 python bench.py --kernel 4 --no-cpu --steps 20 --workload quadrotor_hard > gpurun_out/bench_tmem2_hard.json 2> gpurun_out/bench_tmem2_hard.err
+timeout 600 python tools/gpu_rollout.py > gpurun_out/rollout.json 2> gpurun_out/rollout.err; echo "rollout rc=$?"; cat gpurun_out/rollout.json
 timeout 600 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "bench ref rc=$?"; cat gpurun_out/bench_ref.json
 timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/plain.log 2>&1 && \
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_launch.log 2>&1
