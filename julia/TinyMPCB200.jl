@@ -13,7 +13,7 @@ using Libdl
 
 export TinyMPCBatchSolver, setup_batch, set_x0, set_x_ref, set_u_ref, set_bound_constraints, set_linear_constraints,
        set_cone_constraints, set_cache_terms, update_settings, reset!, solve, get_solution, get_status,
-       set_kernel, rollout!, destroy!
+       set_kernel, rollout!, solve_host, destroy!
 
 const lib_path = joinpath(dirname(@__DIR__), "lib", "libtinympc_jl." * Libdl.dlext)   # as reference src/TinyMPC.jl:12-13
 
@@ -133,6 +133,22 @@ function get_solution(s::TinyMPCBatchSolver)
     check(ccall((:tmpc_batch_get_states, lib_path), Int32, (Ptr{Cvoid}, Ptr{Float64}), s.handle, X), "Failed to get states")
     check(ccall((:tmpc_batch_get_controls, lib_path), Int32, (Ptr{Cvoid}, Ptr{Float64}), s.handle, U), "Failed to get controls")
     return (states = X, controls = U)
+end
+
+"""
+One call on host arrays: set_x0 (+ cold start) + solve + get_solution + get_status, the batch cut into chunks so that
+the solution of one chunk crosses PCIe while the next chunk solves (tmpc_batch_solve_host).
+Returns (ret, (states, controls), status, iterations); `ret` as `solve`.
+"""
+function solve_host(s::TinyMPCBatchSolver, x0::Matrix{Float64}; cold::Bool = false, chunks::Integer = 0)
+    X = Array{Float64}(undef, s.nx, s.N, s.B)
+    U = Array{Float64}(undef, s.nu, s.N - 1, s.B)
+    st = Vector{Int32}(undef, s.B); it = Vector{Int32}(undef, s.B)
+    ret = ccall((:tmpc_batch_solve_host, lib_path), Int32,
+                (Ptr{Cvoid}, Ptr{Float64}, Int32, Ptr{Float64}, Ptr{Float64}, Ptr{Int32}, Ptr{Int32}, Int32),
+                s.handle, x0, Int32(cold), X, U, st, it, Int32(chunks))
+    ret in (0, 1) || error("solve_host failed with status $ret")
+    return ret, (states = X, controls = U), st, it
 end
 
 """
