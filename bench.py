@@ -38,6 +38,16 @@ import time
 
 import numpy as np
 
+# The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner on stdout during
+# init), so everything else is sent to stderr: fd 1 is duplicated for the final line and then pointed at fd 2.
+_JSON_OUT = os.fdopen(os.dup(1), "w")
+os.dup2(2, 1)
+
+
+def emit(line: dict) -> None:
+    _JSON_OUT.write(json.dumps(line) + "\n")
+    _JSON_OUT.flush()
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 for p in (ROOT, os.path.join(ROOT, "tests")):
     if p not in sys.path:
@@ -237,7 +247,7 @@ def run_reference(args, rank, world):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_name(args):
@@ -447,7 +457,7 @@ def run_gpu(args, rank, local_rank, world):
                                 "path": "set_x0 -> solve_mpc -> get_controls through the reference's own symbols, B=1"}
 
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
