@@ -214,3 +214,63 @@ def test_solve_host_pipelined_matches_stepwise(orc):
     r, s1, st1, it1 = sol.solve_host(c["x0"], cold=True)
     assert np.array_equal(it1, want["iters"][0]) and np.array_equal(st1, want["ret"][0])
     np.testing.assert_allclose(s1.controls, want["U"], rtol=1e-5, atol=1e-6)
+
+
+def _device_rollout(sol, nsteps, xlong=None, fused=True):
+    import ctypes as C
+    import torch
+    from tinympc_julia_b200 import _lib
+    B = sol.B
+    assert _lib.load().tmpc_batch_set_rollout_fused(sol._h, 1 if fused else 0) == 0
+    st_out = torch.full((nsteps, B), -1, dtype=torch.int32, device="cuda")
+    it_out = torch.full((nsteps, B), -1, dtype=torch.int32, device="cuda")
+    xl = None
+    if xlong is not None:     # (nx, cols, B) Fortran == (B, cols, nx) C-contiguous
+        xl = torch.from_numpy(np.ascontiguousarray(np.asfortranarray(xlong).transpose(2, 1, 0))).cuda()
+    torch.cuda.synchronize()
+    sol.rollout_async(nsteps, xl.data_ptr() if xl is not None else 0, st_out.data_ptr(), it_out.data_ptr(), 0)
+    sol.synchronize()
+    xf = torch.empty((B, sol.nx), dtype=torch.float64, device="cuda")
+    assert _lib.load().tmpc_batch_get_x0(sol._h, C.cast(xf.data_ptr(), C.c_void_p), 1) == 0
+    return st_out.cpu().numpy(), it_out.cpu().numpy(), xf.cpu().numpy().T
+
+
+def test_fused_rollout_constant_references(orc):
+    """Fused closed loop without a sliding window: no references (cartpole, quadrotor hover) and shared references;
+    fused and launch-sequence forms against the oracle's closed loop."""
+    for c, nsteps in ((cases.cartpole_batch(40), 12), (cases.quadrotor_batch(33, hard=True, max_iter=30), 9),
+                      (cases.GOLDEN_CASES["quadrotor_hover"](), 5)):
+        c["nsteps"] = nsteps
+        want = cases.run_checker(c, orc, nthreads=4)
+        for fused in (True, False):
+            sol = cases.make_cuda_solver(c, kernel=TMEM)
+            if c["ref_mode"] == 1:
+                if c["Xref"] is not None:
+                    t.set_x_ref(sol, c["Xref"])
+                if c["Uref"] is not None:
+                    t.set_u_ref(sol, c["Uref"])
+            t.set_x0(sol, c["x0"])
+            st, it, xf = _device_rollout(sol, nsteps, fused=fused)
+            assert np.array_equal(it, want["iters"]) and np.array_equal(st, want["ret"]), f"fused={fused}"
+            np.testing.assert_allclose(xf, want["x_final"], rtol=1e-5, atol=1e-6)
+            X, U = t.get_solution(sol)
+            np.testing.assert_allclose(U, want["U"], rtol=1e-5, atol=1e-6)
+
+
+def test_fused_rollout_split_in_two_launches(orc):
+    """A rollout continued by a second call: the instances leave the chip after the first launch (write-out with the
+    lagging slacks of converged solves) and are warm-installed by the second.  Includes solves that stop at max_iter."""
+    n1, n2, B = 6, 8, 24
+    c = cases.quadrotor_closed_loop(B, n1 + n2)
+    c["x0"] = np.asfortranarray(c["x0"] * 4.0)
+    c["max_iter"] = 12
+    want = cases.run_checker(c, orc, nthreads=4)
+    assert (want["ret"] != 0).any() and (want["ret"] == 0).any()
+    N = c["N"]
+    sol = cases.make_cuda_solver(c, kernel=TMEM)
+    t.set_x0(sol, c["x0"])
+    st1, it1, _ = _device_rollout(sol, n1, xlong=c["Xref"][:, :N + n1 - 1, :])
+    st2, it2, xf = _device_rollout(sol, n2, xlong=c["Xref"][:, n1:n1 + N + n2 - 1, :])
+    assert np.array_equal(np.vstack([it1, it2]), want["iters"])
+    assert np.array_equal(np.vstack([st1, st2]), want["ret"])
+    np.testing.assert_allclose(xf, want["x_final"], rtol=1e-5, atol=1e-6)

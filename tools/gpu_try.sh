@@ -1,3 +1,3 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -15 gpurun_out/pytest_gpu.log
-timeout 600 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"; cat gpurun_out/bench.json | python -c "import sys,json; d=json.loads(sys.stdin.read()); print(d['value'], d['roofline']['frac'], d['e2e'])"; tail -5 gpurun_out/bench.err
+timeout 900 python -m pytest tests -m gpu -x -q -k "rollout" > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -30 gpurun_out/pytest_gpu.log
+timeout 300 python bench.py --steps 5 --no-cpu > gpurun_out/b.json 2>gpurun_out/b.err; echo "bench rc=$? lines=$(wc -l < gpurun_out/b.json)"
