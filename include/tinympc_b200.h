@@ -169,6 +169,16 @@ int tmpc_batch_set_cone_constraints_jl(tmpc_batch* h, const int* Acu, const int*
 /* tols[2] = {abs_pri_tol, abs_dua_tol}; ints[8] = {max_iter, check_termination, en_state_bound,
  * en_input_bound, en_state_soc, en_input_soc, en_state_linear, en_input_linear} */
 int tmpc_batch_get_settings(tmpc_batch* h, double* tols, int* ints);
+/* Per-instance dynamics: B different systems in one batch.  The setup the reference runs once per
+ * solver (tiny_setup + tiny_precompute_and_set_cache, tiny_api.cpp:21-137, :244-318) runs on the device, one thread per
+ * instance, operation by operation as the host path does (the Riccati stop rule makes the cache only 1e-5-converged, so
+ * iteration-count parity needs the same arithmetic).  A nx x nx x B, Bdyn nx x nu x B, f nx x B or NULL, Q nx x nx [x B],
+ * R nu x nu [x B] (qr_batch = 1 shared / B per instance); host pointers, Julia layout; rho as given to create.  Later
+ * solves use the thread kernel with coalesced per-instance operands; nx <= 12, nu <= 4. */
+int tmpc_batch_set_instance_dynamics(tmpc_batch* h, const double* A, const double* Bdyn, const double* f, const double* Q,
+                                     const double* R, int qr_batch);
+int tmpc_batch_get_instance_cache(tmpc_batch* h, int b, double* Kinf, double* Pinf, double* Quu_inv, double* AmBKt,
+                                  double* APf, double* BPf);
 int tmpc_batch_set_cache_terms(tmpc_batch* h, const double* Kinf, const double* Pinf,
                                const double* Quu_inv, const double* AmBKt);
 int tmpc_batch_get_cache_terms(tmpc_batch* h, double* Kinf, double* Pinf, double* Quu_inv, double* AmBKt,

@@ -13,7 +13,7 @@ using Libdl
 
 export TinyMPCBatchSolver, setup_batch, set_x0, set_x_ref, set_u_ref, set_bound_constraints, set_linear_constraints,
        set_cone_constraints, set_cache_terms, update_settings, reset!, solve, get_solution, get_status,
-       set_kernel, rollout!, solve_host, destroy!
+       set_kernel, rollout!, solve_host, set_instance_dynamics, destroy!
 
 const lib_path = joinpath(dirname(@__DIR__), "lib", "libtinympc_jl." * Libdl.dlext)   # as reference src/TinyMPC.jl:12-13
 
@@ -133,6 +133,18 @@ function get_solution(s::TinyMPCBatchSolver)
     check(ccall((:tmpc_batch_get_states, lib_path), Int32, (Ptr{Cvoid}, Ptr{Float64}), s.handle, X), "Failed to get states")
     check(ccall((:tmpc_batch_get_controls, lib_path), Int32, (Ptr{Cvoid}, Ptr{Float64}), s.handle, U), "Failed to get controls")
     return (states = X, controls = U)
+end
+
+"""
+Per-instance dynamics: A (nx, nx, B), Bdyn (nx, nu, B), f (nx, B), Q (nx, nx[, B]), R (nu, nu[, B]); the LQR cache of every
+instance is computed on the device (tmpc_batch_set_instance_dynamics).
+"""
+function set_instance_dynamics(s::TinyMPCBatchSolver, A::Array{Float64,3}, Bdyn::Array{Float64,3}, f::Matrix{Float64},
+                               Q::Array{Float64}, R::Array{Float64})
+    qb = ndims(Q) == 3 ? s.B : 1
+    check(ccall((:tmpc_batch_set_instance_dynamics, lib_path), Int32,
+                (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}, Int32),
+                s.handle, A, Bdyn, f, Q, R, Int32(qb)), "Failed to set per-instance dynamics")
 end
 
 """

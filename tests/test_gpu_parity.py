@@ -9,6 +9,7 @@ import pytest
 
 import cases
 import tinympc_julia_b200 as t
+from tinympc_julia_b200 import problems as problems_mod
 
 pytestmark = pytest.mark.gpu
 
@@ -274,3 +275,51 @@ def test_fused_rollout_split_in_two_launches(orc):
     assert np.array_equal(np.vstack([it1, it2]), want["iters"])
     assert np.array_equal(np.vstack([st1, st2]), want["ret"])
     np.testing.assert_allclose(xf, want["x_final"], rtol=1e-5, atol=1e-6)
+
+
+def test_per_instance_dynamics(orc):
+    """B different systems in one batch.  The device setup kernel must reproduce the host cache bit
+    for bit (same operation order), and every instance must solve exactly like a single-instance reference solver set up
+    with that instance's A, B, f, Q, R."""
+    import ctypes as C
+    import dataclasses
+    from tinympc_julia_b200 import _lib
+    lib = _lib.load()
+    for base, B, scale in ((problems_mod.quadrotor(), 9, 0.3), (problems_mod.cartpole(), 7, 0.5)):
+        rng = np.random.default_rng(17)
+        n, m, N = base.nx, base.nu, 20 if base.nx == 12 else 15
+        A = np.stack([base.A * (1.0 + 0.05 * rng.uniform(-1, 1, base.A.shape)) for _ in range(B)], axis=2)
+        Bm = np.stack([base.B * (1.0 + 0.2 * rng.uniform(-1, 1, base.B.shape)) for _ in range(B)], axis=2)
+        f = 0.01 * rng.uniform(-1, 1, (n, B))
+        Q = np.stack([np.diag(np.diag(base.Q) * (1.0 + 0.3 * rng.uniform(-1, 1, n))) for _ in range(B)], axis=2)
+        R = np.stack([np.diag(np.diag(base.R) * (1.0 + 0.3 * rng.uniform(-1, 1, m))) for _ in range(B)], axis=2)
+        x0 = np.asfortranarray(scale * rng.uniform(-1, 1, (n, B)))
+        c = cases._base(base, N, bounds=base.bounds(N), x0=x0, max_iter=60)
+        sol = cases.make_cuda_solver(c)
+        t.set_instance_dynamics(sol, A, Bm, f, Q, R)
+        assert sol.kernel == THREAD
+        t.set_x0(sol, x0)
+        t.solve(sol)
+        st, it = sol.status()
+        X, U = t.get_solution(sol)
+        for b in range(B):
+            sb = dataclasses.replace(base, A=np.asfortranarray(A[:, :, b]), B=np.asfortranarray(Bm[:, :, b]),
+                                     f=f[:, b].copy(), Q=np.asfortranarray(Q[:, :, b]), R=np.asfortranarray(R[:, :, b]))
+            cb = cases._base(sb, N, bounds=sb.bounds(N), x0=np.asfortranarray(x0[:, b:b + 1]), max_iter=60)
+            want = cases.run_checker(cb, orc)
+            assert it[b] == want["iters"][0, 0] and st[b] == want["ret"][0, 0], f"instance {b}"
+            np.testing.assert_allclose(X[:, :, b], want["X"][:, :, 0], rtol=1e-5, atol=1e-6)
+            np.testing.assert_allclose(U[:, :, b], want["U"][:, :, 0], rtol=1e-5, atol=1e-6)
+            # device setup kernel == host setup (tmpc_compute_cache), bit for bit
+            dev = [np.zeros((m, n), order="F"), np.zeros((n, n), order="F"), np.zeros((m, m), order="F"),
+                   np.zeros((n, n), order="F"), np.zeros(n), np.zeros(m)]
+            dp = lambda a: a.ctypes.data_as(C.POINTER(C.c_double))
+            assert lib.tmpc_batch_get_instance_cache(sol._h, b, *[dp(a) for a in dev]) == 0
+            host = [np.zeros_like(a) for a in dev] + [np.zeros(n), np.zeros(m)]
+            assert lib.tmpc_compute_cache(dp(sb.A), dp(sb.B), dp(np.ascontiguousarray(sb.f)), dp(sb.Q), dp(sb.R), base.rho, n, m,
+                                          *[dp(a) for a in host]) == 0
+            for d, hh in zip(dev, host):
+                assert np.array_equal(d, hh), f"instance {b}: device cache differs from the host cache"
+    # warm start keeps working per instance, and the rollout refuses per-instance dynamics
+    t.set_x0(sol, np.asfortranarray(0.9 * x0))
+    assert t.solve(sol) in (0, 1)

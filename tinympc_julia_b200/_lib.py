@@ -59,6 +59,8 @@ SIGNATURES = {
     "tmpc_batch_reset": (_I, [_V]),
     "tmpc_batch_solve": (_I, [_V]),
     "tmpc_batch_solve_async": (_I, [_V, _V]),
+    "tmpc_batch_set_instance_dynamics": (_I, [_V, _P, _P, _P, _P, _P, _I]),
+    "tmpc_batch_get_instance_cache": (_I, [_V, _I, _P, _P, _P, _P, _P, _P]),
     "tmpc_batch_set_rollout_fused": (_I, [_V, _I]),
     "tmpc_batch_solve_host": (_I, [_V, _P, _I, _P, _P, _IP, _IP, _I]),
     "tmpc_batch_synchronize": (_I, [_V]),

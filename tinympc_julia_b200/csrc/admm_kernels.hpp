@@ -18,8 +18,24 @@ struct HostMats {
     std::vector<double> A, B, f, Kinf, Pinf, Quu_inv, AmBKt, APf, BPf, Qd, Rd;
 };
 
+// ---- per-instance dynamics: every instance has its own A, B, f, Q, R and therefore its own cache.
+// Element-major device arrays [e][ld] (column-major matrix entries e), written by the batched setup kernel
+// (lqr_cache_device.cu) and read coalesced by the thread kernel.
+constexpr int kPerInstanceMaxNx = 12;
+constexpr int kPerInstanceMaxNu = 4;
+struct PerInstanceMats {
+    double *A, *B, *f, *Kinf, *Pinf, *Quu_inv, *AmBKt, *APf, *BPf, *Qd, *Rd;
+};
+// Inputs in the Julia layout (nx x nx x B, ...); q_stride / r_stride = elements between instances (0 = shared Q / R).
+// *fail is set to 1 when a matrix that must be inverted is singular for some instance.
+cudaError_t launch_riccati_cache(int nx, int nu, int B, long long ld, double rho, const double* A, const double* Bdyn,
+                                 const double* f, const double* Q, long long q_stride, const double* R,
+                                 long long r_stride, const PerInstanceMats& out, int* fail, cudaStream_t stream);
+
 // ---- one thread per instance (admm_thread.cu)
 bool thread_kernel_supports(int nx, int nu);
+cudaError_t launch_admm_thread_per_instance(const BatchView& bv, const AdmmSettings& st, const PerInstanceMats& pm,
+                                            cudaStream_t stream);
 cudaError_t launch_admm_thread(const BatchView& bv, const AdmmSettings& st, const HostMats& h, cudaStream_t stream);
 
 // ---- one instance per 4-lane sub-warp, shared-memory resident (admm_subwarp.cu)

@@ -33,6 +33,7 @@ template <int NX, int NU>
 struct MatsConst {           // by-value kernel parameter -> constant bank
     static constexpr int kMaxNx = NX, kMaxNu = NU;
     static constexpr bool kStatic = true;
+    __device__ __forceinline__ const MatsConst& bound(int) const { return *this; }
     double A_[NX * NX], B_[NX * NU], Kinf_[NU * NX], AmBKt_[NX * NX], Quu_inv_[NU * NU], Pinf_[NX * NX];
     double f_[NX], APf_[NX], BPf_[NU], Qd_[NX], Rd_[NU];
     __device__ __forceinline__ int nx() const { return NX; }
@@ -53,6 +54,7 @@ struct MatsConst {           // by-value kernel parameter -> constant bank
 struct MatsGlobal {          // runtime dimensions: uniform loads through the read-only path
     static constexpr int kMaxNx = kThreadKernelMaxNx, kMaxNu = kThreadKernelMaxNu;
     static constexpr bool kStatic = false;
+    __device__ __forceinline__ const MatsGlobal& bound(int) const { return *this; }
     int nx_, nu_;
     const double *A_, *B_, *Kinf_, *AmBKt_, *Quu_inv_, *Pinf_, *f_, *APf_, *BPf_, *Qd_, *Rd_;
     __device__ __forceinline__ int nx() const { return nx_; }
@@ -68,6 +70,32 @@ struct MatsGlobal {          // runtime dimensions: uniform loads through the re
     __device__ __forceinline__ double BPf(int i) const { return __ldg(BPf_ + i); }
     __device__ __forceinline__ double Qd(int i) const { return __ldg(Qd_ + i); }
     __device__ __forceinline__ double Rd(int i) const { return __ldg(Rd_ + i); }
+};
+
+// per-instance dynamics: element-major arrays [e][ld], one coalesced load per operand (bound to the thread's instance)
+template <int NX, int NU>            // NX = 0: run-time dimensions (rolled loops); else compiled-in shape, fully unrolled
+struct MatsPerInstance {
+    static constexpr int kMaxNx = NX ? NX : kPerInstanceMaxNx, kMaxNu = NX ? NU : kPerInstanceMaxNu;
+    static constexpr bool kStatic = NX != 0;
+    int nx_, nu_;
+    long long ld_;
+    PerInstanceMats p_;
+    long long b_;
+    __device__ __forceinline__ MatsPerInstance bound(int b) const { MatsPerInstance m = *this; m.b_ = b; return m; }
+    __device__ __forceinline__ int nx() const { return NX ? NX : nx_; }
+    __device__ __forceinline__ int nu() const { return NX ? NU : nu_; }
+    __device__ __forceinline__ double at(const double* a, int e) const { return __ldg(a + e * ld_ + b_); }
+    __device__ __forceinline__ double A(int i, int k) const { return at(p_.A, k * nx() + i); }
+    __device__ __forceinline__ double B(int i, int k) const { return at(p_.B, k * nx() + i); }
+    __device__ __forceinline__ double Kinf(int i, int k) const { return at(p_.Kinf, k * nu() + i); }
+    __device__ __forceinline__ double AmBKt(int i, int k) const { return at(p_.AmBKt, k * nx() + i); }
+    __device__ __forceinline__ double Quu_inv(int i, int k) const { return at(p_.Quu_inv, k * nu() + i); }
+    __device__ __forceinline__ double Pinf(int i, int k) const { return at(p_.Pinf, k * nx() + i); }
+    __device__ __forceinline__ double f(int i) const { return at(p_.f, i); }
+    __device__ __forceinline__ double APf(int i) const { return at(p_.APf, i); }
+    __device__ __forceinline__ double BPf(int i) const { return at(p_.BPf, i); }
+    __device__ __forceinline__ double Qd(int i) const { return at(p_.Qd, i); }
+    __device__ __forceinline__ double Rd(int i) const { return at(p_.Rd, i); }
 };
 
 // Second-order-cone projection of a 3-block, with the reference's mixed precision: mu and the
@@ -106,12 +134,13 @@ __device__ __forceinline__ void project_halfspaces(double* col, int len, const d
 
 template <class M>
 __global__ void __launch_bounds__(kThreadKernelBlock)
-admm_thread_kernel(const __grid_constant__ M mt, const __grid_constant__ BatchView bv,
+admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ BatchView bv,
                    const __grid_constant__ AdmmSettings st) {
     constexpr int MX = M::kMaxNx, MU = M::kMaxNu;
     constexpr int UNR = M::kStatic ? 64 : 1;   // full unroll for compiled-in shapes, rolled loops otherwise
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= bv.B) return;
+    const auto& mt = mt_param.bound(b);        // per-instance dynamics: operands of THIS instance; else the parameter itself
     const int nx = mt.nx(), nu = mt.nu(), N = bv.N;
     const size_t ld = static_cast<size_t>(bv.ld);
     const double rho = bv.rho;
@@ -382,6 +411,21 @@ cudaError_t launch_admm_thread(const BatchView& bv, const AdmmSettings& st, cons
     const int grid = (bv.B + kThreadKernelBlock - 1) / kThreadKernelBlock;
     admm_thread_kernel<MatsGlobal><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
     return cudaGetLastError();
+}
+
+cudaError_t launch_admm_thread_per_instance(const BatchView& bv, const AdmmSettings& st, const PerInstanceMats& pm,
+                                            cudaStream_t stream) {
+    if (bv.B <= 0) return cudaSuccess;
+    if (bv.nx > kPerInstanceMaxNx || bv.nu > kPerInstanceMaxNu) return cudaErrorInvalidValue;
+    const int grid = (bv.B + kThreadKernelBlock - 1) / kThreadKernelBlock;
+    auto go = [&](auto m) {
+        m.nx_ = bv.nx; m.nu_ = bv.nu; m.ld_ = bv.ld; m.p_ = pm; m.b_ = 0;
+        admm_thread_kernel<decltype(m)><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
+        return cudaGetLastError();
+    };
+    if (bv.nx == 12 && bv.nu == 4) return go(MatsPerInstance<12, 4>{});
+    if (bv.nx == 4 && bv.nu == 1) return go(MatsPerInstance<4, 1>{});
+    return go(MatsPerInstance<0, 0>{});
 }
 
 }  // namespace tmpc

@@ -43,6 +43,12 @@ using namespace tmu;
 // backward sweep: all-gather p by warp shuffles instead of STS -> LDS.  Measured on B200: +1.7 % for the cartpole
 // shape (one row per lane: 4 shuffles replace 1 store + 2 loads), -0.7 % for the quadrotor shape (24 SHFL vs 9
 // shared-memory instructions per knot point), so it is on for NX = 4 only.
+#ifndef TMPC_FENCE_A
+#define TMPC_FENCE_A 0
+#endif
+#ifndef TMPC_FENCE_C
+#define TMPC_FENCE_C 0
+#endif
 #ifndef TMPC_BWD_SHFL_MAX_NX
 #define TMPC_BWD_SHFL_MAX_NX 4
 #endif
@@ -620,6 +626,9 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 state_column(chk);                            // needs only the lane's own x: covers the broadcast round trip
                 tcol += W;
                 tm_load<W>(tcol, w);                          // next knot point; consumed after the next broadcast
+#if TMPC_FENCE_A
+                SCHED_FENCE();
+#endif
 
                 // d_i = Quu_inv t_i ;  Kinf x_i (own row) ;  A x_i (own rows): RX + 2 independent chains, interleaved
                 double d = 0.0;
@@ -671,7 +680,9 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                     else r_def = dsub(REFS == 1 ? crs : cr, dmul(rho, dsub(znew, ynew)));
                 }
 
-
+#if TMPC_FENCE_C
+                SCHED_FENCE();
+#endif
                 // x_{i+1} = A x_i + B u_i + f
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {

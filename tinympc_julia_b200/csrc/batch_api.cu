@@ -96,6 +96,9 @@ struct tmpc_batch {
     // results
     DevBuf<double> Xsol, Usol;
     DevBuf<int> status, iters, counter;
+    // per-instance dynamics (tmpc_batch_set_instance_dynamics): element-major [e][ld] cache of every instance
+    bool per_instance = false;
+    DevBuf<double> piA, piB, pif, piKinf, piPinf, piQuu, piAmBKt, piAPf, piBPf, piQd, piRd;
     DevBuf<double> state_im;  // instance-major twin of the carried state (TMEM kernel), allocated on first use
     bool state_in_im = false; // which format holds the current carried state (meaningless while state_zero)
 
@@ -151,7 +154,14 @@ tmpc::BatchView make_view(tmpc_batch* h) {
     return v;
 }
 
+tmpc::PerInstanceMats per_instance_view(tmpc_batch* h) {
+    return tmpc::PerInstanceMats{h->piA.p, h->piB.p, h->pif.p, h->piKinf.p, h->piPinf.p, h->piQuu.p, h->piAmBKt.p,
+                                 h->piAPf.p, h->piBPf.p, h->piQd.p, h->piRd.p};
+}
+
 int resolve_kernel(tmpc_batch* h) {
+    if (h->per_instance)   // every instance has its own cache: the thread kernel reads it per instance, coalesced
+        return (h->kernel_pref == TMPC_KERNEL_AUTO || h->kernel_pref == TMPC_KERNEL_THREAD) ? TMPC_KERNEL_THREAD : -1;
     const bool sub_ok = tmpc::subwarp_kernel_supports(h->nx, h->nu, h->N, h->st);
     const bool tm_ok = tmpc::tmem_kernel_supports(make_view(h), h->st);
     const bool tm2_ok = tmpc::tmem2_kernel_supports(make_view(h), h->st);
@@ -201,6 +211,7 @@ cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v_in, cuda
     if (sub && k == TMPC_KERNEL_TMEM2) e = tmpc::launch_admm_tmem2(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
     else if (sub && k == TMPC_KERNEL_TMEM) e = tmpc::launch_admm_tmem(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
     else if (sub) e = tmpc::launch_admm_subwarp(v, h->st, h->hm, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
+    else if (h->per_instance) e = tmpc::launch_admm_thread_per_instance(v, h->st, per_instance_view(h), s);
     else e = tmpc::launch_admm_thread(v, h->st, h->hm, s);
     h->launches += 1;
     if (h->st.max_iter > 0) { h->state_zero = false; h->mem_zero = false; h->state_in_im = wants_im; }
@@ -479,6 +490,67 @@ int tmpc_batch_get_settings(tmpc_batch* h, double* tols, int* ints) {
     return TMPC_OK;
 }
 
+/* Per-instance dynamics (the setup the reference runs once per solver, tiny_api.cpp:21-137 and
+ * :244-318, run for B different systems on the device).  A nx x nx x B, Bdyn nx x nu x B, f nx x B or NULL (zeros),
+ * Q nx x nx [x B], R nu x nu [x B] (qr_batch = 1: shared, B: per instance), Julia layout, host pointers; rho is the
+ * handle's.  Replaces the shared cache for every later solve and clears the carried state (as a new setup would). */
+int tmpc_batch_set_instance_dynamics(tmpc_batch* h, const double* A, const double* Bdyn, const double* f, const double* Q,
+                                     const double* R, int qr_batch) {
+    return guarded([&]() -> int {
+        if (!h || !A || !Bdyn || !Q || !R) { set_error("set_instance_dynamics: null argument"); return TMPC_ERR_DIM; }
+        if (qr_batch != 1 && qr_batch != h->B) { set_error("set_instance_dynamics: qr_batch must be 1 or B"); return TMPC_ERR_DIM; }
+        if (h->nx > tmpc::kPerInstanceMaxNx || h->nu > tmpc::kPerInstanceMaxNu) {
+            set_error("set_instance_dynamics: per-instance dynamics are compiled for nx <= 12, nu <= 4"); return TMPC_ERR_DIM;
+        }
+        h->use_device();
+        const size_t n = h->nx, m = h->nu, B = h->B, ld = h->ld;
+        if (!finite_all(A, n * n * B) || !finite_all(Bdyn, n * m * B) || (f && !finite_all(f, n * B)) ||
+            !finite_all(Q, n * n * (qr_batch > 1 ? B : 1)) || !finite_all(R, m * m * (qr_batch > 1 ? B : 1))) {
+            set_error("set_instance_dynamics: non-finite input"); return TMPC_ERR_DIM;
+        }
+        DevBuf<double> dA, dB, df, dQ, dR;
+        DevBuf<int> fail;
+        dA.upload(A, n * n * B, h->stream); dB.upload(Bdyn, n * m * B, h->stream);
+        if (f) df.upload(f, n * B, h->stream);
+        dQ.upload(Q, n * n * (qr_batch > 1 ? B : 1), h->stream); dR.upload(R, m * m * (qr_batch > 1 ? B : 1), h->stream);
+        fail.alloc(1); fail.zero(h->stream);
+        h->piA.alloc(n * n * ld); h->piB.alloc(n * m * ld); h->pif.alloc(n * ld); h->piKinf.alloc(m * n * ld);
+        h->piPinf.alloc(n * n * ld); h->piQuu.alloc(m * m * ld); h->piAmBKt.alloc(n * n * ld); h->piAPf.alloc(n * ld);
+        h->piBPf.alloc(m * ld); h->piQd.alloc(n * ld); h->piRd.alloc(m * ld);
+        cudaError_t e = tmpc::launch_riccati_cache(h->nx, h->nu, h->B, h->ld, h->rho, dA.p, dB.p, f ? df.p : nullptr, dQ.p,
+                                                   qr_batch > 1 ? static_cast<long long>(n * n) : 0, dR.p,
+                                                   qr_batch > 1 ? static_cast<long long>(m * m) : 0, per_instance_view(h),
+                                                   fail.p, h->stream);
+        if (e != cudaSuccess) throw CudaFail{e, "batched cache kernel launch"};
+        h->launches += 1;
+        int failed = 0;
+        CUDA_TRY(cudaMemcpyAsync(&failed, fail.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        if (failed) { h->per_instance = false; set_error("set_instance_dynamics: singular R + B'PB for some instance"); return TMPC_ERR_STATE; }
+        h->per_instance = true;
+        h->state_zero = true;
+        return TMPC_OK;
+    });
+}
+
+/* Cache of ONE instance of a per-instance batch (column-major; any pointer may be NULL). */
+int tmpc_batch_get_instance_cache(tmpc_batch* h, int b, double* Kinf, double* Pinf, double* Quu_inv, double* AmBKt,
+                                  double* APf, double* BPf) {
+    return guarded([&]() -> int {
+        if (!h || !h->per_instance || b < 0 || b >= h->B) return TMPC_ERR_DIM;
+        h->use_device();
+        const size_t n = h->nx, m = h->nu, pitch = sizeof(double) * h->ld;
+        auto get = [&](double* dst, const DevBuf<double>& src, size_t elems) {
+            if (dst) CUDA_TRY(cudaMemcpy2DAsync(dst, sizeof(double), src.p + b, pitch, sizeof(double), elems,
+                                               cudaMemcpyDeviceToHost, h->stream));
+        };
+        get(Kinf, h->piKinf, m * n); get(Pinf, h->piPinf, n * n); get(Quu_inv, h->piQuu, m * m);
+        get(AmBKt, h->piAmBKt, n * n); get(APf, h->piAPf, n); get(BPf, h->piBPf, m);
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        return TMPC_OK;
+    });
+}
+
 int tmpc_batch_set_cache_terms(tmpc_batch* h, const double* Kinf, const double* Pinf, const double* Quu_inv,
                                const double* AmBKt) {
     return guarded([&]() -> int {
@@ -708,6 +780,7 @@ int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_lo
             h->ext_x0 = nullptr;
         }
         if (h->st.check_termination == 0) { set_error("check_termination = 0 is not supported"); return TMPC_ERR_STATE; }
+        if (h->per_instance) { set_error("rollout with per-instance dynamics is not supported (the plant step uses the shared A, B, f)"); return TMPC_ERR_STATE; }
         ensure_aux_state(h);
         const int k = resolve_kernel(h);
         if (k < 0) { set_error("requested kernel does not support this problem"); return TMPC_ERR_STATE; }

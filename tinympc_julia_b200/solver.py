@@ -371,6 +371,26 @@ def set_cache_terms(solver, Kinf, Pinf, Quu_inv, AmBKt, *, verbose: bool = False
 
 # ------------------------------------------------------------------------------------------ solve / results
 
+def set_instance_dynamics(solver, A, B, f, Q, R) -> int:
+    """Batched solver only: per-instance dynamics.  A (nx, nx, B), B (nx, nu, B), f (nx, B) or None, Q (nx, nx[, B]),
+    R (nu, nu[, B]); the LQR cache of every instance is computed on the device (tmpc_batch_set_instance_dynamics)."""
+    _need_setup(solver)
+    if not isinstance(solver, TinyMPCBatchSolver):
+        raise TinyMPCError("set_instance_dynamics needs a batched solver")
+    n, m, Bn = solver.nx, solver.nu, solver.B
+    Aa = np.asfortranarray(np.asarray(A, dtype=np.float64).reshape((n, n, Bn), order="F"))
+    Ba = np.asfortranarray(np.asarray(B, dtype=np.float64).reshape((n, m, Bn), order="F"))
+    fa = None if f is None else np.asfortranarray(np.asarray(f, dtype=np.float64).reshape((n, Bn), order="F"))
+    Qa = np.asfortranarray(np.asarray(Q, dtype=np.float64))
+    Ra = np.asfortranarray(np.asarray(R, dtype=np.float64))
+    qb = Bn if Qa.ndim == 3 else 1
+    if (Ra.ndim == 3) != (Qa.ndim == 3):
+        raise TinyMPCError("Q and R must both be shared or both per instance")
+    _chk(_lib.load().tmpc_batch_set_instance_dynamics(solver._h, _dp(Aa), _dp(Ba), _dp(fa) if fa is not None else None,
+                                                      _dp(Qa), _dp(Ra), qb), "Failed to set per-instance dynamics")
+    return 0
+
+
 def solve(solver, *, verbose: bool = False) -> int:
     """reference src/TinyMPC.jl:143-148: returns the status WITHOUT raising (0 converged, 1 max_iter).
     Batch solver: 0 when every instance converged, 1 when at least one stopped at max_iter."""

@@ -1,3 +1,3 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q -k "rollout" > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -30 gpurun_out/pytest_gpu.log
-timeout 300 python bench.py --steps 5 --no-cpu > gpurun_out/b.json 2>gpurun_out/b.err; echo "bench rc=$? lines=$(wc -l < gpurun_out/b.json)"
+timeout 900 python -m pytest tests -m gpu -x -q -k "per_instance_dynamics" > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -5 gpurun_out/pytest_gpu.log
+timeout 600 python tools/gpu_perinstance.py > gpurun_out/perinst.json 2> gpurun_out/perinst.err; echo rc=$?; cat gpurun_out/perinst.json; tail -3 gpurun_out/perinst.err
