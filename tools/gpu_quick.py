@@ -68,3 +68,23 @@ for k in KS:
     best = min(ts)
     print(f"cartpole kernel={k} B={B} best {best*1e3:.3f} ms  solves/s {B/best:.3e} iters/s {it.sum()/best:.3e} "
           f"TFLOP/s {it.sum()*Fc/best/1e12:.2f} mean iters {it.mean():.2f} solved {(st==0).mean():.3f}", flush=True)
+
+# config 4: batched rocket landing, nx=6 nu=3 N=50, box + both cones + half-spaces (thread kernel), B = 65,536
+if not FAST or os.environ.get("QROCKET"):
+    Fr = problems.flops_per_iteration(6, 3, 50)["F"]
+    c = cases.rocket(B, N=50)
+    sol = cases.make_cuda_solver(c, kernel=0)
+    t.set_x_ref(sol, c["Xref"]); t.set_u_ref(sol, c["Uref"])
+    t.set_x0(sol, c["x0"])
+    ts = []
+    for rep in range(3):
+        sol.reset()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        sol.solve_async(0)
+        sol.synchronize()
+        ts.append(time.perf_counter() - t0)
+    st, it = sol.status()
+    best = min(ts)
+    print(f"rocket kernel={sol.kernel} B={B} best {best*1e3:.3f} ms  solves/s {B/best:.3e} iters/s {it.sum()/best:.3e} "
+          f"TFLOP/s(box part) {it.sum()*Fr/best/1e12:.2f} mean iters {it.mean():.2f} solved {(st==0).mean():.3f}", flush=True)
