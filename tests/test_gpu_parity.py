@@ -297,11 +297,22 @@ def test_per_instance_dynamics(orc):
         c = cases._base(base, N, bounds=base.bounds(N), x0=x0, max_iter=60)
         sol = cases.make_cuda_solver(c)
         t.set_instance_dynamics(sol, A, Bm, f, Q, R)
-        assert sol.kernel == THREAD
-        t.set_x0(sol, x0)
-        t.solve(sol)
-        st, it = sol.status()
-        X, U = t.get_solution(sol)
+        assert sol.kernel == TMEM                 # AUTO: the on-chip kernel reading per-instance blocks
+        res = {}
+        for k in (TMEM, THREAD):
+            sol.set_kernel(k)
+            assert sol.kernel == k
+            sol.reset()
+            t.set_x0(sol, x0)
+            t.solve(sol)
+            res[k] = (sol.status(), t.get_solution(sol))
+            # warm-started second solve from a nearby state: carried state per instance
+            t.set_x0(sol, np.asfortranarray(0.9 * x0))
+            t.solve(sol)
+            res[k] += (sol.status(), t.get_solution(sol))
+        for a, bb in zip(res[TMEM], res[THREAD]):
+            assert np.array_equal(a[0], bb[0]) and np.array_equal(a[1], bb[1]), "TMEM and thread kernels disagree"
+        (st, it), (X, U) = res[TMEM][0], res[TMEM][1]
         for b in range(B):
             sb = dataclasses.replace(base, A=np.asfortranarray(A[:, :, b]), B=np.asfortranarray(Bm[:, :, b]),
                                      f=f[:, b].copy(), Q=np.asfortranarray(Q[:, :, b]), R=np.asfortranarray(R[:, :, b]))

@@ -52,6 +52,16 @@ bool tmem_kernel_supports(const BatchView& bv, const AdmmSettings& st);
 cudaError_t launch_admm_tmem(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms,
                              cudaStream_t stream);
 
+// Per-instance dynamics on the TMEM kernel: one QConst-layout block of constants per instance (packed once from the
+// element-major cache); the lane's matrix rows come from its instance's block at every sweep start (L2-resident for
+// the instances on chip), the per-knot B / Quu_inv rows from a lane-private shared-memory slot filled at install.
+long long tmem_pi_block_doubles(int nx, int nu);      // 0 = shape not compiled
+cudaError_t launch_tmem_pi_pack(int nx, int nu, const PerInstanceMats& pm, long long ld, int B, double* blocks,
+                                cudaStream_t stream);
+bool tmem_pi_kernel_supports(const BatchView& bv, const AdmmSettings& st);
+cudaError_t launch_admm_tmem_pi(const BatchView& bv, const AdmmSettings& st, int cold, const double* pi_blocks,
+                                int* counter, int num_sms, cudaStream_t stream);
+
 // Fused closed loop on the TMEM kernel: every instance runs `nsteps` MPC steps (solve -> apply znew(:,0) -> plant step ->
 // slide the reference window -> next solve) on the sub-warp that owns it, its ADMM state staying on chip between steps.
 // bv.Xref / bv.xref_stride describe the LONG per-instance reference (nx x (N + nsteps - 1)) when `slide` is set.

@@ -69,6 +69,9 @@ struct QuadParams {
     double* x0_rw;          // plant state, nx x B: read at install, written back after the last step
     int* status_out;        // [nsteps][B] per-step solve status / iteration count (may be null)
     int* iters_out;
+    // per-instance dynamics (PI): one QConst-layout block of constants per instance in global memory
+    const double* pi_blocks;
+    int off_pi;             // per-warp offset (doubles) of the lanes' private B / Quu_inv row slots
 };
 
 
@@ -79,7 +82,7 @@ struct QuadParams {
 
 // REFS: 0 = no references (Xref = Uref = 0), 1 = references shared by all instances (staged in shared memory as
 // the products the linear cost needs), 2 = per-instance references read through the read-only path.
-template <int NX, int NU, bool COLD, int REFS, bool ROLL = false>
+template <int NX, int NU, bool COLD, int REFS, bool ROLL = false, bool PI = false>
 __global__ void __launch_bounds__(kQWarps * 32, 1)
 admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ AdmmSettings st,
                  const __grid_constant__ QuadParams qp) {
@@ -107,12 +110,15 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
 
     // ---------------- stage the shared constants once per CTA
     double* sc = smem + qp.off_consts;
+    static_assert(!PI || (REFS != 1 && !ROLL), "per-instance dynamics: references go through the per-instance path; no fused rollout");
+    if (!PI)
     for (int idx = threadIdx.x; idx < NX * NX; idx += blockDim.x) {
         const int row = idx / NX, k = idx % NX;
         sc[CL::A_rm + idx] = bv.A[k * NX + row];
         sc[CL::AmBKt_rm + idx] = bv.AmBKt[k * NX + row];
         sc[CL::Pinf_cm + idx] = bv.Pinf[idx];
     }
+    if (!PI)
     for (int idx = threadIdx.x; idx < NX * NU; idx += blockDim.x) {
         const int row = idx / NU, k = idx % NU;          // B(row, k)
         sc[CL::B_rm + idx] = bv.Bm[k * NX + row];
@@ -121,12 +127,14 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
         sc[CL::Kinf_rm + idx] = bv.Kinf[kk * NU + j];
         sc[CL::Kinf_cm + idx] = bv.Kinf[idx];
     }
+    if (!PI) {
     for (int idx = threadIdx.x; idx < NU * NU; idx += blockDim.x)
         sc[CL::Quu_rm + idx] = bv.Quu_inv[(idx % NU) * NU + idx / NU];
     for (int idx = threadIdx.x; idx < NX; idx += blockDim.x) {
         sc[CL::f + idx] = bv.f[idx]; sc[CL::APf + idx] = bv.APf[idx]; sc[CL::Qd + idx] = bv.Qd[idx];
     }
     for (int idx = threadIdx.x; idx < NU; idx += blockDim.x) { sc[CL::BPf + idx] = bv.BPf[idx]; sc[CL::Rd + idx] = bv.Rd[idx]; }
+    }
 
     // box bounds as (lo, hi) pairs; a disabled side is (-inf, +inf), for which the clamp is the identity
     double* s_xb = smem + qp.off_bounds;              // [N][NX][2]
@@ -182,17 +190,27 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     const uint32_t a_ub = smem_addr(s_ub) + usub * 16;                               // + i * NU * 16
     const uint32_t a_xb = smem_addr(s_xb) + sub * 16;                                // + i * NX * 16 ; row r: + r * 64
     const uint32_t a_sc = smem_addr(sc);
-    const uint32_t a_Mb = a_sc + (CL::B_rm + sub * NU) * 8;                          // row r: + r * 4 * NU * 8
-    const uint32_t a_Mq = a_sc + (CL::Quu_rm + usub * NU) * 8;
+    // B rows / Quu_inv row read every knot point: the shared staging, or (PI) the lane's private slot of 18 doubles
+    // (9 16-byte chunks: conflict-free LDS.128): [B row r = 0..RX-1 (NU each)] [Quu_inv row]
+    constexpr int MBS = PI ? NU * 8 : 4 * NU * 8;                                    // bytes between the lane's B rows
+    double* s_pi = wbase + qp.off_pi + lane * 18;
+    const uint32_t a_Mb = PI ? smem_addr(s_pi) : a_sc + (CL::B_rm + sub * NU) * 8;   // row r: + r * MBS
+    const uint32_t a_Mq = PI ? smem_addr(s_pi) + RX * NU * 8 : a_sc + (CL::Quu_rm + usub * NU) * 8;
+    const double* scl = sc;                           // constants of the lane's instance: shared staging, or (PI) its block
     const uint32_t a_cq = smem_addr(s_cq) + sub * 8;                                 // + i * NX * 8 ; row r: + r * 32
     const uint32_t a_cr = smem_addr(s_cr) + usub * 8;                                // + i * NU * 8
     uint32_t a_slot = a_slotA;
 
-    const double fr_BPf = urow ? sc[CL::BPf + usub] : 0.0;
-    const double fr_Rd = urow ? sc[CL::Rd + usub] : 0.0;
+    double fr_BPf = 0.0, fr_Rd = 0.0;
     double fr_f[RX], fr_APf[RX], fr_Qd[RX];
 #pragma unroll
-    for (int r = 0; r < RX; ++r) { fr_f[r] = sc[CL::f + r * 4 + sub]; fr_APf[r] = sc[CL::APf + r * 4 + sub]; fr_Qd[r] = sc[CL::Qd + r * 4 + sub]; }
+    for (int r = 0; r < RX; ++r) { fr_f[r] = 0.0; fr_APf[r] = 0.0; fr_Qd[r] = 0.0; }
+    if (!PI) {
+        fr_BPf = urow ? sc[CL::BPf + usub] : 0.0;
+        fr_Rd = urow ? sc[CL::Rd + usub] : 0.0;
+#pragma unroll
+        for (int r = 0; r < RX; ++r) { fr_f[r] = sc[CL::f + r * 4 + sub]; fr_APf[r] = sc[CL::APf + r * 4 + sub]; fr_Qd[r] = sc[CL::Qd + r * 4 + sub]; }
+    }
 
     // ---------------- per-lane instance state
     int b = 0, iter = 0, status = 1;
@@ -351,6 +369,19 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 sblk = nblk;
                 valid = nvalid; iter = 0; first = true; status = 1; fin = false;
                 step = 0; cont = false; fix = false;
+                if (PI) {                                 // constants of the new instance: registers + the lane's B / Quu_inv slot
+                    scl = qp.pi_blocks + nbb * CL::size;
+                    fr_BPf = urow ? scl[CL::BPf + usub] : 0.0;
+                    fr_Rd = urow ? scl[CL::Rd + usub] : 0.0;
+#pragma unroll
+                    for (int r = 0; r < RX; ++r) {
+                        fr_f[r] = scl[CL::f + r * 4 + sub]; fr_APf[r] = scl[CL::APf + r * 4 + sub]; fr_Qd[r] = scl[CL::Qd + r * 4 + sub];
+#pragma unroll
+                        for (int k = 0; k < NU; ++k) s_pi[r * NU + k] = scl[CL::B_rm + (r * 4 + sub) * NU + k];
+                    }
+#pragma unroll
+                    for (int k = 0; k < NU; ++k) s_pi[RX * NU + k] = scl[CL::Quu_rm + usub * NU + k];
+                }
                 if (REFS == 2) {
                     xref_g = bv.Xref ? bv.Xref + nbb * bv.xref_stride + sub : nullptr;      // + i NX + 4 r
                     uref_g = (bv.Uref && urow) ? bv.Uref + nbb * bv.uref_stride + sub : nullptr;   // + i NU
@@ -372,12 +403,12 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
 #pragma unroll
             for (int r = 0; r < RX; ++r) {
 #pragma unroll
-                for (int k = 0; k < NX; k += 2) ld2(sc + CL::AmBKt_rm + (r * 4 + sub) * NX + k, Mab[r][k], Mab[r][k + 1]);
+                for (int k = 0; k < NX; k += 2) ld2(scl + CL::AmBKt_rm + (r * 4 + sub) * NX + k, Mab[r][k], Mab[r][k + 1]);
 #pragma unroll
-                for (int k = 0; k < NU; ++k) Mkt[r][k] = sc[CL::Kinf_cm + (r * 4 + sub) * NU + k];
+                for (int k = 0; k < NU; ++k) Mkt[r][k] = scl[CL::Kinf_cm + (r * 4 + sub) * NU + k];
             }
 #pragma unroll
-            for (int k = 0; k < NX; ++k) Mbt[k] = urow ? sc[CL::B_cm + usub * NX + k] : 0.0;
+            for (int k = 0; k < NX; ++k) Mbt[k] = urow ? scl[CL::B_cm + usub * NX + k] : 0.0;
 
             double p[RX];
 #pragma unroll
@@ -529,10 +560,10 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
 #pragma unroll
             for (int r = 0; r < RX; ++r) {
 #pragma unroll
-                for (int k = 0; k < NX; k += 2) ld2(sc + CL::A_rm + (r * 4 + sub) * NX + k, Ma[r][k], Ma[r][k + 1]);
+                for (int k = 0; k < NX; k += 2) ld2(scl + CL::A_rm + (r * 4 + sub) * NX + k, Ma[r][k], Ma[r][k + 1]);
             }
 #pragma unroll
-            for (int k = 0; k < NX; ++k) Mk[k] = urow ? sc[CL::Kinf_rm + usub * NX + k] : 0.0;
+            for (int k = 0; k < NX; ++k) Mk[k] = urow ? scl[CL::Kinf_rm + usub * NX + k] : 0.0;
 
             double x[RX];
 #pragma unroll
@@ -614,7 +645,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 if (NU == 4) { lds2<0>(a_Mq, mq[0], mq[1]); lds2<16>(a_Mq, mq[2], mq[3]); }
                 else {
 #pragma unroll
-                    for (int k = 0; k < NU; ++k) mq[k] = sc[CL::Quu_rm + usub * NU + k];
+                    for (int k = 0; k < NU; ++k) mq[k] = scl[CL::Quu_rm + usub * NU + k];
                 }
                 double yj = 0.0, zold = 0.0, ulo = 0.0, uhi = 0.0, crs = 0.0;
                 if (urow) {
@@ -657,11 +688,11 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 for (int r = 0; r < RX; ++r) {
                     if (NU == 4) {
                         if (r == 0) { lds2<0>(a_Mb, mb[r][0], mb[r][1]); lds2<16>(a_Mb, mb[r][2], mb[r][3]); }
-                        else if (r == 1) { lds2<4 * NU * 8>(a_Mb, mb[r][0], mb[r][1]); lds2<4 * NU * 8 + 16>(a_Mb, mb[r][2], mb[r][3]); }
-                        else { lds2<8 * NU * 8>(a_Mb, mb[r][0], mb[r][1]); lds2<8 * NU * 8 + 16>(a_Mb, mb[r][2], mb[r][3]); }
+                        else if (r == 1) { lds2<MBS>(a_Mb, mb[r][0], mb[r][1]); lds2<MBS + 16>(a_Mb, mb[r][2], mb[r][3]); }
+                        else { lds2<2 * MBS>(a_Mb, mb[r][0], mb[r][1]); lds2<2 * MBS + 16>(a_Mb, mb[r][2], mb[r][3]); }
                     } else {
 #pragma unroll
-                        for (int k = 0; k < NU; ++k) mb[r][k] = sc[CL::B_rm + (r * 4 + sub) * NU + k];
+                        for (int k = 0; k < NU; ++k) mb[r][k] = scl[CL::B_rm + (r * 4 + sub) * NU + k];
                     }
                 }
                 if (urow) {
@@ -712,7 +743,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 else if (REFS == 1) p_term[r] = dsub(s_tq[r * 4 + sub], dmul(rho, vg[r]));
                 else {
                     double s = 0.0;
-                    if (xref_g) for (int k = 0; k < NX; ++k) s = fma(__ldg(xref_g - sub + (N - 1) * NX + k), sc[CL::Pinf_cm + (r * 4 + sub) * NX + k], s);
+                    if (xref_g) for (int k = 0; k < NX; ++k) s = fma(__ldg(xref_g - sub + (N - 1) * NX + k), scl[CL::Pinf_cm + (r * 4 + sub) * NX + k], s);
                     p_term[r] = dsub(-s, dmul(rho, vg[r]));
                 }
             }
@@ -751,7 +782,7 @@ double dual_threshold_q(double rho, double tol) {
 struct QPlan { size_t smem_bytes; QuadParams qp; };
 
 template <int NX, int NU>
-bool make_qplan(int N, int refs, QPlan& pl) {
+bool make_qplan(int N, int refs, QPlan& pl, bool pi = false) {
     constexpr int XP = QPad<NX>::value;
     constexpr int W = 4 * (NX / 4);
     if (N < 2 || N * W > kTmemColsPerWarp) return false;           // g, v of a lane must fit its 256 TMEM columns
@@ -765,6 +796,8 @@ bool make_qplan(int N, int refs, QPlan& pl) {
     qp.off_warp0 = off;
     int per_warp = (N - 1) * 96 + 2 * kQInst * XP;
     per_warp = (per_warp + 1) / 2 * 2;
+    qp.off_pi = per_warp;
+    if (pi) per_warp += 32 * 18;                                   // the lanes' private B / Quu_inv row slots
     qp.warp_stride = per_warp;
     pl.smem_bytes = (static_cast<size_t>(off) + static_cast<size_t>(per_warp) * kQWarps) * sizeof(double);
     pl.qp = qp;
@@ -777,9 +810,9 @@ int refs_mode(const BatchView& bv) {
     return (xs && us) ? 1 : 2;
 }
 
-template <int NX, int NU, bool COLD, int REFS, bool ROLL = false>
+template <int NX, int NU, bool COLD, int REFS, bool ROLL = false, bool PI = false>
 cudaError_t launch_q(const BatchView& bv, const AdmmSettings& st, const QPlan& pl, int num_sms, cudaStream_t stream) {
-    auto kern = admm_tmem_kernel<NX, NU, COLD, REFS, ROLL>;
+    auto kern = admm_tmem_kernel<NX, NU, COLD, REFS, ROLL, PI>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(pl.smem_bytes));
     if (e != cudaSuccess) return e;
     const int per_cta = kQWarps * kQInst;
@@ -811,6 +844,54 @@ cudaError_t launch_shape(const BatchView& bv, const AdmmSettings& st, int cold, 
 }
 
 template <int NX, int NU>
+cudaError_t launch_shape_pi(const BatchView& bv, const AdmmSettings& st, int cold, const double* pi_blocks, int* counter,
+                            int num_sms, cudaStream_t stream) {
+    QPlan pl;
+    const int refs = refs_mode(bv) == 0 ? 0 : 2;       // references, shared or not, go through the per-instance path
+    if (!make_qplan<NX, NU>(bv.N, refs, pl, true)) return cudaErrorInvalidConfiguration;
+    pl.qp.counter = counter;
+    pl.qp.pri_thresh = st.abs_pri_tol;
+    pl.qp.dua_thresh = dual_threshold_q(bv.rho, st.abs_dua_tol);
+    pl.qp.pi_blocks = pi_blocks;
+    cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(int), stream);
+    if (e != cudaSuccess) return e;
+    if (cold) {
+        if (refs == 0) return launch_q<NX, NU, true, 0, false, true>(bv, st, pl, num_sms, stream);
+        return launch_q<NX, NU, true, 2, false, true>(bv, st, pl, num_sms, stream);
+    }
+    if (refs == 0) return launch_q<NX, NU, false, 0, false, true>(bv, st, pl, num_sms, stream);
+    return launch_q<NX, NU, false, 2, false, true>(bv, st, pl, num_sms, stream);
+}
+
+// element-major per-instance cache [e][ld]  ->  one QConst-layout block per instance (what the kernel stages for shared
+// dynamics, so the sweeps read either through the same offsets)
+template <int NX, int NU>
+__global__ void pi_pack_kernel(PerInstanceMats pm, long long ld, int B, double* __restrict__ blocks) {
+    using CL = QConst<NX, NU>;
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    double* o = blocks + static_cast<size_t>(b) * CL::size;
+    auto at = [&](const double* a, int e) { return a[static_cast<size_t>(e) * ld + b]; };
+    for (int idx = 0; idx < NX * NX; ++idx) {
+        const int row = idx / NX, k = idx % NX;
+        o[CL::A_rm + idx] = at(pm.A, k * NX + row);
+        o[CL::AmBKt_rm + idx] = at(pm.AmBKt, k * NX + row);
+        o[CL::Pinf_cm + idx] = at(pm.Pinf, idx);
+    }
+    for (int idx = 0; idx < NX * NU; ++idx) {
+        const int row = idx / NU, k = idx % NU;
+        o[CL::B_rm + idx] = at(pm.B, k * NX + row);
+        o[CL::B_cm + idx] = at(pm.B, idx);
+        const int j = idx / NX, kk = idx % NX;
+        o[CL::Kinf_rm + idx] = at(pm.Kinf, kk * NU + j);
+        o[CL::Kinf_cm + idx] = at(pm.Kinf, idx);
+    }
+    for (int idx = 0; idx < NU * NU; ++idx) o[CL::Quu_rm + idx] = at(pm.Quu_inv, (idx % NU) * NU + idx / NU);
+    for (int idx = 0; idx < NX; ++idx) { o[CL::f + idx] = at(pm.f, idx); o[CL::APf + idx] = at(pm.APf, idx); o[CL::Qd + idx] = at(pm.Qd, idx); }
+    for (int idx = 0; idx < NU; ++idx) { o[CL::BPf + idx] = at(pm.BPf, idx); o[CL::Rd + idx] = at(pm.Rd, idx); }
+}
+
+template <int NX, int NU>
 cudaError_t launch_shape_roll(const BatchView& bv, const AdmmSettings& st, const RolloutArgs& ra, int* counter,
                               int num_sms, cudaStream_t stream) {
     QPlan pl;
@@ -836,6 +917,40 @@ cudaError_t launch_admm_tmem_rollout(const BatchView& bv, const AdmmSettings& st
     if (bv.nx == 12 && bv.nu == 4) return launch_shape_roll<12, 4>(bv, st, ra, counter, num_sms, stream);
     if (bv.nx == 4 && bv.nu == 1) return launch_shape_roll<4, 1>(bv, st, ra, counter, num_sms, stream);
     return cudaErrorNotSupported;
+}
+
+long long tmem_pi_block_doubles(int nx, int nu) {
+    if (nx == 12 && nu == 4) return QConst<12, 4>::size;
+    if (nx == 4 && nu == 1) return QConst<4, 1>::size;
+    return 0;
+}
+
+cudaError_t launch_tmem_pi_pack(int nx, int nu, const PerInstanceMats& pm, long long ld, int B, double* blocks,
+                                cudaStream_t stream) {
+    const int block = 128, grid = (B + block - 1) / block;
+    if (nx == 12 && nu == 4) pi_pack_kernel<12, 4><<<grid, block, 0, stream>>>(pm, ld, B, blocks);
+    else if (nx == 4 && nu == 1) pi_pack_kernel<4, 1><<<grid, block, 0, stream>>>(pm, ld, B, blocks);
+    else return cudaErrorNotSupported;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_admm_tmem_pi(const BatchView& bv, const AdmmSettings& st, int cold, const double* pi_blocks,
+                                int* counter, int num_sms, cudaStream_t stream) {
+    if (bv.B <= 0) return cudaSuccess;
+    if (bv.nx == 12 && bv.nu == 4) return launch_shape_pi<12, 4>(bv, st, cold, pi_blocks, counter, num_sms, stream);
+    if (bv.nx == 4 && bv.nu == 1) return launch_shape_pi<4, 1>(bv, st, cold, pi_blocks, counter, num_sms, stream);
+    return cudaErrorNotSupported;
+}
+
+bool tmem_pi_kernel_supports(const BatchView& bv, const AdmmSettings& st) {
+    if (st.en_state_soc || st.en_input_soc || st.en_state_linear || st.en_input_linear) return false;
+    if (st.max_iter <= 0 || !(bv.rho > 0.0)) return false;
+    if (bv.x_min != nullptr && (bv.xb_stride != 0 || bv.ub_stride != 0)) return false;
+    QPlan pl;
+    const int refs = refs_mode(bv) == 0 ? 0 : 2;
+    if (bv.nx == 12 && bv.nu == 4) return make_qplan<12, 4>(bv.N, refs, pl, true);
+    if (bv.nx == 4 && bv.nu == 1) return make_qplan<4, 1>(bv.N, refs, pl, true);
+    return false;
 }
 
 bool tmem_kernel_supports(const BatchView& bv, const AdmmSettings& st) {

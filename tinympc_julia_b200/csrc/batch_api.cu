@@ -98,6 +98,7 @@ struct tmpc_batch {
     DevBuf<int> status, iters, counter;
     // per-instance dynamics (tmpc_batch_set_instance_dynamics): element-major [e][ld] cache of every instance
     bool per_instance = false;
+    DevBuf<double> pi_blocks;   // the same, one QConst-layout block per instance, for the TMEM kernel (compiled shapes)
     DevBuf<double> piA, piB, pif, piKinf, piPinf, piQuu, piAmBKt, piAPf, piBPf, piQd, piRd;
     DevBuf<double> state_im;  // instance-major twin of the carried state (TMEM kernel), allocated on first use
     bool state_in_im = false; // which format holds the current carried state (meaningless while state_zero)
@@ -160,8 +161,13 @@ tmpc::PerInstanceMats per_instance_view(tmpc_batch* h) {
 }
 
 int resolve_kernel(tmpc_batch* h) {
-    if (h->per_instance)   // every instance has its own cache: the thread kernel reads it per instance, coalesced
-        return (h->kernel_pref == TMPC_KERNEL_AUTO || h->kernel_pref == TMPC_KERNEL_THREAD) ? TMPC_KERNEL_THREAD : -1;
+    if (h->per_instance) {   // every instance has its own cache: TMEM kernel reading per-instance blocks, else thread kernel
+        const bool tm_pi = h->pi_blocks.p && tmpc::tmem_pi_kernel_supports(make_view(h), h->st);
+        if (h->kernel_pref == TMPC_KERNEL_THREAD) return TMPC_KERNEL_THREAD;
+        if (h->kernel_pref == TMPC_KERNEL_TMEM) return tm_pi ? TMPC_KERNEL_TMEM : -1;
+        if (h->kernel_pref != TMPC_KERNEL_AUTO) return -1;
+        return tm_pi ? TMPC_KERNEL_TMEM : TMPC_KERNEL_THREAD;
+    }
     const bool sub_ok = tmpc::subwarp_kernel_supports(h->nx, h->nu, h->N, h->st);
     const bool tm_ok = tmpc::tmem_kernel_supports(make_view(h), h->st);
     const bool tm2_ok = tmpc::tmem2_kernel_supports(make_view(h), h->st);
@@ -209,6 +215,8 @@ cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v_in, cuda
     }
     cudaError_t e;
     if (sub && k == TMPC_KERNEL_TMEM2) e = tmpc::launch_admm_tmem2(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
+    else if (sub && k == TMPC_KERNEL_TMEM && h->per_instance)
+        e = tmpc::launch_admm_tmem_pi(v, h->st, h->state_zero ? 1 : 0, h->pi_blocks.p, h->counter.p, h->num_sms, s);
     else if (sub && k == TMPC_KERNEL_TMEM) e = tmpc::launch_admm_tmem(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
     else if (sub) e = tmpc::launch_admm_subwarp(v, h->st, h->hm, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
     else if (h->per_instance) e = tmpc::launch_admm_thread_per_instance(v, h->st, per_instance_view(h), s);
@@ -527,6 +535,15 @@ int tmpc_batch_set_instance_dynamics(tmpc_batch* h, const double* A, const doubl
         CUDA_TRY(cudaMemcpyAsync(&failed, fail.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
         CUDA_TRY(cudaStreamSynchronize(h->stream));
         if (failed) { h->per_instance = false; set_error("set_instance_dynamics: singular R + B'PB for some instance"); return TMPC_ERR_STATE; }
+        const long long blk = tmpc::tmem_pi_block_doubles(h->nx, h->nu);
+        h->pi_blocks.release();
+        if (blk > 0) {
+            h->pi_blocks.alloc(static_cast<size_t>(blk) * B);
+            e = tmpc::launch_tmem_pi_pack(h->nx, h->nu, per_instance_view(h), h->ld, h->B, h->pi_blocks.p, h->stream);
+            if (e != cudaSuccess) throw CudaFail{e, "per-instance block packing"};
+            h->launches += 1;
+            CUDA_TRY(cudaStreamSynchronize(h->stream));
+        }
         h->per_instance = true;
         h->state_zero = true;
         return TMPC_OK;
@@ -640,7 +657,7 @@ int tmpc_batch_solve_host(tmpc_batch* h, const double* x0, int cold, double* X, 
         // waves each, so that a chunk runs at the efficiency of the full batch
         const int wave = h->num_sms * 64;
         int nch = chunks > 0 ? chunks : 4;
-        if (!tm || h->B < 3 * wave) nch = 1;
+        if (!tm || h->B < 3 * wave || h->per_instance) nch = 1;
         int chunk_size = h->B;
         if (nch > 1) {
             chunk_size = ((h->B + nch - 1) / nch + wave - 1) / wave * wave;

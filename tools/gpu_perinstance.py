@@ -16,9 +16,11 @@ Bm = np.asfortranarray(base.B[:, :, None] * (1.0 + 0.2 * rng.uniform(-1, 1, (n, 
 x0 = np.asfortranarray(0.1 * rng.uniform(-1, 1, (n, B)))
 c = cases._base(base, N, bounds=base.bounds(N), x0=x0)
 sol = cases.make_cuda_solver(c)
+KPI = int(os.environ.get("QK", 0))
 t0 = time.perf_counter()
 t.set_instance_dynamics(sol, A, Bm, None, base.Q, base.R)
 t_setup = time.perf_counter() - t0
+sol.set_kernel(KPI)
 t.set_x0(sol, x0)
 best = 1e9
 for rep in range(3):
