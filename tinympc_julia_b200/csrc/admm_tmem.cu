@@ -53,7 +53,10 @@ using namespace tmu;
 #define TMPC_BWD_SHFL_MAX_NX 4
 #endif
 
-constexpr int kQWarps = 8;           // warps per CTA (one CTA per SM): two per scheduler
+#ifndef TMPC_QWARPS
+#define TMPC_QWARPS 8
+#endif
+constexpr int kQWarps = TMPC_QWARPS;           // warps per CTA (one CTA per SM): two per scheduler
 constexpr int kQInst = 8;            // instances per warp
 constexpr int kTmemColsPerWarp = 256;
 
@@ -86,6 +89,11 @@ template <int NX, int NU, bool COLD, int REFS, bool ROLL = false, bool PI = fals
 __global__ void __launch_bounds__(kQWarps * 32, 1)
 admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ AdmmSettings st,
                  const __grid_constant__ QuadParams qp) {
+    // A global access in uniform control flow before anything else: ptxas then keeps the global-memory descriptor in a
+    // uniform register for the whole kernel.  Without it the first global access sits in a divergent region (the
+    // staging loop), the descriptor lands in a vector register pair and EVERY load/store pays two R2UR (7 % of all
+    // instructions issued).  The queue counter never reaches the value tested.
+    if (*reinterpret_cast<const volatile int*>(qp.counter) == 0x7ffffff0) return;
     static_assert(NX % 4 == 0 && NX >= 4, "state rows are dealt 4 lanes x RX rows");
     static_assert(NU >= 1 && NU <= 4, "one input row per lane");
     constexpr int RX = NX / 4;
@@ -93,6 +101,10 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     constexpr int W = 4 * RX;                         // 32-bit TMEM words per knot point per lane: g(RX), v(RX)
     static_assert(W == 12 || W == 4, "tm_wait_ld is specialised for 3 or 1 state rows per lane");
     using CL = QConst<NX, NU>;
+#ifndef TMPC_CREG
+#define TMPC_CREG 1
+#endif
+    constexpr bool CREG = TMPC_CREG != 0;
 
     extern __shared__ __align__(16) double smem[];
     __shared__ uint32_t s_tmem_base;
@@ -564,6 +576,19 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             }
 #pragma unroll
             for (int k = 0; k < NX; ++k) Mk[k] = urow ? scl[CL::Kinf_rm + usub * NX + k] : 0.0;
+            // rows of B and of Quu_inv: registers where the variant has room for them (CREG), else re-read from
+            // shared memory at every knot point.  Shared-memory bandwidth (4 bytes per lane per clock) is what the
+            // two warps of a scheduler and their six neighbours contend for: 128 of the 336 bytes a lane reads per
+            // forward knot point are these constants.
+            double Mb[CREG ? RX : 1][NU], Mq[NU];
+            if (CREG) {
+#pragma unroll
+                for (int r = 0; r < RX; ++r)
+#pragma unroll
+                    for (int k = 0; k < NU; ++k) Mb[r][k] = scl[CL::B_rm + (r * 4 + sub) * NU + k];
+#pragma unroll
+                for (int k = 0; k < NU; ++k) Mq[k] = scl[CL::Quu_rm + usub * NU + k];
+            }
 
             double x[RX];
 #pragma unroll
@@ -642,7 +667,10 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 double tt[4], mq[4];
                 lds2<0>(a_rt4 + o_rt, tt[0], tt[1]);
                 lds2<128>(a_rt4 + o_rt, tt[2], tt[3]);
-                if (NU == 4) { lds2<0>(a_Mq, mq[0], mq[1]); lds2<16>(a_Mq, mq[2], mq[3]); }
+                if (CREG) {
+#pragma unroll
+                    for (int k = 0; k < NU; ++k) mq[k] = Mq[k];
+                } else if (NU == 4) { lds2<0>(a_Mq, mq[0], mq[1]); lds2<16>(a_Mq, mq[2], mq[3]); }
                 else {
 #pragma unroll
                     for (int k = 0; k < NU; ++k) mq[k] = scl[CL::Quu_rm + usub * NU + k];
@@ -686,7 +714,10 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 double mb[RX][4];
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
-                    if (NU == 4) {
+                    if (CREG) {
+#pragma unroll
+                        for (int k = 0; k < NU; ++k) mb[r][k] = Mb[r][k];
+                    } else if (NU == 4) {
                         if (r == 0) { lds2<0>(a_Mb, mb[r][0], mb[r][1]); lds2<16>(a_Mb, mb[r][2], mb[r][3]); }
                         else if (r == 1) { lds2<MBS>(a_Mb, mb[r][0], mb[r][1]); lds2<MBS + 16>(a_Mb, mb[r][2], mb[r][3]); }
                         else { lds2<2 * MBS>(a_Mb, mb[r][0], mb[r][1]); lds2<2 * MBS + 16>(a_Mb, mb[r][2], mb[r][3]); }
