@@ -12,6 +12,8 @@ timeout 300 python bench.py --kernel 2 --no-cpu --steps 10 > gpurun_out/bench_su
 timeout 300 python bench.py --kernel 4 --no-cpu --steps 20 > gpurun_out/bench_tmem2.json 2> gpurun_out/bench_tmem2.err; echo "bench tmem2 rc=$?"
 timeout 300 python bench.py --kernel 4 --no-cpu --steps 20 --workload quadrotor_hard > gpurun_out/bench_tmem2_hard.json 2> gpurun_out/bench_tmem2_hard.err
 timeout 600 python tools/gpu_rollout.py > gpurun_out/rollout.json 2> gpurun_out/rollout.err; echo "rollout rc=$?"; cat gpurun_out/rollout.json
+timeout 600 python tools/gpu_perinstance.py > gpurun_out/perinst.json 2> gpurun_out/perinst.err; echo "perinst rc=$?"; cat gpurun_out/perinst.json
+timeout 300 python tools/gpu_steady.py > gpurun_out/steady.json 2> gpurun_out/steady.err; echo "steady rc=$?"; cat gpurun_out/steady.json
 timeout 600 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "bench ref rc=$?"; cat gpurun_out/bench_ref.json
 timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/plain.log 2>&1 && \
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/ncu_launch.log 2>&1
