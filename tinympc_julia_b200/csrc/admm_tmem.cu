@@ -108,6 +108,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
 
     extern __shared__ __align__(16) double smem[];
     __shared__ uint32_t s_tmem_base;
+    __shared__ uint32_t s_smem_base;
     const int N = bv.N;
     const int nxN = NX * N, nuN = NU * (N - 1);
     const size_t ld = static_cast<size_t>(bv.ld);
@@ -174,9 +175,16 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             s_tq[row] = -s;
         }
     }
+    if (threadIdx.x == 0) s_smem_base = smem_addr(smem);
     asm volatile("tcgen05.fence::before_thread_sync;");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;");
+    // The shared-window address of smem[], read back through a volatile load: ptxas otherwise rematerialises it inside
+    // the sweeps when registers are short (S2UR SR_CgaCtaId + ULEA per knot point, the S2UR latency exposed: 4 % of
+    // the samples of the forward sweep).  A loaded value can only be kept.
+    uint32_t sbase;
+    asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(sbase) : "r"(smem_addr(&s_smem_base)) : "memory");
+    auto sa = [&](const double* q) { return sbase + static_cast<uint32_t>((q - smem) * sizeof(double)); };
 
     // ---------------- per-warp carve-up
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -194,23 +202,23 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     double* my_rt = s_rt + (sub >> 1) * 16 + inst * 2 + (sub & 1);   // + i * 32 : own row
 
     // 32-bit shared addresses of everything the sweeps touch (byte strides per knot point in the comments)
-    const uint32_t a_yz = smem_addr(s_yz) + lane * 16;                               // + i * 512
-    const uint32_t a_rt4 = smem_addr(s_rt) + inst * 16;                              // + i * 256 ; rows 2,3: + 128
-    const uint32_t a_myrt = smem_addr(my_rt);                                        // + i * 256
-    const uint32_t a_slotA = smem_addr(s_bc) + inst * XP * 8;
+    const uint32_t a_yz = sa(s_yz) + lane * 16;                               // + i * 512
+    const uint32_t a_rt4 = sa(s_rt) + inst * 16;                              // + i * 256 ; rows 2,3: + 128
+    const uint32_t a_myrt = sa(my_rt);                                        // + i * 256
+    const uint32_t a_slotA = sa(s_bc) + inst * XP * 8;
     const uint32_t a_slot_sum = 2 * a_slotA + kQInst * XP * 8;                       // slot B = sum - slot A
-    const uint32_t a_ub = smem_addr(s_ub) + usub * 16;                               // + i * NU * 16
-    const uint32_t a_xb = smem_addr(s_xb) + sub * 16;                                // + i * NX * 16 ; row r: + r * 64
-    const uint32_t a_sc = smem_addr(sc);
+    const uint32_t a_ub = sa(s_ub) + usub * 16;                               // + i * NU * 16
+    const uint32_t a_xb = sa(s_xb) + sub * 16;                                // + i * NX * 16 ; row r: + r * 64
+    const uint32_t a_sc = sa(sc);
     // B rows / Quu_inv row read every knot point: the shared staging, or (PI) the lane's private slot of 18 doubles
     // (9 16-byte chunks: conflict-free LDS.128): [B row r = 0..RX-1 (NU each)] [Quu_inv row]
     constexpr int MBS = PI ? NU * 8 : 4 * NU * 8;                                    // bytes between the lane's B rows
     double* s_pi = wbase + qp.off_pi + lane * 18;
-    const uint32_t a_Mb = PI ? smem_addr(s_pi) : a_sc + (CL::B_rm + sub * NU) * 8;   // row r: + r * MBS
-    const uint32_t a_Mq = PI ? smem_addr(s_pi) + RX * NU * 8 : a_sc + (CL::Quu_rm + usub * NU) * 8;
+    const uint32_t a_Mb = PI ? sa(s_pi) : a_sc + (CL::B_rm + sub * NU) * 8;   // row r: + r * MBS
+    const uint32_t a_Mq = PI ? sa(s_pi) + RX * NU * 8 : a_sc + (CL::Quu_rm + usub * NU) * 8;
     const double* scl = sc;                           // constants of the lane's instance: shared staging, or (PI) its block
-    const uint32_t a_cq = smem_addr(s_cq) + sub * 8;                                 // + i * NX * 8 ; row r: + r * 32
-    const uint32_t a_cr = smem_addr(s_cr) + usub * 8;                                // + i * NU * 8
+    const uint32_t a_cq = sa(s_cq) + sub * 8;                                 // + i * NX * 8 ; row r: + r * 32
+    const uint32_t a_cr = sa(s_cr) + usub * 8;                                // + i * NU * 8
     uint32_t a_slot = a_slotA;
 
     double fr_BPf = 0.0, fr_Rd = 0.0;
