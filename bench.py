@@ -257,6 +257,28 @@ def workload_name(args):
 
 # ------------------------------------------------------------------------------------------ GPU arm
 
+def bind_to_gpu_numa(torch, local_rank):
+    """Multi-GPU runs: pin this rank's threads to the CPUs local to its GPU (sysfs local_cpulist of the PCI device) so
+    that its pinned host buffers are allocated on that NUMA node; 8 ranks sharing one node's memory do not scale on the
+    host <-> device leg.  Best effort: returns a short description or None."""
+    try:
+        p = torch.cuda.get_device_properties(local_rank)
+        bus = f"{p.pci_domain_id:04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        base = f"/sys/bus/pci/devices/{bus}"
+        cpus = set()
+        for part in open(f"{base}/local_cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        node = open(f"{base}/numa_node").read().strip()
+        return {"pci": bus, "numa_node": int(node), "cpus": len(cpus)}
+    except Exception:
+        return None
+
+
 def run_gpu(args, rank, local_rank, world):
     import torch
     import torch.distributed as dist
@@ -267,7 +289,9 @@ def run_gpu(args, rank, local_rank, world):
         raise SystemExit("bench.py: no CUDA device — the solve path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    numa = None
     if world > 1:
+        numa = bind_to_gpu_numa(torch, local_rank)      # before any pinned allocation
         dist.init_process_group("nccl", device_id=dev)
     lib = _lib.load()
     hard = args.workload == "quadrotor_hard"
@@ -436,6 +460,8 @@ def run_gpu(args, rank, local_rank, world):
                    "path": "tmpc_batch_solve_host on pinned host buffers (x0 up, chunked solve overlapped with the D2H of the previous chunk's solution)",
                    "unpipelined_ms_per_step": 1e3 * calls_s,
                    "unpipelined_path": "tmpc_batch_set_x0 / reset / solve / get_states / get_controls / get_status"}
+    if numa is not None:
+        line["e2e"]["host_binding_rank0"] = numa
     assert torch.equal(X_chk, X_host[:64]) and torch.equal(U_chk, U_host[:64]), "pipelined e2e path returned a different solution"
 
     # ---- CPU baseline + single-solve latency: N=1, rank 0 only
