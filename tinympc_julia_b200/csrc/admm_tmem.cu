@@ -101,6 +101,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     constexpr int W = 4 * RX;                         // 32-bit TMEM words per knot point per lane: g(RX), v(RX)
     static_assert(W == 12 || W == 4, "tm_wait_ld is specialised for 3 or 1 state rows per lane");
     using CL = QConst<NX, NU>;
+    using PL = QLane<NX, NU>;
 #ifndef TMPC_CREG
 #define TMPC_CREG 1
 #endif
@@ -216,7 +217,9 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     double* s_pi = wbase + qp.off_pi + lane * 18;
     const uint32_t a_Mb = PI ? sa(s_pi) : a_sc + (CL::B_rm + sub * NU) * 8;   // row r: + r * MBS
     const uint32_t a_Mq = PI ? sa(s_pi) + RX * NU * 8 : a_sc + (CL::Quu_rm + usub * NU) * 8;
-    const double* scl = sc;                           // constants of the lane's instance: shared staging, or (PI) its block
+    const double* scl = sc;                           // constants of the lane's instance: shared staging, or (PI) its block + 2 sub
+    // element of the constants: offset `so` in the shared staging (QConst), element `li` of the lane's array (QLane)
+    auto cst = [&](int so, int li) -> const double* { return PI ? scl + PL::at(li, 0) : scl + so; };
     const uint32_t a_cq = sa(s_cq) + sub * 8;                                 // + i * NX * 8 ; row r: + r * 32
     const uint32_t a_cr = sa(s_cr) + usub * 8;                                // + i * NU * 8
     uint32_t a_slot = a_slotA;
@@ -390,17 +393,17 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 valid = nvalid; iter = 0; first = true; status = 1; fin = false;
                 step = 0; cont = false; fix = false;
                 if (PI) {                                 // constants of the new instance: registers + the lane's B / Quu_inv slot
-                    scl = qp.pi_blocks + nbb * CL::size;
-                    fr_BPf = urow ? scl[CL::BPf + usub] : 0.0;
-                    fr_Rd = urow ? scl[CL::Rd + usub] : 0.0;
+                    scl = qp.pi_blocks + nbb * PL::size + 2 * sub;
+                    fr_BPf = urow ? *cst(0, PL::BPf) : 0.0;
+                    fr_Rd = urow ? *cst(0, PL::Rd) : 0.0;
 #pragma unroll
                     for (int r = 0; r < RX; ++r) {
-                        fr_f[r] = scl[CL::f + r * 4 + sub]; fr_APf[r] = scl[CL::APf + r * 4 + sub]; fr_Qd[r] = scl[CL::Qd + r * 4 + sub];
+                        fr_f[r] = *cst(0, PL::f + r); fr_APf[r] = *cst(0, PL::APf + r); fr_Qd[r] = *cst(0, PL::Qd + r);
 #pragma unroll
-                        for (int k = 0; k < NU; ++k) s_pi[r * NU + k] = scl[CL::B_rm + (r * 4 + sub) * NU + k];
+                        for (int k = 0; k < NU; ++k) s_pi[r * NU + k] = *cst(0, PL::B_rm + r * NU + k);
                     }
 #pragma unroll
-                    for (int k = 0; k < NU; ++k) s_pi[RX * NU + k] = scl[CL::Quu_rm + usub * NU + k];
+                    for (int k = 0; k < NU; ++k) s_pi[RX * NU + k] = *cst(0, PL::Quu + k);
                 }
                 if (REFS == 2) {
                     xref_g = bv.Xref ? bv.Xref + nbb * bv.xref_stride + sub : nullptr;      // + i NX + 4 r
@@ -423,12 +426,12 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
 #pragma unroll
             for (int r = 0; r < RX; ++r) {
 #pragma unroll
-                for (int k = 0; k < NX; k += 2) ld2(scl + CL::AmBKt_rm + (r * 4 + sub) * NX + k, Mab[r][k], Mab[r][k + 1]);
+                for (int k = 0; k < NX; k += 2) ld2(cst(CL::AmBKt_rm + (r * 4 + sub) * NX + k, PL::AmBKt + r * NX + k), Mab[r][k], Mab[r][k + 1]);
 #pragma unroll
-                for (int k = 0; k < NU; ++k) Mkt[r][k] = scl[CL::Kinf_cm + (r * 4 + sub) * NU + k];
+                for (int k = 0; k < NU; ++k) Mkt[r][k] = *cst(CL::Kinf_cm + (r * 4 + sub) * NU + k, PL::Kinf_cm + r * NU + k);
             }
 #pragma unroll
-            for (int k = 0; k < NX; ++k) Mbt[k] = urow ? scl[CL::B_cm + usub * NX + k] : 0.0;
+            for (int k = 0; k < NX; ++k) Mbt[k] = urow ? *cst(CL::B_cm + usub * NX + k, PL::B_cm + k) : 0.0;
 
             double p[RX];
 #pragma unroll
@@ -580,10 +583,10 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
 #pragma unroll
             for (int r = 0; r < RX; ++r) {
 #pragma unroll
-                for (int k = 0; k < NX; k += 2) ld2(scl + CL::A_rm + (r * 4 + sub) * NX + k, Ma[r][k], Ma[r][k + 1]);
+                for (int k = 0; k < NX; k += 2) ld2(cst(CL::A_rm + (r * 4 + sub) * NX + k, PL::A + r * NX + k), Ma[r][k], Ma[r][k + 1]);
             }
 #pragma unroll
-            for (int k = 0; k < NX; ++k) Mk[k] = urow ? scl[CL::Kinf_rm + usub * NX + k] : 0.0;
+            for (int k = 0; k < NX; ++k) Mk[k] = urow ? *cst(CL::Kinf_rm + usub * NX + k, PL::Kinf_rm + k) : 0.0;
             // rows of B and of Quu_inv: registers where the variant has room for them (CREG), else re-read from
             // shared memory at every knot point.  Shared-memory bandwidth (4 bytes per lane per clock) is what the
             // two warps of a scheduler and their six neighbours contend for: 128 of the 336 bytes a lane reads per
@@ -593,9 +596,9 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
 #pragma unroll
                 for (int r = 0; r < RX; ++r)
 #pragma unroll
-                    for (int k = 0; k < NU; ++k) Mb[r][k] = scl[CL::B_rm + (r * 4 + sub) * NU + k];
+                    for (int k = 0; k < NU; ++k) Mb[r][k] = *cst(CL::B_rm + (r * 4 + sub) * NU + k, PL::B_rm + r * NU + k);
 #pragma unroll
-                for (int k = 0; k < NU; ++k) Mq[k] = scl[CL::Quu_rm + usub * NU + k];
+                for (int k = 0; k < NU; ++k) Mq[k] = *cst(CL::Quu_rm + usub * NU + k, PL::Quu + k);
             }
 
             double x[RX];
@@ -681,7 +684,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 } else if (NU == 4) { lds2<0>(a_Mq, mq[0], mq[1]); lds2<16>(a_Mq, mq[2], mq[3]); }
                 else {
 #pragma unroll
-                    for (int k = 0; k < NU; ++k) mq[k] = scl[CL::Quu_rm + usub * NU + k];
+                    for (int k = 0; k < NU; ++k) mq[k] = *cst(CL::Quu_rm + usub * NU + k, PL::Quu + k);
                 }
                 double yj = 0.0, zold = 0.0, ulo = 0.0, uhi = 0.0, crs = 0.0;
                 if (urow) {
@@ -731,7 +734,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                         else { lds2<2 * MBS>(a_Mb, mb[r][0], mb[r][1]); lds2<2 * MBS + 16>(a_Mb, mb[r][2], mb[r][3]); }
                     } else {
 #pragma unroll
-                        for (int k = 0; k < NU; ++k) mb[r][k] = scl[CL::B_rm + (r * 4 + sub) * NU + k];
+                        for (int k = 0; k < NU; ++k) mb[r][k] = *cst(CL::B_rm + (r * 4 + sub) * NU + k, PL::B_rm + r * NU + k);
                     }
                 }
                 if (urow) {
@@ -782,7 +785,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 else if (REFS == 1) p_term[r] = dsub(s_tq[r * 4 + sub], dmul(rho, vg[r]));
                 else {
                     double s = 0.0;
-                    if (xref_g) for (int k = 0; k < NX; ++k) s = fma(__ldg(xref_g - sub + (N - 1) * NX + k), scl[CL::Pinf_cm + (r * 4 + sub) * NX + k], s);
+                    if (xref_g) for (int k = 0; k < NX; ++k) s = fma(__ldg(xref_g - sub + (N - 1) * NX + k), *cst(CL::Pinf_cm + (r * 4 + sub) * NX + k, PL::Pinf + r * NX + k), s);
                     p_term[r] = dsub(-s, dmul(rho, vg[r]));
                 }
             }
@@ -902,32 +905,41 @@ cudaError_t launch_shape_pi(const BatchView& bv, const AdmmSettings& st, int col
     return launch_q<NX, NU, false, 2, false, true>(bv, st, pl, num_sms, stream);
 }
 
-// element-major per-instance cache [e][ld]  ->  one QConst-layout block per instance (what the kernel stages for shared
-// dynamics, so the sweeps read either through the same offsets)
+// element-major per-instance cache [e][ld]  ->  one lane-interleaved block per instance (QLane: what each lane of the
+// sub-warp reads, in 16-byte chunks dealt round-robin to the four lanes)
 template <int NX, int NU>
 __global__ void pi_pack_kernel(PerInstanceMats pm, long long ld, int B, double* __restrict__ blocks) {
-    using CL = QConst<NX, NU>;
+    using PL = QLane<NX, NU>;
+    constexpr int RX = NX / 4;
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= B) return;
-    double* o = blocks + static_cast<size_t>(b) * CL::size;
+    double* o = blocks + static_cast<size_t>(b) * PL::size;
     auto at = [&](const double* a, int e) { return a[static_cast<size_t>(e) * ld + b]; };
-    for (int idx = 0; idx < NX * NX; ++idx) {
-        const int row = idx / NX, k = idx % NX;
-        o[CL::A_rm + idx] = at(pm.A, k * NX + row);
-        o[CL::AmBKt_rm + idx] = at(pm.AmBKt, k * NX + row);
-        o[CL::Pinf_cm + idx] = at(pm.Pinf, idx);
+    for (int sub = 0; sub < 4; ++sub) {
+        auto put = [&](int idx, double v) { o[PL::at(idx, sub)] = v; };
+        for (int idx = 0; idx < PL::per_lane; ++idx) put(idx, 0.0);
+        for (int r = 0; r < RX; ++r) {
+            const int row = r * 4 + sub;
+            for (int k = 0; k < NX; ++k) {
+                put(PL::A + r * NX + k, at(pm.A, k * NX + row));
+                put(PL::AmBKt + r * NX + k, at(pm.AmBKt, k * NX + row));
+                put(PL::Pinf + r * NX + k, at(pm.Pinf, row * NX + k));
+            }
+            for (int k = 0; k < NU; ++k) {
+                put(PL::B_rm + r * NU + k, at(pm.B, k * NX + row));
+                put(PL::Kinf_cm + r * NU + k, at(pm.Kinf, row * NU + k));
+            }
+            put(PL::f + r, at(pm.f, row)); put(PL::APf + r, at(pm.APf, row)); put(PL::Qd + r, at(pm.Qd, row));
+        }
+        if (sub < NU) {
+            for (int k = 0; k < NX; ++k) {
+                put(PL::B_cm + k, at(pm.B, sub * NX + k));
+                put(PL::Kinf_rm + k, at(pm.Kinf, k * NU + sub));
+            }
+            for (int k = 0; k < NU; ++k) put(PL::Quu + k, at(pm.Quu_inv, k * NU + sub));
+            put(PL::BPf, at(pm.BPf, sub)); put(PL::Rd, at(pm.Rd, sub));
+        }
     }
-    for (int idx = 0; idx < NX * NU; ++idx) {
-        const int row = idx / NU, k = idx % NU;
-        o[CL::B_rm + idx] = at(pm.B, k * NX + row);
-        o[CL::B_cm + idx] = at(pm.B, idx);
-        const int j = idx / NX, kk = idx % NX;
-        o[CL::Kinf_rm + idx] = at(pm.Kinf, kk * NU + j);
-        o[CL::Kinf_cm + idx] = at(pm.Kinf, idx);
-    }
-    for (int idx = 0; idx < NU * NU; ++idx) o[CL::Quu_rm + idx] = at(pm.Quu_inv, (idx % NU) * NU + idx / NU);
-    for (int idx = 0; idx < NX; ++idx) { o[CL::f + idx] = at(pm.f, idx); o[CL::APf + idx] = at(pm.APf, idx); o[CL::Qd + idx] = at(pm.Qd, idx); }
-    for (int idx = 0; idx < NU; ++idx) { o[CL::BPf + idx] = at(pm.BPf, idx); o[CL::Rd + idx] = at(pm.Rd, idx); }
 }
 
 template <int NX, int NU>
@@ -959,8 +971,8 @@ cudaError_t launch_admm_tmem_rollout(const BatchView& bv, const AdmmSettings& st
 }
 
 long long tmem_pi_block_doubles(int nx, int nu) {
-    if (nx == 12 && nu == 4) return QConst<12, 4>::size;
-    if (nx == 4 && nu == 1) return QConst<4, 1>::size;
+    if (nx == 12 && nu == 4) return QLane<12, 4>::size;
+    if (nx == 4 && nu == 1) return QLane<4, 1>::size;
     return 0;
 }
 
