@@ -204,6 +204,24 @@ def test_solve_host_pipelined_matches_stepwise(orc):
         assert r0 == r1
         assert np.array_equal(st0, st1) and np.array_equal(it0, it1)
         assert np.array_equal(sol0.states, sol1.states) and np.array_equal(sol0.controls, sol1.controls)
+    # the same with per-instance dynamics (each chunk reads its own slice of the operand blocks)
+    base = problems_mod.quadrotor()
+    A = np.asfortranarray(base.A[:, :, None] * (1.0 + 0.05 * rng.uniform(-1, 1, (12, 12, B))))
+    Bm = np.asfortranarray(base.B[:, :, None] * (1.0 + 0.1 * rng.uniform(-1, 1, (12, 4, B))))
+    for sol in (ref, pip):
+        t.set_instance_dynamics(sol, A, Bm, None, base.Q, base.R)
+        assert sol.kernel == TMEM
+    for step, cold in enumerate((True, False)):
+        x0 = np.asfortranarray(c["x0"] * (1.0 - 0.1 * step))
+        t.set_x0(ref, x0)
+        if cold:
+            ref.reset()
+        r0 = t.solve(ref)
+        sol0 = t.get_solution(ref)
+        st0, it0 = ref.status()
+        r1, sol1, st1, it1 = pip.solve_host(x0, cold=cold, chunks=3)
+        assert r0 == r1 and np.array_equal(st0, st1) and np.array_equal(it0, it1)
+        assert np.array_equal(sol0.states, sol1.states) and np.array_equal(sol0.controls, sol1.controls)
     # small batch / other kernels: single chunk path
     c = cases.rocket(40, N=50)
     want = cases.run_checker(c, orc)
@@ -331,6 +349,42 @@ def test_per_instance_dynamics(orc):
                                           *[dp(a) for a in host]) == 0
             for d, hh in zip(dev, host):
                 assert np.array_equal(d, hh), f"instance {b}: device cache differs from the host cache"
-    # warm start keeps working per instance, and the rollout refuses per-instance dynamics
+    # warm start keeps working per instance
     t.set_x0(sol, np.asfortranarray(0.9 * x0))
     assert t.solve(sol) in (0, 1)
+
+
+def test_per_instance_dynamics_closed_loop(orc):
+    """Closed loop over B different systems (domain-randomised plant = the instance's own A, B, f): the fused rollout of
+    the TMEM kernel's PI variant, the launch sequence (TMEM and thread kernels) and, per instance, the oracle's closed
+    loop of a single-instance problem with that instance's matrices."""
+    import dataclasses
+    base = problems_mod.quadrotor()
+    B, N, nsteps = 7, 20, 6
+    rng = np.random.default_rng(23)
+    n, m = base.nx, base.nu
+    A = np.stack([base.A * (1.0 + 0.05 * rng.uniform(-1, 1, base.A.shape)) for _ in range(B)], axis=2)
+    Bm = np.stack([base.B * (1.0 + 0.2 * rng.uniform(-1, 1, base.B.shape)) for _ in range(B)], axis=2)
+    f = 0.005 * rng.uniform(-1, 1, (n, B))
+    x0 = np.asfortranarray(0.3 * rng.uniform(-1, 1, (n, B)))
+    want = []
+    for b in range(B):
+        sb = dataclasses.replace(base, A=np.asfortranarray(A[:, :, b]), B=np.asfortranarray(Bm[:, :, b]), f=f[:, b].copy())
+        cb = cases._base(sb, N, bounds=sb.bounds(N), x0=np.asfortranarray(x0[:, b:b + 1]), max_iter=25, nsteps=nsteps)
+        want.append(cases.run_checker(cb, orc))
+    w_it = np.hstack([w["iters"] for w in want]); w_st = np.hstack([w["ret"] for w in want])
+    w_xf = np.hstack([w["x_final"] for w in want])
+    assert (w_st == 0).any()
+    c = cases._base(base, N, bounds=base.bounds(N), x0=x0, max_iter=25)
+    for kernel, fused in ((TMEM, True), (TMEM, False), (THREAD, False)):
+        sol = cases.make_cuda_solver(c)
+        t.set_instance_dynamics(sol, A, Bm, f, base.Q, base.R)
+        sol.set_kernel(kernel)
+        assert sol.kernel == kernel
+        t.set_x0(sol, x0)
+        n0 = sol.launch_count
+        st, it, xf = _device_rollout(sol, nsteps, fused=fused)
+        if fused:
+            assert sol.launch_count - n0 <= 2, "the fused closed loop is one solve launch (+ at most a state conversion)"
+        assert np.array_equal(it, w_it) and np.array_equal(st, w_st), f"kernel {kernel} fused={fused}"
+        np.testing.assert_allclose(xf, w_xf, rtol=1e-5, atol=1e-6)

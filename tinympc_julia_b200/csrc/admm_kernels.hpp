@@ -72,6 +72,7 @@ struct RolloutArgs {
     double* x0_rw;          // plant state nx x B (the same memory as bv.x0)
     int* status_out;        // [nsteps][B], may be null
     int* iters_out;
+    const double* pi_blocks = nullptr;   // per-instance dynamics: the packed operand blocks (launch_tmem_pi_pack)
 };
 cudaError_t launch_admm_tmem_rollout(const BatchView& bv, const AdmmSettings& st, const RolloutArgs& ra, int* counter,
                                      int num_sms, cudaStream_t stream);
@@ -88,6 +89,8 @@ cudaError_t launch_state_convert(const BatchView& bv, bool to_instance_major, cu
 
 // ---- closed-loop plant step (rollout.cu): x0 <- A x0 + B Usol(:,0) + f, optional reference slide
 cudaError_t launch_plant_step(const BatchView& bv, double* x0_rw, cudaStream_t stream);
+cudaError_t launch_plant_step_per_instance(const BatchView& bv, const PerInstanceMats& pm, long long ld, double* x0_rw,
+                                           cudaStream_t stream);
 cudaError_t launch_record_step(const BatchView& bv, int* status_out, int* iters_out, cudaStream_t stream);
 
 }  // namespace tmpc

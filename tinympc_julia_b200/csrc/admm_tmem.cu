@@ -124,7 +124,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
 
     // ---------------- stage the shared constants once per CTA
     double* sc = smem + qp.off_consts;
-    static_assert(!PI || (REFS != 1 && !ROLL), "per-instance dynamics: references go through the per-instance path; no fused rollout");
+    static_assert(!PI || REFS != 1, "per-instance dynamics take references, shared or not, through the per-instance path");
     if (!PI)
     for (int idx = threadIdx.x; idx < NX * NX; idx += blockDim.x) {
         const int row = idx / NX, k = idx % NX;
@@ -280,9 +280,9 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             for (int r = 0; r < RX; ++r) {
                 double s1 = 0.0, s2 = 0.0;
 #pragma unroll
-                for (int k = 0; k < NX; ++k) s1 = fma(sc[CL::A_rm + (r * 4 + sub) * NX + k], xs[k], s1);
+                for (int k = 0; k < NX; ++k) s1 = fma(*cst(CL::A_rm + (r * 4 + sub) * NX + k, PL::A + r * NX + k), xs[k], s1);
 #pragma unroll
-                for (int k = 0; k < NU; ++k) s2 = fma(sc[CL::B_rm + (r * 4 + sub) * NU + k], u0[k], s2);
+                for (int k = 0; k < NU; ++k) s2 = fma(*cst(CL::B_rm + (r * 4 + sub) * NU + k, PL::B_rm + r * NU + k), u0[k], s2);
                 const double xn = dadd(dadd(s1, s2), fr_f[r]);
                 if (tr) x0r[r] = xn;
             }
@@ -946,15 +946,20 @@ template <int NX, int NU>
 cudaError_t launch_shape_roll(const BatchView& bv, const AdmmSettings& st, const RolloutArgs& ra, int* counter,
                               int num_sms, cudaStream_t stream) {
     QPlan pl;
-    const int refs = refs_mode(bv);
-    if (!make_qplan<NX, NU>(bv.N, refs, pl)) return cudaErrorInvalidConfiguration;
+    const int refs = ra.pi_blocks ? (refs_mode(bv) == 0 ? 0 : 2) : refs_mode(bv);
+    if (!make_qplan<NX, NU>(bv.N, refs, pl, ra.pi_blocks != nullptr)) return cudaErrorInvalidConfiguration;
     pl.qp.counter = counter;
     pl.qp.pri_thresh = st.abs_pri_tol;
     pl.qp.dua_thresh = dual_threshold_q(bv.rho, st.abs_dua_tol);
+    pl.qp.pi_blocks = ra.pi_blocks;
     pl.qp.nsteps = ra.nsteps; pl.qp.cold_install = ra.cold; pl.qp.slide = ra.slide;
     pl.qp.x0_rw = ra.x0_rw; pl.qp.status_out = ra.status_out; pl.qp.iters_out = ra.iters_out;
     cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(int), stream);
     if (e != cudaSuccess) return e;
+    if (ra.pi_blocks) {
+        if (refs == 0) return launch_q<NX, NU, false, 0, true, true>(bv, st, pl, num_sms, stream);
+        return launch_q<NX, NU, false, 2, true, true>(bv, st, pl, num_sms, stream);
+    }
     if (refs == 0) return launch_q<NX, NU, false, 0, true>(bv, st, pl, num_sms, stream);
     if (refs == 1) return launch_q<NX, NU, false, 1, true>(bv, st, pl, num_sms, stream);
     return launch_q<NX, NU, false, 2, true>(bv, st, pl, num_sms, stream);

@@ -657,7 +657,7 @@ int tmpc_batch_solve_host(tmpc_batch* h, const double* x0, int cold, double* X, 
         // waves each, so that a chunk runs at the efficiency of the full batch
         const int wave = h->num_sms * 64;
         int nch = chunks > 0 ? chunks : 4;
-        if (!tm || h->B < 3 * wave || h->per_instance) nch = 1;
+        if (!tm || h->B < 3 * wave) nch = 1;
         int chunk_size = h->B;
         if (nch > 1) {
             chunk_size = ((h->B + nch - 1) / nch + wave - 1) / wave * wave;
@@ -693,6 +693,10 @@ int tmpc_batch_solve_host(tmpc_batch* h, const double* x0, int cold, double* X, 
                 vc.status = v.status + b0; vc.iters = v.iters + b0;
                 cudaError_t e = (k == TMPC_KERNEL_TMEM2)
                     ? tmpc::launch_admm_tmem2(vc, h->st, was_cold ? 1 : 0, h->counter.p, h->num_sms, h->stream)
+                    : h->per_instance
+                    ? tmpc::launch_admm_tmem_pi(vc, h->st, was_cold ? 1 : 0,
+                                                h->pi_blocks.p + static_cast<size_t>(b0) * tmpc::tmem_pi_block_doubles(h->nx, h->nu),
+                                                h->counter.p, h->num_sms, h->stream)
                     : tmpc::launch_admm_tmem(vc, h->st, was_cold ? 1 : 0, h->counter.p, h->num_sms, h->stream);
                 if (e != cudaSuccess) throw CudaFail{e, "solve kernel launch"};
                 h->launches += 1;
@@ -797,7 +801,6 @@ int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_lo
             h->ext_x0 = nullptr;
         }
         if (h->st.check_termination == 0) { set_error("check_termination = 0 is not supported"); return TMPC_ERR_STATE; }
-        if (h->per_instance) { set_error("rollout with per-instance dynamics is not supported (the plant step uses the shared A, B, f)"); return TMPC_ERR_STATE; }
         ensure_aux_state(h);
         const int k = resolve_kernel(h);
         if (k < 0) { set_error("requested kernel does not support this problem"); return TMPC_ERR_STATE; }
@@ -806,14 +809,15 @@ int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_lo
             // one launch: every instance runs all its steps on the sub-warp that owns it (admm_tmem.cu, ROLL)
             tmpc::BatchView v = make_view(h);
             if (d_x_ref_long) { v.Xref = d_x_ref_long; v.xref_stride = ref_len; }
-            if (tmpc::tmem_kernel_supports(v, h->st)) {
+            if (h->per_instance ? tmpc::tmem_pi_kernel_supports(v, h->st) : tmpc::tmem_kernel_supports(v, h->st)) {
                 if (!h->state_im.p) { h->state_im.alloc(static_cast<size_t>(v.state_im_stride) * h->B); v.state_im = h->state_im.p; }
                 if (!h->state_zero && !h->state_in_im) {
                     cudaError_t ce = tmpc::launch_state_convert(v, true, s);
                     if (ce != cudaSuccess) throw CudaFail{ce, "state conversion"};
                     h->launches += 1;
                 }
-                tmpc::RolloutArgs ra{nsteps, h->state_zero ? 1 : 0, d_x_ref_long ? 1 : 0, h->x0.p, d_status_out, d_iters_out};
+                tmpc::RolloutArgs ra{nsteps, h->state_zero ? 1 : 0, d_x_ref_long ? 1 : 0, h->x0.p, d_status_out, d_iters_out,
+                                     h->per_instance ? h->pi_blocks.p : nullptr};
                 cudaError_t e = tmpc::launch_admm_tmem_rollout(v, h->st, ra, h->counter.p, h->num_sms, s);
                 if (e != cudaSuccess) throw CudaFail{e, "fused rollout launch"};
                 h->launches += 1;
@@ -832,7 +836,8 @@ int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_lo
                 if (e != cudaSuccess) throw CudaFail{e, "rollout record launch"};
                 h->launches += 1;
             }
-            e = tmpc::launch_plant_step(v, h->x0.p, s);
+            e = h->per_instance ? tmpc::launch_plant_step_per_instance(v, per_instance_view(h), h->ld, h->x0.p, s)
+                                : tmpc::launch_plant_step(v, h->x0.p, s);
             if (e != cudaSuccess) throw CudaFail{e, "rollout plant-step launch"};
             h->launches += 1;
         }

@@ -27,6 +27,25 @@ __global__ void plant_step_kernel(const __grid_constant__ BatchView bv, double* 
     for (int j = 0; j < nx; ++j) x[j] = xn[j];
 }
 
+// the same with each instance's own A, B, f (element-major [e][ld], tmpc_batch_set_instance_dynamics)
+__global__ void plant_step_pi_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ PerInstanceMats pm,
+                                     long long ld, double* __restrict__ x0) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= bv.B) return;
+    const int nx = bv.nx, nu = bv.nu;
+    double* x = x0 + static_cast<size_t>(b) * nx;
+    const double* u = bv.Usol + static_cast<size_t>(b) * nu * (bv.N - 1);
+    auto at = [&](const double* a, int e) { return __ldg(a + static_cast<size_t>(e) * ld + b); };
+    double xn[kThreadKernelMaxNx];
+    for (int j = 0; j < nx; ++j) {
+        double s1 = 0.0, s2 = 0.0;
+        for (int k = 0; k < nx; ++k) s1 = fma(at(pm.A, k * nx + j), x[k], s1);
+        for (int k = 0; k < nu; ++k) s2 = fma(at(pm.B, k * nx + j), u[k], s2);
+        xn[j] = dadd(dadd(s1, s2), at(pm.f, j));
+    }
+    for (int j = 0; j < nx; ++j) x[j] = xn[j];
+}
+
 __global__ void record_step_kernel(const __grid_constant__ BatchView bv, int* __restrict__ status_out,
                                    int* __restrict__ iters_out) {
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
@@ -40,6 +59,13 @@ __global__ void record_step_kernel(const __grid_constant__ BatchView bv, int* __
 cudaError_t launch_plant_step(const BatchView& bv, double* x0_rw, cudaStream_t stream) {
     const int block = 128, grid = (bv.B + block - 1) / block;
     plant_step_kernel<<<grid, block, 0, stream>>>(bv, x0_rw);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_plant_step_per_instance(const BatchView& bv, const PerInstanceMats& pm, long long ld, double* x0_rw,
+                                           cudaStream_t stream) {
+    const int block = 128, grid = (bv.B + block - 1) / block;
+    plant_step_pi_kernel<<<grid, block, 0, stream>>>(bv, pm, ld, x0_rw);
     return cudaGetLastError();
 }
 

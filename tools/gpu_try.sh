@@ -1,3 +1,2 @@
 mkdir -p gpurun_out
-QMI=20 timeout 600 python tools/gpu_perinstance.py 2>/dev/null | tee gpurun_out/perinst_mi20.json
-QMI=100 timeout 600 python tools/gpu_perinstance.py 2>/dev/null | tee gpurun_out/perinst.json
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -25 gpurun_out/pytest_gpu.log
