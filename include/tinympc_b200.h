@@ -174,7 +174,9 @@ int tmpc_batch_get_settings(tmpc_batch* h, double* tols, int* ints);
  * instance, operation by operation as the host path does (the Riccati stop rule makes the cache only 1e-5-converged, so
  * iteration-count parity needs the same arithmetic).  A nx x nx x B, Bdyn nx x nu x B, f nx x B or NULL, Q nx x nx [x B],
  * R nu x nu [x B] (qr_batch = 1 shared / B per instance); host pointers, Julia layout; rho as given to create.  Later
- * solves use the thread kernel with coalesced per-instance operands; nx <= 12, nu <= 4. */
+ * solves (tmpc_batch_solve*, tmpc_batch_solve_host, tmpc_batch_rollout_async with each instance's own plant) use the
+ * TMEM kernel reading one packed operand block per instance where its shapes apply (nx = 12 / nu = 4, nx = 4 / nu = 1,
+ * box constraints), else the thread kernel with coalesced per-instance operands; nx <= 12, nu <= 4. */
 int tmpc_batch_set_instance_dynamics(tmpc_batch* h, const double* A, const double* Bdyn, const double* f, const double* Q,
                                      const double* R, int qr_batch);
 int tmpc_batch_get_instance_cache(tmpc_batch* h, int b, double* Kinf, double* Pinf, double* Quu_inv, double* AmBKt,
