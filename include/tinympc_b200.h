@@ -131,6 +131,12 @@ int tmpc_compute_cache(const double* A, const double* Bdyn, const double* f, con
                        int nx, int nu, double* Kinf, double* Pinf, double* Quu_inv, double* AmBKt, double* APf,
                        double* BPf, double* Qd, double* Rd);
 
+/* The same for the reference's float build (`typedef float tinytype`): inputs rounded to float as in
+ * src/bindings.cpp:50-55, every operation in float; float values returned in doubles. */
+int tmpc_compute_cache_f32(const double* A, const double* Bdyn, const double* f, const double* Q, const double* R, double rho,
+                           int nx, int nu, double* Kinf, double* Pinf, double* Quu_inv, double* AmBKt, double* APf,
+                           double* BPf, double* Qd, double* Rd);
+
 /* Create a batch of B instances sharing A, B, f, Q, R, rho (same meaning as setup_solver) on
  * CUDA device `device` (-1 = current).  All instances start from the zero workspace tiny_setup
  * produces (reference: tiny_api.cpp:68-105); settings start at the Julia defaults
@@ -145,6 +151,13 @@ int tmpc_batch_update_settings(tmpc_batch* h, double abs_pri_tol, double abs_dua
                                int en_state_soc, int en_input_soc, int en_state_linear, int en_input_linear,
                                int adaptive_rho, double adaptive_rho_min, double adaptive_rho_max,
                                int adaptive_rho_enable_clipping);
+/* Arithmetic type of the solve = the reference's `tinytype` (tinympc/TinyMPC/src/tinympc/types.hpp:15: `typedef double
+ * tinytype`, float being its other build).  bits = 32: the setup is redone as the float build does it (problem data and
+ * rho rounded to float as in src/bindings.cpp:50-55, cache computed in float) and later solves run the float
+ * instantiation of the kernel, inputs rounded on load as in bindings.cpp:82,105,128 and results widened as in :172,194;
+ * the ABI stays double.  Only on a fresh / reset batch with shared dynamics; the float build runs the thread kernel. */
+int tmpc_batch_set_precision(tmpc_batch* h, int bits);   /* 32 or 64 (default) */
+int tmpc_batch_get_precision(tmpc_batch* h);
 int tmpc_batch_set_kernel(tmpc_batch* h, int kernel);   /* TMPC_KERNEL_*; AUTO picks TMEM, then SUBWARP, where they apply */
 int tmpc_batch_get_kernel(tmpc_batch* h);               /* kernel the next solve will run (resolved AUTO) */
 

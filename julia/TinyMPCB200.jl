@@ -13,7 +13,7 @@ using Libdl
 
 export TinyMPCBatchSolver, setup_batch, set_x0, set_x_ref, set_u_ref, set_bound_constraints, set_linear_constraints,
        set_cone_constraints, set_cache_terms, update_settings, reset!, solve, get_solution, get_status,
-       set_kernel, rollout!, solve_host, set_instance_dynamics, destroy!
+       set_kernel, set_precision, rollout!, solve_host, set_instance_dynamics, destroy!
 
 const lib_path = joinpath(dirname(@__DIR__), "lib", "libtinympc_jl." * Libdl.dlext)   # as reference src/TinyMPC.jl:12-13
 
@@ -113,6 +113,10 @@ set_cache_terms(s::TinyMPCBatchSolver, Kinf, Pinf, Quu_inv, AmBKt) =
 
 "cold start: back to the workspace `setup` leaves"
 reset!(s::TinyMPCBatchSolver) = check(ccall((:tmpc_batch_reset, lib_path), Int32, (Ptr{Cvoid},), s.handle), "Failed to reset")
+
+"arithmetic type of the solve: 64 (`typedef double tinytype`) or 32 (the reference's float build); right after `setup` / `reset!`"
+set_precision(s::TinyMPCBatchSolver, bits::Integer) =
+    check(ccall((:tmpc_batch_set_precision, lib_path), Int32, (Ptr{Cvoid}, Int32), s.handle, bits), "Failed to set precision")
 
 set_kernel(s::TinyMPCBatchSolver, k::Integer) =
     check(ccall((:tmpc_batch_set_kernel, lib_path), Int32, (Ptr{Cvoid}, Int32), s.handle, k), "Failed to select kernel")

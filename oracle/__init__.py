@@ -21,6 +21,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 ORACLE_SO = os.path.join(HERE, "liboracle.so")
+REFBATCH32_SO = os.path.join(HERE, "_ref", "libtinympc_refbatch32.so")
 REFBATCH_SO = os.path.join(HERE, "_ref", "libtinympc_refbatch.so")
 REFJL_SO = os.path.join(HERE, "_ref", "libtinympc_jl.so")
 REFERENCE_ROOT = "/root/reference"
@@ -205,7 +206,7 @@ def build(ref: bool = True, quiet: bool = True) -> None:
     skipped when that tree is absent (e.g. on the GPU box, which uses the prebuilt oracle/_ref)."""
     targets = ["oracle"]
     if ref and os.path.isdir(os.path.join(REFERENCE_ROOT, "tinympc", "TinyMPC", "src")):
-        targets.append("ref")
+        targets += ["ref", "ref32"]
     subprocess.run(["make", "-C", HERE, "-j8"] + targets, check=True,
                    stdout=subprocess.DEVNULL if quiet else None)
 
@@ -221,3 +222,11 @@ def load_ref() -> Optional[BatchLib]:
     if not os.path.exists(REFBATCH_SO):
         return None
     return BatchLib(REFBATCH_SO, "ref", "reference")
+
+
+def load_ref32() -> Optional[BatchLib]:
+    """The FLOAT build of the reference (`typedef float tinytype`; oracle/Makefile target ref32), same batch
+    contract with doubles at the boundary (cast where src/bindings.cpp casts), or None when it has not been built."""
+    if not os.path.exists(REFBATCH32_SO):
+        return None
+    return BatchLib(REFBATCH32_SO, "ref32", "reference-f32")

@@ -7,6 +7,11 @@
 // reference's own C ABI (src/bindings.cpp) is a process-wide singleton that hides
 // `solution->iter` and cannot run instances on several host threads.
 //
+// Precision: the file only assumes `tinytype` (types.hpp:15).  The float build of the reference
+// (oracle/Makefile target ref32: the same sources compiled against a types.hpp whose typedef reads `float`)
+// exports the same entry points with the prefix ref32_; inputs are cast double -> tinytype and the
+// results tinytype -> double exactly where src/bindings.cpp does (:50-55, :82, :105, :128, :172, :194).
+//
 // One TinySolver per host thread; instances are dealt to threads in contiguous blocks.
 // The per-solve "Solver converged in N iterations" line (admm.cpp:373) is silenced by
 // putting std::cout into a failed state for the duration of the run.
@@ -21,7 +26,21 @@
 
 #include "batch_problem.h"
 
+#ifndef REF_PREFIX
+#define REF_PREFIX ref
+#endif
+#define REF_CAT2(a, b) a##b
+#define REF_CAT(a, b) REF_CAT2(a, b)
+#define REF_SYM(name) REF_CAT(REF_PREFIX, name)
+
 namespace {
+
+// double (C ABI) -> tinytype
+template <class D> auto tt(const D &m) { return m.template cast<tinytype>(); }
+// tinytype matrix -> caller's double buffer
+template <class D> void to_double(double *dst, const D &m) {
+    for (Eigen::Index k = 0; k < m.size(); ++k) dst[k] = static_cast<double>(m.data()[k]);
+}
 
 using MapMat = Eigen::Map<const Eigen::Matrix<double, Eigen::Dynamic, Eigen::Dynamic>>;
 using MapVec = Eigen::Map<const Eigen::Matrix<double, Eigen::Dynamic, 1>>;
@@ -35,35 +54,35 @@ void free_solver(TinySolver *s) {
 // Build a solver the way bindings.cpp does, then apply constraints/settings from P.
 TinySolver *make_solver(const tmpc_problem *P) {
     const int nx = P->nx, nu = P->nu, N = P->N;
-    tinyMatrix A = MapMat(P->A, nx, nx), B = MapMat(P->B, nx, nu), f = MapMat(P->f, nx, 1);
-    tinyMatrix Q = MapMat(P->Q, nx, nx), R = MapMat(P->R, nu, nu);
+    tinyMatrix A = tt(MapMat(P->A, nx, nx)), B = tt(MapMat(P->B, nx, nu)), f = tt(MapMat(P->f, nx, 1));
+    tinyMatrix Q = tt(MapMat(P->Q, nx, nx)), R = tt(MapMat(P->R, nu, nu));
     TinySolver *s = nullptr;
-    if (tiny_setup(&s, A, B, f, Q, R, P->rho, nx, nu, N, 0) != 0) { free_solver(s); return nullptr; }
+    if (tiny_setup(&s, A, B, f, Q, R, static_cast<tinytype>(P->rho), nx, nu, N, 0) != 0) { free_solver(s); return nullptr; }
 
     if (P->x_min && !P->bounds_per_instance) {
-        tiny_set_bound_constraints(s, MapMat(P->x_min, nx, N), MapMat(P->x_max, nx, N),
-                                   MapMat(P->u_min, nu, N - 1), MapMat(P->u_max, nu, N - 1));
+        tiny_set_bound_constraints(s, tt(MapMat(P->x_min, nx, N)), tt(MapMat(P->x_max, nx, N)),
+                                   tt(MapMat(P->u_min, nu, N - 1)), tt(MapMat(P->u_max, nu, N - 1)));
     }
     if (P->num_state_cones > 0 || P->num_input_cones > 0) {
         // definition order is (state triple, input triple): tiny_api.cpp:166-168
         Eigen::VectorXi Acx = MapVecI(P->Acx, P->num_state_cones), qcx = MapVecI(P->qcx, P->num_state_cones);
         Eigen::VectorXi Acu = MapVecI(P->Acu, P->num_input_cones), qcu = MapVecI(P->qcu, P->num_input_cones);
-        tinyVector cx = MapVec(P->cx, P->num_state_cones), cu = MapVec(P->cu, P->num_input_cones);
+        tinyVector cx = tt(MapVec(P->cx, P->num_state_cones)), cu = tt(MapVec(P->cu, P->num_input_cones));
         tiny_set_cone_constraints(s, Acx, qcx, cx, Acu, qcu, cu);
     }
     if (P->num_state_linear > 0 || P->num_input_linear > 0) {
-        tinyMatrix Ax = MapMat(P->Alin_x, P->num_state_linear, nx), Au = MapMat(P->Alin_u, P->num_input_linear, nu);
-        tinyVector bx = MapVec(P->blin_x, P->num_state_linear), bu = MapVec(P->blin_u, P->num_input_linear);
+        tinyMatrix Ax = tt(MapMat(P->Alin_x, P->num_state_linear, nx)), Au = tt(MapMat(P->Alin_u, P->num_input_linear, nu));
+        tinyVector bx = tt(MapVec(P->blin_x, P->num_state_linear)), bu = tt(MapVec(P->blin_u, P->num_input_linear));
         tiny_set_linear_constraints(s, Ax, bx, Au, bu);
     }
     if (P->Kinf) {  // set_cache_terms semantics: bindings.cpp:277-280
-        s->cache->Kinf = MapMat(P->Kinf, nu, nx);
-        s->cache->Pinf = MapMat(P->Pinf, nx, nx);
-        s->cache->Quu_inv = MapMat(P->Quu_inv, nu, nu);
-        s->cache->AmBKt = MapMat(P->AmBKt, nx, nx);
+        s->cache->Kinf = tt(MapMat(P->Kinf, nu, nx));
+        s->cache->Pinf = tt(MapMat(P->Pinf, nx, nx));
+        s->cache->Quu_inv = tt(MapMat(P->Quu_inv, nu, nu));
+        s->cache->AmBKt = tt(MapMat(P->AmBKt, nx, nx));
     }
     TinySettings *st = s->settings;
-    st->abs_pri_tol = P->abs_pri_tol; st->abs_dua_tol = P->abs_dua_tol;
+    st->abs_pri_tol = static_cast<tinytype>(P->abs_pri_tol); st->abs_dua_tol = static_cast<tinytype>(P->abs_dua_tol);
     st->max_iter = P->max_iter; st->check_termination = P->check_termination;
     st->en_state_bound = P->en_state_bound; st->en_input_bound = P->en_input_bound;
     st->en_state_soc = P->en_state_soc; st->en_input_soc = P->en_input_soc;
@@ -86,7 +105,7 @@ void zero_workspace(TinySolver *s) {
 
 }  // namespace
 
-extern "C" int ref_batch_run(const tmpc_problem *P, int B, int nsteps, const double *x0, const double *Xref,
+extern "C" int REF_SYM(_batch_run)(const tmpc_problem *P, int B, int nsteps, const double *x0, const double *Xref,
                              const double *Uref, int ref_mode, int nthreads, int *ret, int *iters, double *Xsol,
                              double *Usol, double *x_final, double *seconds) {
     if (!P || B < 0 || nsteps < 1 || !x0) return 1;
@@ -111,24 +130,24 @@ extern "C" int ref_batch_run(const tmpc_problem *P, int B, int nsteps, const dou
         for (int b = lo; b < hi; ++b) {
             zero_workspace(s);
             if (P->x_min && P->bounds_per_instance) {
-                tiny_set_bound_constraints(s, MapMat(P->x_min + sx * b, nx, N), MapMat(P->x_max + sx * b, nx, N),
-                                           MapMat(P->u_min + su * b, nu, N - 1), MapMat(P->u_max + su * b, nu, N - 1));
+                tiny_set_bound_constraints(s, tt(MapMat(P->x_min + sx * b, nx, N)), tt(MapMat(P->x_max + sx * b, nx, N)),
+                                           tt(MapMat(P->u_min + su * b, nu, N - 1)), tt(MapMat(P->u_max + su * b, nu, N - 1)));
             }
-            x = MapVec(x0 + (size_t)nx * b, nx);
+            x = tt(MapVec(x0 + (size_t)nx * b, nx));
             if (ref_mode == TMPC_REF_SHARED) {
-                if (Xref) tiny_set_x_ref(s, MapMat(Xref, nx, N));
-                if (Uref) tiny_set_u_ref(s, MapMat(Uref, nu, N - 1));
+                if (Xref) tiny_set_x_ref(s, tt(MapMat(Xref, nx, N)));
+                if (Uref) tiny_set_u_ref(s, tt(MapMat(Uref, nu, N - 1)));
             } else if (ref_mode == TMPC_REF_PER_INSTANCE) {
-                if (Xref) tiny_set_x_ref(s, MapMat(Xref + sx * b, nx, N));
-                if (Uref) tiny_set_u_ref(s, MapMat(Uref + su * b, nu, N - 1));
+                if (Xref) tiny_set_x_ref(s, tt(MapMat(Xref + sx * b, nx, N)));
+                if (Uref) tiny_set_u_ref(s, tt(MapMat(Uref + su * b, nu, N - 1)));
             } else if (ref_mode == TMPC_REF_SLIDING) {
-                if (Uref) tiny_set_u_ref(s, MapMat(Uref, nu, N - 1));
+                if (Uref) tiny_set_u_ref(s, tt(MapMat(Uref, nu, N - 1)));
             }
             for (int k = 0; k < nsteps; ++k) {
                 tiny_set_x0(s, x);
                 if (ref_mode == TMPC_REF_SLIDING && Xref) {
                     const size_t len = (size_t)nx * (N + nsteps - 1);
-                    tiny_set_x_ref(s, MapMat(Xref + len * b + (size_t)nx * k, nx, N));
+                    tiny_set_x_ref(s, tt(MapMat(Xref + len * b + (size_t)nx * k, nx, N)));
                 }
                 const int r = tiny_solve(s);
                 if (ret) ret[(size_t)k * B + b] = r;
@@ -136,9 +155,9 @@ extern "C" int ref_batch_run(const tmpc_problem *P, int B, int nsteps, const dou
                 // Julia convention: apply the clamped first control, solution.u(:,0) (cartpole_example_mpc.jl:44-48)
                 x = s->work->Adyn * x + s->work->Bdyn * s->solution->u.col(0) + s->work->fdyn;
             }
-            if (Xsol) std::memcpy(Xsol + sx * b, s->solution->x.data(), sx * sizeof(double));
-            if (Usol) std::memcpy(Usol + su * b, s->solution->u.data(), su * sizeof(double));
-            if (x_final) std::memcpy(x_final + (size_t)nx * b, x.data(), nx * sizeof(double));
+            if (Xsol) to_double(Xsol + sx * b, s->solution->x);
+            if (Usol) to_double(Usol + su * b, s->solution->u);
+            if (x_final) to_double(x_final + (size_t)nx * b, x);
         }
     };
 
@@ -157,17 +176,17 @@ extern "C" int ref_batch_run(const tmpc_problem *P, int B, int nsteps, const dou
     return 0;
 }
 
-extern "C" int ref_get_cache(const tmpc_problem *P, double *Kinf, double *Pinf, double *Quu_inv, double *AmBKt,
+extern "C" int REF_SYM(_get_cache)(const tmpc_problem *P, double *Kinf, double *Pinf, double *Quu_inv, double *AmBKt,
                              double *APf, double *BPf) {
     TinySolver *s = make_solver(P);
     if (!s) return 3;
     const int nx = P->nx, nu = P->nu;
-    if (Kinf) std::memcpy(Kinf, s->cache->Kinf.data(), sizeof(double) * nu * nx);
-    if (Pinf) std::memcpy(Pinf, s->cache->Pinf.data(), sizeof(double) * nx * nx);
-    if (Quu_inv) std::memcpy(Quu_inv, s->cache->Quu_inv.data(), sizeof(double) * nu * nu);
-    if (AmBKt) std::memcpy(AmBKt, s->cache->AmBKt.data(), sizeof(double) * nx * nx);
-    if (APf) std::memcpy(APf, s->cache->APf.data(), sizeof(double) * nx);
-    if (BPf) std::memcpy(BPf, s->cache->BPf.data(), sizeof(double) * nu);
+    if (Kinf) to_double(Kinf, s->cache->Kinf);
+    if (Pinf) to_double(Pinf, s->cache->Pinf);
+    if (Quu_inv) to_double(Quu_inv, s->cache->Quu_inv);
+    if (AmBKt) to_double(AmBKt, s->cache->AmBKt);
+    if (APf) to_double(APf, s->cache->APf);
+    if (BPf) to_double(BPf, s->cache->BPf);
     free_solver(s);
     return 0;
 }

@@ -24,6 +24,8 @@ GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 # tolerance north_star states for tinytype = double
 RTOL, ATOL = 1e-5, 1e-6
+# ... and for tinytype = float
+RTOL_F32, ATOL_F32 = 1e-4, 1e-5
 
 
 def _base(sys_, N, **kw):
@@ -167,7 +169,7 @@ def run_checker(c, lib: oracle.BatchLib, nthreads=1):
     return lib.batch_run(to_oracle_problem(c), c["x0"], c["Xref"], c["Uref"], c["ref_mode"], c["nsteps"], nthreads)
 
 
-def make_cuda_solver(c, kernel=0, device=-1):
+def make_cuda_solver(c, kernel=0, device=-1, precision=64):
     """Drive the CUDA library through the Julia-mirror API, in the order a Julia user would."""
     import tinympc_julia_b200 as t
     s = c["sys"]
@@ -176,6 +178,8 @@ def make_cuda_solver(c, kernel=0, device=-1):
     t.setup(sol, s.A, s.B, s.f, s.Q, s.R, s.rho, s.nx, s.nu, c["N"], batch=B, device=device,
             abs_pri_tol=c["abs_pri_tol"], abs_dua_tol=c["abs_dua_tol"], max_iter=c["max_iter"],
             check_termination=bool(c["check_termination"]))
+    if precision != 64:
+        sol.set_precision(precision)
     if c["cache"] is not None:
         k = c["cache"]
         t.set_cache_terms(sol, k["Kinf"], k["Pinf"], k["Quu_inv"], k["AmBKt"])
@@ -199,7 +203,7 @@ def make_cuda_solver(c, kernel=0, device=-1):
     return sol
 
 
-def run_cuda(c, kernel=0, sol=None):
+def run_cuda(c, kernel=0, sol=None, precision=64):
     """Returns the same dict layout as the checkers (ret, iters [nsteps,B], X, U, x_final)."""
     import tinympc_julia_b200 as t
     s = c["sys"]
@@ -208,7 +212,7 @@ def run_cuda(c, kernel=0, sol=None):
     B = x0.shape[1]
     nsteps = c["nsteps"]
     if sol is None:
-        sol = make_cuda_solver(c, kernel)
+        sol = make_cuda_solver(c, kernel, precision=precision)
     mode = c["ref_mode"]
     if mode in (oracle.REF_SHARED, oracle.REF_PER_INSTANCE):
         if c["Xref"] is not None:
@@ -260,6 +264,46 @@ def compare(got, want, what="", rtol=RTOL, atol=ATOL, allow_iter_mismatch=0):
     return nbad_ret, nbad_it
 
 
+def golden_f32_case(name):
+    """(case with the float reference's cache installed, fixture) for one of GOLDEN_F32_CASES."""
+    g = load_golden("f32_" + name)
+    c = GOLDEN_CASES[name]()
+    n, m = c["sys"].nx, c["sys"].nu
+    c["cache"] = {"Kinf": g["cache_Kinf"].reshape(m, n, order="F"), "Pinf": g["cache_Pinf"].reshape(n, n, order="F"),
+                  "Quu_inv": g["cache_Quu_inv"].reshape(m, m, order="F"), "AmBKt": g["cache_AmBKt"].reshape(n, n, order="F")}
+    return c, g
+
+
+def compare_f32(got, want, what="", max_flip_frac=0.02):
+    """Float build.  The CUDA kernel and the float reference round differently inside the mat-vecs (Eigen sums float
+    packets of 8, the kernel one ascending FMA chain), so an instance whose residual lands within a few float ulps of
+    the tolerance can stop one iteration apart: at most `max_flip_frac` of the instances (and at least one allowed),
+    each by at most 2 iterations.  Instances that stop at the same iteration: states / controls within north_star's
+    float tolerance (1e-4 relative / 1e-5 absolute) when the solve converged within 20 iterations; within 10x that
+    for longer solves and for those that ran into max_iter (the two roundings differ by a float ulp per operation and
+    the difference compounds over every iteration: measured on B200, quadrotor x0 ~ U(+-0.5), a solve that converges
+    after 40-90 iterations ends up to 1.2e-5 away in absolute terms).  Returns (flips, worst excess over the tight
+    tolerance among the short converged solves)."""
+    gi, wi = got["iters"][-1], want["iters"][-1]
+    same = (gi == wi) & (got["ret"][-1] == want["ret"][-1])
+    nflip = int((~same).sum())
+    assert nflip <= max(1, int(max_flip_frac * same.size)), f"{what}: {nflip} of {same.size} instances stop at another iteration"
+    assert np.abs(gi - wi).max() <= 2, f"{what}: iteration counts differ by {np.abs(gi - wi).max()}"
+    conv = same & (want["ret"][-1] == 0) & (wi <= 20)
+    unconv = same & ~conv
+    worst = 0.0
+    for key in ("X", "U"):
+        for sel, k in ((conv, 1.0), (unconv, 10.0)):
+            g, w = got[key][..., sel], want[key][..., sel]
+            if g.size == 0:
+                continue
+            err = np.abs(g - w) - k * (ATOL_F32 + RTOL_F32 * np.abs(w))
+            assert err.max() <= 0, f"{what}: {key} out of the float tolerance (x{k:g}) by {err.max():.3e}"
+            if k == 1.0:
+                worst = max(worst, float(err.max()))
+    return nflip, worst
+
+
 # ------------------------------------------------------------------------------------------ golden fixtures
 # name -> zero-argument constructor.  tests/golden/make_golden.py runs the COMPILED REFERENCE on each and
 # stores its outputs in tests/golden/<name>.npz; the tests re-create the inputs from the same seeds.
@@ -287,6 +331,14 @@ SURVEY_GOLDEN = {
     "quadrotor_hover": dict(ret=1, iter=100, u0=[0.5, 0.5, 0.5, 0.5]),
     "rocket_julia_example": dict(ret=0, iter=37, u0=[12.34232183, -10.0, 65.2407144]),
 }
+
+
+# float build (`typedef float tinytype`): single cold solves of these cases through oracle/_ref/libtinympc_refbatch32.so;
+# the fixtures (tests/golden/f32_<name>.npz) also hold the float reference's Riccati cache, which the tests install
+# through set_cache_terms (the cache is only 1e-5-converged, so parity needs identical cache inputs)
+GOLDEN_F32_CASES = ["cartpole_one_solve", "cartpole_test_basic_bounds", "cartpole_batch_64", "quadrotor_hover",
+                    "quadrotor_easy_64", "quadrotor_hard_64", "rocket_julia_example", "rocket_soc_linear_16",
+                    "rocket_soc_16_N20", "random_5x2_16", "random_9x3_16"]
 
 
 def load_golden(name):

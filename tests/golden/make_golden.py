@@ -43,6 +43,19 @@ def main():
                             x_final=out["x_final"], digest=np.array(digest(c)))
         print(f"{name:32s} B={c['x0'].shape[1]:4d} steps={c['nsteps']:3d} iters[min/max]={out['iters'].min()}/{out['iters'].max()} "
               f"solved={(out['ret'] == 0).mean():.2f}")
+    # ---- float build of the reference (oracle/Makefile target ref32)
+    ref32 = oracle.load_ref32()
+    if ref32 is None:
+        raise SystemExit("oracle/_ref/libtinympc_refbatch32.so is not built: run `make -C oracle ref32`")
+    for name in cases.GOLDEN_F32_CASES:
+        c = cases.GOLDEN_CASES[name]()
+        out = cases.run_checker(c, ref32)
+        cache = ref32.get_cache(cases.to_oracle_problem(c))
+        np.savez_compressed(os.path.join(HERE, "f32_" + name + ".npz"), ret=out["ret"], iters=out["iters"], X=out["X"],
+                            U=out["U"], x_final=out["x_final"], digest=np.array(digest(c)),
+                            **{"cache_" + k: v for k, v in cache.items()})
+        print(f"f32 {name:28s} B={c['x0'].shape[1]:4d} iters[min/max]={out['iters'].min()}/{out['iters'].max()} "
+              f"solved={(out['ret'] == 0).mean():.2f}")
 
 
 if __name__ == "__main__":

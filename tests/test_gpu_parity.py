@@ -388,3 +388,54 @@ def test_per_instance_dynamics_closed_loop(orc):
             assert sol.launch_count - n0 <= 2, "the fused closed loop is one solve launch (+ at most a state conversion)"
         assert np.array_equal(it, w_it) and np.array_equal(st, w_st), f"kernel {kernel} fused={fused}"
         np.testing.assert_allclose(xf, w_xf, rtol=1e-5, atol=1e-6)
+
+
+# ------------------------------------------------------------------------------------------ float build
+# `typedef float tinytype` (reference types.hpp:15).  Checker: the reference itself compiled with the
+# float typedef (oracle/_ref/libtinympc_refbatch32.so) — committed outputs in tests/golden/f32_*.npz, the live library
+# where oracle/_ref travelled to this box.  Tolerance: cases.compare_f32.
+
+@pytest.mark.parametrize("name", cases.GOLDEN_F32_CASES)
+def test_float_build_matches_float_reference_fixture(name):
+    c, want = cases.golden_f32_case(name)
+    got = cases.run_cuda(c, kernel=THREAD, precision=32)
+    for k in ("X", "U"):
+        assert np.array_equal(got[k], got[k].astype(np.float32).astype(np.float64)), "results must be floats widened to double"
+    cases.compare_f32(got, want, what=f"cuda float vs float reference[{name}]")
+
+
+def test_float_build_seeded_batches_against_live_float_reference():
+    import oracle
+    ref32 = oracle.load_ref32()
+    if ref32 is None:
+        pytest.skip("oracle/_ref/libtinympc_refbatch32.so did not travel to this box")
+    for make, B in ((cases.cartpole_batch, 3000), (cases.quadrotor_batch, 3000),
+                    (lambda B: cases.quadrotor_batch(B, hard=True), 2000), (lambda B: cases.rocket(B, N=50), 200)):
+        c = make(B)
+        cache = ref32.get_cache(cases.to_oracle_problem(c))
+        c["cache"] = {k: cache[k] for k in ("Kinf", "Pinf", "Quu_inv", "AmBKt")}
+        want = cases.run_checker(c, ref32, nthreads=8)
+        got = cases.run_cuda(c, kernel=THREAD, precision=32)
+        cases.compare_f32(got, want, what=f"cuda float vs live float reference (B={B})")
+
+
+def test_float_build_warm_start_and_guards():
+    """A second solve warm-starts from float state held in the double arrays; the float build runs the thread kernel
+    only and says so; switching precision needs a reset batch."""
+    c, _ = cases.golden_f32_case("quadrotor_easy_64")
+    sol = cases.make_cuda_solver(c, kernel=THREAD, precision=32)
+    assert sol.precision == 32 and sol.kernel == THREAD
+    first = cases.run_cuda(c, sol=sol)
+    again = cases.run_cuda(c, sol=sol)                      # same x0, warm start: converges at once or nearly
+    assert again["iters"].max() <= first["iters"].min()
+    with pytest.raises(t.TinyMPCError):
+        sol.set_precision(64)                               # carries state
+    sol.set_kernel(TMEM)
+    assert sol.kernel == -1                                 # the on-chip kernels are 64-bit only
+    assert t.solve(sol) not in (0, 1)                       # refused, not silently run on another kernel
+    sol.set_kernel(THREAD)
+    sol.reset()
+    sol.set_precision(64)
+    sol.set_kernel(t.KERNEL_AUTO)
+    back = cases.run_cuda(cases.GOLDEN_CASES["quadrotor_easy_64"](), sol=sol)
+    cases.compare(back, cases.load_golden("quadrotor_easy_64"), what="double again after set_precision(64)")

@@ -41,9 +41,12 @@ SIGNATURES = {
     "get_solve_info": (_I, [_IP, _IP]),
     # PART 2: batched variants
     "tmpc_compute_cache": (_I, [_P, _P, _P, _P, _P, _D, _I, _I] + [_P] * 8),
+    "tmpc_compute_cache_f32": (_I, [_P, _P, _P, _P, _P, _D, _I, _I] + [_P] * 8),
     "tmpc_batch_create": (_I, [C.POINTER(_V), _P, _P, _P, _P, _P, _D, _I, _I, _I, _I, _I, _I]),
     "tmpc_batch_destroy": (_I, [_V]),
     "tmpc_batch_update_settings": (_I, [_V, _D, _D, _I, _I, _I, _I, _I, _I, _I, _I, _I, _D, _D, _I]),
+    "tmpc_batch_set_precision": (_I, [_V, _I]),
+    "tmpc_batch_get_precision": (_I, [_V]),
     "tmpc_batch_set_kernel": (_I, [_V, _I]),
     "tmpc_batch_get_kernel": (_I, [_V]),
     "tmpc_batch_set_x0": (_I, [_V, _P, _I, _I]),

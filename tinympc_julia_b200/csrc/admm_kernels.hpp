@@ -34,9 +34,12 @@ cudaError_t launch_riccati_cache(int nx, int nu, int B, long long ld, double rho
 
 // ---- one thread per instance (admm_thread.cu)
 bool thread_kernel_supports(int nx, int nu);
+// `precision` = 64 (the reference's default `typedef double tinytype`) or 32 (its float build): the arithmetic type of
+// the solve; the arrays in HBM are double either way.
 cudaError_t launch_admm_thread_per_instance(const BatchView& bv, const AdmmSettings& st, const PerInstanceMats& pm,
-                                            cudaStream_t stream);
-cudaError_t launch_admm_thread(const BatchView& bv, const AdmmSettings& st, const HostMats& h, cudaStream_t stream);
+                                            cudaStream_t stream, int precision = 64);
+cudaError_t launch_admm_thread(const BatchView& bv, const AdmmSettings& st, const HostMats& h, cudaStream_t stream,
+                               int precision = 64);
 
 // ---- one instance per 4-lane sub-warp, shared-memory resident (admm_subwarp.cu)
 // Applies to box-constrained problems (no cone / half-space flags) of a compiled-in shape.

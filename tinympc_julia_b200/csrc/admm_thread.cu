@@ -28,27 +28,60 @@ namespace tmpc {
 
 namespace {
 
+// ---------------------------------------------------------------- arithmetic at the reference's `tinytype`
+// The reference's precision is one typedef (types.hpp:15, `typedef double tinytype`; float is the other supported
+// value).  The kernel is instantiated for both: T = double is the default build of the reference, T = float its
+// float build.  In the float instantiation every input is rounded to float where
+// src/bindings.cpp casts (:50-55, :82, :105, :128) and results widen back to double (:172, :194); the arrays in HBM
+// stay double (a float widens exactly), so the two precisions share the runtime, the layouts and the C ABI.
+template <class T> struct Ar;
+template <> struct Ar<double> {
+    static __device__ __forceinline__ double add(double a, double b) { return __dadd_rn(a, b); }
+    static __device__ __forceinline__ double sub(double a, double b) { return __dsub_rn(a, b); }
+    static __device__ __forceinline__ double mul(double a, double b) { return __dmul_rn(a, b); }
+    static __device__ __forceinline__ double div(double a, double b) { return __ddiv_rn(a, b); }
+    static __device__ __forceinline__ double fma(double a, double b, double c) { return ::fma(a, b, c); }
+    static __device__ __forceinline__ double abs(double a) { return ::fabs(a); }
+    static __device__ __forceinline__ double max(double a, double b) { return ::fmax(a, b); }
+    static __device__ __forceinline__ double sqrt(double a) { return ::sqrt(a); }
+    static __device__ __forceinline__ double clamp(double t, double lo, double hi) { return clampd(t, lo, hi); }
+};
+template <> struct Ar<float> {
+    static __device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
+    static __device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
+    static __device__ __forceinline__ float mul(float a, float b) { return __fmul_rn(a, b); }
+    static __device__ __forceinline__ float div(float a, float b) { return __fdiv_rn(a, b); }
+    static __device__ __forceinline__ float fma(float a, float b, float c) { return ::fmaf(a, b, c); }
+    static __device__ __forceinline__ float abs(float a) { return ::fabsf(a); }
+    static __device__ __forceinline__ float max(float a, float b) { return ::fmaxf(a, b); }
+    static __device__ __forceinline__ float sqrt(float a) { return __fsqrt_rn(a); }
+    static __device__ __forceinline__ float clamp(float t, float lo, float hi) {
+        const float w = (lo < t) ? t : lo;       // std::max(lo, t)
+        return (w < hi) ? w : hi;                // std::min(hi, w)
+    }
+};
+
 // ---------------------------------------------------------------- matrix operand providers
-template <int NX, int NU>
+template <class T, int NX, int NU>
 struct MatsConst {           // by-value kernel parameter -> constant bank
     static constexpr int kMaxNx = NX, kMaxNu = NU;
     static constexpr bool kStatic = true;
     __device__ __forceinline__ const MatsConst& bound(int) const { return *this; }
-    double A_[NX * NX], B_[NX * NU], Kinf_[NU * NX], AmBKt_[NX * NX], Quu_inv_[NU * NU], Pinf_[NX * NX];
-    double f_[NX], APf_[NX], BPf_[NU], Qd_[NX], Rd_[NU];
+    T A_[NX * NX], B_[NX * NU], Kinf_[NU * NX], AmBKt_[NX * NX], Quu_inv_[NU * NU], Pinf_[NX * NX];
+    T f_[NX], APf_[NX], BPf_[NU], Qd_[NX], Rd_[NU];
     __device__ __forceinline__ int nx() const { return NX; }
     __device__ __forceinline__ int nu() const { return NU; }
-    __device__ __forceinline__ double A(int i, int k) const { return A_[k * NX + i]; }
-    __device__ __forceinline__ double B(int i, int k) const { return B_[k * NX + i]; }
-    __device__ __forceinline__ double Kinf(int i, int k) const { return Kinf_[k * NU + i]; }
-    __device__ __forceinline__ double AmBKt(int i, int k) const { return AmBKt_[k * NX + i]; }
-    __device__ __forceinline__ double Quu_inv(int i, int k) const { return Quu_inv_[k * NU + i]; }
-    __device__ __forceinline__ double Pinf(int i, int k) const { return Pinf_[k * NX + i]; }
-    __device__ __forceinline__ double f(int i) const { return f_[i]; }
-    __device__ __forceinline__ double APf(int i) const { return APf_[i]; }
-    __device__ __forceinline__ double BPf(int i) const { return BPf_[i]; }
-    __device__ __forceinline__ double Qd(int i) const { return Qd_[i]; }
-    __device__ __forceinline__ double Rd(int i) const { return Rd_[i]; }
+    __device__ __forceinline__ T A(int i, int k) const { return A_[k * NX + i]; }
+    __device__ __forceinline__ T B(int i, int k) const { return B_[k * NX + i]; }
+    __device__ __forceinline__ T Kinf(int i, int k) const { return Kinf_[k * NU + i]; }
+    __device__ __forceinline__ T AmBKt(int i, int k) const { return AmBKt_[k * NX + i]; }
+    __device__ __forceinline__ T Quu_inv(int i, int k) const { return Quu_inv_[k * NU + i]; }
+    __device__ __forceinline__ T Pinf(int i, int k) const { return Pinf_[k * NX + i]; }
+    __device__ __forceinline__ T f(int i) const { return f_[i]; }
+    __device__ __forceinline__ T APf(int i) const { return APf_[i]; }
+    __device__ __forceinline__ T BPf(int i) const { return BPf_[i]; }
+    __device__ __forceinline__ T Qd(int i) const { return Qd_[i]; }
+    __device__ __forceinline__ T Rd(int i) const { return Rd_[i]; }
 };
 
 struct MatsGlobal {          // runtime dimensions: uniform loads through the read-only path
@@ -100,42 +133,47 @@ struct MatsPerInstance {
 
 // Second-order-cone projection of a 3-block, with the reference's mixed precision: mu and the
 // norm are rounded to float (reference admm.cpp:39,42), the last entry comes from a float division (:54).
-__device__ __forceinline__ void project_soc3(double* s, double mu_d) {
+template <class T>
+__device__ __forceinline__ void project_soc3(T* s, double mu_d) {
+    using R = Ar<T>;
     const float mu = static_cast<float>(mu_d);
-    const double u0 = dmul(s[2], static_cast<double>(mu));
-    const float a = static_cast<float>(sqrt(dadd(dmul(s[0], s[0]), dmul(s[1], s[1]))));
-    const double ad = static_cast<double>(a);
+    const T u0 = R::mul(s[2], static_cast<T>(mu));
+    const float a = static_cast<float>(R::sqrt(R::add(R::mul(s[0], s[0]), R::mul(s[1], s[1]))));
+    const T ad = static_cast<T>(a);
     if (ad <= -u0) {
-        s[0] = 0.0; s[1] = 0.0; s[2] = 0.0;
+        s[0] = 0; s[1] = 0; s[2] = 0;
     } else if (ad <= u0) {
         // inside the cone: unchanged
     } else {
-        const double scale = dmul(0.5, dadd(1.0, u0 / ad));
-        const double last = static_cast<double>(a / mu);
-        s[0] = dmul(scale, s[0]); s[1] = dmul(scale, s[1]); s[2] = dmul(scale, last);
+        const T scale = R::mul(T(0.5), R::add(T(1), R::div(u0, ad)));
+        const T last = static_cast<T>(__fdiv_rn(a, mu));
+        s[0] = R::mul(scale, s[0]); s[1] = R::mul(scale, s[1]); s[2] = R::mul(scale, last);
     }
 }
 
 // Sequential (Gauss-Seidel) half-space projections, reference admm.cpp:148-173.
-__device__ __forceinline__ void project_halfspaces(double* col, int len, const double* __restrict__ Alin,
+template <class T>
+__device__ __forceinline__ void project_halfspaces(T* col, int len, const double* __restrict__ Alin,
                                                    const double* __restrict__ blin, int nrows) {
     for (int k = 0; k < nrows; ++k) {
-        double dot = 0.0;
-        for (int j = 0; j < len; ++j) dot = fma(__ldg(Alin + j * nrows + k), col[j], dot);
-        const double bk = __ldg(blin + k);
+        using R = Ar<T>;
+        T dot = 0;
+        for (int j = 0; j < len; ++j) dot = R::fma(static_cast<T>(__ldg(Alin + j * nrows + k)), col[j], dot);
+        const T bk = static_cast<T>(__ldg(blin + k));
         if (dot > bk) {
-            double sq = 0.0;
-            for (int j = 0; j < len; ++j) { const double a = __ldg(Alin + j * nrows + k); sq = fma(a, a, sq); }
-            const double dist = dsub(dot, bk) / sq;
-            for (int j = 0; j < len; ++j) col[j] = dsub(col[j], dmul(dist, __ldg(Alin + j * nrows + k)));
+            T sq = 0;
+            for (int j = 0; j < len; ++j) { const T a = static_cast<T>(__ldg(Alin + j * nrows + k)); sq = R::fma(a, a, sq); }
+            const T dist = R::div(R::sub(dot, bk), sq);
+            for (int j = 0; j < len; ++j) col[j] = R::sub(col[j], R::mul(dist, static_cast<T>(__ldg(Alin + j * nrows + k))));
         }
     }
 }
 
-template <class M>
+template <class T, class M>
 __global__ void __launch_bounds__(kThreadKernelBlock)
 admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ BatchView bv,
                    const __grid_constant__ AdmmSettings st) {
+    using R = Ar<T>;
     constexpr int MX = M::kMaxNx, MU = M::kMaxNu;
     constexpr int UNR = M::kStatic ? 64 : 1;   // full unroll for compiled-in shapes, rolled loops otherwise
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
@@ -143,7 +181,8 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
     const auto& mt = mt_param.bound(b);        // per-instance dynamics: operands of THIS instance; else the parameter itself
     const int nx = mt.nx(), nu = mt.nu(), N = bv.N;
     const size_t ld = static_cast<size_t>(bv.ld);
-    const double rho = bv.rho;
+    const T rho = static_cast<T>(bv.rho);                       // bindings.cpp:55
+    const T tol_pri = static_cast<T>(st.abs_pri_tol), tol_dua = static_cast<T>(st.abs_dua_tol);   // types.hpp:64-65
 #define ST(arr, e) (arr)[static_cast<size_t>(e) * ld + b]
 
     if (st.max_iter <= 0) {   // the reference's loop does not run: solution keeps the previous slacks
@@ -165,8 +204,8 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
     const double* umin = box_u ? bv.u_min + static_cast<size_t>(b) * bv.ub_stride : nullptr;
     const double* umax = box_u ? bv.u_max + static_cast<size_t>(b) * bv.ub_stride : nullptr;
 
-    double p[MX], x[MX], tmp[MX], acc[MX], u[MU], t[MU], rr[MU];
-    double vc[MX];   // cone / half-space slack column (state or input)
+    T p[MX], x[MX], tmp[MX], acc[MX], u[MU], t[MU], rr[MU];
+    T vc[MX];   // cone / half-space slack column (state or input)
 
 #pragma unroll UNR
     for (int j = 0; j < MX; ++j) if (j < nx) p[j] = ST(bv.pN, j);
@@ -187,26 +226,26 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
             for (int j = 0; j < MU; ++j) if (j < nu) rr[j] = ST(bv.r, i * nu + j);
 #pragma unroll UNR
             for (int j = 0; j < MU; ++j) if (j < nu) {
-                double s = 0.0;
+                T s = 0;
 #pragma unroll UNR
-                for (int k = 0; k < MX; ++k) if (k < nx) s = fma(mt.B(k, j), p[k], s);
-                t[j] = dadd(dadd(s, rr[j]), mt.BPf(j));
+                for (int k = 0; k < MX; ++k) if (k < nx) s = R::fma(mt.B(k, j), p[k], s);
+                t[j] = R::add(R::add(s, rr[j]), mt.BPf(j));
             }
 #pragma unroll UNR
             for (int j = 0; j < MU; ++j) if (j < nu) {
-                double s = 0.0;
+                T s = 0;
 #pragma unroll UNR
-                for (int k = 0; k < MU; ++k) if (k < nu) s = fma(mt.Quu_inv(j, k), t[k], s);
+                for (int k = 0; k < MU; ++k) if (k < nu) s = R::fma(mt.Quu_inv(j, k), t[k], s);
                 ST(bv.d, i * nu + j) = s;
             }
 #pragma unroll UNR
             for (int j = 0; j < MX; ++j) if (j < nx) {
-                double s1 = 0.0, s2 = 0.0;
+                T s1 = 0.0, s2 = 0.0;
 #pragma unroll UNR
-                for (int k = 0; k < MX; ++k) if (k < nx) s1 = fma(mt.AmBKt(j, k), p[k], s1);
+                for (int k = 0; k < MX; ++k) if (k < nx) s1 = R::fma(mt.AmBKt(j, k), p[k], s1);
 #pragma unroll UNR
-                for (int k = 0; k < MU; ++k) if (k < nu) s2 = fma(mt.Kinf(k, j), rr[k], s2);
-                tmp[j] = dadd(dsub(dadd(ST(bv.q, i * nx + j), s1), s2), mt.APf(j));
+                for (int k = 0; k < MU; ++k) if (k < nu) s2 = R::fma(mt.Kinf(k, j), rr[k], s2);
+                tmp[j] = R::add(R::sub(R::add(ST(bv.q, i * nx + j), s1), s2), mt.APf(j));
             }
 #pragma unroll UNR
             for (int j = 0; j < MX; ++j) if (j < nx) p[j] = tmp[j];
@@ -215,7 +254,7 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
         // ---------------- forward pass fused with slack / dual / linear-cost / residual updates
 #pragma unroll UNR
         for (int j = 0; j < MX; ++j) if (j < nx) x[j] = bv.x0[static_cast<size_t>(b) * nx + j];
-        double pri_x = 0.0, dua_x = 0.0, pri_u = 0.0, dua_u = 0.0;
+        T pri_x = 0, dua_x = 0, pri_u = 0, dua_u = 0;
 
         for (int i = 0; i < N; ++i) {
             const bool terminal = (i == N - 1);
@@ -223,49 +262,49 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
                 // u_i = -Kinf x_i - d_i
 #pragma unroll UNR
                 for (int j = 0; j < MU; ++j) if (j < nu) {
-                    double s = 0.0;
+                    T s = 0;
 #pragma unroll UNR
-                    for (int k = 0; k < MX; ++k) if (k < nx) s = fma(mt.Kinf(j, k), x[k], s);
-                    u[j] = dsub(-s, ST(bv.d, i * nu + j));
+                    for (int k = 0; k < MX; ++k) if (k < nx) s = R::fma(mt.Kinf(j, k), x[k], s);
+                    u[j] = R::sub(-s, ST(bv.d, i * nu + j));
                 }
                 // ---- input column i
 #pragma unroll UNR
                 for (int j = 0; j < MU; ++j) if (j < nu) {
                     const int e = i * nu + j;
-                    const double yj = ST(bv.y, e);
-                    double znew = dadd(u[j], yj);
-                    if (box_u) znew = clampd(znew, umin[e], umax[e]);
-                    const double ynew = dsub(dadd(yj, u[j]), znew);
-                    pri_u = fmax(pri_u, fabs(dsub(u[j], znew)));
-                    dua_u = fmax(dua_u, fabs(dsub(ST(z_old, e), znew)));
-                    double racc = -dmul(uref ? uref[e] : 0.0, mt.Rd(j));
-                    racc = dsub(racc, dmul(rho, dsub(znew, ynew)));
+                    const T yj = ST(bv.y, e);
+                    T znew = R::add(u[j], yj);
+                    if (box_u) znew = R::clamp(znew, umin[e], umax[e]);
+                    const T ynew = R::sub(R::add(yj, u[j]), znew);
+                    pri_u = R::max(pri_u, R::abs(R::sub(u[j], znew)));
+                    dua_u = R::max(dua_u, R::abs(R::sub(ST(z_old, e), znew)));
+                    T racc = -R::mul(uref ? uref[e] : 0.0, mt.Rd(j));
+                    racc = R::sub(racc, R::mul(rho, R::sub(znew, ynew)));
                     ST(bv.y, e) = ynew;
                     ST(z_new, e) = znew;
                     t[j] = racc;
                 }
                 if (soc_u) {
 #pragma unroll UNR
-                    for (int j = 0; j < MU; ++j) if (j < nu) vc[j] = dadd(u[j], ST(bv.yc, i * nu + j));
+                    for (int j = 0; j < MU; ++j) if (j < nu) vc[j] = R::add(u[j], ST(bv.yc, i * nu + j));
                     if (st.en_input_soc)
                         for (int k = 0; k < bv.ncu; ++k) project_soc3(vc + bv.Acu[k], bv.cu[k]);
 #pragma unroll UNR
                     for (int j = 0; j < MU; ++j) if (j < nu) {
                         const int e = i * nu + j;
-                        const double ycn = dsub(dadd(ST(bv.yc, e), u[j]), vc[j]);
-                        t[j] = dsub(t[j], dmul(rho, dsub(vc[j], ycn)));
+                        const T ycn = R::sub(R::add(ST(bv.yc, e), u[j]), vc[j]);
+                        t[j] = R::sub(t[j], R::mul(rho, R::sub(vc[j], ycn)));
                         ST(bv.yc, e) = ycn;
                     }
                 }
                 if (lin_u) {
 #pragma unroll UNR
-                    for (int j = 0; j < MU; ++j) if (j < nu) vc[j] = dadd(u[j], ST(bv.yl, i * nu + j));
+                    for (int j = 0; j < MU; ++j) if (j < nu) vc[j] = R::add(u[j], ST(bv.yl, i * nu + j));
                     project_halfspaces(vc, nu, bv.Alin_u, bv.blin_u, bv.nlu);
 #pragma unroll UNR
                     for (int j = 0; j < MU; ++j) if (j < nu) {
                         const int e = i * nu + j;
-                        const double yln = dsub(dadd(ST(bv.yl, e), u[j]), vc[j]);
-                        t[j] = dsub(t[j], dmul(rho, dsub(vc[j], yln)));
+                        const T yln = R::sub(R::add(ST(bv.yl, e), u[j]), vc[j]);
+                        t[j] = R::sub(t[j], R::mul(rho, R::sub(vc[j], yln)));
                         ST(bv.yl, e) = yln;
                     }
                 }
@@ -277,55 +316,55 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
 #pragma unroll UNR
             for (int j = 0; j < MX; ++j) if (j < nx) {
                 const int e = i * nx + j;
-                const double gj = ST(bv.g, e);
-                double vnew = dadd(x[j], gj);
-                if (box_x) vnew = clampd(vnew, xmin[e], xmax[e]);
-                const double gnew = dsub(dadd(gj, x[j]), vnew);
-                pri_x = fmax(pri_x, fabs(dsub(x[j], vnew)));
-                dua_x = fmax(dua_x, fabs(dsub(ST(v_old, e), vnew)));
+                const T gj = ST(bv.g, e);
+                T vnew = R::add(x[j], gj);
+                if (box_x) vnew = R::clamp(vnew, xmin[e], xmax[e]);
+                const T gnew = R::sub(R::add(gj, x[j]), vnew);
+                pri_x = R::max(pri_x, R::abs(R::sub(x[j], vnew)));
+                dua_x = R::max(dua_x, R::abs(R::sub(ST(v_old, e), vnew)));
                 ST(bv.g, e) = gnew;
                 ST(v_new, e) = vnew;
-                acc[j] = dmul(rho, dsub(vnew, gnew));       // rho * (vnew - g)
+                acc[j] = R::mul(rho, R::sub(vnew, gnew));       // rho * (vnew - g)
             }
             // linear cost: q_i = -(Xref_i .* Qd) - rho (vnew - g) [- cone] [- half-space];
             // terminal column: p_{N-1} = -(Xref_{N-1}' Pinf)' - ...   (reference admm.cpp:238-246)
             if (!terminal) {
 #pragma unroll UNR
                 for (int j = 0; j < MX; ++j) if (j < nx)
-                    acc[j] = dsub(-dmul(xref ? xref[i * nx + j] : 0.0, mt.Qd(j)), acc[j]);
+                    acc[j] = R::sub(-R::mul(xref ? xref[i * nx + j] : 0.0, mt.Qd(j)), acc[j]);
             } else {
 #pragma unroll UNR
                 for (int j = 0; j < MX; ++j) if (j < nx) {
-                    double s = 0.0;
+                    T s = 0;
                     if (xref) {
 #pragma unroll UNR
-                        for (int k = 0; k < MX; ++k) if (k < nx) s = fma(xref[i * nx + k], mt.Pinf(k, j), s);
+                        for (int k = 0; k < MX; ++k) if (k < nx) s = R::fma(xref[i * nx + k], mt.Pinf(k, j), s);
                     }
-                    acc[j] = dsub(-s, acc[j]);
+                    acc[j] = R::sub(-s, acc[j]);
                 }
             }
             if (soc_x) {
 #pragma unroll UNR
-                for (int j = 0; j < MX; ++j) if (j < nx) vc[j] = dadd(x[j], ST(bv.gc, i * nx + j));
+                for (int j = 0; j < MX; ++j) if (j < nx) vc[j] = R::add(x[j], ST(bv.gc, i * nx + j));
                 if (st.en_state_soc)
                     for (int k = 0; k < bv.ncx; ++k) project_soc3(vc + bv.Acx[k], bv.cx[k]);
 #pragma unroll UNR
                 for (int j = 0; j < MX; ++j) if (j < nx) {
                     const int e = i * nx + j;
-                    const double gcn = dsub(dadd(ST(bv.gc, e), x[j]), vc[j]);
-                    acc[j] = dsub(acc[j], dmul(rho, dsub(vc[j], gcn)));
+                    const T gcn = R::sub(R::add(ST(bv.gc, e), x[j]), vc[j]);
+                    acc[j] = R::sub(acc[j], R::mul(rho, R::sub(vc[j], gcn)));
                     ST(bv.gc, e) = gcn;
                 }
             }
             if (lin_x) {
 #pragma unroll UNR
-                for (int j = 0; j < MX; ++j) if (j < nx) vc[j] = dadd(x[j], ST(bv.gl, i * nx + j));
+                for (int j = 0; j < MX; ++j) if (j < nx) vc[j] = R::add(x[j], ST(bv.gl, i * nx + j));
                 project_halfspaces(vc, nx, bv.Alin_x, bv.blin_x, bv.nlx);
 #pragma unroll UNR
                 for (int j = 0; j < MX; ++j) if (j < nx) {
                     const int e = i * nx + j;
-                    const double gln = dsub(dadd(ST(bv.gl, e), x[j]), vc[j]);
-                    acc[j] = dsub(acc[j], dmul(rho, dsub(vc[j], gln)));
+                    const T gln = R::sub(R::add(ST(bv.gl, e), x[j]), vc[j]);
+                    acc[j] = R::sub(acc[j], R::mul(rho, R::sub(vc[j], gln)));
                     ST(bv.gl, e) = gln;
                 }
             }
@@ -335,12 +374,12 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
                 // x_{i+1} = A x_i + B u_i + f
 #pragma unroll UNR
                 for (int j = 0; j < MX; ++j) if (j < nx) {
-                    double s1 = 0.0, s2 = 0.0;
+                    T s1 = 0.0, s2 = 0.0;
 #pragma unroll UNR
-                    for (int k = 0; k < MX; ++k) if (k < nx) s1 = fma(mt.A(j, k), x[k], s1);
+                    for (int k = 0; k < MX; ++k) if (k < nx) s1 = R::fma(mt.A(j, k), x[k], s1);
 #pragma unroll UNR
-                    for (int k = 0; k < MU; ++k) if (k < nu) s2 = fma(mt.B(j, k), u[k], s2);
-                    tmp[j] = dadd(dadd(s1, s2), mt.f(j));
+                    for (int k = 0; k < MU; ++k) if (k < nu) s2 = R::fma(mt.B(j, k), u[k], s2);
+                    tmp[j] = R::add(R::add(s1, s2), mt.f(j));
                 }
 #pragma unroll UNR
                 for (int j = 0; j < MX; ++j) if (j < nx) x[j] = tmp[j];
@@ -352,8 +391,8 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
 
         iter += 1;
         if (iter % st.check_termination == 0) {
-            converged = pri_x < st.abs_pri_tol && pri_u < st.abs_pri_tol &&
-                        dmul(dua_x, rho) < st.abs_dua_tol && dmul(dua_u, rho) < st.abs_dua_tol;
+            converged = pri_x < tol_pri && pri_u < tol_pri &&
+                        R::mul(dua_x, rho) < tol_dua && R::mul(dua_u, rho) < tol_dua;
         }
         if (converged) break;     // v, z deliberately NOT advanced (reference admm.cpp:375 precedes :379-380)
         cur ^= 1;
@@ -377,20 +416,51 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
 #undef ST
 }
 
-template <int NX, int NU>
-void fill_const(MatsConst<NX, NU>& m, const HostMats& h) {
-    auto cp = [](double* dst, const std::vector<double>& src) { for (size_t i = 0; i < src.size(); ++i) dst[i] = src[i]; };
+template <class T, int NX, int NU>
+void fill_const(MatsConst<T, NX, NU>& m, const HostMats& h) {
+    auto cp = [](T* dst, const std::vector<double>& src) { for (size_t i = 0; i < src.size(); ++i) dst[i] = static_cast<T>(src[i]); };
     cp(m.A_, h.A); cp(m.B_, h.B); cp(m.Kinf_, h.Kinf); cp(m.AmBKt_, h.AmBKt); cp(m.Quu_inv_, h.Quu_inv);
     cp(m.Pinf_, h.Pinf); cp(m.f_, h.f); cp(m.APf_, h.APf); cp(m.BPf_, h.BPf); cp(m.Qd_, h.Qd); cp(m.Rd_, h.Rd);
 }
 
-template <int NX, int NU>
+template <class T, int NX, int NU>
 cudaError_t launch_const(const BatchView& bv, const AdmmSettings& st, const HostMats& h, cudaStream_t stream) {
-    MatsConst<NX, NU> m;
+    MatsConst<T, NX, NU> m;
     fill_const(m, h);
     const int grid = (bv.B + kThreadKernelBlock - 1) / kThreadKernelBlock;
-    admm_thread_kernel<MatsConst<NX, NU>><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
+    admm_thread_kernel<T, MatsConst<T, NX, NU>><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
     return cudaGetLastError();
+}
+
+template <class T>
+cudaError_t launch_shared(const BatchView& bv, const AdmmSettings& st, const HostMats& h, cudaStream_t stream) {
+    if (bv.B <= 0) return cudaSuccess;
+    if (bv.nx == 12 && bv.nu == 4) return launch_const<T, 12, 4>(bv, st, h, stream);
+    if (bv.nx == 4 && bv.nu == 1) return launch_const<T, 4, 1>(bv, st, h, stream);
+    if (bv.nx == 6 && bv.nu == 3) return launch_const<T, 6, 3>(bv, st, h, stream);
+    MatsGlobal m;
+    m.nx_ = bv.nx; m.nu_ = bv.nu;
+    m.A_ = bv.A; m.B_ = bv.Bm; m.Kinf_ = bv.Kinf; m.AmBKt_ = bv.AmBKt; m.Quu_inv_ = bv.Quu_inv; m.Pinf_ = bv.Pinf;
+    m.f_ = bv.f; m.APf_ = bv.APf; m.BPf_ = bv.BPf; m.Qd_ = bv.Qd; m.Rd_ = bv.Rd;
+    const int grid = (bv.B + kThreadKernelBlock - 1) / kThreadKernelBlock;
+    admm_thread_kernel<T, MatsGlobal><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
+    return cudaGetLastError();
+}
+
+template <class T>
+cudaError_t launch_per_instance(const BatchView& bv, const AdmmSettings& st, const PerInstanceMats& pm,
+                                cudaStream_t stream) {
+    if (bv.B <= 0) return cudaSuccess;
+    if (bv.nx > kPerInstanceMaxNx || bv.nu > kPerInstanceMaxNu) return cudaErrorInvalidValue;
+    const int grid = (bv.B + kThreadKernelBlock - 1) / kThreadKernelBlock;
+    auto go = [&](auto m) {
+        m.nx_ = bv.nx; m.nu_ = bv.nu; m.ld_ = bv.ld; m.p_ = pm; m.b_ = 0;
+        admm_thread_kernel<T, decltype(m)><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
+        return cudaGetLastError();
+    };
+    if (bv.nx == 12 && bv.nu == 4) return go(MatsPerInstance<12, 4>{});
+    if (bv.nx == 4 && bv.nu == 1) return go(MatsPerInstance<4, 1>{});
+    return go(MatsPerInstance<0, 0>{});
 }
 
 }  // namespace
@@ -399,33 +469,15 @@ bool thread_kernel_supports(int nx, int nu) {
     return nx >= 1 && nu >= 1 && nx <= kThreadKernelMaxNx && nu <= kThreadKernelMaxNu;
 }
 
-cudaError_t launch_admm_thread(const BatchView& bv, const AdmmSettings& st, const HostMats& h, cudaStream_t stream) {
-    if (bv.B <= 0) return cudaSuccess;
-    if (bv.nx == 12 && bv.nu == 4) return launch_const<12, 4>(bv, st, h, stream);
-    if (bv.nx == 4 && bv.nu == 1) return launch_const<4, 1>(bv, st, h, stream);
-    if (bv.nx == 6 && bv.nu == 3) return launch_const<6, 3>(bv, st, h, stream);
-    MatsGlobal m;
-    m.nx_ = bv.nx; m.nu_ = bv.nu;
-    m.A_ = bv.A; m.B_ = bv.Bm; m.Kinf_ = bv.Kinf; m.AmBKt_ = bv.AmBKt; m.Quu_inv_ = bv.Quu_inv; m.Pinf_ = bv.Pinf;
-    m.f_ = bv.f; m.APf_ = bv.APf; m.BPf_ = bv.BPf; m.Qd_ = bv.Qd; m.Rd_ = bv.Rd;
-    const int grid = (bv.B + kThreadKernelBlock - 1) / kThreadKernelBlock;
-    admm_thread_kernel<MatsGlobal><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
-    return cudaGetLastError();
+cudaError_t launch_admm_thread(const BatchView& bv, const AdmmSettings& st, const HostMats& h, cudaStream_t stream,
+                               int precision) {
+    return precision == 32 ? launch_shared<float>(bv, st, h, stream) : launch_shared<double>(bv, st, h, stream);
 }
 
 cudaError_t launch_admm_thread_per_instance(const BatchView& bv, const AdmmSettings& st, const PerInstanceMats& pm,
-                                            cudaStream_t stream) {
-    if (bv.B <= 0) return cudaSuccess;
-    if (bv.nx > kPerInstanceMaxNx || bv.nu > kPerInstanceMaxNu) return cudaErrorInvalidValue;
-    const int grid = (bv.B + kThreadKernelBlock - 1) / kThreadKernelBlock;
-    auto go = [&](auto m) {
-        m.nx_ = bv.nx; m.nu_ = bv.nu; m.ld_ = bv.ld; m.p_ = pm; m.b_ = 0;
-        admm_thread_kernel<decltype(m)><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
-        return cudaGetLastError();
-    };
-    if (bv.nx == 12 && bv.nu == 4) return go(MatsPerInstance<12, 4>{});
-    if (bv.nx == 4 && bv.nu == 1) return go(MatsPerInstance<4, 1>{});
-    return go(MatsPerInstance<0, 0>{});
+                                            cudaStream_t stream, int precision) {
+    return precision == 32 ? launch_per_instance<float>(bv, st, pm, stream)
+                           : launch_per_instance<double>(bv, st, pm, stream);
 }
 
 }  // namespace tmpc

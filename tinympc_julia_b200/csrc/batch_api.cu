@@ -65,6 +65,9 @@ struct tmpc_batch {
     int device = 0;
     int nx = 0, nu = 0, N = 0, B = 0, ld = 0;
     double rho = 0.0;
+    int precision = 64;                       // arithmetic type of the solve: 64 = `typedef double tinytype`, 32 = float build
+    std::vector<double> hQ, hR, hA, hB, hf;   // the problem as given (doubles), kept so that set_precision can redo the setup
+    double rho_given = 0.0;
     int num_sms = 148;
     tmpc::HostMats hm;
     tmpc::AdmmSettings st{};
@@ -161,6 +164,10 @@ tmpc::PerInstanceMats per_instance_view(tmpc_batch* h) {
 }
 
 int resolve_kernel(tmpc_batch* h) {
+    if (h->precision == 32) {   // float build: the thread kernel is the one instantiated for float
+        if (h->per_instance) return -1;
+        return (h->kernel_pref == TMPC_KERNEL_AUTO || h->kernel_pref == TMPC_KERNEL_THREAD) ? TMPC_KERNEL_THREAD : -1;
+    }
     if (h->per_instance) {   // every instance has its own cache: TMEM kernel reading per-instance blocks, else thread kernel
         const bool tm_pi = h->pi_blocks.p && tmpc::tmem_pi_kernel_supports(make_view(h), h->st);
         if (h->kernel_pref == TMPC_KERNEL_THREAD) return TMPC_KERNEL_THREAD;
@@ -219,8 +226,8 @@ cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v_in, cuda
         e = tmpc::launch_admm_tmem_pi(v, h->st, h->state_zero ? 1 : 0, h->pi_blocks.p, h->counter.p, h->num_sms, s);
     else if (sub && k == TMPC_KERNEL_TMEM) e = tmpc::launch_admm_tmem(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
     else if (sub) e = tmpc::launch_admm_subwarp(v, h->st, h->hm, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
-    else if (h->per_instance) e = tmpc::launch_admm_thread_per_instance(v, h->st, per_instance_view(h), s);
-    else e = tmpc::launch_admm_thread(v, h->st, h->hm, s);
+    else if (h->per_instance) e = tmpc::launch_admm_thread_per_instance(v, h->st, per_instance_view(h), s, h->precision);
+    else e = tmpc::launch_admm_thread(v, h->st, h->hm, s, h->precision);
     h->launches += 1;
     if (h->st.max_iter > 0) { h->state_zero = false; h->mem_zero = false; h->state_in_im = wants_im; }
     return e;
@@ -271,19 +278,31 @@ extern "C" {
 const char* tmpc_last_error(void) { return g_last_error.c_str(); }
 const char* tmpc_version(void) { return "tinympc_b200 0.1 (sm_100a)"; }
 
-int tmpc_compute_cache(const double* A, const double* Bdyn, const double* f, const double* Q, const double* R, double rho,
+static int compute_cache_any(int bits, const double* A, const double* Bdyn, const double* f, const double* Q, const double* R, double rho,
                        int nx, int nu, double* Kinf, double* Pinf, double* Quu_inv, double* AmBKt, double* APf,
                        double* BPf, double* Qd, double* Rd) {
     return guarded([&]() -> int {
         if (!A || !Bdyn || !f || !Q || !R || nx < 1 || nu < 1) { set_error("tmpc_compute_cache: bad argument"); return TMPC_ERR_DIM; }
         tmpc::LqrCache c;
         Mat mA(nx, nx, A), mB(nx, nu, Bdyn), mf(nx, 1, f), mQ(nx, nx, Q), mR(nu, nu, R);
-        if (tmpc::compute_lqr_cache(mA, mB, mf, mQ, mR, rho, c) != 0) { set_error("tmpc_compute_cache: singular matrix"); return TMPC_ERR_DIM; }
+        if ((bits == 32 ? tmpc::compute_lqr_cache_f32(mA, mB, mf, mQ, mR, rho, c) : tmpc::compute_lqr_cache(mA, mB, mf, mQ, mR, rho, c)) != 0) { set_error("tmpc_compute_cache: singular matrix"); return TMPC_ERR_DIM; }
         auto cp = [](double* dst, const std::vector<double>& v) { if (dst) std::memcpy(dst, v.data(), v.size() * sizeof(double)); };
         cp(Kinf, c.Kinf.a); cp(Pinf, c.Pinf.a); cp(Quu_inv, c.Quu_inv.a); cp(AmBKt, c.AmBKt.a); cp(APf, c.APf.a); cp(BPf, c.BPf.a);
         cp(Qd, c.Qd); cp(Rd, c.Rd);
         return c.riccati_sweeps > 0 ? TMPC_OK : TMPC_ERR_DIM;
     });
+}
+
+int tmpc_compute_cache(const double* A, const double* Bdyn, const double* f, const double* Q, const double* R, double rho,
+                       int nx, int nu, double* Kinf, double* Pinf, double* Quu_inv, double* AmBKt, double* APf,
+                       double* BPf, double* Qd, double* Rd) {
+    return compute_cache_any(64, A, Bdyn, f, Q, R, rho, nx, nu, Kinf, Pinf, Quu_inv, AmBKt, APf, BPf, Qd, Rd);
+}
+
+int tmpc_compute_cache_f32(const double* A, const double* Bdyn, const double* f, const double* Q, const double* R, double rho,
+                           int nx, int nu, double* Kinf, double* Pinf, double* Quu_inv, double* AmBKt, double* APf,
+                           double* BPf, double* Qd, double* Rd) {
+    return compute_cache_any(32, A, Bdyn, f, Q, R, rho, nx, nu, Kinf, Pinf, Quu_inv, AmBKt, APf, BPf, Qd, Rd);
 }
 
 int tmpc_batch_create(tmpc_batch** out, const double* A, const double* Bdyn, const double* f, const double* Q,
@@ -321,6 +340,7 @@ int tmpc_batch_create(tmpc_batch** out, const double* A, const double* Bdyn, con
         }
         if (verbose) std::printf("tinympc_b200: Kinf converged after %d Riccati sweeps (nx=%d nu=%d N=%d B=%d)\n",
                                  c.riccati_sweeps, nx, nu, N, B);
+        h->hA = mA.a; h->hB = mB.a; h->hf = mf.a; h->hQ = mQ.a; h->hR = mR.a; h->rho_given = rho;
         h->hm.nx = nx; h->hm.nu = nu;
         h->hm.A = mA.a; h->hm.B = mB.a; h->hm.f = mf.a; h->hm.Kinf = c.Kinf.a; h->hm.Pinf = c.Pinf.a;
         h->hm.Quu_inv = c.Quu_inv.a; h->hm.AmBKt = c.AmBKt.a; h->hm.APf = c.APf.a; h->hm.BPf = c.BPf.a;
@@ -374,6 +394,43 @@ int tmpc_batch_update_settings(tmpc_batch* h, double abs_pri_tol, double abs_dua
         return TMPC_OK;
     });
 }
+
+/* Arithmetic type of the solve (reference: `typedef double tinytype`, types.hpp:15; float is its other build).
+ * bits = 32 redoes the setup the way the float build of the reference does it — A, B, f, Q, R, rho rounded to float
+ * (src/bindings.cpp:50-55), Qd / Rd and the Riccati cache computed in float (tiny_api.cpp:107-108, 244-318) — and
+ * makes every later solve run the float instantiation of the thread kernel: inputs are rounded to float on load,
+ * results widen to double, the C ABI and the device arrays stay double.  bits = 64 restores the default.  Call it on
+ * a fresh or reset batch; a cache installed with set_cache_terms is replaced by the recomputed one. */
+int tmpc_batch_set_precision(tmpc_batch* h, int bits) {
+    return guarded([&]() -> int {
+        if (!h || (bits != 32 && bits != 64)) { set_error("set_precision: bits must be 32 or 64"); return TMPC_ERR_DIM; }
+        if (!h->state_zero) { set_error("set_precision: the batch carries solver state; reset it first"); return TMPC_ERR_STATE; }
+        if (h->per_instance) { set_error("set_precision: per-instance dynamics are built for 64-bit only"); return TMPC_ERR_STATE; }
+        if (bits == h->precision) return TMPC_OK;
+        h->use_device();
+        const int nx = h->nx, nu = h->nu;
+        tmpc::LqrCache c;
+        Mat mA(nx, nx, h->hA.data()), mB(nx, nu, h->hB.data()), mf(nx, 1, h->hf.data()), mQ(nx, nx, h->hQ.data()),
+            mR(nu, nu, h->hR.data());
+        const int rc = bits == 32 ? tmpc::compute_lqr_cache_f32(mA, mB, mf, mQ, mR, h->rho_given, c)
+                                  : tmpc::compute_lqr_cache(mA, mB, mf, mQ, mR, h->rho_given, c);
+        if (rc != 0) { set_error("set_precision: singular matrix in the Riccati recursion"); return TMPC_ERR_DIM; }
+        auto rnd = [&](std::vector<double> v) {
+            if (bits == 32) for (double& x : v) x = static_cast<double>(static_cast<float>(x));
+            return v;
+        };
+        h->hm.A = rnd(h->hA); h->hm.B = rnd(h->hB); h->hm.f = rnd(h->hf);
+        h->hm.Kinf = c.Kinf.a; h->hm.Pinf = c.Pinf.a; h->hm.Quu_inv = c.Quu_inv.a; h->hm.AmBKt = c.AmBKt.a;
+        h->hm.APf = c.APf.a; h->hm.BPf = c.BPf.a; h->hm.Qd = c.Qd; h->hm.Rd = c.Rd;
+        h->rho = bits == 32 ? static_cast<double>(static_cast<float>(h->rho_given)) : h->rho_given;
+        h->precision = bits;
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        upload_mats(h);
+        return TMPC_OK;
+    });
+}
+
+int tmpc_batch_get_precision(tmpc_batch* h) { return h ? h->precision : -1; }
 
 int tmpc_batch_set_kernel(tmpc_batch* h, int kernel) {
     if (!h || kernel < TMPC_KERNEL_AUTO || kernel > TMPC_KERNEL_TMEM2) return TMPC_ERR_DIM;
@@ -507,6 +564,7 @@ int tmpc_batch_set_instance_dynamics(tmpc_batch* h, const double* A, const doubl
     return guarded([&]() -> int {
         if (!h || !A || !Bdyn || !Q || !R) { set_error("set_instance_dynamics: null argument"); return TMPC_ERR_DIM; }
         if (qr_batch != 1 && qr_batch != h->B) { set_error("set_instance_dynamics: qr_batch must be 1 or B"); return TMPC_ERR_DIM; }
+        if (h->precision == 32) { set_error("set_instance_dynamics: per-instance dynamics are built for 64-bit only"); return TMPC_ERR_STATE; }
         if (h->nx > tmpc::kPerInstanceMaxNx || h->nu > tmpc::kPerInstanceMaxNu) {
             set_error("set_instance_dynamics: per-instance dynamics are compiled for nx <= 12, nu <= 4"); return TMPC_ERR_DIM;
         }
@@ -578,6 +636,9 @@ int tmpc_batch_set_cache_terms(tmpc_batch* h, const double* Kinf, const double* 
         h->hm.Pinf.assign(Pinf, Pinf + static_cast<size_t>(n) * n);
         h->hm.Quu_inv.assign(Quu_inv, Quu_inv + static_cast<size_t>(m) * m);
         h->hm.AmBKt.assign(AmBKt, AmBKt + static_cast<size_t>(n) * n);
+        if (h->precision == 32)      // Kinf.cast<tinytype>() ... (src/bindings.cpp:277-280)
+            for (auto* vec : {&h->hm.Kinf, &h->hm.Pinf, &h->hm.Quu_inv, &h->hm.AmBKt})
+                for (double& x : *vec) x = static_cast<double>(static_cast<float>(x));
         CUDA_TRY(cudaStreamSynchronize(h->stream));
         upload_mats(h);      // APf, BPf, rho deliberately untouched
         return TMPC_OK;
@@ -794,6 +855,7 @@ int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_lo
                              void* cuda_stream) {
     return guarded([&]() -> int {
         if (!h || nsteps < 1) return TMPC_ERR_DIM;
+        if (h->precision == 32) { set_error("rollout: the device closed loop is built for 64-bit only"); return TMPC_ERR_STATE; }
         h->use_device();
         cudaStream_t s = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : h->stream;
         if (h->ext_x0) {   // the plant state is advanced in place: work on the internal copy

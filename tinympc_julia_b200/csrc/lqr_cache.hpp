@@ -52,4 +52,9 @@ struct LqrCache {
 int compute_lqr_cache(const Mat& A, const Mat& B, const Mat& f, const Mat& Q, const Mat& R, double rho,
                       LqrCache& out);
 
+// The same recursion with every input and operation rounded to float (the reference built with
+// `typedef float tinytype`); the values come back as doubles.
+int compute_lqr_cache_f32(const Mat& A, const Mat& B, const Mat& f, const Mat& Q, const Mat& R, double rho,
+                          LqrCache& out);
+
 }  // namespace tmpc

@@ -95,6 +95,15 @@ class TinyMPCBatchSolver:
         """Cold start: clear duals, slacks and linear cost terms (state right after ``setup``)."""
         _chk(_lib.load().tmpc_batch_reset(self._h), "Failed to reset batch")
 
+    def set_precision(self, bits: int):
+        """Arithmetic type of the solve: 64 (``typedef double tinytype``, the reference's default) or 32 (its float
+        build, tinympc/TinyMPC/src/tinympc/types.hpp:15).  Call right after ``setup`` / ``reset``."""
+        _chk(_lib.load().tmpc_batch_set_precision(self._h, int(bits)), "Failed to set precision")
+
+    @property
+    def precision(self) -> int:
+        return int(_lib.load().tmpc_batch_get_precision(self._h))
+
     def set_kernel(self, kernel: int):
         _chk(_lib.load().tmpc_batch_set_kernel(self._h, int(kernel)), "Failed to select kernel")
 
