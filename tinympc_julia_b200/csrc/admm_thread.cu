@@ -32,8 +32,8 @@ namespace {
 // The reference's precision is one typedef (types.hpp:15, `typedef double tinytype`; float is the other supported
 // value).  The kernel is instantiated for both: T = double is the default build of the reference, T = float its
 // float build.  In the float instantiation every input is rounded to float where
-// src/bindings.cpp casts (:50-55, :82, :105, :128) and results widen back to double (:172, :194); the arrays in HBM
-// stay double (a float widens exactly), so the two precisions share the runtime, the layouts and the C ABI.
+// src/bindings.cpp casts (:50-55, :82, :105, :128) and results widen back to double (:172, :194).  Inputs, solutions
+// and the C ABI stay double; the carried state, which only this kernel reads in float mode, is stored as T.
 template <class T> struct Ar;
 template <> struct Ar<double> {
     static __device__ __forceinline__ double add(double a, double b) { return __dadd_rn(a, b); }
@@ -183,7 +183,9 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
     const size_t ld = static_cast<size_t>(bv.ld);
     const T rho = static_cast<T>(bv.rho);                       // bindings.cpp:55
     const T tol_pri = static_cast<T>(st.abs_pri_tol), tol_dua = static_cast<T>(st.abs_dua_tol);   // types.hpp:64-65
-#define ST(arr, e) (arr)[static_cast<size_t>(e) * ld + b]
+    // Carried state and scratch are the kernel's private format: element-major arrays of T.  The float instantiation
+    // uses the first half of each (double-sized) allocation, which halves the bytes an iteration streams through L2 / HBM.
+#define ST(arr, e) reinterpret_cast<T*>(arr)[static_cast<size_t>(e) * ld + b]
 
     if (st.max_iter <= 0) {   // the reference's loop does not run: solution keeps the previous slacks
         bv.status[b] = 1; bv.iters[b] = 0;
