@@ -395,13 +395,27 @@ def test_per_instance_dynamics_closed_loop(orc):
 # float typedef (oracle/_ref/libtinympc_refbatch32.so) — committed outputs in tests/golden/f32_*.npz, the live library
 # where oracle/_ref travelled to this box.  Tolerance: cases.compare_f32.
 
+def kernels32_for(c):
+    """Float build: the thread kernel always, the shared-memory sub-warp kernel where it applies."""
+    sol = cases.make_cuda_solver(c, kernel=t.KERNEL_AUTO, precision=32)
+    sol.set_kernel(SUBWARP)
+    ks = [THREAD] + ([SUBWARP] if sol.kernel == SUBWARP else [])
+    del sol
+    return ks
+
+
 @pytest.mark.parametrize("name", cases.GOLDEN_F32_CASES)
 def test_float_build_matches_float_reference_fixture(name):
     c, want = cases.golden_f32_case(name)
-    got = cases.run_cuda(c, kernel=THREAD, precision=32)
-    for k in ("X", "U"):
-        assert np.array_equal(got[k], got[k].astype(np.float32).astype(np.float64)), "results must be floats widened to double"
-    cases.compare_f32(got, want, what=f"cuda float vs float reference[{name}]")
+    outs = {}
+    for kern in kernels32_for(c):
+        got = outs[kern] = cases.run_cuda(c, kernel=kern, precision=32)
+        for k in ("X", "U"):
+            assert np.array_equal(got[k], got[k].astype(np.float32).astype(np.float64)), "results must be floats widened to double"
+        cases.compare_f32(got, want, what=f"cuda float[kernel {kern}] vs float reference[{name}]")
+    if SUBWARP in outs:      # same sequence of rounded operations: the two float kernels agree bit for bit
+        for k in ("ret", "iters", "X", "U"):
+            assert np.array_equal(outs[THREAD][k], outs[SUBWARP][k]), f"float thread vs sub-warp kernel: {k} differs"
 
 
 def test_float_build_seeded_batches_against_live_float_reference():
@@ -415,19 +429,26 @@ def test_float_build_seeded_batches_against_live_float_reference():
         cache = ref32.get_cache(cases.to_oracle_problem(c))
         c["cache"] = {k: cache[k] for k in ("Kinf", "Pinf", "Quu_inv", "AmBKt")}
         want = cases.run_checker(c, ref32, nthreads=8)
-        got = cases.run_cuda(c, kernel=THREAD, precision=32)
-        cases.compare_f32(got, want, what=f"cuda float vs live float reference (B={B})")
+        for kern in kernels32_for(c):
+            got = cases.run_cuda(c, kernel=kern, precision=32)
+            cases.compare_f32(got, want, what=f"cuda float[kernel {kern}] vs live float reference (B={B})")
 
 
 def test_float_build_warm_start_and_guards():
-    """A second solve warm-starts from float state held in the double arrays; the float build runs the thread kernel
-    only and says so; switching precision needs a reset batch."""
+    """A second solve warm-starts from the float carried state, whichever float kernel wrote it; the TMEM kernels are
+    64-bit only and say so; switching precision needs a reset batch."""
     c, _ = cases.golden_f32_case("quadrotor_easy_64")
-    sol = cases.make_cuda_solver(c, kernel=THREAD, precision=32)
-    assert sol.precision == 32 and sol.kernel == THREAD
+    sol = cases.make_cuda_solver(c, kernel=t.KERNEL_AUTO, precision=32)
+    assert sol.precision == 32 and sol.kernel == SUBWARP   # AUTO: the on-chip float kernel where it applies
     first = cases.run_cuda(c, sol=sol)
-    again = cases.run_cuda(c, sol=sol)                      # same x0, warm start: converges at once or nearly
+    sol.set_kernel(THREAD)
+    again = cases.run_cuda(c, sol=sol)                      # same x0, warm start from the other kernel's state
     assert again["iters"].max() <= first["iters"].min()
+    ref_sol = cases.make_cuda_solver(c, kernel=THREAD, precision=32)      # the same two solves on the thread kernel alone
+    cases.run_cuda(c, sol=ref_sol)
+    again_ref = cases.run_cuda(c, sol=ref_sol)
+    for k in ("ret", "iters", "X", "U"):
+        assert np.array_equal(again[k], again_ref[k]), f"warm start across float kernels: {k} differs"
     with pytest.raises(t.TinyMPCError):
         sol.set_precision(64)                               # carries state
     sol.set_kernel(TMEM)

@@ -43,11 +43,11 @@ cudaError_t launch_admm_thread(const BatchView& bv, const AdmmSettings& st, cons
 
 // ---- one instance per 4-lane sub-warp, shared-memory resident (admm_subwarp.cu)
 // Applies to box-constrained problems (no cone / half-space flags) of a compiled-in shape.
-bool subwarp_kernel_supports(int nx, int nu, int N, const AdmmSettings& st);
+bool subwarp_kernel_supports(int nx, int nu, int N, const AdmmSettings& st, int precision = 64);
 // `cold` = 1: the carried state is known to be all-zero (fresh / reset batch): it is not read.
 // `counter` = device int used as the tile work queue (zeroed by the launcher).
 cudaError_t launch_admm_subwarp(const BatchView& bv, const AdmmSettings& st, const HostMats& h, int cold,
-                                int* counter, int num_sms, cudaStream_t stream);
+                                int* counter, int num_sms, cudaStream_t stream, int precision = 64);
 
 // ---- one instance per 4-lane sub-warp, state rows in Tensor Memory + input rows in shared memory, per-instance
 // refill from a global queue (admm_tmem.cu).  Box-constrained (or unconstrained) problems with shared bounds.

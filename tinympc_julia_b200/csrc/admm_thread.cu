@@ -34,32 +34,7 @@ namespace {
 // float build.  In the float instantiation every input is rounded to float where
 // src/bindings.cpp casts (:50-55, :82, :105, :128) and results widen back to double (:172, :194).  Inputs, solutions
 // and the C ABI stay double; the carried state, which only this kernel reads in float mode, is stored as T.
-template <class T> struct Ar;
-template <> struct Ar<double> {
-    static __device__ __forceinline__ double add(double a, double b) { return __dadd_rn(a, b); }
-    static __device__ __forceinline__ double sub(double a, double b) { return __dsub_rn(a, b); }
-    static __device__ __forceinline__ double mul(double a, double b) { return __dmul_rn(a, b); }
-    static __device__ __forceinline__ double div(double a, double b) { return __ddiv_rn(a, b); }
-    static __device__ __forceinline__ double fma(double a, double b, double c) { return ::fma(a, b, c); }
-    static __device__ __forceinline__ double abs(double a) { return ::fabs(a); }
-    static __device__ __forceinline__ double max(double a, double b) { return ::fmax(a, b); }
-    static __device__ __forceinline__ double sqrt(double a) { return ::sqrt(a); }
-    static __device__ __forceinline__ double clamp(double t, double lo, double hi) { return clampd(t, lo, hi); }
-};
-template <> struct Ar<float> {
-    static __device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
-    static __device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
-    static __device__ __forceinline__ float mul(float a, float b) { return __fmul_rn(a, b); }
-    static __device__ __forceinline__ float div(float a, float b) { return __fdiv_rn(a, b); }
-    static __device__ __forceinline__ float fma(float a, float b, float c) { return ::fmaf(a, b, c); }
-    static __device__ __forceinline__ float abs(float a) { return ::fabsf(a); }
-    static __device__ __forceinline__ float max(float a, float b) { return ::fmaxf(a, b); }
-    static __device__ __forceinline__ float sqrt(float a) { return __fsqrt_rn(a); }
-    static __device__ __forceinline__ float clamp(float t, float lo, float hi) {
-        const float w = (lo < t) ? t : lo;       // std::max(lo, t)
-        return (w < hi) ? w : hi;                // std::min(hi, w)
-    }
-};
+// (the traits class Ar<T> lives in admm_device.cuh)
 
 // ---------------------------------------------------------------- matrix operand providers
 template <class T, int NX, int NU>

@@ -164,9 +164,13 @@ tmpc::PerInstanceMats per_instance_view(tmpc_batch* h) {
 }
 
 int resolve_kernel(tmpc_batch* h) {
-    if (h->precision == 32) {   // float build: the thread kernel is the one instantiated for float
+    if (h->precision == 32) {   // float build: the sub-warp (shared-memory) and thread kernels are instantiated for float
         if (h->per_instance) return -1;
-        return (h->kernel_pref == TMPC_KERNEL_AUTO || h->kernel_pref == TMPC_KERNEL_THREAD) ? TMPC_KERNEL_THREAD : -1;
+        const bool sub32 = tmpc::subwarp_kernel_supports(h->nx, h->nu, h->N, h->st, 32);
+        if (h->kernel_pref == TMPC_KERNEL_THREAD) return TMPC_KERNEL_THREAD;
+        if (h->kernel_pref == TMPC_KERNEL_SUBWARP) return sub32 ? TMPC_KERNEL_SUBWARP : -1;
+        if (h->kernel_pref != TMPC_KERNEL_AUTO) return -1;
+        return sub32 ? TMPC_KERNEL_SUBWARP : TMPC_KERNEL_THREAD;
     }
     if (h->per_instance) {   // every instance has its own cache: TMEM kernel reading per-instance blocks, else thread kernel
         const bool tm_pi = h->pi_blocks.p && tmpc::tmem_pi_kernel_supports(make_view(h), h->st);
@@ -225,7 +229,7 @@ cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v_in, cuda
     else if (sub && k == TMPC_KERNEL_TMEM && h->per_instance)
         e = tmpc::launch_admm_tmem_pi(v, h->st, h->state_zero ? 1 : 0, h->pi_blocks.p, h->counter.p, h->num_sms, s);
     else if (sub && k == TMPC_KERNEL_TMEM) e = tmpc::launch_admm_tmem(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
-    else if (sub) e = tmpc::launch_admm_subwarp(v, h->st, h->hm, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
+    else if (sub) e = tmpc::launch_admm_subwarp(v, h->st, h->hm, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s, h->precision);
     else if (h->per_instance) e = tmpc::launch_admm_thread_per_instance(v, h->st, per_instance_view(h), s, h->precision);
     else e = tmpc::launch_admm_thread(v, h->st, h->hm, s, h->precision);
     h->launches += 1;

@@ -50,6 +50,8 @@ for hard in (False, True):
         want = cases.run_checker(c, ref32, nthreads=nth)
         r["ref32_host_seconds"] = want["seconds"]; r["ref32_threads"] = nth
     g32 = cases.run_cuda(c, kernel=t.KERNEL_THREAD, precision=32)
+    g32s = cases.run_cuda(c, kernel=t.KERNEL_SUBWARP, precision=32)
+    r["float_subwarp_equals_float_thread"] = bool(all(np.array_equal(g32[k], g32s[k]) for k in ("ret", "iters", "X", "U")))
     if ref32 is not None:
         same = (g32["iters"][-1] == want["iters"][-1]) & (g32["ret"][-1] == want["ret"][-1])
         r["gpu32_vs_ref32_iter_mismatch"] = int((~same).sum())
@@ -70,18 +72,19 @@ for hard in (False, True):
     r["gpu32_vs_gpu64_iter_delta_hist"] = {int(k): int(v) for k, v in zip(*np.unique(np.clip(d, -3, 3), return_counts=True))}
     r["mean_iters_32"] = float(g32["iters"].mean()); r["mean_iters_64"] = float(g64["iters"].mean())
     r["gpu32_vs_gpu64_max_abs_dU"] = float(np.abs(g32["U"] - g64["U"])[..., d == 0].max())
-    # thread kernel, float vs double
-    for bits in (32, 64):
-        sol = cases.make_cuda_solver(cases.quadrotor_batch(B, hard=hard), kernel=t.KERNEL_THREAD, precision=bits)
+    # thread and sub-warp kernels, float vs double
+    for bits, kern, kname in ((32, t.KERNEL_THREAD, "thread"), (64, t.KERNEL_THREAD, "thread"),
+                              (32, t.KERNEL_SUBWARP, "subwarp"), (64, t.KERNEL_SUBWARP, "subwarp"), (64, t.KERNEL_TMEM, "tmem")):
+        sol = cases.make_cuda_solver(cases.quadrotor_batch(B, hard=hard), kernel=kern, precision=bits)
         t.set_x0(sol, np.asfortranarray(c["x0"]))
         best = 1e9
         for rep in range(4):
             sol.reset()
             t0 = time.perf_counter(); sol.solve_async(0); sol.synchronize(); best = min(best, time.perf_counter() - t0)
         st, it = sol.status()
-        r[f"thread_kernel_{bits}_ms"] = best * 1e3
-        r[f"thread_kernel_{bits}_solves_per_s"] = B / best
-        r[f"thread_kernel_{bits}_admm_iters_per_s"] = float(it.sum()) / best
+        r[f"{kname}_kernel_{bits}_ms"] = best * 1e3
+        r[f"{kname}_kernel_{bits}_solves_per_s"] = B / best
+        r[f"{kname}_kernel_{bits}_admm_iters_per_s"] = float(it.sum()) / best
         del sol
     out["flip_" + tag] = r
 print(json.dumps(out))
