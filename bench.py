@@ -252,7 +252,8 @@ def run_reference(args, rank, world):
 
 def workload_name(args):
     tag = "hard x0~U(+-0.5)" if args.workload == "quadrotor_hard" else "easy x0~U(+-0.1)"
-    return f"quadrotor hover nx=12 nu=4 N=20, box bounds shared, shared cache, B={args.batch}/GPU, cold start, {tag}"
+    prec = "" if getattr(args, "precision", 64) == 64 else ", float build (tinytype = float)"
+    return f"quadrotor hover nx=12 nu=4 N=20, box bounds shared, shared cache, B={args.batch}/GPU, cold start, {tag}{prec}"
 
 
 # ------------------------------------------------------------------------------------------ GPU arm
@@ -301,6 +302,8 @@ def run_gpu(args, rank, local_rank, world):
 
     sol = t.TinyMPCBatchSolver()
     t.setup(sol, s.A, s.B, s.f, s.Q, s.R, s.rho, NX, NU, NH, batch=B, device=local_rank)
+    if args.precision == 32:
+        sol.set_precision(32)       # float build: setup redone in float, solves compute in float
     t.set_bound_constraints(sol, *s.bounds(NH))
     if args.kernel:
         sol.set_kernel(args.kernel)
@@ -388,7 +391,7 @@ def run_gpu(args, rank, local_rank, world):
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": max(W, 3),
         "ms_per_step": tot_ms_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f64", "data": "synthetic",
+        "dtype": "f64" if args.precision == 64 else "f32", "data": "synthetic",
         "admm_iters_per_s": iters_per_s,
         "mean_iters_per_solve": all_iters_step / (B * world), "solved_fraction": all_solved / (B * world),
         "config": {"workload": workload_name(args), "nx": NX, "nu": NU, "N": NH, "batch_per_gpu": B,
@@ -399,8 +402,10 @@ def run_gpu(args, rank, local_rank, world):
         "gpu_launches": int(all_launches),
         "wall_ms_per_step_incl_flush": 1e3 * (w1 - w0) / K,
         "clocks": clocks,
-        "roofline": {"bound": "fp64_fma", "achieved": achieved_tf, "peak": fma_peak, "unit": "TFLOP/s",
-                     "frac": (achieved_tf / fma_peak) if fma_peak else None, "traffic": traffic,
+        "roofline": {"bound": "fp64_fma" if args.precision == 64 else "fp32_fma", "achieved": achieved_tf,
+                     "peak": fma_peak if args.precision == 64 else pk32.value, "unit": "TFLOP/s",
+                     "frac": ((achieved_tf / fma_peak) if fma_peak else None) if args.precision == 64
+                             else ((achieved_tf / pk32.value) if pk32.value else None), "traffic": traffic,
                      "traffic_note": "DRAM bytes per launch from the ncu --set full capture recorded in profiles/traffic.json (null when none matches this kernel/workload)",
                      "flop_per_iter": F, "kernel_ms": kern_ms,
                      "peak_source": "DFMA chains measured live on this GPU by tmpc_measure_fma_peak (MEASURED_PEAKS.json has no CUDA-core peak)",
@@ -467,6 +472,11 @@ def run_gpu(args, rank, local_rank, world):
     # ---- CPU baseline + single-solve latency: N=1, rank 0 only
     if world == 1 and rank == 0 and not args.no_cpu:
         cpu = load_cpu_checker()
+        if args.precision == 32:    # the float build is checked against (and timed beside) the reference compiled with the float typedef
+            import oracle
+            cpu32 = oracle.load_ref32()
+            if cpu32 is not None:
+                cpu = cpu32
         cores = os.cpu_count() or 1
         secs, cpu_iters, out = cpu_batch_run(cpu, x0_host, hard, cores)
         line["cpu_baseline"] = {"value": B / secs, "unit": UNIT, "cores": cores, "kind": cpu.kind,
@@ -498,6 +508,8 @@ def main():
     ap.add_argument("--batch", type=int, default=65536)
     ap.add_argument("--workload", default="quadrotor_easy", choices=["quadrotor_easy", "quadrotor_hard"])
     ap.add_argument("--kernel", type=int, default=0, help="0 auto, 1 thread-per-instance, 2 sub-warp (shared memory), 3 sub-warp (TMEM + shared memory), 4 the same with two instances per lane")
+    ap.add_argument("--precision", type=int, default=64, choices=[64, 32],
+                    help="arithmetic type of the solve = the reference's tinytype: 64 double (default, the headline), 32 its float build")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline / single_solve legs")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

@@ -87,4 +87,35 @@ for hard in (False, True):
         r[f"{kname}_kernel_{bits}_admm_iters_per_s"] = float(it.sum()) / best
         del sol
     out["flip_" + tag] = r
+# ---- configs 2 (cartpole) and 4 (rocket: box + both cones + half-spaces, thread kernel): float vs double, flips vs the float reference
+for tag, make in (("cartpole", lambda: cases.cartpole_batch(B)), ("rocket", lambda: cases.rocket(B, N=50))):
+    r = {}
+    c = make()
+    want = None
+    if ref32 is not None:
+        cache = ref32.get_cache(cases.to_oracle_problem(c))
+        c["cache"] = {k: cache[k] for k in ("Kinf", "Pinf", "Quu_inv", "AmBKt")}
+        want = cases.run_checker(c, ref32, nthreads=os.cpu_count() or 1)
+        r["ref32_host_seconds"] = want["seconds"]
+    for bits in (32, 64):
+        cc = c if bits == 32 else make()
+        sol = cases.make_cuda_solver(cc, kernel=t.KERNEL_AUTO, precision=bits)
+        t.set_x0(sol, np.asfortranarray(cc["x0"]))
+        if cc["Xref"] is not None: t.set_x_ref(sol, cc["Xref"])
+        if cc["Uref"] is not None: t.set_u_ref(sol, cc["Uref"])
+        best = 1e9
+        for rep in range(3):
+            sol.reset()
+            t0 = time.perf_counter(); sol.solve_async(0); sol.synchronize(); best = min(best, time.perf_counter() - t0)
+        st, it = sol.status()
+        r[f"kernel_{bits}"] = sol.kernel
+        r[f"ms_{bits}"] = best * 1e3
+        r[f"solves_per_s_{bits}"] = B / best
+        r[f"admm_iters_per_s_{bits}"] = float(it.sum()) / best
+        if bits == 32 and want is not None:
+            same = (it == want["iters"][-1]) & (st == want["ret"][-1])
+            r["gpu32_vs_ref32_flip_rate"] = float((~same).mean())
+            r["gpu32_vs_ref32_max_iter_delta"] = int(np.abs(it - want["iters"][-1]).max())
+        del sol
+    out["config_" + tag] = r
 print(json.dumps(out))

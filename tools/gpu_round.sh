@@ -11,6 +11,9 @@ timeout 300 python bench.py --workload quadrotor_hard --no-cpu > gpurun_out/benc
 timeout 300 python bench.py --kernel 2 --no-cpu --steps 10 > gpurun_out/bench_subwarp.json 2> gpurun_out/bench_subwarp.err; echo "bench subwarp rc=$?"; timeout 300 python bench.py --kernel 1 --no-cpu --steps 10 > gpurun_out/bench_thread.json 2> gpurun_out/bench_thread.err; echo "bench thread rc=$?"
 timeout 300 python bench.py --kernel 4 --no-cpu --steps 20 > gpurun_out/bench_tmem2.json 2> gpurun_out/bench_tmem2.err; echo "bench tmem2 rc=$?"
 timeout 300 python bench.py --kernel 4 --no-cpu --steps 20 --workload quadrotor_hard > gpurun_out/bench_tmem2_hard.json 2> gpurun_out/bench_tmem2_hard.err
+timeout 300 python bench.py --precision 32 --steps 20 > gpurun_out/bench_f32.json 2> gpurun_out/bench_f32.err; echo "bench f32 rc=$?"; cat gpurun_out/bench_f32.json
+timeout 300 python bench.py --precision 32 --steps 20 --no-cpu --workload quadrotor_hard > gpurun_out/bench_f32_hard.json 2> gpurun_out/bench_f32_hard.err
+timeout 600 python tools/gpu_float.py > gpurun_out/float.json 2> gpurun_out/float.err; echo "float rc=$?"
 timeout 600 python tools/gpu_rollout.py > gpurun_out/rollout.json 2> gpurun_out/rollout.err; echo "rollout rc=$?"; cat gpurun_out/rollout.json
 timeout 600 python tools/gpu_perinstance.py > gpurun_out/perinst.json 2> gpurun_out/perinst.err; echo "perinst rc=$?"; cat gpurun_out/perinst.json
 timeout 300 python tools/gpu_steady.py > gpurun_out/steady.json 2> gpurun_out/steady.err; echo "steady rc=$?"; cat gpurun_out/steady.json
