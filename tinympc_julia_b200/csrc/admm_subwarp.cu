@@ -2,7 +2,7 @@
 //
 // This is the flagship kernel for the box-constrained shapes (quadrotor 12/4, cartpole 4/1).
 //
-//  * A warp owns a TILE of 8 instances.  lane = sub * 8 + inst: the four lanes {inst, inst+8, inst+16,
+//  * A warp holds 8 instances.  lane = sub * 8 + inst: the four lanes {inst, inst+8, inst+16,
 //    inst+24} cooperate on instance `inst`; lane `sub` owns state rows {r*4 + sub} and input row `sub`.
 //    All four lanes are busy in every mat-vec of the Riccati recursions (100 % lane use for nx % 4 == 0).
 //  * The whole per-instance ADMM state (duals g, y; box slacks v, z; feed-forward d) lives in SHARED
@@ -16,9 +16,11 @@
 //  * update_slack / update_dual / update_linear_cost and the residual tests are fused into the forward
 //    sweep; the linear cost q_i, r_i is never stored — it is recomputed from v, g (z, y) when the
 //    backward sweep needs it, which is bit-identical to storing it.
-//  * Convergence is decided per instance with warp votes; converged instances stop mutating their
-//    state, the warp leaves when its 8 instances are done, and warps pull tiles from a global queue so
-//    that bimodal iteration counts do not idle SMs.
+//  * Convergence is decided per instance with warp votes; a finished instance is written out and its
+//    sub-warp pulls the next instance id from a global queue at once (per-instance refill: only the 4
+//    lanes of the finished instance run the pass), so bimodal iteration counts idle neither lanes nor SMs.
+//  * Templated on the scalar: T = double (the reference's default tinytype) and T = float (its float
+//    build, DESIGN.md 3.8: half the shared memory per instance, 8 resident warps for the quadrotor shape).
 //
 // Reference being reproduced: tinympc/TinyMPC/src/tinympc/admm.cpp:13-32 (Riccati sweeps), :81-98 (box
 // slack), :181-187 (dual), :214-247 (linear cost), :253-271 (termination), :274-389 (solve).
@@ -170,56 +172,115 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
 
     int bcast_phase = 0;
 
+    // ---------------- per-instance refill: a sub-warp whose instance has finished writes it out and pulls the next
+    // instance id from the global queue at once, so a warp never idles on the slowest of its 8 instances (iteration
+    // counts are bimodal on hard workloads).  Only the 4 lanes of a finished instance run the pass (shared memory needs
+    // no warp-collective access); the sweeps carry no "finished" predication, parked lanes (queue empty) just own no
+    // instance (valid = false) and store nothing.
+    // Refill policy.  TILE = false: per instance, as described.  TILE = true: the warp waits until all its 8 instances have
+    // finished and takes 8 CONSECUTIVE instances: stores to the element-major carried-state arrays then cover 8
+    // adjacent entries per row instead of one (whole sectors), which matters more than the idle lanes when the
+    // write-out is a large part of a short solve.  Measured on B200, config 3, B = 65,536: double easy 3.67 ms (tile) vs
+    // 4.10 ms (per instance), hard 45.0 vs 38.0 ms; float easy 1.337 vs 1.308 ms, hard 15.8 vs 11.5 ms.
+    constexpr bool TILE = sizeof(T) == 8;
+    int b = 0, iter = 0, my_status = 1;
+    bool valid = false, fin = true, first = true;
+    size_t bb = 0;
+    T x0r[RX], p_term[RX];
+#pragma unroll
+    for (int r = 0; r < RX; ++r) { x0r[r] = T(0); p_term[r] = T(0); }
+    // per-instance references / bounds (only dereferenced when !shared_refs && has_xref, !shared_bounds && box_x):
+    // addresses are formed where they are used, from the instance index and the constant-bank strides
+#define xref_g (bv.Xref + bb * bv.xref_stride)
+#define uref_g (bv.Uref + bb * bv.uref_stride)
+#define xmin_g (bv.x_min + bb * bv.xb_stride)
+#define xmax_g (bv.x_max + bb * bv.xb_stride)
+#define umin_g (bv.u_min + bb * bv.ub_stride)
+#define umax_g (bv.u_max + bb * bv.ub_stride)
+
     for (;;) {
-        // ---------------- next tile from the queue
-        int tile = 0;
-        if (lane == 0) tile = atomicAdd(sp.counter, 1);
-        tile = __shfl_sync(kFull, tile, 0);
-        if (tile >= sp.num_tiles) break;
-        const int b = tile * kTile + inst;
-        const bool valid = b < bv.B;
-        const size_t bb = valid ? static_cast<size_t>(b) : 0;
-
-        const double* xref_g = bv.Xref + bb * bv.xref_stride;   // only dereferenced when !shared_refs && has_xref
-        const double* uref_g = bv.Uref + bb * bv.uref_stride;
-        const double* xmin_g = bv.x_min + bb * bv.xb_stride;    // only dereferenced when !shared_bounds && box_x
-        const double* xmax_g = bv.x_max + bb * bv.xb_stride;
-        const double* umin_g = bv.u_min + bb * bv.ub_stride;
-        const double* umax_g = bv.u_max + bb * bv.ub_stride;
-
-        // ---------------- carried state -> shared memory (each lane moves exactly the entries it owns)
-        T x0r[RX], p_term[RX];
+        const unsigned finmask = __ballot_sync(kFull, fin);
+        const bool pass = TILE ? (__ballot_sync(kFull, fin || !valid) == kFull) : fin;   // TILE: every instance of the warp finished (or parked)
+        if (pass) {
+            // ---------------- results and carried state of the finished instance back to HBM (each lane writes the entries it owns)
+            if (valid) {
+                double* Xs = bv.Xsol + bb * nxN;
+                double* Us = bv.Usol + bb * nuN;
+                const bool unconverged = (my_status != 0);
+                for (int i = 0; i < N; ++i) {
 #pragma unroll
-        for (int r = 0; r < RX; ++r) {
-            x0r[r] = valid ? bv.x0[bb * NX + r * 4 + sub] : T(0);
-            p_term[r] = (valid && !sp.cold) ? reinterpret_cast<T*>(bv.pN)[(r * 4 + sub) * ld + bb] : T(0);
-        }
-        if (sp.cold || !valid) {
-            for (int i = 0; i < N; ++i) {
+                    for (int r = 0; r < RX; ++r) {
+                        const int e = i * NX + r * 4 + sub;
+                        const size_t ge = static_cast<size_t>(e) * ld + bb;
+                        const T vv = s_v[SX(i, r)], gg = s_g[SX(i, r)];
+                        Xs[e] = vv;                                  // solution = vnew of the last iteration (admm.cpp:370,386)
+                        reinterpret_cast<T*>(bv.g)[ge] = gg;
+                        if (unconverged) reinterpret_cast<T*>(bv.v[0])[ge] = vv;   // v = vnew happened (admm.cpp:379); else the lagging copy is already there
+                        if (i < N - 1) {                             // q as update_linear_cost left it (admm.cpp:218-219)
+                            const T xr = sp.shared_refs ? s_xref[e] : (has_xref ? __ldg(xref_g + e) : T(0));
+                            reinterpret_cast<T*>(bv.q)[ge] = R::sub(-R::mul(xr, fr_Qd[r]), R::mul(rho, R::sub(vv, gg)));
+                        }
+                    }
+                }
+                if (urow) for (int i = 0; i < N - 1; ++i) {
+                    const int e = i * NU + sub;
+                    const size_t ge = static_cast<size_t>(e) * ld + bb;
+                    const T zz = s_z[SU(i)], yy = s_y[SU(i)];
+                    Us[e] = zz;
+                    reinterpret_cast<T*>(bv.y)[ge] = yy;
+                    if (unconverged) reinterpret_cast<T*>(bv.z[0])[ge] = zz;
+                    const T ur = sp.shared_refs ? s_uref[e] : (has_uref ? __ldg(uref_g + e) : T(0));
+                    reinterpret_cast<T*>(bv.r)[ge] = R::sub(-R::mul(ur, fr_Rd), R::mul(rho, R::sub(zz, yy)));
+                }
 #pragma unroll
-                for (int r = 0; r < RX; ++r) { s_g[SX(i, r)] = T(0); s_v[SX(i, r)] = T(0); }
+                for (int r = 0; r < RX; ++r) reinterpret_cast<T*>(bv.pN)[(r * 4 + sub) * ld + bb] = p_term[r];
+                if (sub == 0) { bv.status[b] = my_status; bv.iters[b] = iter; }
             }
-            if (urow) for (int i = 0; i < N - 1; ++i) { s_y[SU(i)] = T(0); s_z[SU(i)] = T(0); s_d[SU(i)] = T(0); }
-        } else {
-            for (int i = 0; i < N; ++i) {
+            // ---------------- next instance from the queue
+            int nb = 0;
+            if (TILE) {
+                if (lane == 0) nb = atomicAdd(sp.counter, kTile);
+                nb = __shfl_sync(kFull, nb, 0) + inst;
+            } else {
+                if (sub == 0) nb = atomicAdd(sp.counter, 1);
+                nb = __shfl_sync(finmask, nb, inst);
+            }
+            valid = nb < bv.B;
+            b = valid ? nb : 0;
+            bb = static_cast<size_t>(b);
+
+            // ---------------- carried state -> shared memory (each lane moves exactly the entries it owns)
 #pragma unroll
-                for (int r = 0; r < RX; ++r) {
-                    const size_t ge = static_cast<size_t>(i * NX + r * 4 + sub) * ld + bb;
-                    s_g[SX(i, r)] = reinterpret_cast<T*>(bv.g)[ge]; s_v[SX(i, r)] = reinterpret_cast<T*>(bv.v[0])[ge];
+            for (int r = 0; r < RX; ++r) {
+                x0r[r] = valid ? static_cast<T>(bv.x0[bb * NX + r * 4 + sub]) : T(0);
+                p_term[r] = (valid && !sp.cold) ? reinterpret_cast<T*>(bv.pN)[(r * 4 + sub) * ld + bb] : T(0);
+            }
+            if (sp.cold || !valid) {
+                for (int i = 0; i < N; ++i) {
+#pragma unroll
+                    for (int r = 0; r < RX; ++r) { s_g[SX(i, r)] = T(0); s_v[SX(i, r)] = T(0); }
+                }
+                if (urow) for (int i = 0; i < N - 1; ++i) { s_y[SU(i)] = T(0); s_z[SU(i)] = T(0); s_d[SU(i)] = T(0); }
+            } else {
+                for (int i = 0; i < N; ++i) {
+#pragma unroll
+                    for (int r = 0; r < RX; ++r) {
+                        const size_t ge = static_cast<size_t>(i * NX + r * 4 + sub) * ld + bb;
+                        s_g[SX(i, r)] = reinterpret_cast<T*>(bv.g)[ge]; s_v[SX(i, r)] = reinterpret_cast<T*>(bv.v[0])[ge];
+                    }
+                }
+                if (urow) for (int i = 0; i < N - 1; ++i) {
+                    const size_t ge = static_cast<size_t>(i * NU + sub) * ld + bb;
+                    s_y[SU(i)] = reinterpret_cast<T*>(bv.y)[ge]; s_z[SU(i)] = reinterpret_cast<T*>(bv.z[0])[ge]; s_d[SU(i)] = T(0);
                 }
             }
-            if (urow) for (int i = 0; i < N - 1; ++i) {
-                const size_t ge = static_cast<size_t>(i * NU + sub) * ld + bb;
-                s_y[SU(i)] = reinterpret_cast<T*>(bv.y)[ge]; s_z[SU(i)] = reinterpret_cast<T*>(bv.z[0])[ge]; s_d[SU(i)] = T(0);
-            }
+            iter = 0; my_status = 1; first = true; fin = false;             // a parked lane (queue empty) owns no instance: valid = false
         }
+        __syncwarp();
+        if (!__any_sync(kFull, valid)) break;
+        const bool live = valid && !fin;     // owns an unfinished instance (TILE: finished ones wait here without mutating their state)
 
-        bool done = !valid;       // a finished (or padding) instance stops mutating its state
-        int my_iters = 0, my_status = 1;
-        bool first = true;
-        int iter = 0;
-
-        for (int it = 0; it < st.max_iter; ++it) {
+        {
             const bool may_converge = ((iter + 1) % st.check_termination) == 0;
 
             // ======================= backward sweep: d_i, p_i for i = N-2 .. 0  (reference admm.cpp:13-20)
@@ -255,16 +316,16 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
                     // r_i (own row) and q_i (own rows): carried values on the first sweep of a solve,
                     // afterwards recomputed from the slacks and duals (reference admm.cpp:218-233)
                     T r_own = T(0), q_own[RX];
-                    if (first) {
-                        if (sp.cold || !valid) {
+                    {
+                        const bool carried = first && valid && !sp.cold;      // first sweep of a warm-started solve: the stored q, r
+                        T r_car = T(0), q_car[RX];
 #pragma unroll
-                            for (int r = 0; r < RX; ++r) q_own[r] = T(0);
-                        } else {
-                            if (urow) r_own = reinterpret_cast<T*>(bv.r)[static_cast<size_t>(i * NU + sub) * ld + bb];
+                        for (int r = 0; r < RX; ++r) q_car[r] = T(0);
+                        if (carried) {
+                            if (urow) r_car = reinterpret_cast<T*>(bv.r)[static_cast<size_t>(i * NU + sub) * ld + bb];
 #pragma unroll
-                            for (int r = 0; r < RX; ++r) q_own[r] = reinterpret_cast<T*>(bv.q)[static_cast<size_t>(i * NX + r * 4 + sub) * ld + bb];
+                            for (int r = 0; r < RX; ++r) q_car[r] = reinterpret_cast<T*>(bv.q)[static_cast<size_t>(i * NX + r * 4 + sub) * ld + bb];
                         }
-                    } else {
                         if (urow) {
                             const int e = i * NU + sub;
                             const T ur = sp.shared_refs ? s_uref[e] : (has_uref ? __ldg(uref_g + e) : T(0));
@@ -275,6 +336,12 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
                             const int e = i * NX + r * 4 + sub;
                             const T xr = sp.shared_refs ? s_xref[e] : (has_xref ? __ldg(xref_g + e) : T(0));
                             q_own[r] = R::sub(-R::mul(xr, fr_Qd[r]), R::mul(rho, R::sub(s_v[SX(i, r)], s_g[SX(i, r)])));
+                        }
+                        // first sweep: the carried values (zeros after setup / reset: admm.cpp sees q = r = p = 0 whatever Xref is)
+                        if (first) {
+                            r_own = r_car;
+#pragma unroll
+                            for (int r = 0; r < RX; ++r) q_own[r] = q_car[r];
                         }
                     }
 
@@ -352,7 +419,7 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
                             }
                             const T zold = s_z[SU(i)];
                             ok = ok && (R::abs(R::sub(u_own, znew)) < sp.pri_thresh) && (R::abs(R::sub(zold, znew)) <= sp.dua_thresh);
-                            if (!done) {
+                            if (live) {
                                 s_y[SU(i)] = R::sub(t, znew);          // y + u - znew  (y + u == u + y bit for bit)
                                 s_z[SU(i)] = znew;
                                 if (may_converge) reinterpret_cast<T*>(bv.z[0])[static_cast<size_t>(e) * ld + bb] = zold;   // carried z lags one iteration
@@ -378,7 +445,7 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
                         const T vold = s_v[SX(i, r)];
                         const T gnew = R::sub(t, vnew);
                         ok = ok && (R::abs(R::sub(x[r], vnew)) < sp.pri_thresh) && (R::abs(R::sub(vold, vnew)) <= sp.dua_thresh);
-                        if (!done) {
+                        if (live) {
                             s_g[SX(i, r)] = gnew;
                             s_v[SX(i, r)] = vnew;
                             if (may_converge) reinterpret_cast<T*>(bv.v[0])[static_cast<size_t>(e) * ld + bb] = vold;       // carried v lags one iteration
@@ -397,7 +464,7 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
                             for (int k = 0; k < NU; ++k) s2 = R::fma(Mb[r][k], ub[k], s2);
                             x[r] = R::add(R::add(s1, s2), fr_f[r]);
                         }
-                    } else if (!done) {
+                    } else if (live) {
                         // p_{N-1} = -(Xref_{N-1}' Pinf)' - rho (vnew - g)   (admm.cpp:238-239)
 #pragma unroll
                         for (int r = 0; r < RX; ++r) {
@@ -414,54 +481,24 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
                 }
             }
 
-            // ======================= termination (admm.cpp:253-271, :364-380)
-            iter += 1;
+            // ======================= termination (admm.cpp:253-271, :364-380), per instance
+            if (live) iter += 1;
             const unsigned votes = __ballot_sync(kFull, ok);
             const unsigned mine = 0x01010101u << inst;
             const bool inst_ok = ((iter % st.check_termination) == 0) && ((votes & mine) == mine);
-            if (!done) {
-                my_iters = iter;
-                if (inst_ok) { done = true; my_status = 0; }
+            if (live) {
+                if (inst_ok) { fin = true; my_status = 0; }
+                else if (iter >= st.max_iter) { fin = true; my_status = 1; }
             }
-            first = false;
-            if (__all_sync(kFull, done)) break;
-        }
-
-        // ---------------- results and carried state back to HBM (each lane writes the entries it owns)
-        if (valid) {
-            double* Xs = bv.Xsol + bb * nxN;
-            double* Us = bv.Usol + bb * nuN;
-            const bool unconverged = (my_status != 0);
-            for (int i = 0; i < N; ++i) {
-#pragma unroll
-                for (int r = 0; r < RX; ++r) {
-                    const int e = i * NX + r * 4 + sub;
-                    const size_t ge = static_cast<size_t>(e) * ld + bb;
-                    const T vv = s_v[SX(i, r)], gg = s_g[SX(i, r)];
-                    Xs[e] = vv;                                  // solution = vnew of the last iteration (admm.cpp:370,386)
-                    reinterpret_cast<T*>(bv.g)[ge] = gg;
-                    if (unconverged) reinterpret_cast<T*>(bv.v[0])[ge] = vv;           // v = vnew happened (admm.cpp:379); else the lagging copy is already there
-                    if (i < N - 1) {                             // q as update_linear_cost left it (admm.cpp:218-219)
-                        const T xr = sp.shared_refs ? s_xref[e] : (has_xref ? __ldg(xref_g + e) : T(0));
-                        reinterpret_cast<T*>(bv.q)[ge] = R::sub(-R::mul(xr, fr_Qd[r]), R::mul(rho, R::sub(vv, gg)));
-                    }
-                }
-            }
-            if (urow) for (int i = 0; i < N - 1; ++i) {
-                const int e = i * NU + sub;
-                const size_t ge = static_cast<size_t>(e) * ld + bb;
-                const T zz = s_z[SU(i)], yy = s_y[SU(i)];
-                Us[e] = zz;
-                reinterpret_cast<T*>(bv.y)[ge] = yy;
-                if (unconverged) reinterpret_cast<T*>(bv.z[0])[ge] = zz;
-                const T ur = sp.shared_refs ? s_uref[e] : (has_uref ? __ldg(uref_g + e) : T(0));
-                reinterpret_cast<T*>(bv.r)[ge] = R::sub(-R::mul(ur, fr_Rd), R::mul(rho, R::sub(zz, yy)));
-            }
-#pragma unroll
-            for (int r = 0; r < RX; ++r) reinterpret_cast<T*>(bv.pN)[(r * 4 + sub) * ld + bb] = p_term[r];
-            if (sub == 0) { bv.status[b] = my_status; bv.iters[b] = my_iters; }
+            if (live) first = false;
         }
     }
+#undef xref_g
+#undef uref_g
+#undef xmin_g
+#undef xmax_g
+#undef umin_g
+#undef umax_g
 #undef SX
 #undef SU
 }
@@ -512,7 +549,7 @@ cudaError_t launch(const BatchView& bv, const AdmmSettings& st, int cold, int* c
     Plan<T> pl;
     if (!make_plan<T, NX, NU, MAXW>(bv, pl)) return cudaErrorInvalidConfiguration;
     pl.sp.cold = cold;
-    pl.sp.num_tiles = (bv.B + kTile - 1) / kTile;
+    pl.sp.num_tiles = (bv.B + kTile - 1) / kTile;      // grid sizing only: the queue hands out instances
     pl.sp.counter = counter;
     pl.sp.pri_thresh = static_cast<T>(st.abs_pri_tol);
     pl.sp.dua_thresh = dual_threshold<T>(static_cast<T>(bv.rho), static_cast<T>(st.abs_dua_tol));
