@@ -155,7 +155,8 @@ int tmpc_batch_update_settings(tmpc_batch* h, double abs_pri_tol, double abs_dua
  * tinytype`, float being its other build).  bits = 32: the setup is redone as the float build does it (problem data and
  * rho rounded to float as in src/bindings.cpp:50-55, cache computed in float) and later solves run the float
  * instantiation of the kernel, inputs rounded on load as in bindings.cpp:82,105,128 and results widened as in :172,194;
- * the ABI stays double.  Only on a fresh / reset batch with shared dynamics; the float build runs the thread kernel. */
+ * the ABI stays double.  Only on a fresh / reset batch with shared dynamics; the float build runs the
+ * shared-memory sub-warp kernel where the shape is compiled and the thread kernel otherwise (the TMEM kernels are 64-bit). */
 int tmpc_batch_set_precision(tmpc_batch* h, int bits);   /* 32 or 64 (default) */
 int tmpc_batch_get_precision(tmpc_batch* h);
 int tmpc_batch_set_kernel(tmpc_batch* h, int kernel);   /* TMPC_KERNEL_*; AUTO picks TMEM, then SUBWARP, where they apply */

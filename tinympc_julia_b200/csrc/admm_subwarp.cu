@@ -54,8 +54,9 @@ struct SubwarpParams {
 };
 
 template <class T, int NX>
-struct Pad {   // row pitch of the broadcast slot: an odd number of pair-sized (2 T) chunks => 8 instances hit 8 bank groups
-    static constexpr int value = ((NX / 2) % 2 == 1) ? NX : NX + 2;
+struct Pad {   // row pitch of the broadcast slot: an odd number of 16-byte chunks => the 8 instances hit 8 different bank groups
+    static constexpr int kChunk = 16 / sizeof(T);                       // values per 128-bit load: 2 doubles, 4 floats
+    static constexpr int value = ((NX / kChunk) % 2 == 1) ? NX : NX + kChunk;
 };
 
 template <int NX, int NU>
@@ -87,6 +88,21 @@ __device__ __forceinline__ void lds128(const double* p, double& a, double& b) {
 __device__ __forceinline__ void lds128(const float* p, float& a, float& b) {
     const float2 t = *reinterpret_cast<const float2*>(p);
     a = t.x; b = t.y;
+}
+// NX consecutive values from a 16-byte aligned row, 128 bits per load
+template <int NX>
+__device__ __forceinline__ void ldrow(const double* p, double* out) {
+#pragma unroll
+    for (int k = 0; k < NX; k += 2) lds128(p + k, out[k], out[k + 1]);
+}
+template <int NX>
+__device__ __forceinline__ void ldrow(const float* p, float* out) {
+    static_assert(NX % 4 == 0, "float rows are read four values at a time");
+#pragma unroll
+    for (int k = 0; k < NX; k += 4) {
+        const float4 t = *reinterpret_cast<const float4*>(p + k);
+        out[k] = t.x; out[k + 1] = t.y; out[k + 2] = t.z; out[k + 3] = t.w;
+    }
 }
 
 template <class T, int NX, int NU, int MAXW>
@@ -288,8 +304,7 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
                 T Mab[RX][NX], Mkt[RX][NU], Mbt[NX], Mq[NU];
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
-#pragma unroll
-                    for (int k = 0; k < NX; k += 2) lds128(sc + CL::AmBKt_rm + (r * 4 + sub) * NX + k, Mab[r][k], Mab[r][k + 1]);
+                    ldrow<NX>(sc + CL::AmBKt_rm + (r * 4 + sub) * NX, Mab[r]);
 #pragma unroll
                     for (int k = 0; k < NU; ++k) Mkt[r][k] = sc[CL::Kinf_cm + (r * 4 + sub) * NU + k];
                 }
@@ -310,8 +325,7 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
                     for (int r = 0; r < RX; ++r) slot[r * 4 + sub] = p[r];
                     __syncwarp();
                     T pb[NX];
-#pragma unroll
-                    for (int k = 0; k < NX; k += 2) lds128(slot + k, pb[k], pb[k + 1]);
+                    ldrow<NX>(slot, pb);
 
                     // r_i (own row) and q_i (own rows): carried values on the first sweep of a solve,
                     // afterwards recomputed from the slacks and duals (reference admm.cpp:218-233)
@@ -377,8 +391,7 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
                 T Ma[RX][NX], Mb[RX][NU], Mk[NX];
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
-#pragma unroll
-                    for (int k = 0; k < NX; k += 2) lds128(sc + CL::A_rm + (r * 4 + sub) * NX + k, Ma[r][k], Ma[r][k + 1]);
+                    ldrow<NX>(sc + CL::A_rm + (r * 4 + sub) * NX, Ma[r]);
 #pragma unroll
                     for (int k = 0; k < NU; ++k) Mb[r][k] = sc[CL::B_rm + (r * 4 + sub) * NU + k];
                 }
@@ -398,8 +411,7 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
 #pragma unroll
                         for (int r = 0; r < RX; ++r) slot[r * 4 + sub] = x[r];
                         __syncwarp();
-#pragma unroll
-                        for (int k = 0; k < NX; k += 2) lds128(slot + k, xb[k], xb[k + 1]);
+                        ldrow<NX>(slot, xb);
 
                         // u_i = -Kinf x_i - d_i ; input slack, dual, residuals (admm.cpp:28, :87, :97, :187, :259-260)
                         T s = T(0);
