@@ -89,6 +89,9 @@ __device__ __forceinline__ void lds128(const float* p, float& a, float& b) {
     const float2 t = *reinterpret_cast<const float2*>(p);
     a = t.x; b = t.y;
 }
+// two consecutive values with one store
+__device__ __forceinline__ void sts_pair(double* p, double a, double b) { *reinterpret_cast<double2*>(p) = make_double2(a, b); }
+__device__ __forceinline__ void sts_pair(float* p, float a, float b) { *reinterpret_cast<float2*>(p) = make_float2(a, b); }
 // NX consecutive values from a 16-byte aligned row, 128 bits per load
 template <int NX>
 __device__ __forceinline__ void ldrow(const double* p, double* out) {
@@ -170,15 +173,14 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
     const int inst = lane & 7, sub = lane >> 3;
     const bool urow = sub < NU;                       // this lane owns an input row
     T* wbase = smem + sp.off_warp0 + static_cast<size_t>(warp) * sp.warp_stride;
-    T* s_g = wbase;
-    T* s_v = s_g + nxN * kTile;
-    T* s_y = s_v + nxN * kTile;
-    T* s_z = s_y + nuN * kTile;
-    T* s_d = s_z + nuN * kTile;
+    T* s_gv = wbase;                             // (g, v) pairs: one load / store moves both
+    T* s_yz = s_gv + 2 * nxN * kTile;            // (y, z) pairs
+    T* s_d = s_yz + 2 * nuN * kTile;
     T* s_bc = s_d + nuN * kTile;                 // 2 x kTile x XP broadcast slots
     // state entry (column i, owned row r):  [(i*NX + r*4)*8 + lane];  input entry (column i): [i*NU*8 + lane]
-#define SX(i, r) (((i) * NX + (r) * 4) * kTile + lane)
-#define SU(i) ((i) * NU * kTile + lane)
+#define SX(i, r) (2 * (((i) * NX + (r) * 4) * kTile + lane))
+#define SU(i) (2 * ((i) * NU * kTile + lane))
+#define SD(i) ((i) * NU * kTile + lane)
 
     const T fr_BPf = urow ? sc[CL::BPf + sub] : T(0);
     const T fr_Rd = urow ? sc[CL::Rd + sub] : T(0);
@@ -228,7 +230,8 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
                     for (int r = 0; r < RX; ++r) {
                         const int e = i * NX + r * 4 + sub;
                         const size_t ge = static_cast<size_t>(e) * ld + bb;
-                        const T vv = s_v[SX(i, r)], gg = s_g[SX(i, r)];
+                        T vv, gg;
+                        lds128(s_gv + SX(i, r), gg, vv);
                         Xs[e] = vv;                                  // solution = vnew of the last iteration (admm.cpp:370,386)
                         reinterpret_cast<T*>(bv.g)[ge] = gg;
                         if (unconverged) reinterpret_cast<T*>(bv.v[0])[ge] = vv;   // v = vnew happened (admm.cpp:379); else the lagging copy is already there
@@ -241,7 +244,8 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
                 if (urow) for (int i = 0; i < N - 1; ++i) {
                     const int e = i * NU + sub;
                     const size_t ge = static_cast<size_t>(e) * ld + bb;
-                    const T zz = s_z[SU(i)], yy = s_y[SU(i)];
+                    T zz, yy;
+                    lds128(s_yz + SU(i), yy, zz);
                     Us[e] = zz;
                     reinterpret_cast<T*>(bv.y)[ge] = yy;
                     if (unconverged) reinterpret_cast<T*>(bv.z[0])[ge] = zz;
@@ -274,20 +278,20 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
             if (sp.cold || !valid) {
                 for (int i = 0; i < N; ++i) {
 #pragma unroll
-                    for (int r = 0; r < RX; ++r) { s_g[SX(i, r)] = T(0); s_v[SX(i, r)] = T(0); }
+                    for (int r = 0; r < RX; ++r) sts_pair(s_gv + SX(i, r), T(0), T(0));
                 }
-                if (urow) for (int i = 0; i < N - 1; ++i) { s_y[SU(i)] = T(0); s_z[SU(i)] = T(0); s_d[SU(i)] = T(0); }
+                if (urow) for (int i = 0; i < N - 1; ++i) { sts_pair(s_yz + SU(i), T(0), T(0)); s_d[SD(i)] = T(0); }
             } else {
                 for (int i = 0; i < N; ++i) {
 #pragma unroll
                     for (int r = 0; r < RX; ++r) {
                         const size_t ge = static_cast<size_t>(i * NX + r * 4 + sub) * ld + bb;
-                        s_g[SX(i, r)] = reinterpret_cast<T*>(bv.g)[ge]; s_v[SX(i, r)] = reinterpret_cast<T*>(bv.v[0])[ge];
+                        sts_pair(s_gv + SX(i, r), reinterpret_cast<T*>(bv.g)[ge], reinterpret_cast<T*>(bv.v[0])[ge]);
                     }
                 }
                 if (urow) for (int i = 0; i < N - 1; ++i) {
                     const size_t ge = static_cast<size_t>(i * NU + sub) * ld + bb;
-                    s_y[SU(i)] = reinterpret_cast<T*>(bv.y)[ge]; s_z[SU(i)] = reinterpret_cast<T*>(bv.z[0])[ge]; s_d[SU(i)] = T(0);
+                    sts_pair(s_yz + SU(i), reinterpret_cast<T*>(bv.y)[ge], reinterpret_cast<T*>(bv.z[0])[ge]); s_d[SD(i)] = T(0);
                 }
             }
             iter = 0; my_status = 1; first = true; fin = false;             // a parked lane (queue empty) owns no instance: valid = false
@@ -343,13 +347,17 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
                         if (urow) {
                             const int e = i * NU + sub;
                             const T ur = sp.shared_refs ? s_uref[e] : (has_uref ? __ldg(uref_g + e) : T(0));
-                            r_own = R::sub(-R::mul(ur, fr_Rd), R::mul(rho, R::sub(s_z[SU(i)], s_y[SU(i)])));
+                            T yy, zz;
+                            lds128(s_yz + SU(i), yy, zz);
+                            r_own = R::sub(-R::mul(ur, fr_Rd), R::mul(rho, R::sub(zz, yy)));
                         }
 #pragma unroll
                         for (int r = 0; r < RX; ++r) {
                             const int e = i * NX + r * 4 + sub;
                             const T xr = sp.shared_refs ? s_xref[e] : (has_xref ? __ldg(xref_g + e) : T(0));
-                            q_own[r] = R::sub(-R::mul(xr, fr_Qd[r]), R::mul(rho, R::sub(s_v[SX(i, r)], s_g[SX(i, r)])));
+                            T gg, vv;
+                            lds128(s_gv + SX(i, r), gg, vv);
+                            q_own[r] = R::sub(-R::mul(xr, fr_Qd[r]), R::mul(rho, R::sub(vv, gg)));
                         }
                         // first sweep: the carried values (zeros after setup / reset: admm.cpp sees q = r = p = 0 whatever Xref is)
                         if (first) {
@@ -370,7 +378,7 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
                         dsum = R::fma(Mq[k], shfl_d(t_own, k * kTile + inst), dsum);
                         rr[k] = shfl_d(r_own, k * kTile + inst);
                     }
-                    if (urow) s_d[SU(i)] = dsum;
+                    if (urow) s_d[SD(i)] = dsum;
 
                     // p_i = q_i + AmBKt p_{i+1} - Kinf' r_i + APf
 #pragma unroll
@@ -420,8 +428,9 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
                         T u_own = T(0);
                         if (urow) {
                             const int e = i * NU + sub;
-                            u_own = R::sub(-s, s_d[SU(i)]);
-                            const T yj = s_y[SU(i)];
+                            u_own = R::sub(-s, s_d[SD(i)]);
+                            T yj, zold;
+                            lds128(s_yz + SU(i), yj, zold);
                             const T t = R::add(u_own, yj);
                             T znew = t;
                             if (box_u) {
@@ -429,11 +438,9 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
                                 const T hi = sp.shared_bounds ? s_umax[e] : __ldg(umax_g + e);
                                 znew = R::clamp(t, lo, hi);
                             }
-                            const T zold = s_z[SU(i)];
                             ok = ok && (R::abs(R::sub(u_own, znew)) < sp.pri_thresh) && (R::abs(R::sub(zold, znew)) <= sp.dua_thresh);
                             if (live) {
-                                s_y[SU(i)] = R::sub(t, znew);          // y + u - znew  (y + u == u + y bit for bit)
-                                s_z[SU(i)] = znew;
+                                sts_pair(s_yz + SU(i), R::sub(t, znew), znew);   // y + u - znew  (y + u == u + y bit for bit)
                                 if (may_converge) reinterpret_cast<T*>(bv.z[0])[static_cast<size_t>(e) * ld + bb] = zold;   // carried z lags one iteration
                             }
                         }
@@ -446,7 +453,8 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
 #pragma unroll
                     for (int r = 0; r < RX; ++r) {
                         const int e = i * NX + r * 4 + sub;
-                        const T gj = s_g[SX(i, r)];
+                        T gj, vold;
+                        lds128(s_gv + SX(i, r), gj, vold);
                         const T t = R::add(x[r], gj);
                         T vnew = t;
                         if (box_x) {
@@ -454,12 +462,10 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
                             const T hi = sp.shared_bounds ? s_xmax[e] : __ldg(xmax_g + e);
                             vnew = R::clamp(t, lo, hi);
                         }
-                        const T vold = s_v[SX(i, r)];
                         const T gnew = R::sub(t, vnew);
                         ok = ok && (R::abs(R::sub(x[r], vnew)) < sp.pri_thresh) && (R::abs(R::sub(vold, vnew)) <= sp.dua_thresh);
                         if (live) {
-                            s_g[SX(i, r)] = gnew;
-                            s_v[SX(i, r)] = vnew;
+                            sts_pair(s_gv + SX(i, r), gnew, vnew);
                             if (may_converge) reinterpret_cast<T*>(bv.v[0])[static_cast<size_t>(e) * ld + bb] = vold;       // carried v lags one iteration
                         }
                         vg[r] = R::sub(vnew, gnew);
@@ -513,6 +519,7 @@ admm_subwarp_kernel(const __grid_constant__ BatchView bv, const __grid_constant_
 #undef umax_g
 #undef SX
 #undef SU
+#undef SD
 }
 
 // Largest a >= 0 with fl(rho * a) < tol (in T), so that  rho * max|.| < tol  <=>  every |.| <= a.
