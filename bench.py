@@ -383,7 +383,7 @@ def run_gpu(args, rank, local_rank, world):
     kname = {1: "thread", 2: "subwarp", 3: "tmem", 4: "tmem2"}.get(sol.kernel, str(sol.kernel))
     traffic = None
     try:
-        rec = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(kname)
+        rec = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(kname + ("_f32" if args.precision == 32 else ""))
         if rec and rec.get("workload") == args.workload and rec.get("B") == B:
             traffic = rec["dram_read_bytes"] + rec["dram_write_bytes"]
     except Exception:
