@@ -460,3 +460,18 @@ def test_float_build_warm_start_and_guards():
     sol.set_kernel(t.KERNEL_AUTO)
     back = cases.run_cuda(cases.GOLDEN_CASES["quadrotor_easy_64"](), sol=sol)
     cases.compare(back, cases.load_golden("quadrotor_easy_64"), what="double again after set_precision(64)")
+
+
+@pytest.mark.gpu
+def test_adaptive_rho_is_refused_not_imitated():
+    """SURVEY.md 8f rank 4 / DESIGN.md 8 item 4: through the reference's own symbols the adaptive-rho branch reads
+    0 x 0 sensitivity matrices (rho_benchmark.cpp:204-207 after src/bindings.cpp:362) and crashes; the device path says
+    so instead, for the batch handle and for the Julia-facing singleton, and the settings in force are unchanged."""
+    from tinympc_julia_b200 import _lib
+    c = cases.GOLDEN_CASES["quadrotor_easy_64"]()
+    sol = cases.make_cuda_solver(c, kernel=t.KERNEL_AUTO)
+    with pytest.raises(t.TinyMPCError):
+        t.update_settings(sol, max_iter=3, en_state_bound=True, en_input_bound=True, adaptive_rho=True)
+    assert "adaptive_rho" in _lib.last_error()
+    out = cases.run_cuda(c, sol=sol)                        # still the case's own settings (max_iter 100, not 3)
+    cases.compare(out, cases.load_golden("quadrotor_easy_64"), what="after a refused update_settings")

@@ -389,7 +389,7 @@ int tmpc_batch_update_settings(tmpc_batch* h, double abs_pri_tol, double abs_dua
     return guarded([&]() -> int {
         if (!h) { set_error("update_settings: null handle"); return TMPC_ERR_DIM; }
         if (check_termination == 0) { set_error("update_settings: check_termination = 0 rejected (reference computes iter % 0)"); return TMPC_ERR_STATE; }
-        if (adaptive_rho) { set_error("update_settings: adaptive_rho is not implemented on the device path"); return TMPC_ERR_STATE; }
+        if (adaptive_rho) { set_error("update_settings: adaptive_rho refused: through this API the reference reads unset (0 x 0) sensitivity matrices in that branch and crashes (DESIGN.md 8, item 4); nothing to be in parity with"); return TMPC_ERR_STATE; }
         h->st.abs_pri_tol = abs_pri_tol; h->st.abs_dua_tol = abs_dua_tol;
         h->st.max_iter = max_iter; h->st.check_termination = check_termination;
         h->st.en_state_bound = en_state_bound != 0; h->st.en_input_bound = en_input_bound != 0;
