@@ -49,6 +49,7 @@ def emit(line: dict) -> None:
     _JSON_OUT.flush()
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
+E2E_CHUNKS = int(os.environ.get("TMPC_E2E_CHUNKS", "0"))   # 0 = the library default; sweep aid for tmpc_batch_solve_host
 for p in (ROOT, os.path.join(ROOT, "tests")):
     if p not in sys.path:
         sys.path.insert(0, p)
@@ -428,7 +429,7 @@ def run_gpu(args, rank, local_rank, world):
 
     def e2e_step():
         # one call: x0 up, solve cut into instance chunks, each chunk's solution crossing PCIe while the next one solves
-        assert lib.tmpc_batch_solve_host(h, dp(x0_pinned), 1, dp(X_host), dp(U_host), ip(st_host), ip(it_host), 0) in (0, 1)
+        assert lib.tmpc_batch_solve_host(h, dp(x0_pinned), 1, dp(X_host), dp(U_host), ip(st_host), ip(it_host), E2E_CHUNKS) in (0, 1)
 
     def e2e_step_calls():
         # the same through the five reference-style calls (no overlap): reported next to the pipelined number

@@ -718,15 +718,17 @@ int tmpc_batch_solve_host(tmpc_batch* h, const double* x0, int cold, double* X, 
         const int k = resolve_kernel(h);
         if (k < 0) { set_error("requested kernel does not support this problem"); return 100 + TMPC_ERR_STATE; }
         const bool tm = (k == TMPC_KERNEL_TMEM || k == TMPC_KERNEL_TMEM2) && h->st.max_iter > 0 && h->rho > 0.0;
-        // chunks are whole waves of the persistent grid (one CTA per SM, 64 resident instances each), at least two
-        // waves each, so that a chunk runs at the efficiency of the full batch
+        // chunks are whole waves of the persistent grid (one CTA per SM, 64 resident instances each).  Default: one
+        // wave per chunk, at most 8 chunks - the device->host copy is the long pole (166 MB against 0.8 ms of solve at
+        // B = 65,536 quadrotors), so an early first copy is worth more than the refill efficiency of longer chunks
+        // (measured: 4 chunks of 2 waves 3.44 ms, 7 chunks of 1 wave 3.37 ms; no difference on the hard workload)
         const int wave = h->num_sms * 64;
-        int nch = chunks > 0 ? chunks : 4;
+        int nch = chunks > 0 ? chunks : std::min(8, (h->B + wave - 1) / wave);
         if (!tm || h->B < 3 * wave) nch = 1;
         int chunk_size = h->B;
         if (nch > 1) {
             chunk_size = ((h->B + nch - 1) / nch + wave - 1) / wave * wave;
-            if (chunk_size < 2 * wave) chunk_size = 2 * wave;
+            if (chunk_size < wave) chunk_size = wave;
             nch = (h->B + chunk_size - 1) / chunk_size;
         }
         if (!h->copy_stream) CUDA_TRY(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
@@ -770,8 +772,10 @@ int tmpc_batch_solve_host(tmpc_batch* h, const double* x0, int cold, double* X, 
                 const size_t nb = static_cast<size_t>(b1 - b0);
                 if (X) CUDA_TRY(cudaMemcpyAsync(X + b0 * sxN, v.Xsol + b0 * sxN, sizeof(double) * sxN * nb, cudaMemcpyDeviceToHost, h->copy_stream));
                 if (U) CUDA_TRY(cudaMemcpyAsync(U + b0 * suN, v.Usol + b0 * suN, sizeof(double) * suN * nb, cudaMemcpyDeviceToHost, h->copy_stream));
-                CUDA_TRY(cudaMemcpyAsync(status + b0, v.status + b0, sizeof(int) * nb, cudaMemcpyDeviceToHost, h->copy_stream));
-                if (iters) CUDA_TRY(cudaMemcpyAsync(iters + b0, v.iters + b0, sizeof(int) * nb, cudaMemcpyDeviceToHost, h->copy_stream));
+                if (c == nch - 1) {   // status / iteration counts of the whole batch behind the last chunk: two copies, not 2 per chunk
+                    CUDA_TRY(cudaMemcpyAsync(status, v.status, sizeof(int) * h->B, cudaMemcpyDeviceToHost, h->copy_stream));
+                    if (iters) CUDA_TRY(cudaMemcpyAsync(iters, v.iters, sizeof(int) * h->B, cudaMemcpyDeviceToHost, h->copy_stream));
+                }
             }
             h->state_zero = false; h->mem_zero = false; h->state_in_im = true;
             CUDA_TRY(cudaStreamSynchronize(h->copy_stream));
