@@ -709,9 +709,9 @@ int tmpc_batch_solve_host(tmpc_batch* h, const double* x0, int cold, double* X, 
         if (!h) return TMPC_ERR_DIM;
         h->use_device();
         if (h->st.check_termination == 0) { set_error("check_termination = 0 is not supported (the reference divides by it)"); return 100 + TMPC_ERR_STATE; }
-        if (x0) {
+        if (x0) {   // copied below: whole before a single launch, else chunk by chunk in front of each chunk's launch
             h->ext_x0 = nullptr;
-            h->x0.upload(x0, static_cast<size_t>(h->nx) * h->B, h->stream);
+            if (h->x0.n < static_cast<size_t>(h->nx) * h->B) h->x0.alloc(static_cast<size_t>(h->nx) * h->B);
         }
         if (cold) h->state_zero = true;
         ensure_aux_state(h);
@@ -752,6 +752,8 @@ int tmpc_batch_solve_host(tmpc_batch* h, const double* x0, int cold, double* X, 
                 const int b1 = std::min(h->B, b0 + chunk_size);
                 tmpc::BatchView vc = v;
                 vc.B = b1 - b0;
+                if (x0) CUDA_TRY(cudaMemcpyAsync(h->x0.p + static_cast<size_t>(b0) * h->nx, x0 + static_cast<size_t>(b0) * h->nx,
+                                                 sizeof(double) * h->nx * (b1 - b0), cudaMemcpyHostToDevice, h->stream));
                 vc.x0 = v.x0 + static_cast<size_t>(b0) * h->nx;
                 if (v.Xref && v.xref_stride) vc.Xref = v.Xref + static_cast<size_t>(b0) * v.xref_stride;
                 if (v.Uref && v.uref_stride) vc.Uref = v.Uref + static_cast<size_t>(b0) * v.uref_stride;
@@ -781,6 +783,7 @@ int tmpc_batch_solve_host(tmpc_batch* h, const double* x0, int cold, double* X, 
             CUDA_TRY(cudaStreamSynchronize(h->copy_stream));
             CUDA_TRY(cudaStreamSynchronize(h->stream));
         } else {
+            if (x0) CUDA_TRY(cudaMemcpyAsync(h->x0.p, x0, sizeof(double) * h->nx * h->B, cudaMemcpyHostToDevice, h->stream));
             cudaError_t e = launch_solve(h, k, v, h->stream);
             if (e != cudaSuccess) throw CudaFail{e, "solve kernel launch"};
             const size_t nb = static_cast<size_t>(h->B);
