@@ -26,6 +26,7 @@
  */
 #ifndef TINYMPC_B200_H
 #define TINYMPC_B200_H
+#include <stddef.h>
 
 #ifdef __cplusplus
 extern "C" {
@@ -118,10 +119,8 @@ enum {
     TMPC_KERNEL_AUTO = 0,
     TMPC_KERNEL_THREAD = 1,   /* one thread per instance, state streamed through L2/HBM each iteration; any nx, nu */
     TMPC_KERNEL_SUBWARP = 2,  /* one instance per 4-lane sub-warp, state resident in shared memory (box constraints) */
-    TMPC_KERNEL_TMEM = 3,     /* 4-lane sub-warp, state rows in Tensor Memory + input rows in shared memory, 8 warps/SM,
+    TMPC_KERNEL_TMEM = 3      /* 4-lane sub-warp, state rows in Tensor Memory + input rows in shared memory, 8 warps/SM,
                                  per-instance refill (box constraints with shared bounds, nx=12 nu=4, N <= 21) */
-    TMPC_KERNEL_TMEM2 = 4     /* the same with two instances per lane and one resident double per element
-                                 (16 instances per warp, 128 per SM); opt-in: measured slower than TMEM, DESIGN.md 3.4 */
 };
 
 /* Host-only: the infinite-horizon LQR cache the solve loop reads (replaces tiny_precompute_and_set_cache,
@@ -161,6 +160,15 @@ int tmpc_batch_set_precision(tmpc_batch* h, int bits);   /* 32 or 64 (default) *
 int tmpc_batch_get_precision(tmpc_batch* h);
 int tmpc_batch_set_kernel(tmpc_batch* h, int kernel);   /* TMPC_KERNEL_*; AUTO picks TMEM, then SUBWARP, where they apply */
 int tmpc_batch_get_kernel(tmpc_batch* h);               /* kernel the next solve will run (resolved AUTO) */
+
+/* Queue order of the on-chip (persistent) kernels.  Iteration counts are data-dependent (admm.cpp:312-381), so an
+ * instance that needs 25 iterations and is pulled in the last wave holds one sub-warp while the other SMs idle.
+ * AUTO (default): instances expected to run longest go first - cold start: by the saturation of the unconstrained LQR
+ * input, max_j |(Kinf x0)_j| / min(|u_min_j|, |u_max_j|); warm start: by the iteration count of the previous solve.
+ * USER: `perm` (host, B entries, a permutation of 0..B-1) is the order.  Results never depend on the order. */
+enum { TMPC_ORDER_NATURAL = 0, TMPC_ORDER_AUTO = 1, TMPC_ORDER_USER = 2 };
+int tmpc_batch_set_order(tmpc_batch* h, int mode, const int* perm);
+int tmpc_batch_get_order(tmpc_batch* h, int* perm);   /* the permutation the last solve used (TMPC_ERR_STATE: natural) */
 
 /* Host-pointer setters.  `batch` = 1: one matrix shared by all instances; `batch` = B: one per instance. */
 int tmpc_batch_set_x0(tmpc_batch* h, const double* x0, int rows, int batch);                 /* nx x B */
@@ -214,6 +222,12 @@ int tmpc_batch_solve_async(tmpc_batch* h, void* cuda_stream);   /* enqueue only;
  * Pinned host buffers make the copies truly asynchronous.  Returns like tmpc_batch_solve (0 / 1 / 100 + error). */
 int tmpc_batch_solve_host(tmpc_batch* h, const double* x0, int cold, double* X, double* U, int* status, int* iters,
                           int chunks);
+/* The same with an output selector: u0 (nu x B) receives the FIRST control of every instance, which is all a closed
+ * loop consumes from a solve (examples/cartpole_example_mpc.jl:41-42: `u = solution.controls[:, 1]`).  Any of X, U, u0,
+ * status, iters may be NULL; with X = U = NULL the device-to-host traffic is nu + 1 words per instance instead of the
+ * 2.5 KB trajectories. */
+int tmpc_batch_solve_host_select(tmpc_batch* h, const double* x0, int cold, double* X, double* U, double* u0,
+                                 int* status, int* iters, int chunks);
 int tmpc_batch_synchronize(tmpc_batch* h);
 
 /* Per-instance results.  status[b] = what solve_mpc would return for that instance (0 / 1). */
@@ -243,6 +257,11 @@ int tmpc_batch_set_rollout_fused(tmpc_batch* h, int fused);
 /* Current x0 of every instance (after a rollout: the plant state reached), nx x B.  `device_dst` != 0: dst is a device
  * pointer on the batch's device (device-to-device copy), else a host buffer. */
 int tmpc_batch_get_x0(tmpc_batch* h, void* dst, int device_dst);
+
+/* Page-locked host memory for the buffers of tmpc_batch_solve_host*: with pageable buffers every copy of the call
+ * blocks the host and the chunks cannot overlap.  NULL when no CUDA device is usable. */
+void* tmpc_host_alloc(size_t bytes);
+void tmpc_host_free(void* p);
 
 /* Introspection */
 int tmpc_batch_dims(tmpc_batch* h, int* nx, int* nu, int* N, int* B);

@@ -49,6 +49,8 @@ SIGNATURES = {
     "tmpc_batch_get_precision": (_I, [_V]),
     "tmpc_batch_set_kernel": (_I, [_V, _I]),
     "tmpc_batch_get_kernel": (_I, [_V]),
+    "tmpc_batch_set_order": (_I, [_V, _I, _IP]),
+    "tmpc_batch_get_order": (_I, [_V, _IP]),
     "tmpc_batch_set_x0": (_I, [_V, _P, _I, _I]),
     "tmpc_batch_set_x_ref": (_I, [_V, _P, _I, _I, _I]),
     "tmpc_batch_set_u_ref": (_I, [_V, _P, _I, _I, _I]),
@@ -66,6 +68,7 @@ SIGNATURES = {
     "tmpc_batch_get_instance_cache": (_I, [_V, _I, _P, _P, _P, _P, _P, _P]),
     "tmpc_batch_set_rollout_fused": (_I, [_V, _I]),
     "tmpc_batch_solve_host": (_I, [_V, _P, _I, _P, _P, _IP, _IP, _I]),
+    "tmpc_batch_solve_host_select": (_I, [_V, _P, _I, _P, _P, _P, _IP, _IP, _I]),
     "tmpc_batch_synchronize": (_I, [_V]),
     "tmpc_batch_get_status": (_I, [_V, _IP, _IP]),
     "tmpc_batch_get_states": (_I, [_V, _P]),
@@ -78,6 +81,8 @@ SIGNATURES = {
     "tmpc_batch_get_x0": (_I, [_V, _V, _I]),
     "tmpc_batch_dims": (_I, [_V, _IP, _IP, _IP, _IP]),
     "tmpc_batch_launch_count": (C.c_longlong, [_V]),
+    "tmpc_host_alloc": (_V, [C.c_size_t]),
+    "tmpc_host_free": (None, [_V]),
     "tmpc_measure_fma_peak": (_I, [_I, _I, _I, _P]),
     "tmpc_last_error": (C.c_char_p, []),
     "tmpc_version": (C.c_char_p, []),

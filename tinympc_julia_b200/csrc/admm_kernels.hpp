@@ -51,9 +51,11 @@ cudaError_t launch_admm_subwarp(const BatchView& bv, const AdmmSettings& st, con
 
 // ---- one instance per 4-lane sub-warp, state rows in Tensor Memory + input rows in shared memory, per-instance
 // refill from a global queue (admm_tmem.cu).  Box-constrained (or unconstrained) problems with shared bounds.
+// `order` (all TMEM launchers): device permutation of 0..B-1 the queue tickets index (queue_order.cu), or nullptr for
+// the natural order.
 bool tmem_kernel_supports(const BatchView& bv, const AdmmSettings& st);
 cudaError_t launch_admm_tmem(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms,
-                             cudaStream_t stream);
+                             cudaStream_t stream, const int* order = nullptr);
 
 // Per-instance dynamics on the TMEM kernel: one QConst-layout block of constants per instance (packed once from the
 // element-major cache); the lane's matrix rows come from its instance's block at every sweep start (L2-resident for
@@ -63,7 +65,7 @@ cudaError_t launch_tmem_pi_pack(int nx, int nu, const PerInstanceMats& pm, long 
                                 cudaStream_t stream);
 bool tmem_pi_kernel_supports(const BatchView& bv, const AdmmSettings& st);
 cudaError_t launch_admm_tmem_pi(const BatchView& bv, const AdmmSettings& st, int cold, const double* pi_blocks,
-                                int* counter, int num_sms, cudaStream_t stream);
+                                int* counter, int num_sms, cudaStream_t stream, const int* order = nullptr);
 
 // Fused closed loop on the TMEM kernel: every instance runs `nsteps` MPC steps (solve -> apply znew(:,0) -> plant step ->
 // slide the reference window -> next solve) on the sub-warp that owns it, its ADMM state staying on chip between steps.
@@ -76,15 +78,27 @@ struct RolloutArgs {
     int* status_out;        // [nsteps][B], may be null
     int* iters_out;
     const double* pi_blocks = nullptr;   // per-instance dynamics: the packed operand blocks (launch_tmem_pi_pack)
+    const int* order = nullptr;          // queue order (queue_order.cu)
 };
 cudaError_t launch_admm_tmem_rollout(const BatchView& bv, const AdmmSettings& st, const RolloutArgs& ra, int* counter,
                                      int num_sms, cudaStream_t stream);
 
-// ---- the same design with TWO instances per lane and one resident double per element (admm_tmem2.cu): 16 instances
-// per warp, 128 per SM.  Same applicability as the TMEM kernel; N is limited to 21 for nx = 12.
-bool tmem2_kernel_supports(const BatchView& bv, const AdmmSettings& st);
-cudaError_t launch_admm_tmem2(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms,
-                              cudaStream_t stream);
+// ---- longest-first instance queue (queue_order.cu): a permutation of the instances, expected-longest first, built by a
+// counting sort over 256 key buckets.  Cold start: key = saturation of the LQR input Kinf x0 against the input box;
+// warm start: key = the previous solve's iteration count.
+constexpr int kOrderBuckets = 256;
+struct OrderArgs {
+    int B, nx, nu;
+    const double* x0;                         // nx x B
+    const double* Kinf; long long kinf_ld;    // column-major nu x nx shared by all instances (kinf_ld = 0), or per instance [e][ld]
+    const double* u_min; const double* u_max; long long ub_stride;   // input bounds, knot 0 (stride 0 = shared)
+    const int* prev_iters;                    // non-null: key = iteration count of the previous solve
+    unsigned char* key;                       // scratch, B
+    int* hist;                                // scratch, 2 * kOrderBuckets ints: histogram, then the per-bucket cursors
+    int* cursor;                              // = hist + kOrderBuckets
+    int* order;                               // out, B
+};
+cudaError_t launch_build_order(const OrderArgs& a, cudaStream_t stream);
 
 // ---- carried-state formats (state_layout.cu): element-major [e][ld] arrays <-> instance-major blocks
 inline long long state_im_doubles(int nx, int nu, int N) { return 3LL * nx * N + 3LL * nu * (N - 1) + nx; }
@@ -95,5 +109,7 @@ cudaError_t launch_plant_step(const BatchView& bv, double* x0_rw, cudaStream_t s
 cudaError_t launch_plant_step_per_instance(const BatchView& bv, const PerInstanceMats& pm, long long ld, double* x0_rw,
                                            cudaStream_t stream);
 cudaError_t launch_record_step(const BatchView& bv, int* status_out, int* iters_out, cudaStream_t stream);
+// out[nu x B] = Usol(:, 0, b): the first control of every instance, packed for one small device-to-host copy
+cudaError_t launch_gather_u0(const double* Usol, long long stride, int nu, int B, double* out, cudaStream_t stream);
 
 }  // namespace tmpc

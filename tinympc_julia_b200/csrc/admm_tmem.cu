@@ -63,7 +63,8 @@ constexpr int kTmemColsPerWarp = 256;
 struct QuadParams {
     double pri_thresh;      // primal residual passes  <=>  |x - vnew| <  pri_thresh
     double dua_thresh;      // dual residual passes    <=>  |v - vnew| <= dua_thresh  (largest a with fl(rho a) < tol)
-    int* counter;           // instance queue
+    int* counter;           // instance queue: ticket counter ...
+    const int* order;       // ... and the permutation the tickets index (longest-first, queue_order.cu); null = identity
     int off_consts, off_bounds, off_refs, off_warp0, warp_stride;   // shared-memory carve-up, in doubles
     // fused closed loop (ROLL): every instance runs `nsteps` MPC steps on the sub-warp that owns it
     int nsteps;             // MPC steps per instance
@@ -328,7 +329,9 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 for (int r = 0; r < RX; ++r) ob[PB + r * 4] = p_term[r];
                 if (sub == 0) { bv.status[b] = status; bv.iters[b] = iter; }
             }
-            // next instance for every finished sub-warp (the atomic was issued at the top of the pass)
+            // next instance for every finished sub-warp (the atomic was issued at the top of the pass); the ticket
+            // indexes the longest-first permutation when there is one
+            if (qp.order != nullptr && nb < bv.B) nb = __ldg(qp.order + nb);
             nb = __shfl_sync(kAll, nb, inst);
             const bool nvalid = fin && nb < bv.B;
             const size_t nbb = nvalid ? static_cast<size_t>(nb) : 0;
@@ -866,11 +869,12 @@ cudaError_t launch_q(const BatchView& bv, const AdmmSettings& st, const QPlan& p
 
 template <int NX, int NU>
 cudaError_t launch_shape(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms,
-                         cudaStream_t stream) {
+                         cudaStream_t stream, const int* order) {
     QPlan pl;
     const int refs = refs_mode(bv);
     if (!make_qplan<NX, NU>(bv.N, refs, pl)) return cudaErrorInvalidConfiguration;
     pl.qp.counter = counter;
+    pl.qp.order = order;
     pl.qp.pri_thresh = st.abs_pri_tol;
     pl.qp.dua_thresh = dual_threshold_q(bv.rho, st.abs_dua_tol);
     cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(int), stream);
@@ -887,7 +891,7 @@ cudaError_t launch_shape(const BatchView& bv, const AdmmSettings& st, int cold, 
 
 template <int NX, int NU>
 cudaError_t launch_shape_pi(const BatchView& bv, const AdmmSettings& st, int cold, const double* pi_blocks, int* counter,
-                            int num_sms, cudaStream_t stream) {
+                            int num_sms, cudaStream_t stream, const int* order) {
     QPlan pl;
     const int refs = refs_mode(bv) == 0 ? 0 : 2;       // references, shared or not, go through the per-instance path
     if (!make_qplan<NX, NU>(bv.N, refs, pl, true)) return cudaErrorInvalidConfiguration;
@@ -895,6 +899,7 @@ cudaError_t launch_shape_pi(const BatchView& bv, const AdmmSettings& st, int col
     pl.qp.pri_thresh = st.abs_pri_tol;
     pl.qp.dua_thresh = dual_threshold_q(bv.rho, st.abs_dua_tol);
     pl.qp.pi_blocks = pi_blocks;
+    pl.qp.order = order;
     cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(int), stream);
     if (e != cudaSuccess) return e;
     if (cold) {
@@ -952,6 +957,7 @@ cudaError_t launch_shape_roll(const BatchView& bv, const AdmmSettings& st, const
     pl.qp.pri_thresh = st.abs_pri_tol;
     pl.qp.dua_thresh = dual_threshold_q(bv.rho, st.abs_dua_tol);
     pl.qp.pi_blocks = ra.pi_blocks;
+    pl.qp.order = ra.order;
     pl.qp.nsteps = ra.nsteps; pl.qp.cold_install = ra.cold; pl.qp.slide = ra.slide;
     pl.qp.x0_rw = ra.x0_rw; pl.qp.status_out = ra.status_out; pl.qp.iters_out = ra.iters_out;
     cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(int), stream);
@@ -991,10 +997,10 @@ cudaError_t launch_tmem_pi_pack(int nx, int nu, const PerInstanceMats& pm, long 
 }
 
 cudaError_t launch_admm_tmem_pi(const BatchView& bv, const AdmmSettings& st, int cold, const double* pi_blocks,
-                                int* counter, int num_sms, cudaStream_t stream) {
+                                int* counter, int num_sms, cudaStream_t stream, const int* order) {
     if (bv.B <= 0) return cudaSuccess;
-    if (bv.nx == 12 && bv.nu == 4) return launch_shape_pi<12, 4>(bv, st, cold, pi_blocks, counter, num_sms, stream);
-    if (bv.nx == 4 && bv.nu == 1) return launch_shape_pi<4, 1>(bv, st, cold, pi_blocks, counter, num_sms, stream);
+    if (bv.nx == 12 && bv.nu == 4) return launch_shape_pi<12, 4>(bv, st, cold, pi_blocks, counter, num_sms, stream, order);
+    if (bv.nx == 4 && bv.nu == 1) return launch_shape_pi<4, 1>(bv, st, cold, pi_blocks, counter, num_sms, stream, order);
     return cudaErrorNotSupported;
 }
 
@@ -1020,10 +1026,10 @@ bool tmem_kernel_supports(const BatchView& bv, const AdmmSettings& st) {
 }
 
 cudaError_t launch_admm_tmem(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms,
-                             cudaStream_t stream) {
+                             cudaStream_t stream, const int* order) {
     if (bv.B <= 0) return cudaSuccess;
-    if (bv.nx == 12 && bv.nu == 4) return launch_shape<12, 4>(bv, st, cold, counter, num_sms, stream);
-    if (bv.nx == 4 && bv.nu == 1) return launch_shape<4, 1>(bv, st, cold, counter, num_sms, stream);
+    if (bv.nx == 12 && bv.nu == 4) return launch_shape<12, 4>(bv, st, cold, counter, num_sms, stream, order);
+    if (bv.nx == 4 && bv.nu == 1) return launch_shape<4, 1>(bv, st, cold, counter, num_sms, stream, order);
     return cudaErrorNotSupported;
 }
 

@@ -42,17 +42,29 @@ template <class T>
 struct DevBuf {
     T* p = nullptr;
     size_t n = 0;
+    bool mapped = false;      // zero-copy: pinned host memory mapped into the device address space (UVA: p is valid on both sides)
     void alloc(size_t count) {
         release();
         n = count;
         if (count) CUDA_TRY(cudaMalloc(reinterpret_cast<void**>(&p), count * sizeof(T)));
+    }
+    // Result buffers of a tiny batch (the B = 1 singleton of PART 1): the kernel's stores go straight to host memory,
+    // so solve_mpc -> get_controls costs one stream synchronisation instead of a copy + synchronisation per getter.
+    void alloc_mapped(size_t count) {
+        release();
+        n = count;
+        if (count) {
+            CUDA_TRY(cudaHostAlloc(reinterpret_cast<void**>(&p), count * sizeof(T), cudaHostAllocMapped));
+            std::memset(p, 0, count * sizeof(T));
+            mapped = true;
+        }
     }
     void zero(cudaStream_t s) { if (p) CUDA_TRY(cudaMemsetAsync(p, 0, n * sizeof(T), s)); }
     void upload(const T* src, size_t count, cudaStream_t s) {
         if (count > n) alloc(count);
         if (count) CUDA_TRY(cudaMemcpyAsync(p, src, count * sizeof(T), cudaMemcpyHostToDevice, s));
     }
-    void release() { if (p) { cudaFree(p); p = nullptr; } n = 0; }
+    void release() { if (p) { if (mapped) cudaFreeHost(p); else cudaFree(p); p = nullptr; } n = 0; mapped = false; }
     ~DevBuf() { release(); }
     DevBuf() = default;
     DevBuf(const DevBuf&) = delete;
@@ -71,11 +83,27 @@ struct tmpc_batch {
     int num_sms = 148;
     tmpc::HostMats hm;
     tmpc::AdmmSettings st{};
+    bool adaptive_rho = false;                // accepted as a setting, refused at solve time (see enqueue_solve)
     int kernel_pref = TMPC_KERNEL_AUTO;
     bool rollout_fused = true;                // tmpc_batch_rollout_async: one fused launch where the TMEM kernel applies
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr;       // tmpc_batch_solve_host: result chunks go home while the next chunk solves
-    std::vector<cudaEvent_t> chunk_done;
+    cudaStream_t up_stream = nullptr;         // ... and the x0 chunks come up in front of their launches
+    std::vector<cudaEvent_t> chunk_done, chunk_up;
+    // A solve / rollout enqueued on a CALLER stream is not ordered against the handle's own stream: the event below is
+    // recorded behind it, and everything that later works on the handle's stream (getters, synchronize, setters, the
+    // next solve) waits on it first.
+    cudaEvent_t foreign_done = nullptr, own_done = nullptr;
+    bool foreign_pending = false;
+    bool own_pending = false;                 // asynchronous work sits on the handle's stream (solve_async / rollout_async with a NULL stream)
+    // queue order of the on-chip kernels (queue_order.cu)
+    int order_mode = TMPC_ORDER_AUTO;
+    bool order_built = false;                 // `order` holds the permutation the last solve used
+    DevBuf<int> order, order_user, order_hist;
+    DevBuf<unsigned char> order_key;
+    bool results_mapped = false;              // Xsol / Usol / status / iters live in mapped pinned host memory (tiny batch)
+    double* x0_stage = nullptr;               // pinned staging of x0 for tiny batches: set_x0 returns without a stream sync
+    cudaEvent_t x0_staged = nullptr;
     long long launches = 0;
     bool state_zero = true;   // carried state is LOGICALLY zero (fresh or reset) ...
     bool mem_zero = true;     // ... and the device buffers physically hold those zeros.  tmpc_batch_reset only flips
@@ -97,7 +125,7 @@ struct tmpc_batch {
     // carried state + scratch
     DevBuf<double> g, y, v0, v1, z0, z1, q, r, pN, d, gc, yc, gl, yl;
     // results
-    DevBuf<double> Xsol, Usol;
+    DevBuf<double> Xsol, Usol, u0_pack;
     DevBuf<int> status, iters, counter;
     // per-instance dynamics (tmpc_batch_set_instance_dynamics): element-major [e][ld] cache of every instance
     bool per_instance = false;
@@ -106,7 +134,12 @@ struct tmpc_batch {
     DevBuf<double> state_im;  // instance-major twin of the carried state (TMEM kernel), allocated on first use
     bool state_in_im = false; // which format holds the current carried state (meaningless while state_zero)
 
-    void use_device() const { CUDA_TRY(cudaSetDevice(device)); }
+    // Every API call starts here: select the device, and make the handle's own stream wait for work a previous call
+    // enqueued on a caller stream (a stream-side wait; the host does not block).
+    void use_device() {
+        CUDA_TRY(cudaSetDevice(device));
+        if (foreign_pending) { CUDA_TRY(cudaStreamWaitEvent(stream, foreign_done, 0)); foreign_pending = false; own_pending = true; }
+    }
 };
 
 namespace {
@@ -121,14 +154,39 @@ void upload_mats(tmpc_batch* h) {
     CUDA_TRY(cudaStreamSynchronize(h->stream));   // sources are host vectors that may change
 }
 
-void ensure_aux_state(tmpc_batch* h) {
+// Cone / half-space duals are allocated on first use and zeroed ON THE STREAM THE SOLVE RUNS ON (a memset on the
+// handle's stream would race with a solve enqueued on a caller stream).
+void ensure_aux_state(tmpc_batch* h, cudaStream_t s) {
     const size_t sx = static_cast<size_t>(h->nx) * h->N * h->ld, su = static_cast<size_t>(h->nu) * (h->N - 1) * h->ld;
     if ((h->st.en_state_soc || h->st.en_input_soc) && !h->gc.p) {
-        h->gc.alloc(sx); h->yc.alloc(su); h->gc.zero(h->stream); h->yc.zero(h->stream);
+        h->gc.alloc(sx); h->yc.alloc(su); h->gc.zero(s); h->yc.zero(s);
     }
     if ((h->st.en_state_linear || h->st.en_input_linear) && !h->gl.p) {
-        h->gl.alloc(sx); h->yl.alloc(su); h->gl.zero(h->stream); h->yl.zero(h->stream);
+        h->gl.alloc(sx); h->yl.alloc(su); h->gl.zero(s); h->yl.zero(s);
     }
+}
+
+// About to enqueue on `s`: a caller stream first waits for asynchronous work still queued on the handle's stream
+// (the other direction is use_device()).
+void order_before_enqueue(tmpc_batch* h, cudaStream_t s) {
+    if (s == h->stream || !h->own_pending) return;
+    if (!h->own_done) CUDA_TRY(cudaEventCreateWithFlags(&h->own_done, cudaEventDisableTiming));
+    CUDA_TRY(cudaEventRecord(h->own_done, h->stream));
+    CUDA_TRY(cudaStreamWaitEvent(s, h->own_done, 0));
+    h->own_pending = false;
+}
+// Work was enqueued on `s`: when that is a caller stream, leave an event behind it ...
+void mark_enqueued(tmpc_batch* h, cudaStream_t s) {
+    if (s == h->stream) { h->own_pending = true; return; }
+    if (!h->foreign_done) CUDA_TRY(cudaEventCreateWithFlags(&h->foreign_done, cudaEventDisableTiming));
+    CUDA_TRY(cudaEventRecord(h->foreign_done, s));
+    h->foreign_pending = true;
+}
+// Block the host until everything this handle enqueued anywhere has finished (use_device() already chained the
+// handle's stream behind caller-stream work).
+void sync_all(tmpc_batch* h) {
+    CUDA_TRY(cudaStreamSynchronize(h->stream));
+    h->own_pending = false;
 }
 
 tmpc::BatchView make_view(tmpc_batch* h) {
@@ -181,8 +239,6 @@ int resolve_kernel(tmpc_batch* h) {
     }
     const bool sub_ok = tmpc::subwarp_kernel_supports(h->nx, h->nu, h->N, h->st);
     const bool tm_ok = tmpc::tmem_kernel_supports(make_view(h), h->st);
-    const bool tm2_ok = tmpc::tmem2_kernel_supports(make_view(h), h->st);
-    if (h->kernel_pref == TMPC_KERNEL_TMEM2) return tm2_ok ? TMPC_KERNEL_TMEM2 : -1;
     if (h->kernel_pref == TMPC_KERNEL_TMEM) return tm_ok ? TMPC_KERNEL_TMEM : -1;
     if (h->kernel_pref == TMPC_KERNEL_SUBWARP) return sub_ok ? TMPC_KERNEL_SUBWARP : -1;
     if (h->kernel_pref == TMPC_KERNEL_THREAD) return TMPC_KERNEL_THREAD;
@@ -200,14 +256,45 @@ void zero_state(tmpc_batch* h, cudaStream_t s) {
 
 // Make a logically-zero state physically zero before something reads it (thread kernel, result getters).
 void materialize_zero(tmpc_batch* h) {
-    if (h->state_zero && !h->mem_zero) zero_state(h, h->stream);
+    if (h->state_zero && !h->mem_zero) { zero_state(h, h->stream); h->own_pending = true; }
+}
+
+// Queue order of the on-chip kernels for the coming solve (queue_order.cu), built on `s` in front of it; nullptr = natural
+// order.  AUTO: longest-first by the LQR saturation of x0 against the input box (cold start) or by the previous solve's
+// iteration counts (warm start); only when the batch is more than one wave of the persistent grid.
+const int* build_order(tmpc_batch* h, const tmpc::BatchView& v, cudaStream_t s, int b0 = 0) {
+    // `v` may be a chunk view [b0, b0 + v.B) of the batch: the permutation is then over the chunk's own instances
+    const bool whole = (b0 == 0 && v.B == h->B);
+    if (whole) h->order_built = false;
+    if (h->order_mode == TMPC_ORDER_NATURAL) return nullptr;
+    if (h->order_mode == TMPC_ORDER_USER) return whole ? h->order_user.p : nullptr;
+    if (v.B <= h->num_sms * 64) return nullptr;
+    tmpc::OrderArgs a{};
+    a.B = v.B; a.nx = h->nx; a.nu = h->nu; a.x0 = v.x0;
+    if (!h->state_zero) {
+        a.prev_iters = v.iters;
+    } else {
+        if (!h->st.en_input_bound || !v.u_min || !v.u_max) return nullptr;
+        a.u_min = v.u_min; a.u_max = v.u_max; a.ub_stride = v.ub_stride;
+        if (h->per_instance) { a.Kinf = h->piKinf.p + b0; a.kinf_ld = h->ld; }
+        else { a.Kinf = v.Kinf; a.kinf_ld = 0; }
+    }
+    if (!h->order.p) {
+        h->order.alloc(h->B); h->order_key.alloc(h->B); h->order_hist.alloc(2 * tmpc::kOrderBuckets);
+    }
+    a.key = h->order_key.p + b0; a.hist = h->order_hist.p; a.cursor = a.hist + tmpc::kOrderBuckets; a.order = h->order.p + b0;
+    const cudaError_t e = tmpc::launch_build_order(a, s);
+    if (e != cudaSuccess) throw CudaFail{e, "queue-order kernels"};
+    h->launches += 2;
+    if (whole) h->order_built = true;
+    return a.order;
 }
 
 // One solve kernel on `s`.  A cold (reset) state is passed to the sub-warp kernel as a flag; every other
 // reader gets physically zeroed buffers first, on the SAME stream as the solve: an earlier solve enqueued on a
 // caller stream may still be running, and memsets on another stream would race with it.
 cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v_in, cudaStream_t s) {
-    const bool tm = (k == TMPC_KERNEL_TMEM || k == TMPC_KERNEL_TMEM2);
+    const bool tm = (k == TMPC_KERNEL_TMEM);
     const bool sub = (k == TMPC_KERNEL_SUBWARP || tm) && h->st.max_iter > 0 && h->rho > 0.0;
     tmpc::BatchView v = v_in;
     const bool wants_im = sub && tm;
@@ -225,10 +312,10 @@ cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v_in, cuda
         zero_state(h, s);
     }
     cudaError_t e;
-    if (sub && k == TMPC_KERNEL_TMEM2) e = tmpc::launch_admm_tmem2(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
-    else if (sub && k == TMPC_KERNEL_TMEM && h->per_instance)
-        e = tmpc::launch_admm_tmem_pi(v, h->st, h->state_zero ? 1 : 0, h->pi_blocks.p, h->counter.p, h->num_sms, s);
-    else if (sub && k == TMPC_KERNEL_TMEM) e = tmpc::launch_admm_tmem(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
+    const int* order = (sub && tm) ? build_order(h, v, s) : nullptr;
+    if (sub && k == TMPC_KERNEL_TMEM && h->per_instance)
+        e = tmpc::launch_admm_tmem_pi(v, h->st, h->state_zero ? 1 : 0, h->pi_blocks.p, h->counter.p, h->num_sms, s, order);
+    else if (sub && k == TMPC_KERNEL_TMEM) e = tmpc::launch_admm_tmem(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s, order);
     else if (sub) e = tmpc::launch_admm_subwarp(v, h->st, h->hm, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s, h->precision);
     else if (h->per_instance) e = tmpc::launch_admm_thread_per_instance(v, h->st, per_instance_view(h), s, h->precision);
     else e = tmpc::launch_admm_thread(v, h->st, h->hm, s, h->precision);
@@ -241,13 +328,16 @@ cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v_in, cuda
 // stream when s is that stream; callers passing another stream order it themselves).
 int enqueue_solve(tmpc_batch* h, cudaStream_t s) {
     if (h->st.check_termination == 0) { set_error("check_termination = 0 is not supported (the reference divides by it)"); return TMPC_ERR_STATE; }
-    ensure_aux_state(h);
+    if (h->adaptive_rho) { set_error("adaptive_rho is set: through this API the reference reads unset (0 x 0) sensitivity matrices in that branch and crashes at its first rho update (admm.cpp:331-357, rho_benchmark.cpp:204-207; DESIGN.md 8); there is no reference behaviour to reproduce, so the solve is refused - clear the flag with update_settings"); return TMPC_ERR_STATE; }
+    order_before_enqueue(h, s);
+    ensure_aux_state(h, s);
     const int k = resolve_kernel(h);
     if (k < 0) { set_error("requested kernel does not support this problem (shape, constraint flags or per-instance bounds)"); return TMPC_ERR_STATE; }
     tmpc::BatchView v = make_view(h);
     cudaError_t e;
     e = launch_solve(h, k, v, s);
     if (e != cudaSuccess) throw CudaFail{e, "solve kernel launch"};
+    mark_enqueued(h, s);
     return TMPC_OK;
 }
 
@@ -360,10 +450,22 @@ int tmpc_batch_create(tmpc_batch** out, const double* A, const double* Bdyn, con
         h->y.alloc(su); h->z0.alloc(su); h->z1.alloc(su); h->r.alloc(su); h->d.alloc(su);
         h->pN.alloc(static_cast<size_t>(nx) * h->ld);
         h->x0.alloc(static_cast<size_t>(nx) * B); h->x0.zero(h->stream);
-        h->Xsol.alloc(static_cast<size_t>(nx) * N * B); h->Usol.alloc(static_cast<size_t>(nu) * (N - 1) * B);
-        h->status.alloc(B); h->iters.alloc(B); h->counter.alloc(8); h->counter.zero(h->stream);
+        // A tiny batch (the B = 1 singleton behind the reference's own symbols) keeps its results in mapped pinned host
+        // memory and stages x0 through a pinned buffer: set_x0 -> solve_mpc -> get_controls then costs ONE stream
+        // synchronisation (in solve_mpc) instead of one per call plus pageable copies.
+        h->results_mapped = (static_cast<size_t>(nx) * N + static_cast<size_t>(nu) * (N - 1)) * B * sizeof(double) <= 64 * 1024;
+        if (h->results_mapped) {
+            h->Xsol.alloc_mapped(static_cast<size_t>(nx) * N * B); h->Usol.alloc_mapped(static_cast<size_t>(nu) * (N - 1) * B);
+            h->status.alloc_mapped(B); h->iters.alloc_mapped(B);
+            CUDA_TRY(cudaHostAlloc(reinterpret_cast<void**>(&h->x0_stage), sizeof(double) * nx * B, cudaHostAllocDefault));
+            CUDA_TRY(cudaEventCreateWithFlags(&h->x0_staged, cudaEventDisableTiming));
+        } else {
+            h->Xsol.alloc(static_cast<size_t>(nx) * N * B); h->Usol.alloc(static_cast<size_t>(nu) * (N - 1) * B);
+            h->status.alloc(B); h->iters.alloc(B);
+        }
+        h->counter.alloc(8); h->counter.zero(h->stream);
         zero_state(h.get(), h->stream);
-        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        sync_all(h.get());
         *out = h.release();
         return TMPC_OK;
     });
@@ -375,7 +477,13 @@ int tmpc_batch_destroy(tmpc_batch* h) {
         cudaSetDevice(h->device);
         if (h->stream) { cudaStreamSynchronize(h->stream); cudaStreamDestroy(h->stream); }
         if (h->copy_stream) { cudaStreamSynchronize(h->copy_stream); cudaStreamDestroy(h->copy_stream); }
+        if (h->up_stream) { cudaStreamSynchronize(h->up_stream); cudaStreamDestroy(h->up_stream); }
         for (cudaEvent_t e : h->chunk_done) cudaEventDestroy(e);
+        for (cudaEvent_t e : h->chunk_up) cudaEventDestroy(e);
+        if (h->foreign_done) { cudaEventSynchronize(h->foreign_done); cudaEventDestroy(h->foreign_done); }
+        if (h->own_done) cudaEventDestroy(h->own_done);
+        if (h->x0_staged) cudaEventDestroy(h->x0_staged);
+        if (h->x0_stage) cudaFreeHost(h->x0_stage);
         delete h;
         return TMPC_OK;
     });
@@ -389,12 +497,14 @@ int tmpc_batch_update_settings(tmpc_batch* h, double abs_pri_tol, double abs_dua
     return guarded([&]() -> int {
         if (!h) { set_error("update_settings: null handle"); return TMPC_ERR_DIM; }
         if (check_termination == 0) { set_error("update_settings: check_termination = 0 rejected (reference computes iter % 0)"); return TMPC_ERR_STATE; }
-        if (adaptive_rho) { set_error("update_settings: adaptive_rho refused: through this API the reference reads unset (0 x 0) sensitivity matrices in that branch and crashes (DESIGN.md 8, item 4); nothing to be in parity with"); return TMPC_ERR_STATE; }
+        if (max_iter <= 0) { set_error("update_settings: max_iter must be >= 1 (with 0 the reference returns whatever its workspace held, admm.cpp:384-388; nothing is solved)"); return TMPC_ERR_STATE; }
         h->st.abs_pri_tol = abs_pri_tol; h->st.abs_dua_tol = abs_dua_tol;
         h->st.max_iter = max_iter; h->st.check_termination = check_termination;
         h->st.en_state_bound = en_state_bound != 0; h->st.en_input_bound = en_input_bound != 0;
         h->st.en_state_soc = en_state_soc != 0; h->st.en_input_soc = en_input_soc != 0;
         h->st.en_state_linear = en_state_linear != 0; h->st.en_input_linear = en_input_linear != 0;
+        // the BINDING is kept (tests/test_settings.jl "Adaptive Rho Settings" only sets it up); solves refuse while it is on
+        h->adaptive_rho = adaptive_rho != 0;
         return TMPC_OK;
     });
 }
@@ -428,7 +538,7 @@ int tmpc_batch_set_precision(tmpc_batch* h, int bits) {
         h->hm.APf = c.APf.a; h->hm.BPf = c.BPf.a; h->hm.Qd = c.Qd; h->hm.Rd = c.Rd;
         h->rho = bits == 32 ? static_cast<double>(static_cast<float>(h->rho_given)) : h->rho_given;
         h->precision = bits;
-        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        sync_all(h);
         upload_mats(h);
         return TMPC_OK;
     });
@@ -437,12 +547,44 @@ int tmpc_batch_set_precision(tmpc_batch* h, int bits) {
 int tmpc_batch_get_precision(tmpc_batch* h) { return h ? h->precision : -1; }
 
 int tmpc_batch_set_kernel(tmpc_batch* h, int kernel) {
-    if (!h || kernel < TMPC_KERNEL_AUTO || kernel > TMPC_KERNEL_TMEM2) return TMPC_ERR_DIM;
+    if (!h || kernel < TMPC_KERNEL_AUTO || kernel > TMPC_KERNEL_TMEM) return TMPC_ERR_DIM;
     h->kernel_pref = kernel;
     return TMPC_OK;
 }
 
 int tmpc_batch_get_kernel(tmpc_batch* h) { return h ? resolve_kernel(h) : -1; }
+
+int tmpc_batch_set_order(tmpc_batch* h, int mode, const int* perm) {
+    return guarded([&]() -> int {
+        if (!h || mode < TMPC_ORDER_NATURAL || mode > TMPC_ORDER_USER) { set_error("set_order: mode must be TMPC_ORDER_NATURAL, _AUTO or _USER"); return TMPC_ERR_DIM; }
+        if (mode == TMPC_ORDER_USER) {
+            if (!perm) { set_error("set_order: TMPC_ORDER_USER needs a permutation of 0..B-1"); return TMPC_ERR_DIM; }
+            std::vector<char> seen(h->B, 0);
+            for (int i = 0; i < h->B; ++i) {
+                if (perm[i] < 0 || perm[i] >= h->B || seen[perm[i]]) { set_error("set_order: not a permutation of 0..B-1"); return TMPC_ERR_DIM; }
+                seen[perm[i]] = 1;
+            }
+            h->use_device();
+            h->order_user.upload(perm, h->B, h->stream);
+            sync_all(h);
+        }
+        h->order_mode = mode;
+        h->order_built = false;
+        return TMPC_OK;
+    });
+}
+
+int tmpc_batch_get_order(tmpc_batch* h, int* perm) {
+    return guarded([&]() -> int {
+        if (!h || !perm) return TMPC_ERR_DIM;
+        const int* src = h->order_mode == TMPC_ORDER_USER ? h->order_user.p : (h->order_built ? h->order.p : nullptr);
+        if (!src) { set_error("get_order: the last solve ran in natural order"); return TMPC_ERR_STATE; }
+        h->use_device();
+        CUDA_TRY(cudaMemcpyAsync(perm, src, sizeof(int) * h->B, cudaMemcpyDeviceToHost, h->stream));
+        sync_all(h);
+        return TMPC_OK;
+    });
+}
 
 int tmpc_batch_set_x0(tmpc_batch* h, const double* x0, int rows, int batch) {
     return guarded([&]() -> int {
@@ -450,8 +592,16 @@ int tmpc_batch_set_x0(tmpc_batch* h, const double* x0, int rows, int batch) {
         if (rows != h->nx || batch != h->B) { set_error("set_x0: expected nx x B"); return TMPC_ERR_DIM; }
         h->use_device();
         h->ext_x0 = nullptr;
+        if (h->x0_stage) {      // tiny batch: copy into the pinned staging buffer and return; the upload is stream-ordered
+            CUDA_TRY(cudaEventSynchronize(h->x0_staged));      // the previous upload has left the staging buffer
+            std::memcpy(h->x0_stage, x0, sizeof(double) * h->nx * h->B);
+            CUDA_TRY(cudaMemcpyAsync(h->x0.p, h->x0_stage, sizeof(double) * h->nx * h->B, cudaMemcpyHostToDevice, h->stream));
+            CUDA_TRY(cudaEventRecord(h->x0_staged, h->stream));
+            h->own_pending = true;
+            return TMPC_OK;
+        }
         h->x0.upload(x0, static_cast<size_t>(h->nx) * h->B, h->stream);
-        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        sync_all(h);
         return TMPC_OK;
     });
 }
@@ -464,7 +614,7 @@ int tmpc_batch_set_x_ref(tmpc_batch* h, const double* x_ref, int rows, int cols,
         h->ext_xref = nullptr;
         h->Xref.upload(x_ref, static_cast<size_t>(rows) * cols * batch, h->stream);
         h->xref_batch = batch;
-        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        sync_all(h);
         return TMPC_OK;
     });
 }
@@ -477,7 +627,7 @@ int tmpc_batch_set_u_ref(tmpc_batch* h, const double* u_ref, int rows, int cols,
         h->ext_uref = nullptr;
         h->Uref.upload(u_ref, static_cast<size_t>(rows) * cols * batch, h->stream);
         h->uref_batch = batch;
-        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        sync_all(h);
         return TMPC_OK;
     });
 }
@@ -493,7 +643,7 @@ int tmpc_batch_set_bound_constraints(tmpc_batch* h, const double* x_min, const d
         h->umin.upload(u_min, su, h->stream); h->umax.upload(u_max, su, h->stream);
         h->bounds_batch = batch;
         h->st.en_state_bound = 1; h->st.en_input_bound = 1;     // src/bindings.cpp:400-404
-        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        sync_all(h);
         return TMPC_OK;
     });
 }
@@ -509,7 +659,7 @@ int tmpc_batch_set_linear_constraints(tmpc_batch* h, const double* Alin_x, int n
         if (nlu) { h->Alin_u.upload(Alin_u, static_cast<size_t>(nlu) * h->nu, h->stream); h->blin_u.upload(blin_u, nlu, h->stream); }
         if (nlx > 0) h->st.en_state_linear = 1;                 // src/bindings.cpp:438-443
         if (nlu > 0) h->st.en_input_linear = 1;
-        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        sync_all(h);
         return TMPC_OK;
     });
 }
@@ -595,7 +745,7 @@ int tmpc_batch_set_instance_dynamics(tmpc_batch* h, const double* A, const doubl
         h->launches += 1;
         int failed = 0;
         CUDA_TRY(cudaMemcpyAsync(&failed, fail.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
-        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        sync_all(h);
         if (failed) { h->per_instance = false; set_error("set_instance_dynamics: singular R + B'PB for some instance"); return TMPC_ERR_STATE; }
         const long long blk = tmpc::tmem_pi_block_doubles(h->nx, h->nu);
         h->pi_blocks.release();
@@ -604,7 +754,7 @@ int tmpc_batch_set_instance_dynamics(tmpc_batch* h, const double* A, const doubl
             e = tmpc::launch_tmem_pi_pack(h->nx, h->nu, per_instance_view(h), h->ld, h->B, h->pi_blocks.p, h->stream);
             if (e != cudaSuccess) throw CudaFail{e, "per-instance block packing"};
             h->launches += 1;
-            CUDA_TRY(cudaStreamSynchronize(h->stream));
+            sync_all(h);
         }
         h->per_instance = true;
         h->state_zero = true;
@@ -625,7 +775,7 @@ int tmpc_batch_get_instance_cache(tmpc_batch* h, int b, double* Kinf, double* Pi
         };
         get(Kinf, h->piKinf, m * n); get(Pinf, h->piPinf, n * n); get(Quu_inv, h->piQuu, m * m);
         get(AmBKt, h->piAmBKt, n * n); get(APf, h->piAPf, n); get(BPf, h->piBPf, m);
-        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        sync_all(h);
         return TMPC_OK;
     });
 }
@@ -634,6 +784,7 @@ int tmpc_batch_set_cache_terms(tmpc_batch* h, const double* Kinf, const double* 
                                const double* AmBKt) {
     return guarded([&]() -> int {
         if (!h || !Kinf || !Pinf || !Quu_inv || !AmBKt) { set_error("set_cache_terms: null argument"); return TMPC_ERR_DIM; }
+        if (h->per_instance) { set_error("set_cache_terms: the batch has per-instance dynamics (tmpc_batch_set_instance_dynamics); one shared cache cannot replace B of them"); return TMPC_ERR_STATE; }
         h->use_device();
         const int n = h->nx, m = h->nu;
         h->hm.Kinf.assign(Kinf, Kinf + static_cast<size_t>(m) * n);
@@ -643,7 +794,7 @@ int tmpc_batch_set_cache_terms(tmpc_batch* h, const double* Kinf, const double* 
         if (h->precision == 32)      // Kinf.cast<tinytype>() ... (src/bindings.cpp:277-280)
             for (auto* vec : {&h->hm.Kinf, &h->hm.Pinf, &h->hm.Quu_inv, &h->hm.AmBKt})
                 for (double& x : *vec) x = static_cast<double>(static_cast<float>(x));
-        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        sync_all(h);
         upload_mats(h);      // APf, BPf, rho deliberately untouched
         return TMPC_OK;
     });
@@ -662,8 +813,8 @@ int tmpc_batch_reset(tmpc_batch* h) {
     return guarded([&]() -> int {
         if (!h) return TMPC_ERR_DIM;
         h->use_device();
-        CUDA_TRY(cudaStreamSynchronize(h->stream));
-        h->state_zero = true;            // physical zeroing is deferred to the first reader that needs it
+        h->state_zero = true;            // logical: physical zeroing is deferred to the first reader that needs it (stream-ordered there)
+        h->order_built = false;
         return TMPC_OK;
     });
 }
@@ -680,7 +831,7 @@ int tmpc_batch_synchronize(tmpc_batch* h) {
     return guarded([&]() -> int {
         if (!h) return TMPC_ERR_DIM;
         h->use_device();
-        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        sync_all(h);
         return TMPC_OK;
     });
 }
@@ -691,9 +842,14 @@ int tmpc_batch_solve(tmpc_batch* h) {
         h->use_device();
         const int rc = enqueue_solve(h, h->stream);
         if (rc != TMPC_OK) return rc < 0 ? rc : 100 + rc;
+        if (h->results_mapped) {      // the kernel wrote the status words to host memory
+            sync_all(h);
+            for (int b = 0; b < h->B; ++b) if (h->status.p[b] != 0) return 1;
+            return 0;
+        }
         std::vector<int> st(h->B);
         CUDA_TRY(cudaMemcpyAsync(st.data(), h->status.p, sizeof(int) * h->B, cudaMemcpyDeviceToHost, h->stream));
-        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        sync_all(h);
         for (int s : st) if (s != 0) return 1;
         return 0;
     });
@@ -702,43 +858,71 @@ int tmpc_batch_solve(tmpc_batch* h) {
 /* One call, host buffers in and out: x0 up, solve, solution + status down.  The batch is cut into chunks of whole
  * instances (the on-chip kernels own an instance per sub-warp and the carried state is one block per instance, so a
  * chunk is just an offset view); chunk c solves on the handle's stream while chunk c-1 travels home on a second
- * stream, which hides the solve behind the PCIe transfer of the solution (166 MB for the quadrotor at B = 65,536). */
-int tmpc_batch_solve_host(tmpc_batch* h, const double* x0, int cold, double* X, double* U, int* status, int* iters,
-                          int chunks) {
+ * stream and the x0 of the chunks ahead come up on a third, which hides the solve behind the PCIe transfer of the
+ * solution (166 MB for the quadrotor at B = 65,536).  Output selector: any of X, U, u0 (the first control of every
+ * instance, nu x B - what a closed loop consumes, examples/cartpole_example_mpc.jl:41-42), status, iters may be NULL. */
+static int solve_host_impl(tmpc_batch* h, const double* x0, int cold, double* X, double* U, double* u0, int* status,
+                           int* iters, int chunks) {
     return guarded([&]() -> int {
         if (!h) return TMPC_ERR_DIM;
         h->use_device();
         if (h->st.check_termination == 0) { set_error("check_termination = 0 is not supported (the reference divides by it)"); return 100 + TMPC_ERR_STATE; }
+        if (h->adaptive_rho) { set_error("adaptive_rho is set: through this API the reference reads unset (0 x 0) sensitivity matrices in that branch and crashes at its first rho update (admm.cpp:331-357, rho_benchmark.cpp:204-207; DESIGN.md 8); there is no reference behaviour to reproduce, so the solve is refused - clear the flag with update_settings"); return 100 + TMPC_ERR_STATE; }
         if (x0) {   // copied below: whole before a single launch, else chunk by chunk in front of each chunk's launch
             h->ext_x0 = nullptr;
             if (h->x0.n < static_cast<size_t>(h->nx) * h->B) h->x0.alloc(static_cast<size_t>(h->nx) * h->B);
         }
-        if (cold) h->state_zero = true;
-        ensure_aux_state(h);
+        if (cold) { h->state_zero = true; h->order_built = false; }
+        ensure_aux_state(h, h->stream);
         const int k = resolve_kernel(h);
         if (k < 0) { set_error("requested kernel does not support this problem"); return 100 + TMPC_ERR_STATE; }
-        const bool tm = (k == TMPC_KERNEL_TMEM || k == TMPC_KERNEL_TMEM2) && h->st.max_iter > 0 && h->rho > 0.0;
-        // chunks are whole waves of the persistent grid (one CTA per SM, 64 resident instances each).  Default: one
-        // wave per chunk, at most 8 chunks - the device->host copy is the long pole (166 MB against 0.8 ms of solve at
-        // B = 65,536 quadrotors), so an early first copy is worth more than the refill efficiency of longer chunks
-        // (measured: 4 chunks of 2 waves 3.44 ms, 7 chunks of 1 wave 3.37 ms; no difference on the hard workload)
+        const bool tm = (k == TMPC_KERNEL_TMEM) && h->st.max_iter > 0 && h->rho > 0.0;
+        // chunks are whole waves of the persistent grid (one CTA per SM, 64 resident instances each).  Default with the
+        // full solution going home: one wave per chunk, at most 8 chunks - the device->host copy is the long pole
+        // (166 MB against 0.8 ms of solve at B = 65,536 quadrotors), so an early first copy is worth more than the
+        // refill efficiency of longer chunks (measured: 4 chunks of 2 waves 3.44 ms, 7 chunks of 1 wave 3.37 ms).
+        // With only u0 / status going home the solve is the long pole: two chunks, a short one first so that the
+        // rest of x0 comes up behind it, the second keeping the queue (and its longest-first order) over 7/8 of the batch.
         const int wave = h->num_sms * 64;
-        int nch = chunks > 0 ? chunks : std::min(8, (h->B + wave - 1) / wave);
+        const bool small_out = !X && !U;
+        int nch = chunks > 0 ? chunks : (small_out ? 2 : std::min(8, (h->B + wave - 1) / wave));
         if (!tm || h->B < 3 * wave) nch = 1;
-        int chunk_size = h->B;
-        if (nch > 1) {
-            chunk_size = ((h->B + nch - 1) / nch + wave - 1) / wave * wave;
+        std::vector<int> cut;     // chunk c = [cut[c], cut[c + 1])
+        if (nch > 1 && small_out && chunks <= 0) {
+            cut = {0, wave, h->B};
+        } else if (nch > 1) {
+            int chunk_size = ((h->B + nch - 1) / nch + wave - 1) / wave * wave;
             if (chunk_size < wave) chunk_size = wave;
-            nch = (h->B + chunk_size - 1) / chunk_size;
+            for (int b0 = 0; b0 < h->B; b0 += chunk_size) cut.push_back(b0);
+            cut.push_back(h->B);
+        } else {
+            cut = {0, h->B};
         }
+        nch = static_cast<int>(cut.size()) - 1;
         if (!h->copy_stream) CUDA_TRY(cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+        if (!h->up_stream) CUDA_TRY(cudaStreamCreateWithFlags(&h->up_stream, cudaStreamNonBlocking));
         while (static_cast<int>(h->chunk_done.size()) < nch) {
             cudaEvent_t e; CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); h->chunk_done.push_back(e);
+            CUDA_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); h->chunk_up.push_back(e);
         }
         std::vector<int> st_tmp;
         if (!status) { st_tmp.resize(h->B); status = st_tmp.data(); }
         tmpc::BatchView v = make_view(h);
         const size_t sxN = static_cast<size_t>(h->nx) * h->N, suN = static_cast<size_t>(h->nu) * (h->N - 1);
+        const size_t nu = static_cast<size_t>(h->nu);
+        if (u0 && h->u0_pack.n < nu * h->B) h->u0_pack.alloc(nu * h->B);
+        // [b0, b1) of the results, on stream `cs` (the solve that produced them is already ordered before it)
+        auto fetch = [&](int b0, int b1, cudaStream_t cs) {
+            const size_t nb = static_cast<size_t>(b1 - b0);
+            if (X) CUDA_TRY(cudaMemcpyAsync(X + b0 * sxN, v.Xsol + b0 * sxN, sizeof(double) * sxN * nb, cudaMemcpyDeviceToHost, cs));
+            if (U) CUDA_TRY(cudaMemcpyAsync(U + b0 * suN, v.Usol + b0 * suN, sizeof(double) * suN * nb, cudaMemcpyDeviceToHost, cs));
+            if (u0) {
+                cudaError_t ge = tmpc::launch_gather_u0(v.Usol + b0 * suN, static_cast<long long>(suN), h->nu, b1 - b0, h->u0_pack.p + b0 * nu, cs);
+                if (ge != cudaSuccess) throw CudaFail{ge, "u0 gather launch"};
+                h->launches += 1;
+                CUDA_TRY(cudaMemcpyAsync(u0 + b0 * nu, h->u0_pack.p + b0 * nu, sizeof(double) * nu * nb, cudaMemcpyDeviceToHost, cs));
+            }
+        };
         if (nch > 1) {
             const bool was_cold = h->state_zero;
             if (!h->state_im.p) { h->state_im.alloc(static_cast<size_t>(v.state_im_stride) * h->B); v.state_im = h->state_im.p; }
@@ -747,55 +931,68 @@ int tmpc_batch_solve_host(tmpc_batch* h, const double* x0, int cold, double* X, 
                 if (ce != cudaSuccess) throw CudaFail{ce, "state conversion"};
                 h->launches += 1;
             }
+            if (x0) {   // every chunk's x0 on the upload stream, each followed by its event; nothing older may still read h->x0
+                CUDA_TRY(cudaEventRecord(h->chunk_done[0], h->stream));
+                CUDA_TRY(cudaStreamWaitEvent(h->up_stream, h->chunk_done[0], 0));
+                for (int c = 0; c < nch; ++c) {
+                    const size_t o = static_cast<size_t>(cut[c]) * h->nx;
+                    CUDA_TRY(cudaMemcpyAsync(h->x0.p + o, x0 + o, sizeof(double) * h->nx * (cut[c + 1] - cut[c]), cudaMemcpyHostToDevice, h->up_stream));
+                    CUDA_TRY(cudaEventRecord(h->chunk_up[c], h->up_stream));
+                }
+            }
             for (int c = 0; c < nch; ++c) {
-                const int b0 = c * chunk_size;
-                const int b1 = std::min(h->B, b0 + chunk_size);
+                const int b0 = cut[c], b1 = cut[c + 1];
                 tmpc::BatchView vc = v;
                 vc.B = b1 - b0;
-                if (x0) CUDA_TRY(cudaMemcpyAsync(h->x0.p + static_cast<size_t>(b0) * h->nx, x0 + static_cast<size_t>(b0) * h->nx,
-                                                 sizeof(double) * h->nx * (b1 - b0), cudaMemcpyHostToDevice, h->stream));
+                if (x0) CUDA_TRY(cudaStreamWaitEvent(h->stream, h->chunk_up[c], 0));
                 vc.x0 = v.x0 + static_cast<size_t>(b0) * h->nx;
                 if (v.Xref && v.xref_stride) vc.Xref = v.Xref + static_cast<size_t>(b0) * v.xref_stride;
                 if (v.Uref && v.uref_stride) vc.Uref = v.Uref + static_cast<size_t>(b0) * v.uref_stride;
                 vc.state_im = v.state_im + static_cast<size_t>(b0) * v.state_im_stride;
                 vc.Xsol = v.Xsol + b0 * sxN; vc.Usol = v.Usol + b0 * suN;
                 vc.status = v.status + b0; vc.iters = v.iters + b0;
-                cudaError_t e = (k == TMPC_KERNEL_TMEM2)
-                    ? tmpc::launch_admm_tmem2(vc, h->st, was_cold ? 1 : 0, h->counter.p, h->num_sms, h->stream)
-                    : h->per_instance
+                // a chunk longer than one wave goes through the queue: longest-first order over the chunk's own instances
+                const int* order = build_order(h, vc, h->stream, b0);
+                cudaError_t e = h->per_instance
                     ? tmpc::launch_admm_tmem_pi(vc, h->st, was_cold ? 1 : 0,
                                                 h->pi_blocks.p + static_cast<size_t>(b0) * tmpc::tmem_pi_block_doubles(h->nx, h->nu),
-                                                h->counter.p, h->num_sms, h->stream)
-                    : tmpc::launch_admm_tmem(vc, h->st, was_cold ? 1 : 0, h->counter.p, h->num_sms, h->stream);
+                                                h->counter.p, h->num_sms, h->stream, order)
+                    : tmpc::launch_admm_tmem(vc, h->st, was_cold ? 1 : 0, h->counter.p, h->num_sms, h->stream, order);
                 if (e != cudaSuccess) throw CudaFail{e, "solve kernel launch"};
                 h->launches += 1;
                 CUDA_TRY(cudaEventRecord(h->chunk_done[c], h->stream));
                 CUDA_TRY(cudaStreamWaitEvent(h->copy_stream, h->chunk_done[c], 0));
-                const size_t nb = static_cast<size_t>(b1 - b0);
-                if (X) CUDA_TRY(cudaMemcpyAsync(X + b0 * sxN, v.Xsol + b0 * sxN, sizeof(double) * sxN * nb, cudaMemcpyDeviceToHost, h->copy_stream));
-                if (U) CUDA_TRY(cudaMemcpyAsync(U + b0 * suN, v.Usol + b0 * suN, sizeof(double) * suN * nb, cudaMemcpyDeviceToHost, h->copy_stream));
+                fetch(b0, b1, h->copy_stream);
                 if (c == nch - 1) {   // status / iteration counts of the whole batch behind the last chunk: two copies, not 2 per chunk
                     CUDA_TRY(cudaMemcpyAsync(status, v.status, sizeof(int) * h->B, cudaMemcpyDeviceToHost, h->copy_stream));
                     if (iters) CUDA_TRY(cudaMemcpyAsync(iters, v.iters, sizeof(int) * h->B, cudaMemcpyDeviceToHost, h->copy_stream));
                 }
             }
-            h->state_zero = false; h->mem_zero = false; h->state_in_im = true;
+            h->state_zero = false; h->mem_zero = false; h->state_in_im = true; h->order_built = false;
             CUDA_TRY(cudaStreamSynchronize(h->copy_stream));
-            CUDA_TRY(cudaStreamSynchronize(h->stream));
+            sync_all(h);
         } else {
             if (x0) CUDA_TRY(cudaMemcpyAsync(h->x0.p, x0, sizeof(double) * h->nx * h->B, cudaMemcpyHostToDevice, h->stream));
             cudaError_t e = launch_solve(h, k, v, h->stream);
             if (e != cudaSuccess) throw CudaFail{e, "solve kernel launch"};
-            const size_t nb = static_cast<size_t>(h->B);
-            if (X) CUDA_TRY(cudaMemcpyAsync(X, h->Xsol.p, sizeof(double) * sxN * nb, cudaMemcpyDeviceToHost, h->stream));
-            if (U) CUDA_TRY(cudaMemcpyAsync(U, h->Usol.p, sizeof(double) * suN * nb, cudaMemcpyDeviceToHost, h->stream));
-            CUDA_TRY(cudaMemcpyAsync(status, h->status.p, sizeof(int) * nb, cudaMemcpyDeviceToHost, h->stream));
-            if (iters) CUDA_TRY(cudaMemcpyAsync(iters, h->iters.p, sizeof(int) * nb, cudaMemcpyDeviceToHost, h->stream));
-            CUDA_TRY(cudaStreamSynchronize(h->stream));
+            fetch(0, h->B, h->stream);
+            CUDA_TRY(cudaMemcpyAsync(status, h->status.p, sizeof(int) * h->B, cudaMemcpyDeviceToHost, h->stream));
+            if (iters) CUDA_TRY(cudaMemcpyAsync(iters, h->iters.p, sizeof(int) * h->B, cudaMemcpyDeviceToHost, h->stream));
+            sync_all(h);
         }
         for (int b = 0; b < h->B; ++b) if (status[b] != 0) return 1;
         return 0;
     });
+}
+
+int tmpc_batch_solve_host(tmpc_batch* h, const double* x0, int cold, double* X, double* U, int* status, int* iters,
+                          int chunks) {
+    return solve_host_impl(h, x0, cold, X, U, nullptr, status, iters, chunks);
+}
+
+int tmpc_batch_solve_host_select(tmpc_batch* h, const double* x0, int cold, double* X, double* U, double* u0, int* status,
+                                 int* iters, int chunks) {
+    return solve_host_impl(h, x0, cold, X, U, u0, status, iters, chunks);
 }
 
 int tmpc_batch_get_status(tmpc_batch* h, int* status, int* iters) {
@@ -803,9 +1000,15 @@ int tmpc_batch_get_status(tmpc_batch* h, int* status, int* iters) {
         if (!h) return TMPC_ERR_DIM;
         h->use_device();
         materialize_zero(h);
+        if (h->results_mapped) {
+            if (h->own_pending) sync_all(h);
+            if (status) std::memcpy(status, h->status.p, sizeof(int) * h->B);
+            if (iters) std::memcpy(iters, h->iters.p, sizeof(int) * h->B);
+            return TMPC_OK;
+        }
         if (status) CUDA_TRY(cudaMemcpyAsync(status, h->status.p, sizeof(int) * h->B, cudaMemcpyDeviceToHost, h->stream));
         if (iters) CUDA_TRY(cudaMemcpyAsync(iters, h->iters.p, sizeof(int) * h->B, cudaMemcpyDeviceToHost, h->stream));
-        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        sync_all(h);
         return TMPC_OK;
     });
 }
@@ -815,8 +1018,13 @@ int tmpc_batch_get_states(tmpc_batch* h, double* buf) {
         if (!h || !buf) return TMPC_ERR_DIM;
         h->use_device();
         materialize_zero(h);
+        if (h->results_mapped) {
+            if (h->own_pending) sync_all(h);
+            std::memcpy(buf, h->Xsol.p, sizeof(double) * h->nx * h->N * h->B);
+            return TMPC_OK;
+        }
         CUDA_TRY(cudaMemcpyAsync(buf, h->Xsol.p, sizeof(double) * h->nx * h->N * h->B, cudaMemcpyDeviceToHost, h->stream));
-        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        sync_all(h);
         return TMPC_OK;
     });
 }
@@ -826,8 +1034,13 @@ int tmpc_batch_get_controls(tmpc_batch* h, double* buf) {
         if (!h || !buf) return TMPC_ERR_DIM;
         h->use_device();
         materialize_zero(h);
+        if (h->results_mapped) {
+            if (h->own_pending) sync_all(h);
+            std::memcpy(buf, h->Usol.p, sizeof(double) * h->nu * (h->N - 1) * h->B);
+            return TMPC_OK;
+        }
         CUDA_TRY(cudaMemcpyAsync(buf, h->Usol.p, sizeof(double) * h->nu * (h->N - 1) * h->B, cudaMemcpyDeviceToHost, h->stream));
-        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        sync_all(h);
         return TMPC_OK;
     });
 }
@@ -874,7 +1087,9 @@ int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_lo
             h->ext_x0 = nullptr;
         }
         if (h->st.check_termination == 0) { set_error("check_termination = 0 is not supported"); return TMPC_ERR_STATE; }
-        ensure_aux_state(h);
+        if (h->adaptive_rho) { set_error("adaptive_rho is set: through this API the reference reads unset (0 x 0) sensitivity matrices in that branch and crashes at its first rho update (admm.cpp:331-357, rho_benchmark.cpp:204-207; DESIGN.md 8); there is no reference behaviour to reproduce, so the solve is refused - clear the flag with update_settings"); return TMPC_ERR_STATE; }
+        order_before_enqueue(h, s);
+        ensure_aux_state(h, s);
         const int k = resolve_kernel(h);
         if (k < 0) { set_error("requested kernel does not support this problem"); return TMPC_ERR_STATE; }
         const long long ref_len = static_cast<long long>(h->nx) * (h->N + nsteps - 1);
@@ -890,11 +1105,13 @@ int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_lo
                     h->launches += 1;
                 }
                 tmpc::RolloutArgs ra{nsteps, h->state_zero ? 1 : 0, d_x_ref_long ? 1 : 0, h->x0.p, d_status_out, d_iters_out,
-                                     h->per_instance ? h->pi_blocks.p : nullptr};
+                                     h->per_instance ? h->pi_blocks.p : nullptr,
+                                     h->order_mode == TMPC_ORDER_USER ? h->order_user.p : nullptr};
                 cudaError_t e = tmpc::launch_admm_tmem_rollout(v, h->st, ra, h->counter.p, h->num_sms, s);
                 if (e != cudaSuccess) throw CudaFail{e, "fused rollout launch"};
                 h->launches += 1;
-                h->state_zero = false; h->mem_zero = false; h->state_in_im = true;
+                h->state_zero = false; h->mem_zero = false; h->state_in_im = true; h->order_built = false;
+                mark_enqueued(h, s);
                 return TMPC_OK;
             }
         }
@@ -914,6 +1131,7 @@ int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_lo
             if (e != cudaSuccess) throw CudaFail{e, "rollout plant-step launch"};
             h->launches += 1;
         }
+        mark_enqueued(h, s);
         return TMPC_OK;
     });
 }
@@ -931,7 +1149,7 @@ int tmpc_batch_get_x0(tmpc_batch* h, void* dst, int device_dst) {
         const double* src = h->ext_x0 ? h->ext_x0 : h->x0.p;
         CUDA_TRY(cudaMemcpyAsync(dst, src, sizeof(double) * h->nx * h->B,
                                  device_dst ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, h->stream));
-        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        sync_all(h);
         return TMPC_OK;
     });
 }
@@ -946,5 +1164,13 @@ int tmpc_batch_dims(tmpc_batch* h, int* nx, int* nu, int* N, int* B) {
 }
 
 long long tmpc_batch_launch_count(tmpc_batch* h) { return h ? h->launches : 0; }
+
+void* tmpc_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    if (bytes == 0 || cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return p;
+}
+
+void tmpc_host_free(void* p) { if (p) cudaFreeHost(p); }
 
 }  // extern "C"

@@ -54,7 +54,22 @@ __global__ void record_step_kernel(const __grid_constant__ BatchView bv, int* __
     if (iters_out) iters_out[b] = bv.iters[b];
 }
 
+// first control of every instance, packed nu x B: what a closed loop consumes from a solve (cartpole_example_mpc.jl:41-42)
+__global__ void gather_u0_kernel(const double* __restrict__ Usol, long long stride, int nu, int B, double* __restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= B * nu) return;
+    const int b = i / nu, j = i - b * nu;
+    out[i] = Usol[static_cast<size_t>(b) * stride + j];
+}
+
 }  // namespace
+
+cudaError_t launch_gather_u0(const double* Usol, long long stride, int nu, int B, double* out, cudaStream_t stream) {
+    if (B <= 0) return cudaSuccess;
+    const int block = 256, grid = (B * nu + block - 1) / block;
+    gather_u0_kernel<<<grid, block, 0, stream>>>(Usol, stride, nu, B, out);
+    return cudaGetLastError();
+}
 
 cudaError_t launch_plant_step(const BatchView& bv, double* x0_rw, cudaStream_t stream) {
     const int block = 128, grid = (bv.B + block - 1) / block;

@@ -55,6 +55,22 @@ def _ivec(a) -> np.ndarray:
     return np.ascontiguousarray(np.asarray(a, dtype=np.int32).reshape(-1))
 
 
+def pinned_empty(shape, dtype=np.float64) -> np.ndarray:
+    """Fortran-ordered array in page-locked host memory (tmpc_host_alloc): the buffers of ``solve_host`` must be pinned
+    for the chunks' copies to overlap the solves.  Freed when the array (and every view of it) is collected."""
+    import weakref
+    lib = _lib.load()
+    dt = np.dtype(dtype)
+    n = int(np.prod(shape)) if np.ndim(shape) else int(shape)
+    ptr = lib.tmpc_host_alloc(C.c_size_t(max(n, 1) * dt.itemsize))
+    if not ptr:
+        raise TinyMPCError("tmpc_host_alloc failed (no CUDA device?)")
+    raw = (C.c_char * (max(n, 1) * dt.itemsize)).from_address(ptr)
+    arr = np.frombuffer(raw, dtype=dt, count=n).reshape(shape, order="F")
+    weakref.finalize(raw, lib.tmpc_host_free, C.c_void_p(ptr))
+    return arr
+
+
 class TinyMPCSolver:
     """Mirror of the Julia ``struct TinyMPCSolver`` (reference src/TinyMPC.jl:35-49)."""
 
@@ -150,23 +166,51 @@ class TinyMPCBatchSolver:
     def synchronize(self):
         _chk(_lib.load().tmpc_batch_synchronize(self._h), "synchronize failed")
 
-    def solve_host(self, x0=None, *, cold: bool = False, chunks: int = 0, want_states: bool = True):
+    def set_order(self, mode: int = 1, perm=None):
+        """Queue order of the on-chip kernels: 0 natural, 1 longest-first (default), 2 the given permutation of 0..B-1."""
+        p = None
+        if perm is not None:
+            pa = _ivec(perm)
+            p = pa.ctypes.data_as(_IP)
+        _chk(_lib.load().tmpc_batch_set_order(self._h, int(mode), p), "set_order failed")
+
+    def get_order(self):
+        """The permutation the last solve used, or None when it ran in natural order."""
+        out = np.zeros(self.B, dtype=np.int32)
+        rc = _lib.load().tmpc_batch_get_order(self._h, out.ctypes.data_as(_IP))
+        return out if rc == 0 else None
+
+    def solve_host(self, x0=None, *, cold: bool = False, chunks: int = 0, want_states: bool = True,
+                   want_controls: bool = True, want_u0: bool = False):
         """set_x0 (+ reset) + solve + get_solution + status in one call, pipelined over instance chunks
-        (tmpc_batch_solve_host).  Returns (ret, Solution, status[B], iters[B]); ret as ``solve``."""
+        (tmpc_batch_solve_host_select).  Output buffers are page-locked (reused between calls), so the chunks' copies
+        overlap the solves.  Returns (ret, Solution, status[B], iters[B]); ret as ``solve``; with ``want_u0`` the
+        Solution's controls are the first control of every instance (nu x B) when ``want_controls`` is off."""
         n, m, N, B = self.nx, self.nu, self.N, self.B
+        buf = self.__dict__.setdefault("_pinned", {})
+
+        def pin(key, shape, dtype=np.float64):
+            if key not in buf:
+                buf[key] = pinned_empty(shape, dtype)
+            return buf[key]
+
         x0p = None
         if x0 is not None:
-            x0a = _mat(x0, (n, B))
+            x0a = pin("x0", (n, B))
+            x0a[...] = _mat(x0, (n, B))
             x0p = _dp(x0a)
-        X = np.empty((n, N, B), order="F") if want_states else None
-        U = np.empty((m, N - 1, B), order="F")
-        st = np.zeros(B, dtype=np.int32)
-        it = np.zeros(B, dtype=np.int32)
-        ret = _lib.load().tmpc_batch_solve_host(self._h, x0p, int(bool(cold)), _dp(X) if X is not None else None, _dp(U),
-                                                st.ctypes.data_as(_IP), it.ctypes.data_as(_IP), int(chunks))
+        X = pin("X", (n, N, B)) if want_states else None
+        U = pin("U", (m, N - 1, B)) if want_controls else None
+        u0 = pin("u0", (m, B)) if want_u0 else None
+        st, it = pin("st", (B,), np.int32), pin("it", (B,), np.int32)
+        ret = _lib.load().tmpc_batch_solve_host_select(self._h, x0p, int(bool(cold)), _dp(X) if X is not None else None,
+                                                       _dp(U) if U is not None else None, _dp(u0) if u0 is not None else None,
+                                                       st.ctypes.data_as(_IP), it.ctypes.data_as(_IP), int(chunks))
         if ret not in (0, 1):
             raise TinyMPCError(f"solve_host failed with status {ret}: {_lib.last_error()}")
-        return ret, Solution(states=X, controls=U), st, it
+        controls = U if U is not None else u0
+        return ret, Solution(states=None if X is None else X.copy(order="F"),
+                             controls=None if controls is None else controls.copy(order="F")), st.copy(), it.copy()
 
     def rollout_async(self, nsteps: int, x_ref_long_ptr: int = 0, status_out_ptr: int = 0, iters_out_ptr: int = 0, stream: int = 0):
         _chk(_lib.load().tmpc_batch_rollout_async(self._h, int(nsteps), C.c_void_p(x_ref_long_ptr), C.c_void_p(status_out_ptr),
