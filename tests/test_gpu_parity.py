@@ -13,14 +13,14 @@ from tinympc_julia_b200 import problems as problems_mod
 
 pytestmark = pytest.mark.gpu
 
-THREAD, SUBWARP, TMEM = t.KERNEL_THREAD, t.KERNEL_SUBWARP, t.KERNEL_TMEM
+THREAD, SUBWARP, TMEM, CONE = t.KERNEL_THREAD, t.KERNEL_SUBWARP, t.KERNEL_TMEM, t.KERNEL_CONE
 
 
 def kernels_for(c):
     """Kernels able to run a case: the thread kernel always; the on-chip kernels where they apply."""
     ks = [THREAD]
     sol = cases.make_cuda_solver(c, kernel=t.KERNEL_AUTO)
-    for k in (SUBWARP, TMEM):
+    for k in (SUBWARP, TMEM, CONE):
         sol.set_kernel(k)
         if sol.kernel == k:
             ks.append(k)

@@ -11,4 +11,4 @@ from .solver import (  # noqa: F401
     set_instance_dynamics, set_linear_constraints, set_u_ref, set_x0, set_x_ref, setup, solve, update_settings,
 )
 
-KERNEL_AUTO, KERNEL_THREAD, KERNEL_SUBWARP, KERNEL_TMEM = 0, 1, 2, 3
+KERNEL_AUTO, KERNEL_THREAD, KERNEL_SUBWARP, KERNEL_TMEM, KERNEL_CONE = 0, 1, 2, 3, 4

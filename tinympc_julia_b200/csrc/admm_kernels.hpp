@@ -83,19 +83,28 @@ struct RolloutArgs {
 cudaError_t launch_admm_tmem_rollout(const BatchView& bv, const AdmmSettings& st, const RolloutArgs& ra, int* counter,
                                      int num_sms, cudaStream_t stream);
 
-// ---- longest-first instance queue (queue_order.cu): a permutation of the instances, expected-longest first, built by a
-// counting sort over 256 key buckets.  Cold start: key = saturation of the LQR input Kinf x0 against the input box;
-// warm start: key = the previous solve's iteration count.
+// ---- cones and half-spaces on chip (admm_cone.cu): a warp owns a tile of 3 instances; the Riccati recursions run with
+// one lane per matrix row, the slack / dual / linear-cost updates with one lane per knot point; state in Tensor Memory
+// and shared memory.  Compiled for nx = 6, nu = 3 (rocket landing), N <= 50, every constraint family, element-major
+// carried state (interchangeable with the thread kernel).
+bool cone_kernel_supports(const BatchView& bv, const AdmmSettings& st);
+cudaError_t launch_admm_cone(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms,
+                             cudaStream_t stream);
+
+// ---- longest-first instance queue (queue_order.cu): a permutation of the instances in which the kOrderTop instances of
+// every 256 expected to run longest jump the queue (one kernel, block-local counting sort over 256 key buckets).
+// Cold start: key = saturation of the LQR input Kinf x0 against the input box; warm start: key = the previous solve's
+// iteration count.
 constexpr int kOrderBuckets = 256;
+constexpr int kOrderTop = 64;   // of every 256: a quarter of the batch may jump the queue (config 2's iteration counts have a
+                                // heavy tail: 12 % of the cartpole instances need more than 1.5x the mean), the rest keeps the natural mix
 struct OrderArgs {
     int B, nx, nu;
     const double* x0;                         // nx x B
     const double* Kinf; long long kinf_ld;    // column-major nu x nx shared by all instances (kinf_ld = 0), or per instance [e][ld]
     const double* u_min; const double* u_max; long long ub_stride;   // input bounds, knot 0 (stride 0 = shared)
     const int* prev_iters;                    // non-null: key = iteration count of the previous solve
-    unsigned char* key;                       // scratch, B
-    int* hist;                                // scratch, 2 * kOrderBuckets ints: histogram, then the per-bucket cursors
-    int* cursor;                              // = hist + kOrderBuckets
+    int top;                                  // instances of every 256 that jump the queue (1..256)
     int* order;                               // out, B
 };
 cudaError_t launch_build_order(const OrderArgs& a, cudaStream_t stream);

@@ -106,44 +106,6 @@ struct MatsPerInstance {
     __device__ __forceinline__ double Rd(int i) const { return at(p_.Rd, i); }
 };
 
-// Second-order-cone projection of a 3-block, with the reference's mixed precision: mu and the
-// norm are rounded to float (reference admm.cpp:39,42), the last entry comes from a float division (:54).
-template <class T>
-__device__ __forceinline__ void project_soc3(T* s, double mu_d) {
-    using R = Ar<T>;
-    const float mu = static_cast<float>(mu_d);
-    const T u0 = R::mul(s[2], static_cast<T>(mu));
-    const float a = static_cast<float>(R::sqrt(R::add(R::mul(s[0], s[0]), R::mul(s[1], s[1]))));
-    const T ad = static_cast<T>(a);
-    if (ad <= -u0) {
-        s[0] = 0; s[1] = 0; s[2] = 0;
-    } else if (ad <= u0) {
-        // inside the cone: unchanged
-    } else {
-        const T scale = R::mul(T(0.5), R::add(T(1), R::div(u0, ad)));
-        const T last = static_cast<T>(__fdiv_rn(a, mu));
-        s[0] = R::mul(scale, s[0]); s[1] = R::mul(scale, s[1]); s[2] = R::mul(scale, last);
-    }
-}
-
-// Sequential (Gauss-Seidel) half-space projections, reference admm.cpp:148-173.
-template <class T>
-__device__ __forceinline__ void project_halfspaces(T* col, int len, const double* __restrict__ Alin,
-                                                   const double* __restrict__ blin, int nrows) {
-    for (int k = 0; k < nrows; ++k) {
-        using R = Ar<T>;
-        T dot = 0;
-        for (int j = 0; j < len; ++j) dot = R::fma(static_cast<T>(__ldg(Alin + j * nrows + k)), col[j], dot);
-        const T bk = static_cast<T>(__ldg(blin + k));
-        if (dot > bk) {
-            T sq = 0;
-            for (int j = 0; j < len; ++j) { const T a = static_cast<T>(__ldg(Alin + j * nrows + k)); sq = R::fma(a, a, sq); }
-            const T dist = R::div(R::sub(dot, bk), sq);
-            for (int j = 0; j < len; ++j) col[j] = R::sub(col[j], R::mul(dist, static_cast<T>(__ldg(Alin + j * nrows + k))));
-        }
-    }
-}
-
 template <class T, class M>
 __global__ void __launch_bounds__(kThreadKernelBlock)
 admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ BatchView bv,

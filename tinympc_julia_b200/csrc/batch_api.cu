@@ -10,6 +10,7 @@
 
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <new>
@@ -99,8 +100,7 @@ struct tmpc_batch {
     // queue order of the on-chip kernels (queue_order.cu)
     int order_mode = TMPC_ORDER_AUTO;
     bool order_built = false;                 // `order` holds the permutation the last solve used
-    DevBuf<int> order, order_user, order_hist;
-    DevBuf<unsigned char> order_key;
+    DevBuf<int> order, order_user;
     bool results_mapped = false;              // Xsol / Usol / status / iters live in mapped pinned host memory (tiny batch)
     double* x0_stage = nullptr;               // pinned staging of x0 for tiny batches: set_x0 returns without a stream sync
     cudaEvent_t x0_staged = nullptr;
@@ -239,10 +239,12 @@ int resolve_kernel(tmpc_batch* h) {
     }
     const bool sub_ok = tmpc::subwarp_kernel_supports(h->nx, h->nu, h->N, h->st);
     const bool tm_ok = tmpc::tmem_kernel_supports(make_view(h), h->st);
+    const bool cone_ok = tmpc::cone_kernel_supports(make_view(h), h->st);
+    if (h->kernel_pref == TMPC_KERNEL_CONE) return cone_ok ? TMPC_KERNEL_CONE : -1;
     if (h->kernel_pref == TMPC_KERNEL_TMEM) return tm_ok ? TMPC_KERNEL_TMEM : -1;
     if (h->kernel_pref == TMPC_KERNEL_SUBWARP) return sub_ok ? TMPC_KERNEL_SUBWARP : -1;
     if (h->kernel_pref == TMPC_KERNEL_THREAD) return TMPC_KERNEL_THREAD;
-    return tm_ok ? TMPC_KERNEL_TMEM : (sub_ok ? TMPC_KERNEL_SUBWARP : TMPC_KERNEL_THREAD);
+    return tm_ok ? TMPC_KERNEL_TMEM : (sub_ok ? TMPC_KERNEL_SUBWARP : (cone_ok ? TMPC_KERNEL_CONE : TMPC_KERNEL_THREAD));
 }
 
 void zero_state(tmpc_batch* h, cudaStream_t s) {
@@ -279,13 +281,14 @@ const int* build_order(tmpc_batch* h, const tmpc::BatchView& v, cudaStream_t s, 
         if (h->per_instance) { a.Kinf = h->piKinf.p + b0; a.kinf_ld = h->ld; }
         else { a.Kinf = v.Kinf; a.kinf_ld = 0; }
     }
-    if (!h->order.p) {
-        h->order.alloc(h->B); h->order_key.alloc(h->B); h->order_hist.alloc(2 * tmpc::kOrderBuckets);
-    }
-    a.key = h->order_key.p + b0; a.hist = h->order_hist.p; a.cursor = a.hist + tmpc::kOrderBuckets; a.order = h->order.p + b0;
+    if (!a.prev_iters && sizeof(double) * (256u * (h->nx + 1) + static_cast<size_t>(h->nu) * h->nx + h->nu) > 48 * 1024) return nullptr;
+    if (!h->order.p) h->order.alloc(h->B);
+    a.order = h->order.p + b0;
+    static const int top_env = [] { const char* e = std::getenv("TMPC_ORDER_TOP"); return e ? std::atoi(e) : 0; }();   // experiment aid
+    a.top = (top_env >= 1 && top_env <= 256) ? top_env : tmpc::kOrderTop;
     const cudaError_t e = tmpc::launch_build_order(a, s);
-    if (e != cudaSuccess) throw CudaFail{e, "queue-order kernels"};
-    h->launches += 2;
+    if (e != cudaSuccess) throw CudaFail{e, "queue-order kernel"};
+    h->launches += 1;
     if (whole) h->order_built = true;
     return a.order;
 }
@@ -295,7 +298,7 @@ const int* build_order(tmpc_batch* h, const tmpc::BatchView& v, cudaStream_t s, 
 // caller stream may still be running, and memsets on another stream would race with it.
 cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v_in, cudaStream_t s) {
     const bool tm = (k == TMPC_KERNEL_TMEM);
-    const bool sub = (k == TMPC_KERNEL_SUBWARP || tm) && h->st.max_iter > 0 && h->rho > 0.0;
+    const bool sub = (k == TMPC_KERNEL_SUBWARP || k == TMPC_KERNEL_CONE || tm) && h->st.max_iter > 0 && h->rho > 0.0;
     tmpc::BatchView v = v_in;
     const bool wants_im = sub && tm;
     if (wants_im && !h->state_im.p) {
@@ -316,6 +319,7 @@ cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v_in, cuda
     if (sub && k == TMPC_KERNEL_TMEM && h->per_instance)
         e = tmpc::launch_admm_tmem_pi(v, h->st, h->state_zero ? 1 : 0, h->pi_blocks.p, h->counter.p, h->num_sms, s, order);
     else if (sub && k == TMPC_KERNEL_TMEM) e = tmpc::launch_admm_tmem(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s, order);
+    else if (sub && k == TMPC_KERNEL_CONE) e = tmpc::launch_admm_cone(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
     else if (sub) e = tmpc::launch_admm_subwarp(v, h->st, h->hm, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s, h->precision);
     else if (h->per_instance) e = tmpc::launch_admm_thread_per_instance(v, h->st, per_instance_view(h), s, h->precision);
     else e = tmpc::launch_admm_thread(v, h->st, h->hm, s, h->precision);
@@ -547,7 +551,7 @@ int tmpc_batch_set_precision(tmpc_batch* h, int bits) {
 int tmpc_batch_get_precision(tmpc_batch* h) { return h ? h->precision : -1; }
 
 int tmpc_batch_set_kernel(tmpc_batch* h, int kernel) {
-    if (!h || kernel < TMPC_KERNEL_AUTO || kernel > TMPC_KERNEL_TMEM) return TMPC_ERR_DIM;
+    if (!h || kernel < TMPC_KERNEL_AUTO || kernel > TMPC_KERNEL_CONE) return TMPC_ERR_DIM;
     h->kernel_pref = kernel;
     return TMPC_OK;
 }
@@ -884,13 +888,16 @@ static int solve_host_impl(tmpc_batch* h, const double* x0, int cold, double* X,
         // With only u0 / status going home the solve is the long pole: two chunks, a short one first so that the
         // rest of x0 comes up behind it, the second keeping the queue (and its longest-first order) over 7/8 of the batch.
         const int wave = h->num_sms * 64;
-        const bool small_out = !X && !U;
-        int nch = chunks > 0 ? chunks : (small_out ? 2 : std::min(8, (h->B + wave - 1) / wave));
+        const size_t out_bytes = sizeof(double) * h->B * ((X ? static_cast<size_t>(h->nx) * h->N : 0) + (U ? static_cast<size_t>(h->nu) * (h->N - 1) : 0));
+        // default: a chunk per 16 MB going home (0.3 ms of PCIe), at most 8 and at most one per wave.  When only u0 /
+        // status go home the solve is the long pole and the batch stays ONE launch: every cut of the queue adds a drain
+        // (a one-wave chunk lasts as long as its longest instance), which costs more than overlapping the 0.1 ms upload
+        // of x0 saves (measured: 61 M solves/s as [1 wave | rest] against the single launch).
+        int nch = chunks > 0 ? chunks : static_cast<int>(std::min<size_t>(std::min(8, (h->B + wave - 1) / wave), out_bytes / (16u << 20)));
+        if (nch < 1) nch = 1;
         if (!tm || h->B < 3 * wave) nch = 1;
         std::vector<int> cut;     // chunk c = [cut[c], cut[c + 1])
-        if (nch > 1 && small_out && chunks <= 0) {
-            cut = {0, wave, h->B};
-        } else if (nch > 1) {
+        if (nch > 1) {
             int chunk_size = ((h->B + nch - 1) / nch + wave - 1) / wave * wave;
             if (chunk_size < wave) chunk_size = wave;
             for (int b0 = 0; b0 < h->B; b0 += chunk_size) cut.push_back(b0);

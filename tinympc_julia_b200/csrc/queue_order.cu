@@ -3,8 +3,8 @@
 // The TMEM kernels are persistent: sub-warps pull instance ids from a global ticket counter.  ADMM iteration counts
 // are data-dependent (reference admm.cpp:312-381: 5 ... max_iter), so an instance that needs 25 iterations and is
 // pulled in the last wave holds one sub-warp for three average solves while 147 SMs idle (measured: the whole
-// 0.90 weak-scaling efficiency of round 1, and ~10 % of single-GPU time on typical seeds).  Here the ticket indexes a
-// permutation that lists the instances expected to run longest first:
+// 0.90 weak-scaling efficiency of round 1, and up to 10 % of single-GPU time depending on the seed).  Here the ticket
+// indexes a permutation in which the instances expected to run longest jump the queue:
 //
 //   * cold start: key = saturation of the unconstrained LQR input against the input box,
 //         p_b = max_j |(Kinf x0_b)_j| / min(|u_min_j|, |u_max_j|)       (knot 0 of the bound table)
@@ -12,9 +12,13 @@
 //     iterations sits in queue positions 0..17 of 65,536 (easy); correlation with the iteration count 0.81 (hard).
 //   * warm start: key = iteration count of the instance's previous solve.
 //
-// Keys are quantised to 256 buckets and the permutation is a counting sort (histogram kernel + scatter kernel, a few
-// microseconds for 65,536 instances).  Results do not depend on the order (instances are independent), only the
-// makespan does.
+// ONE kernel, no global atomics, no scratch: every block ranks its own 256 consecutive instances by key (counting
+// sort in shared memory).  The `top` (kOrderTop by default) highest-ranked instances of every block go first - queue position
+// rank * nblocks + block, so the first nblocks tickets are every block's longest instance, the next nblocks every
+// block's second longest, ... - and all the others follow in their natural order.  Only the few expected stragglers
+// move: the bulk keeps the natural mix of long and short solves per warp (measured: a fully sorted queue costs 1 % on
+// the hard workload, where more than half of the instances run into max_iter and no order can help).
+// Results do not depend on the order (instances are independent), only the makespan does.
 #include <cuda_runtime.h>
 
 #include <cmath>
@@ -24,83 +28,109 @@
 namespace tmpc {
 namespace {
 
-constexpr int kBlock = 256;
+constexpr int kBlock = 256;          // instances per block = threads per block = key buckets
+static_assert(kBlock == kOrderBuckets, "one thread per bucket in the scan");
 
 __global__ void __launch_bounds__(kBlock)
-order_key_kernel(const OrderArgs a) {
-    __shared__ int hist[kOrderBuckets];
-    hist[threadIdx.x] = 0;
-    __syncthreads();
-    const int b = blockIdx.x * kBlock + threadIdx.x;
-    if (b < a.B) {
-        int key = 0;
-        if (a.prev_iters != nullptr) {
-            key = a.prev_iters[b];
-        } else {
-            // max_j |Kinf(j,:) x0| / bound_j ; Kinf column-major nu x nx: shared (stride 1 between entries, kinf_ld = 0 marks
-            // "one matrix") or per instance, element-major [e][ld]
+order_kernel(const OrderArgs a) {
+    extern __shared__ double sx[];                  // [kBlock][nx + 1] x0 of the block (padded pitch), then Kinf [nu * nx], then 1 / bound [nu]
+    __shared__ int hist[kOrderBuckets];             // instances per key, then inclusive suffix sums
+    __shared__ int cursor[kOrderBuckets];
+    __shared__ int warp_tot[kBlock / 32];
+    const int t = threadIdx.x;
+    const int b0 = blockIdx.x * kBlock;
+    const int cnt = min(kBlock, a.B - b0);          // instances of this block
+    const int b = b0 + t;
+    hist[t] = 0; cursor[t] = 0;
+    int key = 0;
+    if (a.prev_iters != nullptr) {
+        if (t < cnt) key = a.prev_iters[b];
+        __syncthreads();
+    } else {
+        const int nx = a.nx, nu = a.nu, pitch = nx + 1;
+        double* sk = sx + kBlock * pitch;
+        double* sr = sk + nu * nx;
+        for (int e = t; e < cnt * nx; e += kBlock) sx[(e / nx) * pitch + e % nx] = a.x0[static_cast<size_t>(b0) * nx + e];   // coalesced
+        if (a.kinf_ld == 0) for (int e = t; e < nu * nx; e += kBlock) sk[e] = a.Kinf[e];
+        if (t < nu) {   // 1 / min(|u_min_j|, |u_max_j|), knot 0 (shared bounds; per-instance bounds are read below)
+            double r = 0.0;
+            if (a.ub_stride == 0) {
+                const double bound = fmin(fabs(a.u_min[t]), fabs(a.u_max[t]));
+                r = (bound > 0.0 && !isinf(bound)) ? 1.0 / bound : 0.0;
+            }
+            sr[t] = r;
+        }
+        __syncthreads();
+        if (t < cnt) {
             double p = 0.0;
-            const double* x0 = a.x0 + static_cast<size_t>(b) * a.nx;
-            for (int j = 0; j < a.nu; ++j) {
-                const double lo = a.u_min ? fabs(a.u_min[(a.ub_stride ? static_cast<size_t>(b) * a.ub_stride : 0) + j]) : INFINITY;
-                const double hi = a.u_max ? fabs(a.u_max[(a.ub_stride ? static_cast<size_t>(b) * a.ub_stride : 0) + j]) : INFINITY;
-                const double bound = fmin(lo, hi);
-                if (!(bound > 0.0) || isinf(bound)) continue;
-                double s = 0.0;
-                for (int k = 0; k < a.nx; ++k) {
-                    const double kv = a.kinf_ld ? a.Kinf[static_cast<size_t>(k * a.nu + j) * a.kinf_ld + b] : a.Kinf[k * a.nu + j];
-                    s = fma(kv, x0[k], s);
+            for (int j = 0; j < nu; ++j) {
+                double rb = sr[j];
+                if (a.ub_stride != 0) {
+                    const size_t o = static_cast<size_t>(b) * a.ub_stride + j;
+                    const double bound = fmin(fabs(a.u_min[o]), fabs(a.u_max[o]));
+                    rb = (bound > 0.0 && !isinf(bound)) ? 1.0 / bound : 0.0;
                 }
-                p = fmax(p, fabs(s) / bound);
+                double s = 0.0;
+                for (int k = 0; k < nx; ++k) {
+                    const double kv = a.kinf_ld ? a.Kinf[static_cast<size_t>(k * nu + j) * a.kinf_ld + b] : sk[k * nu + j];
+                    s = fma(kv, sx[t * pitch + k], s);
+                }
+                p = fmax(p, fabs(s) * rb);
             }
             p *= 64.0;                       // 1/64 of the bound per bucket
             key = p < 255.0 ? static_cast<int>(p) : 255;
         }
-        key = key < 0 ? 0 : (key > kOrderBuckets - 1 ? kOrderBuckets - 1 : key);
-        a.key[b] = static_cast<unsigned char>(key);
-        atomicAdd(&hist[key], 1);
     }
+    key = key < 0 ? 0 : (key > kOrderBuckets - 1 ? kOrderBuckets - 1 : key);
+    if (t < cnt) atomicAdd(&hist[key], 1);
     __syncthreads();
-    if (hist[threadIdx.x]) atomicAdd(&a.hist[threadIdx.x], hist[threadIdx.x]);
-}
-
-__global__ void __launch_bounds__(kBlock)
-order_scatter_kernel(const OrderArgs a) {
-    __shared__ int base[kOrderBuckets];      // instances with a LARGER key (they go first)
-    __shared__ int cnt[kOrderBuckets];       // of this block, per key
-    __shared__ int start[kOrderBuckets];     // of this block's run inside the bucket
-    const int t = threadIdx.x;
-    // suffix sum over the 256 buckets: Hillis-Steele in shared memory
-    base[t] = a.hist[t];
-    cnt[t] = 0;
-    __syncthreads();
+    // inclusive suffix sums over the buckets (Hillis-Steele): hist[k] = instances of the block with key >= k
+    const int own = hist[t];
     for (int off = 1; off < kOrderBuckets; off <<= 1) {
-        const int v = (t + off < kOrderBuckets) ? base[t + off] : 0;
+        const int v = (t + off < kOrderBuckets) ? hist[t + off] : 0;
         __syncthreads();
-        base[t] += v;
+        hist[t] += v;
         __syncthreads();
     }
-    const int b = blockIdx.x * kBlock + t;
-    int key = 0, mine = 0;
-    if (b < a.B) {
-        key = a.key[b];
-        mine = atomicAdd(&cnt[key], 1);
+    (void)own;
+    // rank inside the block, descending key (ties in arrival order: any order of equal keys will do)
+    int rank = kBlock;
+    if (t < cnt) {
+        const int above = key + 1 < kOrderBuckets ? hist[key + 1] : 0;
+        rank = above + atomicAdd(&cursor[key], 1);
     }
+    // the others keep their natural order: exclusive prefix count of "not among the top" over the block
+    const int top = min(a.top, cnt);
+    const bool rest = (t < cnt) && rank >= top;
+    const unsigned m = __ballot_sync(0xffffffffu, rest);
+    const int lane = t & 31, w = t >> 5;
+    if (lane == 0) warp_tot[w] = __popc(m);
     __syncthreads();
-    if (cnt[t]) start[t] = atomicAdd(&a.cursor[t], cnt[t]);
-    __syncthreads();
-    if (b < a.B) a.order[base[key] - a.hist[key] + start[key] + mine] = b;   // base is inclusive: subtract the own bucket
+    int before = __popc(m & ((1u << lane) - 1u));
+    for (int i = 0; i < w; ++i) before += warp_tot[i];
+    if (t >= cnt) return;
+    // queue layout: [rank 0 of every block][rank 1 of every block] ... [rank top-1 ...][the rest, block after block]
+    // Only the last block can be short (cnt_last <= 256): ranks it does not have leave no hole.
+    const int nblk = gridDim.x;
+    const int cnt_last = a.B - (nblk - 1) * kBlock;
+    int pos;
+    if (!rest) {
+        const int full = min(rank, min(a.top, cnt_last));             // rank rows that every block (incl. the last) fills
+        pos = full * nblk + (rank - full) * (nblk - 1) + blockIdx.x;
+    } else {
+        const int top_all = min(a.top, cnt_last) * nblk + (a.top - min(a.top, cnt_last)) * (nblk - 1);
+        pos = top_all + blockIdx.x * (kBlock - a.top) + before;       // blocks before this one are full
+    }
+    a.order[pos] = b;
 }
 
 }  // namespace
 
 cudaError_t launch_build_order(const OrderArgs& a, cudaStream_t stream) {
     if (a.B <= 0) return cudaSuccess;
-    cudaError_t e = cudaMemsetAsync(a.hist, 0, sizeof(int) * 2 * kOrderBuckets, stream);   // hist + cursor are adjacent
-    if (e != cudaSuccess) return e;
     const int grid = (a.B + kBlock - 1) / kBlock;
-    order_key_kernel<<<grid, kBlock, 0, stream>>>(a);
-    order_scatter_kernel<<<grid, kBlock, 0, stream>>>(a);
+    const size_t smem = a.prev_iters ? 0 : sizeof(double) * (static_cast<size_t>(kBlock) * (a.nx + 1) + static_cast<size_t>(a.nu) * a.nx + a.nu);
+    order_kernel<<<grid, kBlock, smem, stream>>>(a);
     return cudaGetLastError();
 }
 
