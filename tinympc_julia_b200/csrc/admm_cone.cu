@@ -54,7 +54,48 @@ struct ConeParams {
     int cold;                       // carried state is logically zero: do not read it
     int smem_tasks;                 // tasks per warp kept in shared memory: max(0, 3 N - 96)
     int off_warp0, warp_stride;     // shared-memory carve-up, in doubles
+    // per-CTA tables staged once (what phase B would otherwise fetch through the read-only path for every task):
+    int tab_refs;                   // shared references as the products the cost uses: cq [N][NX], cr [N-1][NU], tq [NX]
+    int tab_bounds;                 // box bounds that are the same at every knot point: (lo, hi) pairs [NX], [NU]
+    int off_refs, off_bounds, off_lin;   // in doubles; half-spaces: rows of [a (len), b, |a|^2]
 };
+
+// 3-block of a column starting at run-time index `a`, by selects (a dynamic index would push the column into local memory)
+template <int LEN>
+__device__ __forceinline__ void project_cones(double (&vc)[LEN], int ncones, const int* A, const double* mu) {
+    for (int k = 0; k < ncones; ++k) {
+        const int a = A[k];
+        double s3[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            s3[c] = vc[c];
+#pragma unroll
+            for (int o = 1; o + 3 <= LEN; ++o) s3[c] = (a == o) ? vc[c + o] : s3[c];
+        }
+        project_soc3(s3, mu[k]);
+#pragma unroll
+        for (int j = 0; j < LEN; ++j) {
+            const int c = j - a;
+            vc[j] = (c == 0) ? s3[0] : ((c == 1) ? s3[1] : ((c == 2) ? s3[2] : vc[j]));
+        }
+    }
+}
+
+// Sequential (Gauss-Seidel) half-space projections (admm.cpp:148-173) from the staged rows [a (LEN), b, |a|^2]
+template <int LEN>
+__device__ __forceinline__ void project_halfspaces_tab(double (&col)[LEN], const double* tab, int nrows) {
+    for (int k = 0; k < nrows; ++k, tab += LEN + 2) {
+        double dot = 0.0;
+#pragma unroll
+        for (int j = 0; j < LEN; ++j) dot = fma(tab[j], col[j], dot);
+        const double bk = tab[LEN];
+        if (dot > bk) {
+            const double dist = __ddiv_rn(dsub(dot, bk), tab[LEN + 1]);
+#pragma unroll
+            for (int j = 0; j < LEN; ++j) col[j] = dsub(col[j], dmul(dist, tab[j]));
+        }
+    }
+}
 
 // ---- Tensor Memory, 72 words per task: x32 + x32 + x8 (tcgen05.ld is not scoreboarded: see tie_after_wait)
 __device__ __forceinline__ void tm_ld32(uint32_t taddr, uint32_t* r) {
@@ -128,6 +169,35 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     for (int e = threadIdx.x; e < NU * NU; e += blockDim.x) sQu[e] = bv.Quu_inv[e];
     for (int e = threadIdx.x; e < NX; e += blockDim.x) { sf[e] = bv.f[e]; sAPf[e] = bv.APf[e]; sQd[e] = bv.Qd[e]; }
     for (int e = threadIdx.x; e < NU; e += blockDim.x) { sBPf[e] = bv.BPf[e]; sRd[e] = bv.Rd[e]; }
+    // shared references as the terms the linear cost uses: cq = -(Xref .* Qd), cr = -(Uref .* Rd), tq = Xref_{N-1}' Pinf
+    // (admm.cpp:218, :228, :238); knot-invariant box bounds as (lo, hi) pairs; half-space rows with |a|^2
+    double* s_cq = smem + cp.off_refs;  double* s_cr = s_cq + NX * N;  double* s_tq = s_cr + NU * (N - 1);
+    double* s_xb = smem + cp.off_bounds;  double* s_ub = s_xb + 2 * NX;
+    double* s_lx = smem + cp.off_lin;  double* s_lu = s_lx + bv.nlx * (NX + 2);
+    if (cp.tab_refs) {
+        for (int e = threadIdx.x; e < NX * N; e += blockDim.x) s_cq[e] = -dmul(bv.Xref ? bv.Xref[e] : 0.0, bv.Qd[e % NX]);
+        for (int e = threadIdx.x; e < NU * (N - 1); e += blockDim.x) s_cr[e] = -dmul(bv.Uref ? bv.Uref[e] : 0.0, bv.Rd[e % NU]);
+        for (int j = threadIdx.x; j < NX; j += blockDim.x) {
+            double sp = 0.0;
+            if (bv.Xref) for (int k = 0; k < NX; ++k) sp = fma(bv.Xref[(N - 1) * NX + k], bv.Pinf[j * NX + k], sp);
+            s_tq[j] = sp;
+        }
+    }
+    if (cp.tab_bounds) {
+        const bool bx = st.en_state_bound && bv.x_min != nullptr, bu = st.en_input_bound && bv.u_min != nullptr;
+        for (int j = threadIdx.x; j < NX; j += blockDim.x) { s_xb[2 * j] = bx ? bv.x_min[j] : -INFINITY; s_xb[2 * j + 1] = bx ? bv.x_max[j] : INFINITY; }
+        for (int j = threadIdx.x; j < NU; j += blockDim.x) { s_ub[2 * j] = bu ? bv.u_min[j] : -INFINITY; s_ub[2 * j + 1] = bu ? bv.u_max[j] : INFINITY; }
+    }
+    if (st.en_state_linear) for (int k = threadIdx.x; k < bv.nlx; k += blockDim.x) {
+        double sq = 0.0;
+        for (int j = 0; j < NX; ++j) { const double a = bv.Alin_x[j * bv.nlx + k]; s_lx[k * (NX + 2) + j] = a; sq = fma(a, a, sq); }
+        s_lx[k * (NX + 2) + NX] = bv.blin_x[k]; s_lx[k * (NX + 2) + NX + 1] = sq;
+    }
+    if (st.en_input_linear) for (int k = threadIdx.x; k < bv.nlu; k += blockDim.x) {
+        double sq = 0.0;
+        for (int j = 0; j < NU; ++j) { const double a = bv.Alin_u[j * bv.nlu + k]; s_lu[k * (NU + 2) + j] = a; sq = fma(a, a, sq); }
+        s_lu[k * (NU + 2) + NU] = bv.blin_u[k]; s_lu[k * (NU + 2) + NU + 1] = sq;
+    }
     asm volatile("tcgen05.fence::before_thread_sync;");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;");
@@ -332,18 +402,20 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                         for (int j = 0; j < NU; ++j) {
                             const double yj = y[j];
                             const double t = dadd(u[j], yj);
-                            const double znew = box_u ? clampd(t, __ldg(umin + j), __ldg(umax + j)) : t;
+                            double znew;
+                            if (cp.tab_bounds) znew = clampd(t, s_ub[2 * j], s_ub[2 * j + 1]);        // (-inf, inf) when the box is off
+                            else znew = box_u ? clampd(t, __ldg(umin + j), __ldg(umax + j)) : t;
                             const double ynew = dsub(t, znew);
                             zold[j] = z[j];
                             ok = ok && (fabs(dsub(u[j], znew)) < tol_pri) && (dmul(fabs(dsub(zold[j], znew)), rho) < tol_dua);
-                            double ra = -dmul(uref ? __ldg(uref + j) : 0.0, sRd[j]);
+                            double ra = cp.tab_refs ? s_cr[i * NU + j] : -dmul(uref ? __ldg(uref + j) : 0.0, sRd[j]);
                             ra = dsub(ra, dmul(rho, dsub(znew, ynew)));
                             y[j] = ynew; z[j] = znew; racc[j] = ra;
                         }
                         if (soc_u) {
 #pragma unroll
                             for (int j = 0; j < NU; ++j) vc[j] = dadd(u[j], yc[j]);
-                            for (int k = 0; k < bv.ncu; ++k) project_soc3(vc + bv.Acu[k], bv.cu[k]);
+                            { double v3[NU] = {vc[0], vc[1], vc[2]}; project_cones<NU>(v3, bv.ncu, bv.Acu, bv.cu); vc[0] = v3[0]; vc[1] = v3[1]; vc[2] = v3[2]; }
 #pragma unroll
                             for (int j = 0; j < NU; ++j) {
                                 const double ycn = dsub(dadd(yc[j], u[j]), vc[j]);
@@ -354,7 +426,7 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                         if (lin_u) {
 #pragma unroll
                             for (int j = 0; j < NU; ++j) vc[j] = dadd(u[j], yl[j]);
-                            project_halfspaces(vc, NU, bv.Alin_u, bv.blin_u, bv.nlu);
+                            { double v3[NU] = {vc[0], vc[1], vc[2]}; project_halfspaces_tab<NU>(v3, s_lu, bv.nlu); vc[0] = v3[0]; vc[1] = v3[1]; vc[2] = v3[2]; }
 #pragma unroll
                             for (int j = 0; j < NU; ++j) {
                                 const double yln = dsub(dadd(yl[j], u[j]), vc[j]);
@@ -371,7 +443,9 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                         for (int j = 0; j < NX; ++j) {
                             const double gj = g[j];
                             const double t = dadd(x[j], gj);
-                            const double vnew = box_x ? clampd(t, __ldg(xmin + j), __ldg(xmax + j)) : t;
+                            double vnew;
+                            if (cp.tab_bounds) vnew = clampd(t, s_xb[2 * j], s_xb[2 * j + 1]);
+                            else vnew = box_x ? clampd(t, __ldg(xmin + j), __ldg(xmax + j)) : t;
                             const double gnew = dsub(t, vnew);
                             vold[j] = v[j];
                             ok = ok && (fabs(dsub(x[j], vnew)) < tol_pri) && (dmul(fabs(dsub(vold[j], vnew)), rho) < tol_dua);
@@ -380,12 +454,14 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                         }
                         if (!terminal) {
 #pragma unroll
-                            for (int j = 0; j < NX; ++j) acc[j] = dsub(-dmul(xref ? __ldg(xref + j) : 0.0, sQd[j]), acc[j]);
+                            for (int j = 0; j < NX; ++j)
+                                acc[j] = dsub(cp.tab_refs ? s_cq[i * NX + j] : -dmul(xref ? __ldg(xref + j) : 0.0, sQd[j]), acc[j]);
                         } else {
 #pragma unroll
                             for (int j = 0; j < NX; ++j) {
                                 double sp = 0.0;
-                                if (xref) {
+                                if (cp.tab_refs) sp = s_tq[j];
+                                else if (xref) {
 #pragma unroll
                                     for (int k = 0; k < NX; ++k) sp = fma(__ldg(xref + k), sP[j * NX + k], sp);   // Xref_{N-1}' Pinf
                                 }
@@ -395,7 +471,7 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                         if (soc_x) {
 #pragma unroll
                             for (int j = 0; j < NX; ++j) vc[j] = dadd(x[j], gc[j]);
-                            for (int k = 0; k < bv.ncx; ++k) project_soc3(vc + bv.Acx[k], bv.cx[k]);
+                            project_cones<NX>(vc, bv.ncx, bv.Acx, bv.cx);
 #pragma unroll
                             for (int j = 0; j < NX; ++j) {
                                 const double gcn = dsub(dadd(gc[j], x[j]), vc[j]);
@@ -406,7 +482,7 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                         if (lin_x) {
 #pragma unroll
                             for (int j = 0; j < NX; ++j) vc[j] = dadd(x[j], gl[j]);
-                            project_halfspaces(vc, NX, bv.Alin_x, bv.blin_x, bv.nlx);
+                            project_halfspaces_tab<NX>(vc, s_lx, bv.nlx);
 #pragma unroll
                             for (int j = 0; j < NX; ++j) {
                                 const double gln = dsub(dadd(gl[j], x[j]), vc[j]);
@@ -517,19 +593,33 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
 }
 
 template <int NX, int NU>
-bool cone_plan(int N, ConeParams& cp, size_t& smem_bytes) {
+bool cone_plan(const BatchView& bv, ConeParams& cp, size_t& smem_bytes) {
+    const int N = bv.N;
     if (N < 2) return false;
     const int T = kCInst * N;
     if ((T + 31) / 32 > kTmemSlots + 8) return false;
-    int off = 3 * NX * NX + 2 * NX * NU + NU * NU + 3 * NX + 2 * NU;
-    off = (off + 1) / 2 * 2;
-    cp.off_warp0 = off;
+    if (bv.nlx > kMaxLinear || bv.nlu > kMaxLinear) return false;
+    constexpr size_t kLimit = 227 * 1024 - 64;
     cp.smem_tasks = T > kTmemTasks ? T - kTmemTasks : 0;
     int per_warp = T * kRec + kTaskDoubles * cp.smem_tasks;
     per_warp = (per_warp + 1) / 2 * 2;
     cp.warp_stride = per_warp;
-    smem_bytes = (static_cast<size_t>(off) + static_cast<size_t>(per_warp) * kCWarps) * sizeof(double);
-    return smem_bytes <= 227 * 1024 - 64;
+    const bool shared_refs = (bv.Xref == nullptr || bv.xref_stride == 0) && (bv.Uref == nullptr || bv.uref_stride == 0);
+    const bool const_bounds = bv.x_min == nullptr || bv.bounds_const != 0;
+    // tables are optional: dropped (the kernel then fetches through the read-only path) when shared memory is short
+    for (int attempt = 0; attempt < 3; ++attempt) {
+        cp.tab_refs = (attempt == 0) && shared_refs;
+        cp.tab_bounds = (attempt <= 1) && const_bounds;
+        int off = 3 * NX * NX + 2 * NX * NU + NU * NU + 3 * NX + 2 * NU;
+        cp.off_lin = off;    off += bv.nlx * (NX + 2) + bv.nlu * (NU + 2);
+        cp.off_bounds = off; off += cp.tab_bounds ? 2 * (NX + NU) : 0;
+        cp.off_refs = off;   off += cp.tab_refs ? NX * N + NU * (N - 1) + NX : 0;
+        off = (off + 1) / 2 * 2;
+        cp.off_warp0 = off;
+        smem_bytes = (static_cast<size_t>(off) + static_cast<size_t>(per_warp) * kCWarps) * sizeof(double);
+        if (smem_bytes <= kLimit) return true;
+    }
+    return false;
 }
 
 }  // namespace
@@ -540,7 +630,7 @@ bool cone_kernel_supports(const BatchView& bv, const AdmmSettings& st) {
     if (bv.ncx > kMaxCones || bv.ncu > kMaxCones) return false;
     ConeParams cp{};
     size_t bytes = 0;
-    return cone_plan<6, 3>(bv.N, cp, bytes);
+    return cone_plan<6, 3>(bv, cp, bytes);
 }
 
 cudaError_t launch_admm_cone(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms,
@@ -549,7 +639,7 @@ cudaError_t launch_admm_cone(const BatchView& bv, const AdmmSettings& st, int co
     if (bv.nx != 6 || bv.nu != 3) return cudaErrorNotSupported;
     ConeParams cp{};
     size_t bytes = 0;
-    if (!cone_plan<6, 3>(bv.N, cp, bytes)) return cudaErrorInvalidConfiguration;
+    if (!cone_plan<6, 3>(bv, cp, bytes)) return cudaErrorInvalidConfiguration;
     cp.counter = counter;
     cp.cold = cold;
     auto kern = admm_cone_kernel<6, 3>;

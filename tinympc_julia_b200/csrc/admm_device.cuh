@@ -37,6 +37,7 @@ struct BatchView {
     const double* Uref; long long uref_stride;
     const double* x_min; const double* x_max; long long xb_stride;   // nullptr => unbounded
     const double* u_min; const double* u_max; long long ub_stride;
+    int bounds_const;                       // shared bounds that are the same at every knot point (checked when they are set)
 
     // ---- shared problem constants, column-major, device memory
     const double *A, *Bm, *f, *Kinf, *Pinf, *Quu_inv, *AmBKt, *APf, *BPf, *Qd, *Rd;

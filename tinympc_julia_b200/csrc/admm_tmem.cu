@@ -56,9 +56,13 @@ using namespace tmu;
 #ifndef TMPC_QWARPS
 #define TMPC_QWARPS 8
 #endif
-constexpr int kQWarps = TMPC_QWARPS;           // warps per CTA (one CTA per SM): two per scheduler
+// warps per CTA (one CTA per SM).  Quadrotor shape: two per scheduler (238 registers per thread, 240 of 256 Tensor-Memory
+// columns and 16.4 KB of shared memory per warp).  Cartpole shape (one state row per lane: 139 registers, 80 TMEM columns,
+// 15.4 KB per warp): three per scheduler - the kernel is latency-bound (ncu: 2.0 fixed-latency stall cycles per issue
+// at 8 warps, profiles/r02_a_ncu_full_cartpole_summary.csv).
+template <int NX, bool PI = false> struct QWarps { static constexpr int value = (NX == 4 && !PI) ? 12 : TMPC_QWARPS; };   // per-instance operands: + 4.6 KB of shared memory per warp
 constexpr int kQInst = 8;            // instances per warp
-constexpr int kTmemColsPerWarp = 256;
+template <int NX, bool PI = false> struct QTmemCols { static constexpr int value = (512 / ((QWarps<NX, PI>::value + 3) / 4)) & ~1; };   // columns per warp
 
 struct QuadParams {
     double pri_thresh;      // primal residual passes  <=>  |x - vnew| <  pri_thresh
@@ -87,7 +91,7 @@ struct QuadParams {
 // REFS: 0 = no references (Xref = Uref = 0), 1 = references shared by all instances (staged in shared memory as
 // the products the linear cost needs), 2 = per-instance references read through the read-only path.
 template <int NX, int NU, bool COLD, int REFS, bool ROLL = false, bool PI = false>
-__global__ void __launch_bounds__(kQWarps * 32, 1)
+__global__ void __launch_bounds__(QWarps<NX, PI>::value * 32, 1)
 admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ AdmmSettings st,
                  const __grid_constant__ QuadParams qp) {
     // A global access in uniform control flow before anything else: ptxas then keeps the global-memory descriptor in a
@@ -194,7 +198,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     const bool urow = (NU == 4) || (sub < NU);        // this lane owns an input row
     const int usub = urow ? sub : 0;
     const uint32_t tbase = s_tmem_base + (static_cast<uint32_t>((warp & 3) * 32) << 16) +
-                           static_cast<uint32_t>((warp >> 2) * kTmemColsPerWarp);
+                           static_cast<uint32_t>((warp >> 2) * QTmemCols<NX, PI>::value);
     double* wbase = smem + qp.off_warp0 + static_cast<size_t>(warp) * qp.warp_stride;
     double* s_yz = wbase;                             // [N-1][32 lanes][2] : (y, z) of the lane's input row
     double* s_rt = s_yz + (N - 1) * 64;               // [N-1][2 halves][8 inst][2] : r_i (after a forward sweep) / t_i (after a
@@ -830,7 +834,8 @@ template <int NX, int NU>
 bool make_qplan(int N, int refs, QPlan& pl, bool pi = false) {
     constexpr int XP = QPad<NX>::value;
     constexpr int W = 4 * (NX / 4);
-    if (N < 2 || N * W > kTmemColsPerWarp) return false;           // g, v of a lane must fit its 256 TMEM columns
+    const int warps = pi ? QWarps<NX, true>::value : QWarps<NX, false>::value;
+    if (N < 2 || N * W > (pi ? QTmemCols<NX, true>::value : QTmemCols<NX, false>::value)) return false;   // g, v of a lane must fit the warp's TMEM columns
     const int nxN = NX * N, nuN = NU * (N - 1);
     QuadParams qp{};
     int off = 0;
@@ -844,7 +849,7 @@ bool make_qplan(int N, int refs, QPlan& pl, bool pi = false) {
     qp.off_pi = per_warp;
     if (pi) per_warp += 32 * 18;                                   // the lanes' private B / Quu_inv row slots
     qp.warp_stride = per_warp;
-    pl.smem_bytes = (static_cast<size_t>(off) + static_cast<size_t>(per_warp) * kQWarps) * sizeof(double);
+    pl.smem_bytes = (static_cast<size_t>(off) + static_cast<size_t>(per_warp) * warps) * sizeof(double);
     pl.qp = qp;
     return pl.smem_bytes <= 227 * 1024;
 }
@@ -860,10 +865,10 @@ cudaError_t launch_q(const BatchView& bv, const AdmmSettings& st, const QPlan& p
     auto kern = admm_tmem_kernel<NX, NU, COLD, REFS, ROLL, PI>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(pl.smem_bytes));
     if (e != cudaSuccess) return e;
-    const int per_cta = kQWarps * kQInst;
+    const int per_cta = QWarps<NX, PI>::value * kQInst;
     int grid = (bv.B + per_cta - 1) / per_cta;
     if (grid > num_sms) grid = num_sms;            // persistent: one CTA per SM, sub-warps pull instances from the queue
-    kern<<<grid, kQWarps * 32, pl.smem_bytes, stream>>>(bv, st, pl.qp);
+    kern<<<grid, QWarps<NX, PI>::value * 32, pl.smem_bytes, stream>>>(bv, st, pl.qp);
     return cudaGetLastError();
 }
 

@@ -115,6 +115,7 @@ struct tmpc_batch {
     // inputs
     DevBuf<double> x0, Xref, Uref, xmin, xmax, umin, umax;
     int xref_batch = 0, uref_batch = 0, bounds_batch = 0;      // 0 = never set
+    bool bounds_knot_invariant = false;                        // shared bounds with identical columns (the usual MPC box)
     const double *ext_x0 = nullptr, *ext_xref = nullptr, *ext_uref = nullptr;
     int ext_xref_batch = 0, ext_uref_batch = 0;
     // constraints
@@ -201,6 +202,7 @@ tmpc::BatchView make_view(tmpc_batch* h) {
     if (h->bounds_batch) {
         v.x_min = h->xmin.p; v.x_max = h->xmax.p; v.xb_stride = h->bounds_batch > 1 ? sxN : 0;
         v.u_min = h->umin.p; v.u_max = h->umax.p; v.ub_stride = h->bounds_batch > 1 ? suN : 0;
+        v.bounds_const = h->bounds_knot_invariant ? 1 : 0;
     }
     v.A = h->dA.p; v.Bm = h->dB.p; v.f = h->df.p; v.Kinf = h->dKinf.p; v.Pinf = h->dPinf.p; v.Quu_inv = h->dQuu.p;
     v.AmBKt = h->dAmBKt.p; v.APf = h->dAPf.p; v.BPf = h->dBPf.p; v.Qd = h->dQd.p; v.Rd = h->dRd.p;
@@ -646,6 +648,17 @@ int tmpc_batch_set_bound_constraints(tmpc_batch* h, const double* x_min, const d
         h->xmin.upload(x_min, sx, h->stream); h->xmax.upload(x_max, sx, h->stream);
         h->umin.upload(u_min, su, h->stream); h->umax.upload(u_max, su, h->stream);
         h->bounds_batch = batch;
+        h->bounds_knot_invariant = false;
+        if (batch == 1) {   // the same box at every knot point: kernels may keep one column instead of the nx x N table
+            bool same = true;
+            auto cols_equal = [&](const double* m, int rows, int cols) {
+                for (int c = 1; c < cols && same; ++c)
+                    for (int r = 0; r < rows; ++r) if (!(m[c * rows + r] == m[r])) { same = false; break; }
+            };
+            cols_equal(x_min, h->nx, h->N); cols_equal(x_max, h->nx, h->N);
+            cols_equal(u_min, h->nu, h->N - 1); cols_equal(u_max, h->nu, h->N - 1);
+            h->bounds_knot_invariant = same;
+        }
         h->st.en_state_bound = 1; h->st.en_input_bound = 1;     // src/bindings.cpp:400-404
         sync_all(h);
         return TMPC_OK;
