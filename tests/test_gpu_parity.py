@@ -396,10 +396,13 @@ def test_per_instance_dynamics_closed_loop(orc):
 # where oracle/_ref travelled to this box.  Tolerance: cases.compare_f32.
 
 def kernels32_for(c):
-    """Float build: the thread kernel always, the shared-memory sub-warp kernel where it applies."""
+    """Float build: the thread kernel always, the shared-memory sub-warp kernel and the TMEM kernel where they apply."""
     sol = cases.make_cuda_solver(c, kernel=t.KERNEL_AUTO, precision=32)
-    sol.set_kernel(SUBWARP)
-    ks = [THREAD] + ([SUBWARP] if sol.kernel == SUBWARP else [])
+    ks = [THREAD]
+    for k in (SUBWARP, TMEM):
+        sol.set_kernel(k)
+        if sol.kernel == k:
+            ks.append(k)
     del sol
     return ks
 
@@ -413,9 +416,10 @@ def test_float_build_matches_float_reference_fixture(name):
         for k in ("X", "U"):
             assert np.array_equal(got[k], got[k].astype(np.float32).astype(np.float64)), "results must be floats widened to double"
         cases.compare_f32(got, want, what=f"cuda float[kernel {kern}] vs float reference[{name}]")
-    if SUBWARP in outs:      # same sequence of rounded operations: the two float kernels agree bit for bit
-        for k in ("ret", "iters", "X", "U"):
-            assert np.array_equal(outs[THREAD][k], outs[SUBWARP][k]), f"float thread vs sub-warp kernel: {k} differs"
+    for kern in (SUBWARP, TMEM):      # same sequence of rounded operations: the float kernels agree bit for bit
+        if kern in outs:
+            for k in ("ret", "iters", "X", "U"):
+                assert np.array_equal(outs[THREAD][k], outs[kern][k]), f"float thread vs kernel {kern}: {k} differs"
 
 
 def test_float_build_seeded_batches_against_live_float_reference():
@@ -435,24 +439,32 @@ def test_float_build_seeded_batches_against_live_float_reference():
 
 
 def test_float_build_warm_start_and_guards():
-    """A second solve warm-starts from the float carried state, whichever float kernel wrote it; the TMEM kernels are
-    64-bit only and say so; switching precision needs a reset batch."""
+    """A second solve warm-starts from the float carried state, whichever float kernel wrote it (the TMEM kernel keeps it
+    as instance-major float blocks, the others element-major: converted on the way); the cone kernel and per-instance
+    dynamics are 64-bit only and say so; switching precision needs a reset batch."""
     c, _ = cases.golden_f32_case("quadrotor_easy_64")
+    ref_sol = cases.make_cuda_solver(c, kernel=THREAD, precision=32)      # three solves on the thread kernel alone
+    ref_runs = [cases.run_cuda(c, sol=ref_sol) for _ in range(3)]
     sol = cases.make_cuda_solver(c, kernel=t.KERNEL_AUTO, precision=32)
-    assert sol.precision == 32 and sol.kernel == SUBWARP   # AUTO: the on-chip float kernel where it applies
+    assert sol.precision == 32 and sol.kernel == TMEM      # AUTO: the on-chip float kernel where it applies
     first = cases.run_cuda(c, sol=sol)
     sol.set_kernel(THREAD)
     again = cases.run_cuda(c, sol=sol)                      # same x0, warm start from the other kernel's state
     assert again["iters"].max() <= first["iters"].min()
-    ref_sol = cases.make_cuda_solver(c, kernel=THREAD, precision=32)      # the same two solves on the thread kernel alone
-    cases.run_cuda(c, sol=ref_sol)
-    again_ref = cases.run_cuda(c, sol=ref_sol)
+    sol.set_kernel(SUBWARP)
+    third = cases.run_cuda(c, sol=sol)
+    for got, want in ((first, ref_runs[0]), (again, ref_runs[1]), (third, ref_runs[2])):
+        for k in ("ret", "iters", "X", "U"):
+            assert np.array_equal(got[k], want[k]), f"warm start across float kernels: {k} differs"
+    sol.set_kernel(TMEM)
+    fourth = cases.run_cuda(c, sol=sol)                     # and back onto the TMEM kernel (element-major -> blocks)
+    fourth_ref = cases.run_cuda(c, sol=ref_sol)
     for k in ("ret", "iters", "X", "U"):
-        assert np.array_equal(again[k], again_ref[k]), f"warm start across float kernels: {k} differs"
+        assert np.array_equal(fourth[k], fourth_ref[k]), f"warm start back on the float TMEM kernel: {k} differs"
     with pytest.raises(t.TinyMPCError):
         sol.set_precision(64)                               # carries state
-    sol.set_kernel(TMEM)
-    assert sol.kernel == -1                                 # the on-chip kernels are 64-bit only
+    sol.set_kernel(CONE)
+    assert sol.kernel == -1                                 # not this shape, and 64-bit only
     assert t.solve(sol) not in (0, 1)                       # refused, not silently run on another kernel
     sol.set_kernel(THREAD)
     sol.reset()

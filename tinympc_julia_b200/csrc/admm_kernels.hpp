@@ -53,9 +53,10 @@ cudaError_t launch_admm_subwarp(const BatchView& bv, const AdmmSettings& st, con
 // refill from a global queue (admm_tmem.cu).  Box-constrained (or unconstrained) problems with shared bounds.
 // `order` (all TMEM launchers): device permutation of 0..B-1 the queue tickets index (queue_order.cu), or nullptr for
 // the natural order.
-bool tmem_kernel_supports(const BatchView& bv, const AdmmSettings& st);
+// `precision` = 32: the float instantiation (tinytype = float: 16 warps per SM, carried state as float blocks).
+bool tmem_kernel_supports(const BatchView& bv, const AdmmSettings& st, int precision = 64);
 cudaError_t launch_admm_tmem(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms,
-                             cudaStream_t stream, const int* order = nullptr);
+                             cudaStream_t stream, const int* order = nullptr, int precision = 64);
 
 // Per-instance dynamics on the TMEM kernel: one QConst-layout block of constants per instance (packed once from the
 // element-major cache); the lane's matrix rows come from its instance's block at every sweep start (L2-resident for
@@ -111,7 +112,7 @@ cudaError_t launch_build_order(const OrderArgs& a, cudaStream_t stream);
 
 // ---- carried-state formats (state_layout.cu): element-major [e][ld] arrays <-> instance-major blocks
 inline long long state_im_doubles(int nx, int nu, int N) { return 3LL * nx * N + 3LL * nu * (N - 1) + nx; }
-cudaError_t launch_state_convert(const BatchView& bv, bool to_instance_major, cudaStream_t stream);
+cudaError_t launch_state_convert(const BatchView& bv, bool to_instance_major, cudaStream_t stream, int precision = 64);
 
 // ---- closed-loop plant step (rollout.cu): x0 <- A x0 + B Usol(:,0) + f, optional reference slide
 cudaError_t launch_plant_step(const BatchView& bv, double* x0_rw, cudaStream_t stream);

@@ -60,9 +60,13 @@ using namespace tmu;
 // columns and 16.4 KB of shared memory per warp).  Cartpole shape (one state row per lane: 139 registers, 80 TMEM columns,
 // 15.4 KB per warp): three per scheduler - the kernel is latency-bound (ncu: 2.0 fixed-latency stall cycles per issue
 // at 8 warps, profiles/r02_a_ncu_full_cartpole_summary.csv).
-template <int NX, bool PI = false> struct QWarps { static constexpr int value = (NX == 4 && !PI) ? 12 : TMPC_QWARPS; };   // per-instance operands: + 4.6 KB of shared memory per warp
+// Float build (tinytype = float): half the shared memory and Tensor-Memory columns per warp and one register per value:
+// 16 warps (four per scheduler, <= 128 registers per thread).
+template <class T, int NX, bool PI = false> struct QWarps {
+    static constexpr int value = sizeof(T) == 4 ? 16 : ((NX == 4 && !PI) ? 12 : TMPC_QWARPS);   // per-instance operands: + 4.6 KB of shared memory per warp
+};
 constexpr int kQInst = 8;            // instances per warp
-template <int NX, bool PI = false> struct QTmemCols { static constexpr int value = (512 / ((QWarps<NX, PI>::value + 3) / 4)) & ~1; };   // columns per warp
+template <class T, int NX, bool PI = false> struct QTmemCols { static constexpr int value = (512 / ((QWarps<T, NX, PI>::value + 3) / 4)) & ~1; };   // columns per warp
 
 struct QuadParams {
     double pri_thresh;      // primal residual passes  <=>  |x - vnew| <  pri_thresh
@@ -90,8 +94,8 @@ struct QuadParams {
 
 // REFS: 0 = no references (Xref = Uref = 0), 1 = references shared by all instances (staged in shared memory as
 // the products the linear cost needs), 2 = per-instance references read through the read-only path.
-template <int NX, int NU, bool COLD, int REFS, bool ROLL = false, bool PI = false>
-__global__ void __launch_bounds__(QWarps<NX, PI>::value * 32, 1)
+template <class T, int NX, int NU, bool COLD, int REFS, bool ROLL = false, bool PI = false>
+__global__ void __launch_bounds__(QWarps<T, NX, PI>::value * 32, 1)
 admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ AdmmSettings st,
                  const __grid_constant__ QuadParams qp) {
     // A global access in uniform control flow before anything else: ptxas then keeps the global-memory descriptor in a
@@ -103,8 +107,11 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     static_assert(NU >= 1 && NU <= 4, "one input row per lane");
     constexpr int RX = NX / 4;
     constexpr int XP = QPad<NX>::value;
-    constexpr int W = 4 * RX;                         // 32-bit TMEM words per knot point per lane: g(RX), v(RX)
-    static_assert(W == 12 || W == 4, "tm_wait_ld is specialised for 3 or 1 state rows per lane");
+    using R = Ar<T>;                                  // arithmetic at the reference's tinytype (types.hpp:15)
+    constexpr int S = sizeof(T);                      // bytes per value: every shared-memory byte offset below is a multiple
+    constexpr int W = 2 * RX * (S / 4);               // 32-bit TMEM words per knot point per lane: g(RX), v(RX)
+    static_assert(W == 12 || W == 4 || W == 6 || W == 2, "tm_wait_ld is specialised for 3 or 1 state rows per lane");
+    static_assert(S == 8 || (!ROLL && !PI), "the fused closed loop and per-instance dynamics are built for 64-bit only");
     using CL = QConst<NX, NU>;
     using PL = QLane<NX, NU>;
 #ifndef TMPC_CREG
@@ -112,13 +119,15 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
 #endif
     constexpr bool CREG = TMPC_CREG != 0;
 
-    extern __shared__ __align__(16) double smem[];
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    T* const smem = reinterpret_cast<T*>(smem_raw);
     __shared__ uint32_t s_tmem_base;
     __shared__ uint32_t s_smem_base;
     const int N = bv.N;
     const int nxN = NX * N, nuN = NU * (N - 1);
     const size_t ld = static_cast<size_t>(bv.ld);
-    const double rho = bv.rho, nrho = -bv.rho;
+    const T rho = static_cast<T>(bv.rho), nrho = -rho;      // bindings.cpp:55 casts rho to tinytype
+    const T pri_thresh = static_cast<T>(qp.pri_thresh), dua_thresh = static_cast<T>(qp.dua_thresh);
 
     // ---------------- Tensor Memory: the whole 512-column file of this SM (one CTA per SM)
     if (threadIdx.x < 32) {
@@ -128,7 +137,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     }
 
     // ---------------- stage the shared constants once per CTA
-    double* sc = smem + qp.off_consts;
+    T* sc = smem + qp.off_consts;
     static_assert(!PI || REFS != 1, "per-instance dynamics take references, shared or not, through the per-instance path");
     if (!PI)
     for (int idx = threadIdx.x; idx < NX * NX; idx += blockDim.x) {
@@ -156,28 +165,28 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     }
 
     // box bounds as (lo, hi) pairs; a disabled side is (-inf, +inf), for which the clamp is the identity
-    double* s_xb = smem + qp.off_bounds;              // [N][NX][2]
-    double* s_ub = s_xb + 2 * nxN;                    // [N-1][NU][2]
+    T* s_xb = smem + qp.off_bounds;              // [N][NX][2]
+    T* s_ub = s_xb + 2 * nxN;                    // [N-1][NU][2]
     {
         const bool bx = st.en_state_bound && bv.x_min != nullptr, bu = st.en_input_bound && bv.u_min != nullptr;
         for (int e = threadIdx.x; e < nxN; e += blockDim.x) {
-            s_xb[2 * e] = bx ? bv.x_min[e] : -INFINITY; s_xb[2 * e + 1] = bx ? bv.x_max[e] : INFINITY;
+            s_xb[2 * e] = static_cast<T>(bx ? bv.x_min[e] : -INFINITY); s_xb[2 * e + 1] = static_cast<T>(bx ? bv.x_max[e] : INFINITY);
         }
         for (int e = threadIdx.x; e < nuN; e += blockDim.x) {
-            s_ub[2 * e] = bu ? bv.u_min[e] : -INFINITY; s_ub[2 * e + 1] = bu ? bv.u_max[e] : INFINITY;
+            s_ub[2 * e] = static_cast<T>(bu ? bv.u_min[e] : -INFINITY); s_ub[2 * e + 1] = static_cast<T>(bu ? bv.u_max[e] : INFINITY);
         }
     }
     // shared references, stored as the terms the linear cost uses: cq = -(Xref .* Qd), cr = -(Uref .* Rd),
     // tq = -(Xref_{N-1}' Pinf)'   (reference admm.cpp:218, :228, :238)
-    double* s_cq = smem + qp.off_refs;                // [N][NX]
-    double* s_cr = s_cq + nxN;                        // [N-1][NU]
-    double* s_tq = s_cr + nuN;                        // [NX]
+    T* s_cq = smem + qp.off_refs;                // [N][NX]
+    T* s_cr = s_cq + nxN;                        // [N-1][NU]
+    T* s_tq = s_cr + nuN;                        // [NX]
     if (REFS == 1) {
-        for (int e = threadIdx.x; e < nxN; e += blockDim.x) s_cq[e] = -dmul(bv.Xref ? bv.Xref[e] : 0.0, bv.Qd[e % NX]);
-        for (int e = threadIdx.x; e < nuN; e += blockDim.x) s_cr[e] = -dmul(bv.Uref ? bv.Uref[e] : 0.0, bv.Rd[e % NU]);
+        for (int e = threadIdx.x; e < nxN; e += blockDim.x) s_cq[e] = -R::mul(static_cast<T>(bv.Xref ? bv.Xref[e] : 0.0), static_cast<T>(bv.Qd[e % NX]));
+        for (int e = threadIdx.x; e < nuN; e += blockDim.x) s_cr[e] = -R::mul(static_cast<T>(bv.Uref ? bv.Uref[e] : 0.0), static_cast<T>(bv.Rd[e % NU]));
         for (int row = threadIdx.x; row < NX; row += blockDim.x) {
-            double s = 0.0;
-            if (bv.Xref) for (int k = 0; k < NX; ++k) s = fma(bv.Xref[(N - 1) * NX + k], bv.Pinf[row * NX + k], s);
+            T s = T(0);
+            if (bv.Xref) for (int k = 0; k < NX; ++k) s = R::fma(static_cast<T>(bv.Xref[(N - 1) * NX + k]), static_cast<T>(bv.Pinf[row * NX + k]), s);
             s_tq[row] = -s;
         }
     }
@@ -190,7 +199,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     // the samples of the forward sweep).  A loaded value can only be kept.
     uint32_t sbase;
     asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(sbase) : "r"(smem_addr(&s_smem_base)) : "memory");
-    auto sa = [&](const double* q) { return sbase + static_cast<uint32_t>((q - smem) * sizeof(double)); };
+    auto sa = [&](const T* q) { return sbase + static_cast<uint32_t>((q - smem) * S); };
 
     // ---------------- per-warp carve-up
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -198,44 +207,44 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     const bool urow = (NU == 4) || (sub < NU);        // this lane owns an input row
     const int usub = urow ? sub : 0;
     const uint32_t tbase = s_tmem_base + (static_cast<uint32_t>((warp & 3) * 32) << 16) +
-                           static_cast<uint32_t>((warp >> 2) * QTmemCols<NX, PI>::value);
-    double* wbase = smem + qp.off_warp0 + static_cast<size_t>(warp) * qp.warp_stride;
-    double* s_yz = wbase;                             // [N-1][32 lanes][2] : (y, z) of the lane's input row
-    double* s_rt = s_yz + (N - 1) * 64;               // [N-1][2 halves][8 inst][2] : r_i (after a forward sweep) / t_i (after a
+                           static_cast<uint32_t>((warp >> 2) * QTmemCols<T, NX, PI>::value);
+    T* wbase = smem + qp.off_warp0 + static_cast<size_t>(warp) * qp.warp_stride;
+    T* s_yz = wbase;                             // [N-1][32 lanes][2] : (y, z) of the lane's input row
+    T* s_rt = s_yz + (N - 1) * 64;               // [N-1][2 halves][8 inst][2] : r_i (after a forward sweep) / t_i (after a
                                                       // backward sweep); rows (0,1) and (2,3) of the 8 instances are each 128
                                                       // contiguous bytes, so the 4-vector comes back in two conflict-free LDS.128
-    double* s_bc = s_rt + (N - 1) * 32;               // 2 x 8 x XP broadcast slots
-    double* my_rt = s_rt + (sub >> 1) * 16 + inst * 2 + (sub & 1);   // + i * 32 : own row
+    T* s_bc = s_rt + (N - 1) * 32;               // 2 x 8 x XP broadcast slots
+    T* my_rt = s_rt + (sub >> 1) * 16 + inst * 2 + (sub & 1);   // + i * 32 : own row
 
     // 32-bit shared addresses of everything the sweeps touch (byte strides per knot point in the comments)
-    const uint32_t a_yz = sa(s_yz) + lane * 16;                               // + i * 512
-    const uint32_t a_rt4 = sa(s_rt) + inst * 16;                              // + i * 256 ; rows 2,3: + 128
-    const uint32_t a_myrt = sa(my_rt);                                        // + i * 256
-    const uint32_t a_slotA = sa(s_bc) + inst * XP * 8;
-    const uint32_t a_slot_sum = 2 * a_slotA + kQInst * XP * 8;                       // slot B = sum - slot A
-    const uint32_t a_ub = sa(s_ub) + usub * 16;                               // + i * NU * 16
-    const uint32_t a_xb = sa(s_xb) + sub * 16;                                // + i * NX * 16 ; row r: + r * 64
+    const uint32_t a_yz = sa(s_yz) + lane * 2 * S;                            // + i * 64 S
+    const uint32_t a_rt4 = sa(s_rt) + inst * 2 * S;                           // + i * 32 S ; rows 2,3: + 16 S
+    const uint32_t a_myrt = sa(my_rt);                                        // + i * 32 S
+    const uint32_t a_slotA = sa(s_bc) + inst * XP * S;
+    const uint32_t a_slot_sum = 2 * a_slotA + kQInst * XP * S;                       // slot B = sum - slot A
+    const uint32_t a_ub = sa(s_ub) + usub * 2 * S;                            // + i * NU * 2 S
+    const uint32_t a_xb = sa(s_xb) + sub * 2 * S;                             // + i * NX * 2 S ; row r: + r * 8 S
     const uint32_t a_sc = sa(sc);
     // B rows / Quu_inv row read every knot point: the shared staging, or (PI) the lane's private slot of 18 doubles
     // (9 16-byte chunks: conflict-free LDS.128): [B row r = 0..RX-1 (NU each)] [Quu_inv row]
-    constexpr int MBS = PI ? NU * 8 : 4 * NU * 8;                                    // bytes between the lane's B rows
-    double* s_pi = wbase + qp.off_pi + lane * 18;
-    const uint32_t a_Mb = PI ? sa(s_pi) : a_sc + (CL::B_rm + sub * NU) * 8;   // row r: + r * MBS
-    const uint32_t a_Mq = PI ? sa(s_pi) + RX * NU * 8 : a_sc + (CL::Quu_rm + usub * NU) * 8;
-    const double* scl = sc;                           // constants of the lane's instance: shared staging, or (PI) its block + 2 sub
+    constexpr int MBS = PI ? NU * S : 4 * NU * S;                                    // bytes between the lane's B rows
+    T* s_pi = wbase + qp.off_pi + lane * 18;
+    const uint32_t a_Mb = PI ? sa(s_pi) : a_sc + (CL::B_rm + sub * NU) * S;   // row r: + r * MBS
+    const uint32_t a_Mq = PI ? sa(s_pi) + RX * NU * S : a_sc + (CL::Quu_rm + usub * NU) * S;
+    const T* scl = sc;                           // constants of the lane's instance: shared staging, or (PI) its block + 2 sub
     // element of the constants: offset `so` in the shared staging (QConst), element `li` of the lane's array (QLane)
-    auto cst = [&](int so, int li) -> const double* { return PI ? scl + PL::at(li, 0) : scl + so; };
-    const uint32_t a_cq = sa(s_cq) + sub * 8;                                 // + i * NX * 8 ; row r: + r * 32
-    const uint32_t a_cr = sa(s_cr) + usub * 8;                                // + i * NU * 8
+    auto cst = [&](int so, int li) -> const T* { return PI ? scl + PL::at(li, 0) : scl + so; };
+    const uint32_t a_cq = sa(s_cq) + sub * S;                                 // + i * NX * S ; row r: + r * 4 S
+    const uint32_t a_cr = sa(s_cr) + usub * S;                                // + i * NU * S
     uint32_t a_slot = a_slotA;
 
-    double fr_BPf = 0.0, fr_Rd = 0.0;
-    double fr_f[RX], fr_APf[RX], fr_Qd[RX];
+    T fr_BPf = T(0), fr_Rd = T(0);
+    T fr_f[RX], fr_APf[RX], fr_Qd[RX];
 #pragma unroll
-    for (int r = 0; r < RX; ++r) { fr_f[r] = 0.0; fr_APf[r] = 0.0; fr_Qd[r] = 0.0; }
+    for (int r = 0; r < RX; ++r) { fr_f[r] = T(0); fr_APf[r] = T(0); fr_Qd[r] = T(0); }
     if (!PI) {
-        fr_BPf = urow ? sc[CL::BPf + usub] : 0.0;
-        fr_Rd = urow ? sc[CL::Rd + usub] : 0.0;
+        fr_BPf = urow ? sc[CL::BPf + usub] : T(0);
+        fr_Rd = urow ? sc[CL::Rd + usub] : T(0);
 #pragma unroll
         for (int r = 0; r < RX; ++r) { fr_f[r] = sc[CL::f + r * 4 + sub]; fr_APf[r] = sc[CL::APf + r * 4 + sub]; fr_Qd[r] = sc[CL::Qd + r * 4 + sub]; }
     }
@@ -243,15 +252,16 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     // ---------------- per-lane instance state
     int b = 0, iter = 0, status = 1;
     bool valid = false, first = true, fin = true;     // fin = true: the sub-warp wants a (new) instance
-    double x0r[RX], p_term[RX];
+    T x0r[RX], p_term[RX];
 #pragma unroll
-    for (int r = 0; r < RX; ++r) { x0r[r] = 0.0; p_term[r] = 0.0; }
+    for (int r = 0; r < RX; ++r) { x0r[r] = T(0); p_term[r] = T(0); }
     // carried state of an instance: one contiguous block (instance-major):
     //   knot i < N    : + 3 NX i : g(NX), v(NX), q(NX)
     //   knot i < N - 1: IB + 3 NU i : y(NU), z(NU), r(NU)          PB: terminal p (NX)
     const int IB = 3 * NX * N, PB = IB + 3 * NU * (N - 1);
-    double* sblk = bv.state_im + sub;                 // block of the lane's instance, + sub
-    const double* xref_g = nullptr;                   // REFS == 2 only
+    T* const state_im = reinterpret_cast<T*>(bv.state_im);
+    T* sblk = state_im + sub;                    // block of the lane's instance, + sub
+    const double* xref_g = nullptr;              // REFS == 2 only
     const double* uref_g = nullptr;
     // fused closed loop (ROLL): MPC step of the lane's instance; cont = the instance carries on from its previous
     // step with its state on chip; fix = that step converged, so the carried previous slacks are the lagging copies
@@ -274,21 +284,21 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 if (qp.status_out) qp.status_out[o] = status;
                 if (qp.iters_out) qp.iters_out[o] = iter;
             }
-            double zz0 = 0.0;
+            T zz0 = T(0);
             if (urow) zz0 = s_yz[lane * 2 + 1];           // znew of knot 0, own input row
-            double xs[NX], u0[NU];
+            T xs[NX], u0[NU];
 #pragma unroll
             for (int k = 0; k < NX; ++k) xs[k] = shfl_dq(x0r[k / 4], (k % 4) * kQInst + inst);
 #pragma unroll
             for (int k = 0; k < NU; ++k) u0[k] = shfl_dq(zz0, k * kQInst + inst);
 #pragma unroll
             for (int r = 0; r < RX; ++r) {
-                double s1 = 0.0, s2 = 0.0;
+                T s1 = T(0), s2 = T(0);
 #pragma unroll
-                for (int k = 0; k < NX; ++k) s1 = fma(*cst(CL::A_rm + (r * 4 + sub) * NX + k, PL::A + r * NX + k), xs[k], s1);
+                for (int k = 0; k < NX; ++k) s1 = R::fma(*cst(CL::A_rm + (r * 4 + sub) * NX + k, PL::A + r * NX + k), xs[k], s1);
 #pragma unroll
-                for (int k = 0; k < NU; ++k) s2 = fma(*cst(CL::B_rm + (r * 4 + sub) * NU + k, PL::B_rm + r * NU + k), u0[k], s2);
-                const double xn = dadd(dadd(s1, s2), fr_f[r]);
+                for (int k = 0; k < NU; ++k) s2 = R::fma(*cst(CL::B_rm + (r * 4 + sub) * NU + k, PL::B_rm + r * NU + k), u0[k], s2);
+                const T xn = R::add(R::add(s1, s2), fr_f[r]);
                 if (tr) x0r[r] = xn;
             }
             if (tr) {
@@ -299,7 +309,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                     if (REFS == 2 && qp.slide && xref_g) xref_g += NX;
                 } else {
 #pragma unroll
-                    for (int r = 0; r < RX; ++r) qp.x0_rw[static_cast<size_t>(b) * NX + r * 4 + sub] = x0r[r];
+                    for (int r = 0; r < RX; ++r) qp.x0_rw[static_cast<size_t>(b) * NX + r * 4 + sub] = static_cast<double>(x0r[r]);
                 }
             }
         }
@@ -314,14 +324,14 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             const bool wr = fin && valid;                 // results to write
             const bool unconv = (status != 0);
             const size_t bb = wr ? static_cast<size_t>(b) : 0;
-            double* const ob = sblk;                      // block of the finished instance (+ sub)
+            T* const ob = sblk;                      // block of the finished instance (+ sub)
             if (wr && urow) {
                 double* Us = bv.Usol + bb * nuN + sub;
-                double* ou = ob + IB;                     // knot i: + 3 NU i ; y +0, z +NU, r +2 NU
+                T* ou = ob + IB;                     // knot i: + 3 NU i ; y +0, z +NU, r +2 NU
                 for (int i = 0; i < N - 1; ++i) {
-                    double yy, zz;
+                    T yy, zz;
                     ld2(s_yz + (i * 32 + lane) * 2, yy, zz);
-                    *Us = zz;                                     // solution = znew of the last iteration (admm.cpp:371,387)
+                    *Us = static_cast<double>(zz);                // solution = znew of the last iteration (admm.cpp:371,387)
                     ou[0] = yy;
                     if (unconv) ou[NU] = zz;                      // z = znew happened (admm.cpp:380); else the lagging copy is there
                     ou[2 * NU] = my_rt[i * 32];                   // r as update_linear_cost left it (admm.cpp:228-233)
@@ -340,19 +350,19 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             const bool nvalid = fin && nb < bv.B;
             const size_t nbb = nvalid ? static_cast<size_t>(nb) : 0;
             const bool warm = !COLD && nvalid && !(ROLL && qp.cold_install);
-            double* const nblk = bv.state_im + nbb * static_cast<size_t>(bv.state_im_stride) + sub;
+            T* const nblk = state_im + nbb * static_cast<size_t>(bv.state_im_stride) + sub;
 
             double* Xs = bv.Xsol + bb * nxN + sub;
             const double* xr_old = ROLL ? xref_g : ((REFS == 2 && bv.Xref) ? bv.Xref + bb * bv.xref_stride + sub : nullptr);
-            double* op = ob;                              // knot i of the old / new instance: + 3 NX i ; g +0, v +NX, q +2 NX
-            const double* np = nblk;
+            T* op = ob;                              // knot i of the old / new instance: + 3 NX i ; g +0, v +NX, q +2 NX
+            const T* np = nblk;
             const bool wr_v = wr && unconv;
             for (int i = 0; i < N; ++i) {
                 uint32_t w[W];
                 tm_load<W>(tbase + i * W, w);
-                double gn[RX], vn[RX];
+                T gn[RX], vn[RX];
 #pragma unroll
-                for (int r = 0; r < RX; ++r) { gn[r] = 0.0; vn[r] = 0.0; }
+                for (int r = 0; r < RX; ++r) { gn[r] = T(0); vn[r] = T(0); }
                 if (warm) {
 #pragma unroll
                     for (int r = 0; r < RX; ++r) { gn[r] = np[r * 4]; vn[r] = np[NX + r * 4]; }
@@ -362,29 +372,29 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
                     // branch-free: every lane forms the values, the stores are predicated
-                    const double gg = mk_double(w[2 * r], w[2 * r + 1]);
-                    const double vv = mk_double(w[2 * (RX + r)], w[2 * (RX + r) + 1]);
-                    stg_if(Xs + r * 4, vv, wr);                   // solution = vnew of the last iteration (admm.cpp:370,386)
+                    const T gg = tm_get(w, r, T());
+                    const T vv = tm_get(w, RX + r, T());
+                    stg_if(Xs + r * 4, static_cast<double>(vv), wr);   // solution = vnew of the last iteration (admm.cpp:370,386)
                     stg_if(op + r * 4, gg, wr);
                     stg_if(op + NX + r * 4, vv, wr_v);            // v = vnew happened (admm.cpp:379); else the lagging copy is there
-                    double q;                                     // q as update_linear_cost left it (admm.cpp:218-219)
-                    if (REFS == 0) q = dmul(nrho, dsub(vv, gg));
+                    T q;                                     // q as update_linear_cost left it (admm.cpp:218-219)
+                    if (REFS == 0) q = R::mul(nrho, R::sub(vv, gg));
                     else {
-                        const double cq = (REFS == 1) ? s_cq[(i < N - 1 ? i : 0) * NX + r * 4 + sub]
-                                                      : -dmul((xr_old && wr_q) ? __ldg(xr_old + i * NX + r * 4) : 0.0, fr_Qd[r]);
-                        q = dsub(cq, dmul(rho, dsub(vv, gg)));
+                        const T cq = (REFS == 1) ? s_cq[(i < N - 1 ? i : 0) * NX + r * 4 + sub]
+                                                      : -R::mul(static_cast<T>((xr_old && wr_q) ? __ldg(xr_old + i * NX + r * 4) : 0.0), fr_Qd[r]);
+                        q = R::sub(cq, R::mul(rho, R::sub(vv, gg)));
                     }
                     stg_if(op + 2 * NX + r * 4, q, wr_q);
-                    w[2 * r] = fin ? lo32(gn[r]) : w[2 * r]; w[2 * r + 1] = fin ? hi32(gn[r]) : w[2 * r + 1];
-                    w[2 * (RX + r)] = fin ? lo32(vn[r]) : w[2 * (RX + r)]; w[2 * (RX + r) + 1] = fin ? hi32(vn[r]) : w[2 * (RX + r) + 1];
+                    tm_put_if(w, r, gn[r], fin);
+                    tm_put_if(w, RX + r, vn[r], fin);
                 }
                 tm_store<W>(tbase + i * W, w);
                 Xs += NX; op += 3 * NX; np += 3 * NX;
             }
             if (fin) {
-                const double* nu_p = nblk + IB;
+                const T* nu_p = nblk + IB;
                 for (int i = 0; i < N - 1; ++i) {
-                    double yy = 0.0, zz = 0.0, rr = 0.0;
+                    T yy = T(0), zz = T(0), rr = T(0);
                     if (warm && urow) { yy = nu_p[0]; zz = nu_p[NU]; rr = nu_p[2 * NU]; }
                     st2(s_yz + (i * 32 + lane) * 2, yy, zz);
                     my_rt[i * 32] = rr;
@@ -392,17 +402,17 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 }
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
-                    x0r[r] = nvalid ? bv.x0[nbb * NX + r * 4 + sub] : 0.0;
-                    p_term[r] = warm ? nblk[PB + r * 4] : 0.0;
+                    x0r[r] = nvalid ? static_cast<T>(bv.x0[nbb * NX + r * 4 + sub]) : T(0);
+                    p_term[r] = warm ? nblk[PB + r * 4] : T(0);
                 }
                 b = nvalid ? nb : 0;
                 sblk = nblk;
                 valid = nvalid; iter = 0; first = true; status = 1; fin = false;
                 step = 0; cont = false; fix = false;
                 if (PI) {                                 // constants of the new instance: registers + the lane's B / Quu_inv slot
-                    scl = qp.pi_blocks + nbb * PL::size + 2 * sub;
-                    fr_BPf = urow ? *cst(0, PL::BPf) : 0.0;
-                    fr_Rd = urow ? *cst(0, PL::Rd) : 0.0;
+                    scl = reinterpret_cast<const T*>(qp.pi_blocks) + nbb * PL::size + 2 * sub;
+                    fr_BPf = urow ? *cst(0, PL::BPf) : T(0);
+                    fr_Rd = urow ? *cst(0, PL::Rd) : T(0);
 #pragma unroll
                     for (int r = 0; r < RX; ++r) {
                         fr_f[r] = *cst(0, PL::f + r); fr_APf[r] = *cst(0, PL::APf + r); fr_Qd[r] = *cst(0, PL::Qd + r);
@@ -429,7 +439,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
         // (reference admm.cpp:13-20; d_i = Quu_inv t_i is formed where it is consumed)
         // =====================================================================================================
         {
-            double Mab[RX][NX], Mkt[RX][NU], Mbt[NX];
+            T Mab[RX][NX], Mkt[RX][NU], Mbt[NX];
 #pragma unroll
             for (int r = 0; r < RX; ++r) {
 #pragma unroll
@@ -438,79 +448,79 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 for (int k = 0; k < NU; ++k) Mkt[r][k] = *cst(CL::Kinf_cm + (r * 4 + sub) * NU + k, PL::Kinf_cm + r * NU + k);
             }
 #pragma unroll
-            for (int k = 0; k < NX; ++k) Mbt[k] = urow ? *cst(CL::B_cm + usub * NX + k, PL::B_cm + k) : 0.0;
+            for (int k = 0; k < NX; ++k) Mbt[k] = urow ? *cst(CL::B_cm + usub * NX + k, PL::B_cm + k) : T(0);
 
-            double p[RX];
+            T p[RX];
 #pragma unroll
             for (int r = 0; r < RX; ++r) p[r] = p_term[r];
 
             uint32_t w[W];
             tm_load<W>(tbase + (N - 2) * W, w);
-            double qcar[RX];                              // carried q of the first sweep of a warm-started solve
+            T qcar[RX];                              // carried q of the first sweep of a warm-started solve
 #pragma unroll
-            for (int r = 0; r < RX; ++r) qcar[r] = 0.0;
+            for (int r = 0; r < RX; ++r) qcar[r] = T(0);
             const bool ldq = !COLD && first && valid && !(ROLL && (cont || qp.cold_install));
             // ROLL, first sweep of a solve that continues on chip: q is what update_linear_cost left at the end of the
             // previous step, i.e. built from the slacks and duals in Tensor Memory and the PREVIOUS reference window
             const bool usecar = first && !(ROLL && cont);
             const double* xref_b = (ROLL && REFS == 2 && cont && first && qp.slide && xref_g) ? xref_g - NX : xref_g;
-            const double* qp_g = sblk + 2 * NX + (N - 2) * 3 * NX;          // q of knot N-2; row r: + 4 r
+            const T* qp_g = sblk + 2 * NX + (N - 2) * 3 * NX;          // q of knot N-2; row r: + 4 r
             if (ldq) {
 #pragma unroll
                 for (int r = 0; r < RX; ++r) qcar[r] = qp_g[r * 4];
             }
-            double t_def = 0.0;
-            uint32_t o_rt = (N - 2) * 256;                // byte offset of knot i in the r/t array
-            uint32_t o_cq = (N - 2) * NX * 8;
+            T t_def = T(0);
+            uint32_t o_rt = (N - 2) * 32 * S;                // byte offset of knot i in the r/t array
+            uint32_t o_cq = (N - 2) * NX * S;
 
             for (int i = N - 2; i >= 0; --i) {
-                double cq[RX];
+                T cq[RX];
                 if (REFS == 2) {
 #pragma unroll
-                    for (int r = 0; r < RX; ++r) cq[r] = -dmul(xref_b ? __ldg(xref_b + i * NX + r * 4) : 0.0, fr_Qd[r]);
+                    for (int r = 0; r < RX; ++r) cq[r] = -R::mul(static_cast<T>(xref_b ? __ldg(xref_b + i * NX + r * 4) : 0.0), fr_Qd[r]);
                 }
                 // all-gather p_{i+1} among the 4 lanes of the instance
-                double pb[NX];
+                T pb[NX];
                 if (NX <= TMPC_BWD_SHFL_MAX_NX) {
 #pragma unroll
                 for (int k = 0; k < NX; ++k) pb[k] = shfl_dq(p[k / 4], (k % 4) * kQInst + inst);
                 __syncwarp();
-                if (i < N - 2 && urow) sts1<256>(a_myrt + o_rt, t_def);    // t_{i+1}: every lane has read r_{i+1} by now
+                if (i < N - 2 && urow) sts1<32 * S>(a_myrt + o_rt, t_def);    // t_{i+1}: every lane has read r_{i+1} by now
                 } else {
                 a_slot = a_slot_sum - a_slot;
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
-                    if (r == 0) sts1<0>(a_slot + sub * 8, p[r]);
-                    else if (r == 1) sts1<32>(a_slot + sub * 8, p[r]);
-                    else sts1<64>(a_slot + sub * 8, p[r]);
+                    if (r == 0) sts1<0>(a_slot + sub * S, p[r]);
+                    else if (r == 1) sts1<4 * S>(a_slot + sub * S, p[r]);
+                    else sts1<8 * S>(a_slot + sub * S, p[r]);
                 }
                 __syncwarp();
-                if (i < N - 2 && urow) sts1<256>(a_myrt + o_rt, t_def);    // t_{i+1}: every lane has read r_{i+1} by now
+                if (i < N - 2 && urow) sts1<32 * S>(a_myrt + o_rt, t_def);    // t_{i+1}: every lane has read r_{i+1} by now
                 lds2<0>(a_slot, pb[0], pb[1]);
-                if (NX > 2) lds2<16>(a_slot, pb[2], pb[3]);
-                if (NX > 4) { lds2<32>(a_slot, pb[4], pb[5]); lds2<48>(a_slot, pb[6], pb[7]); }
-                if (NX > 8) { lds2<64>(a_slot, pb[8], pb[9]); lds2<80>(a_slot, pb[10], pb[11]); }
+                if (NX > 2) lds2<2 * S>(a_slot, pb[2], pb[3]);
+                if (NX > 4) { lds2<4 * S>(a_slot, pb[4], pb[5]); lds2<6 * S>(a_slot, pb[6], pb[7]); }
+                if (NX > 8) { lds2<8 * S>(a_slot, pb[8], pb[9]); lds2<10 * S>(a_slot, pb[10], pb[11]); }
                 }
-                double rr[4];
+                T rr[4];
                 lds2<0>(a_rt4 + o_rt, rr[0], rr[1]);
-                lds2<128>(a_rt4 + o_rt, rr[2], rr[3]);
-                const double r_own = lds1<0>(a_myrt + o_rt);
-                double cqs[RX];
+                lds2<16 * S>(a_rt4 + o_rt, rr[2], rr[3]);
+                const T r_own = lds1t<0, T>(a_myrt + o_rt);
+                T cqs[RX];
                 if (REFS == 1) {
 #pragma unroll
-                    for (int r = 0; r < RX; ++r) cqs[r] = (r == 0) ? lds1<0>(a_cq + o_cq) : (r == 1) ? lds1<32>(a_cq + o_cq) : lds1<64>(a_cq + o_cq);
+                    for (int r = 0; r < RX; ++r) cqs[r] = (r == 0) ? lds1t<0, T>(a_cq + o_cq) : (r == 1) ? lds1t<4 * S, T>(a_cq + o_cq) : lds1t<8 * S, T>(a_cq + o_cq);
                 }
 
                 // q_i (own rows): carried on the first sweep of a solve, otherwise rebuilt from slacks and duals
                 tm_wait_ld<W>(w);
-                double q_own[RX];
+                T q_own[RX];
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
-                    const double gg = mk_double(w[2 * r], w[2 * r + 1]);
-                    const double vv = mk_double(w[2 * (RX + r)], w[2 * (RX + r) + 1]);
-                    double q;
-                    if (REFS == 0) q = dmul(nrho, dsub(vv, gg));
-                    else q = dsub(REFS == 1 ? cqs[r] : cq[r], dmul(rho, dsub(vv, gg)));
+                    const T gg = tm_get(w, r, T());
+                    const T vv = tm_get(w, RX + r, T());
+                    T q;
+                    if (REFS == 0) q = R::mul(nrho, R::sub(vv, gg));
+                    else q = R::sub(REFS == 1 ? cqs[r] : cq[r], R::mul(rho, R::sub(vv, gg)));
                     q_own[r] = usecar ? qcar[r] : q;
                 }
                 if (i > 0) {
@@ -523,26 +533,26 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 }
 
                 // own row of B' p_{i+1} and the lane's rows of AmBKt p_{i+1}: RX + 1 independent chains, interleaved
-                double s = 0.0, s1[RX];
+                T s = T(0), s1[RX];
 #pragma unroll
-                for (int r = 0; r < RX; ++r) s1[r] = 0.0;
+                for (int r = 0; r < RX; ++r) s1[r] = T(0);
 #pragma unroll
                 for (int k = 0; k < NX; ++k) {
-                    s = fma(Mbt[k], pb[k], s);
+                    s = R::fma(Mbt[k], pb[k], s);
 #pragma unroll
-                    for (int r = 0; r < RX; ++r) s1[r] = fma(Mab[r][k], pb[k], s1[r]);
+                    for (int r = 0; r < RX; ++r) s1[r] = R::fma(Mab[r][k], pb[k], s1[r]);
                 }
-                t_def = dadd(dadd(s, r_own), fr_BPf);     // t_i = B' p_{i+1} + r_i + BPf
+                t_def = R::add(R::add(s, r_own), fr_BPf);     // t_i = B' p_{i+1} + r_i + BPf
 
                 // p_i = q_i + AmBKt p_{i+1} - Kinf' r_i + APf
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
-                    double s2 = 0.0;
+                    T s2 = T(0);
 #pragma unroll
-                    for (int k = 0; k < NU; ++k) s2 = fma(Mkt[r][k], rr[k], s2);
-                    p[r] = dadd(dsub(dadd(q_own[r], s1[r]), s2), fr_APf[r]);
+                    for (int k = 0; k < NU; ++k) s2 = R::fma(Mkt[r][k], rr[k], s2);
+                    p[r] = R::add(R::sub(R::add(q_own[r], s1[r]), s2), fr_APf[r]);
                 }
-                o_rt -= 256; o_cq -= NX * 8;
+                o_rt -= 32 * S; o_cq -= NX * S;
             }
             __syncwarp();
             if (urow) sts1<0>(a_myrt, t_def);
@@ -552,24 +562,23 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
         // the last sweep parked in its block (admm.cpp:375 returns before :379-380).  The backward sweep above
         // was the last reader of vnew; put v_old / z_old in place for the dual residual of this solve's first iteration.
         if (ROLL && __any_sync(kAll, fix)) {
-            const double* vl = sblk + NX;                 // v of knot i: + 3 NX i ; row r: + 4 r
+            const T* vl = sblk + NX;                 // v of knot i: + 3 NX i ; row r: + 4 r
             for (int i = 0; i < N; ++i) {
                 uint32_t w[W];
                 tm_load<W>(tbase + i * W, w);
-                double vo[RX];
+                T vo[RX];
 #pragma unroll
-                for (int r = 0; r < RX; ++r) vo[r] = fix ? vl[r * 4] : 0.0;
+                for (int r = 0; r < RX; ++r) vo[r] = fix ? vl[r * 4] : T(0);
                 tm_wait_ld<W>(w);
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
-                    w[2 * (RX + r)] = fix ? lo32(vo[r]) : w[2 * (RX + r)];
-                    w[2 * (RX + r) + 1] = fix ? hi32(vo[r]) : w[2 * (RX + r) + 1];
+                    tm_put_if(w, RX + r, vo[r], fix);
                 }
                 tm_store<W>(tbase + i * W, w);
                 vl += 3 * NX;
             }
             if (fix && urow) {
-                const double* zl = sblk + IB + NU;        // z of knot i: + 3 NU i
+                const T* zl = sblk + IB + NU;        // z of knot i: + 3 NU i
                 for (int i = 0; i < N - 1; ++i) { s_yz[(i * 32 + lane) * 2 + 1] = *zl; zl += 3 * NU; }
             }
             fix = false;
@@ -586,19 +595,19 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             // register-resident: the lane's rows of A and Kinf (48 doubles).  B and Quu_inv rows are re-read from
             // shared memory every knot point (8 broadcast LDS.128 off the critical path): keeping them in registers
             // too pushed the sweep over the register file and the compiler into rematerialising addresses.
-            double Ma[RX][NX], Mk[NX];
+            T Ma[RX][NX], Mk[NX];
 #pragma unroll
             for (int r = 0; r < RX; ++r) {
 #pragma unroll
                 for (int k = 0; k < NX; k += 2) ld2(cst(CL::A_rm + (r * 4 + sub) * NX + k, PL::A + r * NX + k), Ma[r][k], Ma[r][k + 1]);
             }
 #pragma unroll
-            for (int k = 0; k < NX; ++k) Mk[k] = urow ? *cst(CL::Kinf_rm + usub * NX + k, PL::Kinf_rm + k) : 0.0;
+            for (int k = 0; k < NX; ++k) Mk[k] = urow ? *cst(CL::Kinf_rm + usub * NX + k, PL::Kinf_rm + k) : T(0);
             // rows of B and of Quu_inv: registers where the variant has room for them (CREG), else re-read from
             // shared memory at every knot point.  Shared-memory bandwidth (4 bytes per lane per clock) is what the
             // two warps of a scheduler and their six neighbours contend for: 128 of the 336 bytes a lane reads per
             // forward knot point are these constants.
-            double Mb[CREG ? RX : 1][NU], Mq[NU];
+            T Mb[CREG ? RX : 1][NU], Mq[NU];
             if (CREG) {
 #pragma unroll
                 for (int r = 0; r < RX; ++r)
@@ -608,7 +617,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 for (int k = 0; k < NU; ++k) Mq[k] = *cst(CL::Quu_rm + usub * NU + k, PL::Quu + k);
             }
 
-            double x[RX];
+            T x[RX];
 #pragma unroll
             for (int r = 0; r < RX; ++r) x[r] = x0r[r];
             uint32_t w[W];
@@ -617,10 +626,10 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             // (admm.cpp:375 returns before :379-380): while this sweep can still end in convergence the lane parks
             // them in the instance's carried-state block in HBM ([pointer + immediate] stores, whole 32-byte sectors)
             const bool lag = valid && ((iter + 1) % st.check_termination == 0);
-            double* vlag = sblk + NX;                                         // v of knot i: + 3 NX i ; row r: + 4 r
-            double* zlag = sblk + IB + NU;                                    // z of knot i: + 3 NU i
-            double r_def = 0.0;
-            double vg[RX];
+            T* vlag = sblk + NX;                                         // v of knot i: + 3 NX i ; row r: + 4 r
+            T* zlag = sblk + IB + NU;                                    // z of knot i: + 3 NU i
+            T r_def = T(0);
+            T vg[RX];
             uint32_t o_xb = 0;                                                // byte offset of knot i in the state-bound table
             uint32_t tcol = tbase;
 
@@ -632,31 +641,31 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             // state column: slack, dual, [residuals]; new (g, v) back to Tensor Memory
             auto state_column = [&](auto chk) {
                 constexpr bool CHK = decltype(chk)::value;
-                double lo[RX], hi[RX];
+                T lo[RX], hi[RX];
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
                     if (r == 0) lds2<0>(a_xb + o_xb, lo[r], hi[r]);
-                    else if (r == 1) lds2<64>(a_xb + o_xb, lo[r], hi[r]);
-                    else lds2<128>(a_xb + o_xb, lo[r], hi[r]);
+                    else if (r == 1) lds2<8 * S>(a_xb + o_xb, lo[r], hi[r]);
+                    else lds2<16 * S>(a_xb + o_xb, lo[r], hi[r]);
                 }
                 tm_wait_ld<W>(w);
                 uint32_t wn[W];
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
-                    const double gold = mk_double(w[2 * r], w[2 * r + 1]);
-                    const double t = dadd(x[r], gold);
-                    const double vnew = clampd(t, lo[r], hi[r]);
-                    const double gnew = dsub(t, vnew);
+                    const T gold = tm_get(w, r, T());
+                    const T t = R::add(x[r], gold);
+                    const T vnew = R::clamp(t, lo[r], hi[r]);
+                    const T gnew = R::sub(t, vnew);
                     if (CHK) {
-                        const double vold = mk_double(w[2 * (RX + r)], w[2 * (RX + r) + 1]);
-                        const bool p1 = fabs(dsub(x[r], vnew)) < qp.pri_thresh;
-                        const bool p2 = fabs(dsub(vold, vnew)) <= qp.dua_thresh;
+                        const T vold = tm_get(w, RX + r, T());
+                        const bool p1 = R::abs(R::sub(x[r], vnew)) < pri_thresh;
+                        const bool p2 = R::abs(R::sub(vold, vnew)) <= dua_thresh;
                         ok = ok & p1 & p2;
                         if (lag & ok) vlag[r * 4] = vold;
                     }
-                    wn[2 * r] = lo32(gnew); wn[2 * r + 1] = hi32(gnew);
-                    wn[2 * (RX + r)] = lo32(vnew); wn[2 * (RX + r) + 1] = hi32(vnew);
-                    vg[r] = dsub(vnew, gnew);
+                    tm_put(wn, r, gnew);
+                    tm_put(wn, RX + r, vnew);
+                    vg[r] = R::sub(vnew, gnew);
                 }
                 tm_store<W>(tcol, wn);
             };
@@ -666,38 +675,38 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             // one non-terminal knot point
             auto knot = [&](auto chk) {
                 constexpr bool CHK = decltype(chk)::value;
-                double cr = 0.0;
-                if (REFS == 2) cr = -dmul(uref_g ? __ldg(uref_g + i * NU) : 0.0, fr_Rd);
+                T cr = T(0);
+                if (REFS == 2) cr = -R::mul(static_cast<T>(uref_g ? __ldg(uref_g + i * NU) : 0.0), fr_Rd);
                 a_slot = a_slot_sum - a_slot;
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
-                    if (r == 0) sts1<0>(a_slot + sub * 8, x[r]);
-                    else if (r == 1) sts1<32>(a_slot + sub * 8, x[r]);
-                    else sts1<64>(a_slot + sub * 8, x[r]);
+                    if (r == 0) sts1<0>(a_slot + sub * S, x[r]);
+                    else if (r == 1) sts1<4 * S>(a_slot + sub * S, x[r]);
+                    else sts1<8 * S>(a_slot + sub * S, x[r]);
                 }
                 __syncwarp();
-                if (i > 0 && urow) sts1<-256>(a_myrt + o_rt, r_def);         // r_{i-1}: every lane has read t_{i-1} by now
-                double xb[NX];
+                if (i > 0 && urow) sts1<-32 * S>(a_myrt + o_rt, r_def);         // r_{i-1}: every lane has read t_{i-1} by now
+                T xb[NX];
                 lds2<0>(a_slot, xb[0], xb[1]);
-                if (NX > 2) lds2<16>(a_slot, xb[2], xb[3]);
-                if (NX > 4) { lds2<32>(a_slot, xb[4], xb[5]); lds2<48>(a_slot, xb[6], xb[7]); }
-                if (NX > 8) { lds2<64>(a_slot, xb[8], xb[9]); lds2<80>(a_slot, xb[10], xb[11]); }
-                double tt[4], mq[4];
+                if (NX > 2) lds2<2 * S>(a_slot, xb[2], xb[3]);
+                if (NX > 4) { lds2<4 * S>(a_slot, xb[4], xb[5]); lds2<6 * S>(a_slot, xb[6], xb[7]); }
+                if (NX > 8) { lds2<8 * S>(a_slot, xb[8], xb[9]); lds2<10 * S>(a_slot, xb[10], xb[11]); }
+                T tt[4], mq[4];
                 lds2<0>(a_rt4 + o_rt, tt[0], tt[1]);
-                lds2<128>(a_rt4 + o_rt, tt[2], tt[3]);
+                lds2<16 * S>(a_rt4 + o_rt, tt[2], tt[3]);
                 if (CREG) {
 #pragma unroll
                     for (int k = 0; k < NU; ++k) mq[k] = Mq[k];
-                } else if (NU == 4) { lds2<0>(a_Mq, mq[0], mq[1]); lds2<16>(a_Mq, mq[2], mq[3]); }
+                } else if (NU == 4) { lds2<0>(a_Mq, mq[0], mq[1]); lds2<2 * S>(a_Mq, mq[2], mq[3]); }
                 else {
 #pragma unroll
                     for (int k = 0; k < NU; ++k) mq[k] = *cst(CL::Quu_rm + usub * NU + k, PL::Quu + k);
                 }
-                double yj = 0.0, zold = 0.0, ulo = 0.0, uhi = 0.0, crs = 0.0;
+                T yj = T(0), zold = T(0), ulo = T(0), uhi = T(0), crs = T(0);
                 if (urow) {
                     lds2<0>(a_yz + o_yz, yj, zold);
                     lds2<0>(a_ub + o_ub, ulo, uhi);
-                    if (REFS == 1) crs = lds1<0>(a_cr + o_cr);
+                    if (REFS == 1) crs = lds1t<0, T>(a_cr + o_cr);
                 }
 
                 state_column(chk);                            // needs only the lane's own x: covers the broadcast round trip
@@ -708,56 +717,56 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
 #endif
 
                 // d_i = Quu_inv t_i ;  Kinf x_i (own row) ;  A x_i (own rows): RX + 2 independent chains, interleaved
-                double d = 0.0;
+                T d = T(0);
 #pragma unroll
-                for (int k = 0; k < NU; ++k) d = fma(mq[k], tt[k], d);
-                double s = 0.0, s1[RX];
+                for (int k = 0; k < NU; ++k) d = R::fma(mq[k], tt[k], d);
+                T s = T(0), s1[RX];
 #pragma unroll
-                for (int r = 0; r < RX; ++r) s1[r] = 0.0;
+                for (int r = 0; r < RX; ++r) s1[r] = T(0);
 #pragma unroll
                 for (int k = 0; k < NX; ++k) {
-                    s = fma(Mk[k], xb[k], s);
+                    s = R::fma(Mk[k], xb[k], s);
 #pragma unroll
-                    for (int r = 0; r < RX; ++r) s1[r] = fma(Ma[r][k], xb[k], s1[r]);
+                    for (int r = 0; r < RX; ++r) s1[r] = R::fma(Ma[r][k], xb[k], s1[r]);
                 }
 
                 SCHED_FENCE();
                 // u_i = -Kinf x_i - d_i, broadcast at once; then input slack, dual, [residuals]
                 // (admm.cpp:28, :87, :97, :187, :259-260)
-                const double u_own = urow ? dsub(-s, d) : 0.0;
-                double ub[NU];
+                const T u_own = urow ? R::sub(-s, d) : T(0);
+                T ub[NU];
 #pragma unroll
                 for (int k = 0; k < NU; ++k) ub[k] = shfl_dq(u_own, k * kQInst + inst);
                 // rows of B for the tail of this knot point: issued now, consumed after the state column
-                double mb[RX][4];
+                T mb[RX][4];
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
                     if (CREG) {
 #pragma unroll
                         for (int k = 0; k < NU; ++k) mb[r][k] = Mb[r][k];
                     } else if (NU == 4) {
-                        if (r == 0) { lds2<0>(a_Mb, mb[r][0], mb[r][1]); lds2<16>(a_Mb, mb[r][2], mb[r][3]); }
-                        else if (r == 1) { lds2<MBS>(a_Mb, mb[r][0], mb[r][1]); lds2<MBS + 16>(a_Mb, mb[r][2], mb[r][3]); }
-                        else { lds2<2 * MBS>(a_Mb, mb[r][0], mb[r][1]); lds2<2 * MBS + 16>(a_Mb, mb[r][2], mb[r][3]); }
+                        if (r == 0) { lds2<0>(a_Mb, mb[r][0], mb[r][1]); lds2<2 * S>(a_Mb, mb[r][2], mb[r][3]); }
+                        else if (r == 1) { lds2<MBS>(a_Mb, mb[r][0], mb[r][1]); lds2<MBS + 2 * S>(a_Mb, mb[r][2], mb[r][3]); }
+                        else { lds2<2 * MBS>(a_Mb, mb[r][0], mb[r][1]); lds2<2 * MBS + 2 * S>(a_Mb, mb[r][2], mb[r][3]); }
                     } else {
 #pragma unroll
                         for (int k = 0; k < NU; ++k) mb[r][k] = *cst(CL::B_rm + (r * 4 + sub) * NU + k, PL::B_rm + r * NU + k);
                     }
                 }
                 if (urow) {
-                    const double t = dadd(u_own, yj);
-                    const double znew = clampd(t, ulo, uhi);
-                    const double ynew = dsub(t, znew);                  // y + u - znew
+                    const T t = R::add(u_own, yj);
+                    const T znew = R::clamp(t, ulo, uhi);
+                    const T ynew = R::sub(t, znew);                  // y + u - znew
                     if (CHK) {
-                        const bool p1 = fabs(dsub(u_own, znew)) < qp.pri_thresh;
-                        const bool p2 = fabs(dsub(zold, znew)) <= qp.dua_thresh;
+                        const bool p1 = R::abs(R::sub(u_own, znew)) < pri_thresh;
+                        const bool p2 = R::abs(R::sub(zold, znew)) <= dua_thresh;
                         ok = ok & p1 & p2;
                         if (lag & ok) *zlag = zold;
                     }
                     sts2<0>(a_yz + o_yz, ynew, znew);
                     // r_i = -(Uref .* Rd) - rho (znew - y)    (admm.cpp:228-229)
-                    if (REFS == 0) r_def = dmul(nrho, dsub(znew, ynew));
-                    else r_def = dsub(REFS == 1 ? crs : cr, dmul(rho, dsub(znew, ynew)));
+                    if (REFS == 0) r_def = R::mul(nrho, R::sub(znew, ynew));
+                    else r_def = R::sub(REFS == 1 ? crs : cr, R::mul(rho, R::sub(znew, ynew)));
                 }
 
 #if TMPC_FENCE_C
@@ -766,13 +775,13 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 // x_{i+1} = A x_i + B u_i + f
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
-                    double s2 = 0.0;
+                    T s2 = T(0);
 #pragma unroll
-                    for (int k = 0; k < NU; ++k) s2 = fma(mb[r][k], ub[k], s2);
-                    x[r] = dadd(dadd(s1[r], s2), fr_f[r]);
+                    for (int k = 0; k < NU; ++k) s2 = R::fma(mb[r][k], ub[k], s2);
+                    x[r] = R::add(R::add(s1[r], s2), fr_f[r]);
                 }
                 vlag += 3 * NX; zlag += 3 * NU;
-                o_rt += 256; o_yz += 512; o_ub += NU * 16; o_cr += NU * 8; o_xb += NX * 16;
+                o_rt += 32 * S; o_yz += 64 * S; o_ub += NU * 2 * S; o_cr += NU * S; o_xb += NX * 2 * S;
             };
 
             bool checking = __any_sync(kAll, lag);            // no instance of the warp can terminate: no tests at all
@@ -788,17 +797,17 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             if (checking) state_column(std::true_type{}); else state_column(std::false_type{});
 #pragma unroll
             for (int r = 0; r < RX; ++r) {
-                if (REFS == 0) p_term[r] = dmul(nrho, vg[r]);
-                else if (REFS == 1) p_term[r] = dsub(s_tq[r * 4 + sub], dmul(rho, vg[r]));
+                if (REFS == 0) p_term[r] = R::mul(nrho, vg[r]);
+                else if (REFS == 1) p_term[r] = R::sub(s_tq[r * 4 + sub], R::mul(rho, vg[r]));
                 else {
-                    double s = 0.0;
-                    if (xref_g) for (int k = 0; k < NX; ++k) s = fma(__ldg(xref_g - sub + (N - 1) * NX + k), *cst(CL::Pinf_cm + (r * 4 + sub) * NX + k, PL::Pinf + r * NX + k), s);
-                    p_term[r] = dsub(-s, dmul(rho, vg[r]));
+                    T s = T(0);
+                    if (xref_g) for (int k = 0; k < NX; ++k) s = R::fma(static_cast<T>(__ldg(xref_g - sub + (N - 1) * NX + k)), *cst(CL::Pinf_cm + (r * 4 + sub) * NX + k, PL::Pinf + r * NX + k), s);
+                    p_term[r] = R::sub(-s, R::mul(rho, vg[r]));
                 }
             }
             tm_wait_st();
             __syncwarp();
-            if (urow) sts1<-256>(a_myrt + o_rt, r_def);       // r_{N-2}
+            if (urow) sts1<-32 * S>(a_myrt + o_rt, r_def);       // r_{N-2}
         }
 
         // =====================================================================================================
@@ -820,22 +829,24 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
 }
 
 // Largest a >= 0 with fl(rho * a) < tol, so that  rho * max|.| < tol  <=>  every |.| <= a.
-double dual_threshold_q(double rho, double tol) {
-    if (!(tol > 0.0) || !(rho > 0.0)) return -1.0;
-    double a = tol / rho;
-    while (rho * a < tol) a = std::nextafter(a, INFINITY);
-    while (!(rho * a < tol)) a = std::nextafter(a, -INFINITY);
+template <class T>
+T dual_threshold_q(T rho, T tol) {
+    if (!(tol > T(0)) || !(rho > T(0))) return T(-1);
+    auto prod = [&](T a) { volatile T p = rho * a; return static_cast<T>(p); };      // rounded to T, no excess precision
+    T a = tol / rho;
+    while (prod(a) < tol) a = std::nextafter(a, static_cast<T>(INFINITY));
+    while (!(prod(a) < tol)) a = std::nextafter(a, static_cast<T>(-INFINITY));
     return a;
 }
 
 struct QPlan { size_t smem_bytes; QuadParams qp; };
 
-template <int NX, int NU>
+template <class T, int NX, int NU>
 bool make_qplan(int N, int refs, QPlan& pl, bool pi = false) {
     constexpr int XP = QPad<NX>::value;
-    constexpr int W = 4 * (NX / 4);
-    const int warps = pi ? QWarps<NX, true>::value : QWarps<NX, false>::value;
-    if (N < 2 || N * W > (pi ? QTmemCols<NX, true>::value : QTmemCols<NX, false>::value)) return false;   // g, v of a lane must fit the warp's TMEM columns
+    constexpr int W = 2 * (NX / 4) * (sizeof(T) / 4);
+    const int warps = pi ? QWarps<T, NX, true>::value : QWarps<T, NX, false>::value;
+    if (N < 2 || N * W > (pi ? QTmemCols<T, NX, true>::value : QTmemCols<T, NX, false>::value)) return false;   // g, v of a lane must fit the warp's TMEM columns
     const int nxN = NX * N, nuN = NU * (N - 1);
     QuadParams qp{};
     int off = 0;
@@ -849,7 +860,7 @@ bool make_qplan(int N, int refs, QPlan& pl, bool pi = false) {
     qp.off_pi = per_warp;
     if (pi) per_warp += 32 * 18;                                   // the lanes' private B / Quu_inv row slots
     qp.warp_stride = per_warp;
-    pl.smem_bytes = (static_cast<size_t>(off) + static_cast<size_t>(per_warp) * warps) * sizeof(double);
+    pl.smem_bytes = (static_cast<size_t>(off) + static_cast<size_t>(per_warp) * warps) * sizeof(T);
     pl.qp = qp;
     return pl.smem_bytes <= 227 * 1024;
 }
@@ -860,38 +871,38 @@ int refs_mode(const BatchView& bv) {
     return (xs && us) ? 1 : 2;
 }
 
-template <int NX, int NU, bool COLD, int REFS, bool ROLL = false, bool PI = false>
+template <class T, int NX, int NU, bool COLD, int REFS, bool ROLL = false, bool PI = false>
 cudaError_t launch_q(const BatchView& bv, const AdmmSettings& st, const QPlan& pl, int num_sms, cudaStream_t stream) {
-    auto kern = admm_tmem_kernel<NX, NU, COLD, REFS, ROLL, PI>;
+    auto kern = admm_tmem_kernel<T, NX, NU, COLD, REFS, ROLL, PI>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(pl.smem_bytes));
     if (e != cudaSuccess) return e;
-    const int per_cta = QWarps<NX, PI>::value * kQInst;
+    const int per_cta = QWarps<T, NX, PI>::value * kQInst;
     int grid = (bv.B + per_cta - 1) / per_cta;
     if (grid > num_sms) grid = num_sms;            // persistent: one CTA per SM, sub-warps pull instances from the queue
-    kern<<<grid, QWarps<NX, PI>::value * 32, pl.smem_bytes, stream>>>(bv, st, pl.qp);
+    kern<<<grid, QWarps<T, NX, PI>::value * 32, pl.smem_bytes, stream>>>(bv, st, pl.qp);
     return cudaGetLastError();
 }
 
-template <int NX, int NU>
+template <class T, int NX, int NU>
 cudaError_t launch_shape(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms,
                          cudaStream_t stream, const int* order) {
     QPlan pl;
     const int refs = refs_mode(bv);
-    if (!make_qplan<NX, NU>(bv.N, refs, pl)) return cudaErrorInvalidConfiguration;
+    if (!make_qplan<T, NX, NU>(bv.N, refs, pl)) return cudaErrorInvalidConfiguration;
     pl.qp.counter = counter;
     pl.qp.order = order;
-    pl.qp.pri_thresh = st.abs_pri_tol;
-    pl.qp.dua_thresh = dual_threshold_q(bv.rho, st.abs_dua_tol);
+    pl.qp.pri_thresh = static_cast<T>(st.abs_pri_tol);                                   // types.hpp:64-65: tolerances are tinytype
+    pl.qp.dua_thresh = dual_threshold_q<T>(static_cast<T>(bv.rho), static_cast<T>(st.abs_dua_tol));
     cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(int), stream);
     if (e != cudaSuccess) return e;
     if (cold) {
-        if (refs == 0) return launch_q<NX, NU, true, 0>(bv, st, pl, num_sms, stream);
-        if (refs == 1) return launch_q<NX, NU, true, 1>(bv, st, pl, num_sms, stream);
-        return launch_q<NX, NU, true, 2>(bv, st, pl, num_sms, stream);
+        if (refs == 0) return launch_q<T, NX, NU, true, 0>(bv, st, pl, num_sms, stream);
+        if (refs == 1) return launch_q<T, NX, NU, true, 1>(bv, st, pl, num_sms, stream);
+        return launch_q<T, NX, NU, true, 2>(bv, st, pl, num_sms, stream);
     }
-    if (refs == 0) return launch_q<NX, NU, false, 0>(bv, st, pl, num_sms, stream);
-    if (refs == 1) return launch_q<NX, NU, false, 1>(bv, st, pl, num_sms, stream);
-    return launch_q<NX, NU, false, 2>(bv, st, pl, num_sms, stream);
+    if (refs == 0) return launch_q<T, NX, NU, false, 0>(bv, st, pl, num_sms, stream);
+    if (refs == 1) return launch_q<T, NX, NU, false, 1>(bv, st, pl, num_sms, stream);
+    return launch_q<T, NX, NU, false, 2>(bv, st, pl, num_sms, stream);
 }
 
 template <int NX, int NU>
@@ -899,20 +910,20 @@ cudaError_t launch_shape_pi(const BatchView& bv, const AdmmSettings& st, int col
                             int num_sms, cudaStream_t stream, const int* order) {
     QPlan pl;
     const int refs = refs_mode(bv) == 0 ? 0 : 2;       // references, shared or not, go through the per-instance path
-    if (!make_qplan<NX, NU>(bv.N, refs, pl, true)) return cudaErrorInvalidConfiguration;
+    if (!make_qplan<double, NX, NU>(bv.N, refs, pl, true)) return cudaErrorInvalidConfiguration;
     pl.qp.counter = counter;
     pl.qp.pri_thresh = st.abs_pri_tol;
-    pl.qp.dua_thresh = dual_threshold_q(bv.rho, st.abs_dua_tol);
+    pl.qp.dua_thresh = dual_threshold_q<double>(bv.rho, st.abs_dua_tol);
     pl.qp.pi_blocks = pi_blocks;
     pl.qp.order = order;
     cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(int), stream);
     if (e != cudaSuccess) return e;
     if (cold) {
-        if (refs == 0) return launch_q<NX, NU, true, 0, false, true>(bv, st, pl, num_sms, stream);
-        return launch_q<NX, NU, true, 2, false, true>(bv, st, pl, num_sms, stream);
+        if (refs == 0) return launch_q<double, NX, NU, true, 0, false, true>(bv, st, pl, num_sms, stream);
+        return launch_q<double, NX, NU, true, 2, false, true>(bv, st, pl, num_sms, stream);
     }
-    if (refs == 0) return launch_q<NX, NU, false, 0, false, true>(bv, st, pl, num_sms, stream);
-    return launch_q<NX, NU, false, 2, false, true>(bv, st, pl, num_sms, stream);
+    if (refs == 0) return launch_q<double, NX, NU, false, 0, false, true>(bv, st, pl, num_sms, stream);
+    return launch_q<double, NX, NU, false, 2, false, true>(bv, st, pl, num_sms, stream);
 }
 
 // element-major per-instance cache [e][ld]  ->  one lane-interleaved block per instance (QLane: what each lane of the
@@ -957,10 +968,10 @@ cudaError_t launch_shape_roll(const BatchView& bv, const AdmmSettings& st, const
                               int num_sms, cudaStream_t stream) {
     QPlan pl;
     const int refs = ra.pi_blocks ? (refs_mode(bv) == 0 ? 0 : 2) : refs_mode(bv);
-    if (!make_qplan<NX, NU>(bv.N, refs, pl, ra.pi_blocks != nullptr)) return cudaErrorInvalidConfiguration;
+    if (!make_qplan<double, NX, NU>(bv.N, refs, pl, ra.pi_blocks != nullptr)) return cudaErrorInvalidConfiguration;
     pl.qp.counter = counter;
     pl.qp.pri_thresh = st.abs_pri_tol;
-    pl.qp.dua_thresh = dual_threshold_q(bv.rho, st.abs_dua_tol);
+    pl.qp.dua_thresh = dual_threshold_q<double>(bv.rho, st.abs_dua_tol);
     pl.qp.pi_blocks = ra.pi_blocks;
     pl.qp.order = ra.order;
     pl.qp.nsteps = ra.nsteps; pl.qp.cold_install = ra.cold; pl.qp.slide = ra.slide;
@@ -968,12 +979,12 @@ cudaError_t launch_shape_roll(const BatchView& bv, const AdmmSettings& st, const
     cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(int), stream);
     if (e != cudaSuccess) return e;
     if (ra.pi_blocks) {
-        if (refs == 0) return launch_q<NX, NU, false, 0, true, true>(bv, st, pl, num_sms, stream);
-        return launch_q<NX, NU, false, 2, true, true>(bv, st, pl, num_sms, stream);
+        if (refs == 0) return launch_q<double, NX, NU, false, 0, true, true>(bv, st, pl, num_sms, stream);
+        return launch_q<double, NX, NU, false, 2, true, true>(bv, st, pl, num_sms, stream);
     }
-    if (refs == 0) return launch_q<NX, NU, false, 0, true>(bv, st, pl, num_sms, stream);
-    if (refs == 1) return launch_q<NX, NU, false, 1, true>(bv, st, pl, num_sms, stream);
-    return launch_q<NX, NU, false, 2, true>(bv, st, pl, num_sms, stream);
+    if (refs == 0) return launch_q<double, NX, NU, false, 0, true>(bv, st, pl, num_sms, stream);
+    if (refs == 1) return launch_q<double, NX, NU, false, 1, true>(bv, st, pl, num_sms, stream);
+    return launch_q<double, NX, NU, false, 2, true>(bv, st, pl, num_sms, stream);
 }
 
 }  // namespace
@@ -1015,26 +1026,36 @@ bool tmem_pi_kernel_supports(const BatchView& bv, const AdmmSettings& st) {
     if (bv.x_min != nullptr && (bv.xb_stride != 0 || bv.ub_stride != 0)) return false;
     QPlan pl;
     const int refs = refs_mode(bv) == 0 ? 0 : 2;
-    if (bv.nx == 12 && bv.nu == 4) return make_qplan<12, 4>(bv.N, refs, pl, true);
-    if (bv.nx == 4 && bv.nu == 1) return make_qplan<4, 1>(bv.N, refs, pl, true);
+    if (bv.nx == 12 && bv.nu == 4) return make_qplan<double, 12, 4>(bv.N, refs, pl, true);
+    if (bv.nx == 4 && bv.nu == 1) return make_qplan<double, 4, 1>(bv.N, refs, pl, true);
     return false;
 }
 
-bool tmem_kernel_supports(const BatchView& bv, const AdmmSettings& st) {
+bool tmem_kernel_supports(const BatchView& bv, const AdmmSettings& st, int precision) {
     if (st.en_state_soc || st.en_input_soc || st.en_state_linear || st.en_input_linear) return false;
     if (st.max_iter <= 0 || !(bv.rho > 0.0)) return false;
     if (bv.x_min != nullptr && (bv.xb_stride != 0 || bv.ub_stride != 0)) return false;   // per-instance bounds: other kernels
     QPlan pl;
-    if (bv.nx == 12 && bv.nu == 4) return make_qplan<12, 4>(bv.N, refs_mode(bv), pl);
-    if (bv.nx == 4 && bv.nu == 1) return make_qplan<4, 1>(bv.N, refs_mode(bv), pl);
+    if (precision == 32) {
+        if (bv.nx == 12 && bv.nu == 4) return make_qplan<float, 12, 4>(bv.N, refs_mode(bv), pl);
+        if (bv.nx == 4 && bv.nu == 1) return make_qplan<float, 4, 1>(bv.N, refs_mode(bv), pl);
+        return false;
+    }
+    if (bv.nx == 12 && bv.nu == 4) return make_qplan<double, 12, 4>(bv.N, refs_mode(bv), pl);
+    if (bv.nx == 4 && bv.nu == 1) return make_qplan<double, 4, 1>(bv.N, refs_mode(bv), pl);
     return false;
 }
 
 cudaError_t launch_admm_tmem(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms,
-                             cudaStream_t stream, const int* order) {
+                             cudaStream_t stream, const int* order, int precision) {
     if (bv.B <= 0) return cudaSuccess;
-    if (bv.nx == 12 && bv.nu == 4) return launch_shape<12, 4>(bv, st, cold, counter, num_sms, stream, order);
-    if (bv.nx == 4 && bv.nu == 1) return launch_shape<4, 1>(bv, st, cold, counter, num_sms, stream, order);
+    if (precision == 32) {
+        if (bv.nx == 12 && bv.nu == 4) return launch_shape<float, 12, 4>(bv, st, cold, counter, num_sms, stream, order);
+        if (bv.nx == 4 && bv.nu == 1) return launch_shape<float, 4, 1>(bv, st, cold, counter, num_sms, stream, order);
+        return cudaErrorNotSupported;
+    }
+    if (bv.nx == 12 && bv.nu == 4) return launch_shape<double, 12, 4>(bv, st, cold, counter, num_sms, stream, order);
+    if (bv.nx == 4 && bv.nu == 1) return launch_shape<double, 4, 1>(bv, st, cold, counter, num_sms, stream, order);
     return cudaErrorNotSupported;
 }
 

@@ -224,13 +224,15 @@ tmpc::PerInstanceMats per_instance_view(tmpc_batch* h) {
 }
 
 int resolve_kernel(tmpc_batch* h) {
-    if (h->precision == 32) {   // float build: the sub-warp (shared-memory) and thread kernels are instantiated for float
+    if (h->precision == 32) {   // float build: the TMEM, sub-warp (shared-memory) and thread kernels are instantiated for float
         if (h->per_instance) return -1;
         const bool sub32 = tmpc::subwarp_kernel_supports(h->nx, h->nu, h->N, h->st, 32);
+        const bool tm32 = tmpc::tmem_kernel_supports(make_view(h), h->st, 32);
         if (h->kernel_pref == TMPC_KERNEL_THREAD) return TMPC_KERNEL_THREAD;
         if (h->kernel_pref == TMPC_KERNEL_SUBWARP) return sub32 ? TMPC_KERNEL_SUBWARP : -1;
+        if (h->kernel_pref == TMPC_KERNEL_TMEM) return tm32 ? TMPC_KERNEL_TMEM : -1;
         if (h->kernel_pref != TMPC_KERNEL_AUTO) return -1;
-        return sub32 ? TMPC_KERNEL_SUBWARP : TMPC_KERNEL_THREAD;
+        return tm32 ? TMPC_KERNEL_TMEM : (sub32 ? TMPC_KERNEL_SUBWARP : TMPC_KERNEL_THREAD);
     }
     if (h->per_instance) {   // every instance has its own cache: TMEM kernel reading per-instance blocks, else thread kernel
         const bool tm_pi = h->pi_blocks.p && tmpc::tmem_pi_kernel_supports(make_view(h), h->st);
@@ -309,7 +311,7 @@ cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v_in, cuda
     }
     if (!h->state_zero && wants_im != h->state_in_im) {      // the previous solve left the other format: convert on `s`
         if (!v.state_im) return cudaErrorInvalidValue;
-        cudaError_t ce = tmpc::launch_state_convert(v, wants_im, s);
+        cudaError_t ce = tmpc::launch_state_convert(v, wants_im, s, h->precision);
         if (ce != cudaSuccess) return ce;
         h->launches += 1;
     }
@@ -320,7 +322,7 @@ cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v_in, cuda
     const int* order = (sub && tm) ? build_order(h, v, s) : nullptr;
     if (sub && k == TMPC_KERNEL_TMEM && h->per_instance)
         e = tmpc::launch_admm_tmem_pi(v, h->st, h->state_zero ? 1 : 0, h->pi_blocks.p, h->counter.p, h->num_sms, s, order);
-    else if (sub && k == TMPC_KERNEL_TMEM) e = tmpc::launch_admm_tmem(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s, order);
+    else if (sub && k == TMPC_KERNEL_TMEM) e = tmpc::launch_admm_tmem(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s, order, h->precision);
     else if (sub && k == TMPC_KERNEL_CONE) e = tmpc::launch_admm_cone(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
     else if (sub) e = tmpc::launch_admm_subwarp(v, h->st, h->hm, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s, h->precision);
     else if (h->per_instance) e = tmpc::launch_admm_thread_per_instance(v, h->st, per_instance_view(h), s, h->precision);
@@ -947,7 +949,7 @@ static int solve_host_impl(tmpc_batch* h, const double* x0, int cold, double* X,
             const bool was_cold = h->state_zero;
             if (!h->state_im.p) { h->state_im.alloc(static_cast<size_t>(v.state_im_stride) * h->B); v.state_im = h->state_im.p; }
             if (!was_cold && !h->state_in_im) {
-                cudaError_t ce = tmpc::launch_state_convert(v, true, h->stream);
+                cudaError_t ce = tmpc::launch_state_convert(v, true, h->stream, h->precision);
                 if (ce != cudaSuccess) throw CudaFail{ce, "state conversion"};
                 h->launches += 1;
             }
@@ -968,7 +970,9 @@ static int solve_host_impl(tmpc_batch* h, const double* x0, int cold, double* X,
                 vc.x0 = v.x0 + static_cast<size_t>(b0) * h->nx;
                 if (v.Xref && v.xref_stride) vc.Xref = v.Xref + static_cast<size_t>(b0) * v.xref_stride;
                 if (v.Uref && v.uref_stride) vc.Uref = v.Uref + static_cast<size_t>(b0) * v.uref_stride;
-                vc.state_im = v.state_im + static_cast<size_t>(b0) * v.state_im_stride;
+                // one block of state_im_stride VALUES per instance: doubles, or floats in the float build
+                vc.state_im = reinterpret_cast<double*>(reinterpret_cast<char*>(v.state_im) +
+                                                        static_cast<size_t>(b0) * v.state_im_stride * (h->precision == 32 ? 4 : 8));
                 vc.Xsol = v.Xsol + b0 * sxN; vc.Usol = v.Usol + b0 * suN;
                 vc.status = v.status + b0; vc.iters = v.iters + b0;
                 // a chunk longer than one wave goes through the queue: longest-first order over the chunk's own instances
@@ -977,7 +981,7 @@ static int solve_host_impl(tmpc_batch* h, const double* x0, int cold, double* X,
                     ? tmpc::launch_admm_tmem_pi(vc, h->st, was_cold ? 1 : 0,
                                                 h->pi_blocks.p + static_cast<size_t>(b0) * tmpc::tmem_pi_block_doubles(h->nx, h->nu),
                                                 h->counter.p, h->num_sms, h->stream, order)
-                    : tmpc::launch_admm_tmem(vc, h->st, was_cold ? 1 : 0, h->counter.p, h->num_sms, h->stream, order);
+                    : tmpc::launch_admm_tmem(vc, h->st, was_cold ? 1 : 0, h->counter.p, h->num_sms, h->stream, order, h->precision);
                 if (e != cudaSuccess) throw CudaFail{e, "solve kernel launch"};
                 h->launches += 1;
                 CUDA_TRY(cudaEventRecord(h->chunk_done[c], h->stream));

@@ -11,6 +11,8 @@
 namespace tmpc {
 namespace {
 
+// T = double, or float for the float build (both formats then hold floats in the first half of their allocations)
+template <class T>
 __global__ void state_convert_kernel(const __grid_constant__ BatchView bv, int to_im) {
     const int nx = bv.nx, nu = bv.nu, N = bv.N;
     const int nxN = nx * N, nuN = nu * (N - 1);
@@ -22,33 +24,34 @@ __global__ void state_convert_kernel(const __grid_constant__ BatchView bv, int t
         // idx enumerates (field element, instance) with the instance fastest: coalesced on the element-major side
         const int b = static_cast<int>(idx % bv.B);
         int e = static_cast<int>(idx / bv.B);
-        double* em;      // element-major address
+        T* em;           // element-major address
         int im;          // offset in the instance block
         if (e < 3 * nxN) {
             const int f = e / nxN, k = e % nxN, i = k / nx, row = k % nx;       // f: 0 g, 1 v, 2 q
-            em = (f == 0 ? bv.g : f == 1 ? bv.v[0] : bv.q) + static_cast<size_t>(k) * ld + b;
+            em = reinterpret_cast<T*>(f == 0 ? bv.g : f == 1 ? bv.v[0] : bv.q) + static_cast<size_t>(k) * ld + b;
             im = 3 * nx * i + f * nx + row;
         } else if (e < 3 * nxN + 3 * nuN) {
             e -= 3 * nxN;
             const int f = e / nuN, k = e % nuN, i = k / nu, row = k % nu;       // f: 0 y, 1 z, 2 r
-            em = (f == 0 ? bv.y : f == 1 ? bv.z[0] : bv.r) + static_cast<size_t>(k) * ld + b;
+            em = reinterpret_cast<T*>(f == 0 ? bv.y : f == 1 ? bv.z[0] : bv.r) + static_cast<size_t>(k) * ld + b;
             im = 3 * nxN + 3 * nu * i + f * nu + row;
         } else {
             e -= 3 * nxN + 3 * nuN;
-            em = bv.pN + static_cast<size_t>(e) * ld + b;
+            em = reinterpret_cast<T*>(bv.pN) + static_cast<size_t>(e) * ld + b;
             im = 3 * nxN + 3 * nuN + e;
         }
-        double* blk = bv.state_im + static_cast<size_t>(b) * bv.state_im_stride + im;
+        T* blk = reinterpret_cast<T*>(bv.state_im) + static_cast<size_t>(b) * bv.state_im_stride + im;
         if (to_im) *blk = *em; else *em = *blk;
     }
 }
 
 }  // namespace
 
-cudaError_t launch_state_convert(const BatchView& bv, bool to_instance_major, cudaStream_t stream) {
+cudaError_t launch_state_convert(const BatchView& bv, bool to_instance_major, cudaStream_t stream, int precision) {
     if (bv.B <= 0) return cudaSuccess;
     if (!bv.state_im) return cudaErrorInvalidValue;
-    state_convert_kernel<<<148 * 8, 256, 0, stream>>>(bv, to_instance_major ? 1 : 0);
+    if (precision == 32) state_convert_kernel<float><<<148 * 8, 256, 0, stream>>>(bv, to_instance_major ? 1 : 0);
+    else state_convert_kernel<double><<<148 * 8, 256, 0, stream>>>(bv, to_instance_major ? 1 : 0);
     return cudaGetLastError();
 }
 

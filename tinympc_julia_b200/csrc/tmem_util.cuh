@@ -80,11 +80,19 @@ __device__ __forceinline__ void tm_st8(uint32_t taddr, const uint32_t* r) {
     asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
                  :: "r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]) : "memory");
 }
-// a knot point of a lane is WORDS 32-bit columns: 12 (x8 + x4: each tcgen05 instruction needs its address in a
-// uniform register, so fewer, wider instructions also mean fewer R2UR) or 4
+__device__ __forceinline__ void tm_ld2(uint32_t taddr, uint32_t* r) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0, %1}, [%2];" : "=r"(r[0]), "=r"(r[1]) : "r"(taddr));
+}
+__device__ __forceinline__ void tm_st2(uint32_t taddr, const uint32_t* r) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x2.b32 [%0], {%1, %2};" :: "r"(taddr), "r"(r[0]), "r"(r[1]) : "memory");
+}
+// a knot point of a lane is WORDS 32-bit columns: doubles 12 (x8 + x4: each tcgen05 instruction needs its address in a
+// uniform register, so fewer, wider instructions also mean fewer R2UR) or 4; floats 6 (x4 + x2) or 2
 template <int WORDS>
 __device__ __forceinline__ void tm_load(uint32_t taddr, uint32_t* w) {
     if (WORDS == 12) { tm_ld8(taddr, w); tm_ld4(taddr + 8, w + 8); }
+    else if (WORDS == 6) { tm_ld4(taddr, w); tm_ld2(taddr + 4, w + 4); }
+    else if (WORDS == 2) tm_ld2(taddr, w);
     else {
 #pragma unroll
         for (int k = 0; k < WORDS; k += 4) tm_ld4(taddr + k, w + k);
@@ -93,6 +101,8 @@ __device__ __forceinline__ void tm_load(uint32_t taddr, uint32_t* w) {
 template <int WORDS>
 __device__ __forceinline__ void tm_store(uint32_t taddr, const uint32_t* w) {
     if (WORDS == 12) { tm_st8(taddr, w); tm_st4(taddr + 8, w + 8); }
+    else if (WORDS == 6) { tm_st4(taddr, w); tm_st2(taddr + 4, w + 4); }
+    else if (WORDS == 2) tm_st2(taddr, w);
     else {
 #pragma unroll
         for (int k = 0; k < WORDS; k += 4) tm_st4(taddr + k, w + k);
@@ -108,6 +118,12 @@ __device__ __forceinline__ void tm_wait_ld12(uint32_t* w) {
 }
 __device__ __forceinline__ void tm_wait_ld4(uint32_t* w) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(w[0]), "+r"(w[1]), "+r"(w[2]), "+r"(w[3]) :: "memory");
+}
+__device__ __forceinline__ void tm_wait_ld6(uint32_t* w) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(w[0]), "+r"(w[1]), "+r"(w[2]), "+r"(w[3]), "+r"(w[4]), "+r"(w[5]) :: "memory");
+}
+__device__ __forceinline__ void tm_wait_ld2(uint32_t* w) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(w[0]), "+r"(w[1]) :: "memory");
 }
 __device__ __forceinline__ void tm_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
@@ -163,6 +179,57 @@ __device__ __forceinline__ void stg_if(double* p, double v, bool pred) {
 template <int W> __device__ __forceinline__ void tm_wait_ld(uint32_t* w);
 template <> __device__ __forceinline__ void tm_wait_ld<12>(uint32_t* w) { tm_wait_ld12(w); }
 template <> __device__ __forceinline__ void tm_wait_ld<4>(uint32_t* w) { tm_wait_ld4(w); }
+template <> __device__ __forceinline__ void tm_wait_ld<6>(uint32_t* w) { tm_wait_ld6(w); }
+template <> __device__ __forceinline__ void tm_wait_ld<2>(uint32_t* w) { tm_wait_ld2(w); }
+
+// ---------------------------------------------------------------- the same helpers at the float value of `tinytype`
+// (the TMEM kernel is instantiated for both scalars; a value is two Tensor-Memory words as a double, one as a float)
+__device__ __forceinline__ double tm_get(const uint32_t* w, int k, double) { return mk_double(w[2 * k], w[2 * k + 1]); }
+__device__ __forceinline__ float tm_get(const uint32_t* w, int k, float) { return __uint_as_float(w[k]); }
+__device__ __forceinline__ void tm_put(uint32_t* w, int k, double v) { w[2 * k] = lo32(v); w[2 * k + 1] = hi32(v); }
+__device__ __forceinline__ void tm_put(uint32_t* w, int k, float v) { w[k] = __float_as_uint(v); }
+// w[k] <- cond ? v : w[k]
+__device__ __forceinline__ void tm_put_if(uint32_t* w, int k, double v, bool c) {
+    w[2 * k] = c ? lo32(v) : w[2 * k]; w[2 * k + 1] = c ? hi32(v) : w[2 * k + 1];
+}
+__device__ __forceinline__ void tm_put_if(uint32_t* w, int k, float v, bool c) { w[k] = c ? __float_as_uint(v) : w[k]; }
+
+__device__ __forceinline__ void ld2(const float* p, float& a, float& b) {
+    const float2 t = *reinterpret_cast<const float2*>(p);
+    a = t.x; b = t.y;
+}
+__device__ __forceinline__ void st2(float* p, float a, float b) { *reinterpret_cast<float2*>(p) = make_float2(a, b); }
+__device__ __forceinline__ float shfl_dq(float v, int src_lane) {
+    uint32_t r;
+    asm volatile("shfl.sync.idx.b32 %0, %1, %2, 0x1f, 0xffffffff;" : "=r"(r) : "r"(__float_as_uint(v)), "r"(src_lane));
+    return __uint_as_float(r);
+}
+template <int OFF = 0>
+__device__ __forceinline__ void lds2(uint32_t a, float& x, float& y) {
+    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2+%3];" : "=f"(x), "=f"(y) : "r"(a), "n"(OFF));
+}
+template <int OFF = 0>
+__device__ __forceinline__ void sts1(uint32_t a, float x) {
+    asm volatile("st.shared.f32 [%0+%1], %2;" :: "r"(a), "n"(OFF), "f"(x) : "memory");
+}
+template <int OFF = 0>
+__device__ __forceinline__ void sts2(uint32_t a, float x, float y) {
+    asm volatile("st.shared.v2.f32 [%0+%1], {%2, %3};" :: "r"(a), "n"(OFF), "f"(x), "f"(y) : "memory");
+}
+// one scalar from shared memory by 32-bit address, typed by the caller
+template <int OFF, class T>
+__device__ __forceinline__ T lds1t(uint32_t a) {
+    if constexpr (sizeof(T) == 8) return lds1<OFF>(a);
+    else {
+        float x;
+        asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(x) : "r"(a), "n"(OFF));
+        return x;
+    }
+}
+__device__ __forceinline__ void stg_if(float* p, float v, bool pred) {
+    asm volatile("{ .reg .pred p; setp.ne.s32 p, %2, 0; @p st.global.f32 [%0], %1; }"
+                 :: "l"(p), "f"(v), "r"(static_cast<int>(pred)) : "memory");
+}
 
 }  // namespace tmu
 }  // namespace tmpc
