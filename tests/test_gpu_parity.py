@@ -152,6 +152,46 @@ def test_full_size_batch_properties():
         np.testing.assert_allclose(a["U"], b["U"], rtol=1e-5, atol=1e-6)
 
 
+def test_full_size_parity_against_compiled_reference(ref, orc):
+    """BASELINE.json's full sizes inside pytest: every instance of a B = 65,536 batch of configs 2 and 3 (AUTO kernel)
+    against the compiled, unmodified reference core (oracle/_ref, the checker of the fixtures; the C restatement where
+    it did not travel) — identical status and iteration count per instance, states / controls within 1e-5 / 1e-6 —
+    and the N = 50 rocket with both cones and half-spaces (config 4) at B = 4,096 on the on-chip cone kernel."""
+    chk = ref if ref is not None else orc
+    for c, kern in ((cases.quadrotor_batch(65536, seed=4), TMEM), (cases.quadrotor_batch(65536, hard=True, seed=6), TMEM),
+                    (cases.cartpole_batch(65536, seed=3), TMEM), (cases.rocket(4096, N=50, seed=5), CONE)):
+        want = cases.run_checker(c, chk, nthreads=16)
+        got = cases.run_cuda(c, kernel=t.KERNEL_AUTO)
+        assert got["solver"].kernel == kern
+        cases.compare(got, want, what=f"full size vs {chk.kind} ({c['sys'].name}, B={c['x0'].shape[1]})")
+
+
+def test_full_size_closed_loop_against_compiled_reference(ref, orc):
+    """config 5 at a size the CPU finishes in seconds: 2,048 instances x 100 warm-started MPC steps with per-instance
+    sliding references, ONE fused launch, per-step status / iteration counts and the final plant state against the
+    reference's closed loop."""
+    import torch
+    chk = ref if ref is not None else orc
+    B, nsteps = 2048, 100
+    c = cases.quadrotor_closed_loop(B, nsteps, seed=8)
+    want = cases.run_checker(c, chk, nthreads=16)
+    sol = cases.make_cuda_solver(c)
+    t.set_x0(sol, c["x0"])
+    xlong = torch.from_numpy(np.ascontiguousarray(np.asfortranarray(c["Xref"]).transpose(2, 1, 0))).cuda()
+    st_out = torch.full((nsteps, B), -1, dtype=torch.int32, device="cuda")
+    it_out = torch.full((nsteps, B), -1, dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    sol.rollout_async(nsteps, xlong.data_ptr(), st_out.data_ptr(), it_out.data_ptr(), 0)
+    sol.synchronize()
+    assert sol.launch_count <= 3
+    assert np.array_equal(it_out.cpu().numpy(), want["iters"]) and np.array_equal(st_out.cpu().numpy(), want["ret"])
+    import ctypes as C
+    from tinympc_julia_b200 import _lib
+    xf = torch.empty((B, 12), dtype=torch.float64, device="cuda")
+    assert _lib.load().tmpc_batch_get_x0(sol._h, C.cast(xf.data_ptr(), C.c_void_p), 1) == 0
+    np.testing.assert_allclose(xf.cpu().numpy().T, want["x_final"], rtol=1e-5, atol=1e-6)
+
+
 @pytest.mark.parametrize("B,nsteps", [(48, 30), (9, 7)])
 def test_device_rollout_matches_oracle(orc, B, nsteps):
     """tmpc_batch_rollout_async (config 5 on the device: solve -> apply u0 -> plant step -> slide the reference window,

@@ -56,14 +56,17 @@ using namespace tmu;
 #ifndef TMPC_QWARPS
 #define TMPC_QWARPS 8
 #endif
+#ifndef TMPC_QWARPS_F32
+#define TMPC_QWARPS_F32 12
+#endif
 // warps per CTA (one CTA per SM).  Quadrotor shape: two per scheduler (238 registers per thread, 240 of 256 Tensor-Memory
 // columns and 16.4 KB of shared memory per warp).  Cartpole shape (one state row per lane: 139 registers, 80 TMEM columns,
 // 15.4 KB per warp): three per scheduler - the kernel is latency-bound (ncu: 2.0 fixed-latency stall cycles per issue
 // at 8 warps, profiles/r02_a_ncu_full_cartpole_summary.csv).
 // Float build (tinytype = float): half the shared memory and Tensor-Memory columns per warp and one register per value:
-// 16 warps (four per scheduler, <= 128 registers per thread).
+// 12 warps (three per scheduler, <= 170 registers per thread; measured 3.5 % faster than 16 warps at 128 registers).
 template <class T, int NX, bool PI = false> struct QWarps {
-    static constexpr int value = sizeof(T) == 4 ? 16 : ((NX == 4 && !PI) ? 12 : TMPC_QWARPS);   // per-instance operands: + 4.6 KB of shared memory per warp
+    static constexpr int value = sizeof(T) == 4 ? TMPC_QWARPS_F32 : ((NX == 4 && !PI) ? 12 : TMPC_QWARPS);   // per-instance operands: + 4.6 KB of shared memory per warp
 };
 constexpr int kQInst = 8;            // instances per warp
 template <class T, int NX, bool PI = false> struct QTmemCols { static constexpr int value = (512 / ((QWarps<T, NX, PI>::value + 3) / 4)) & ~1; };   // columns per warp
@@ -106,7 +109,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     static_assert(NX % 4 == 0 && NX >= 4, "state rows are dealt 4 lanes x RX rows");
     static_assert(NU >= 1 && NU <= 4, "one input row per lane");
     constexpr int RX = NX / 4;
-    constexpr int XP = QPad<NX>::value;
+    constexpr int XP = QPad<NX, sizeof(T)>::value;
     using R = Ar<T>;                                  // arithmetic at the reference's tinytype (types.hpp:15)
     constexpr int S = sizeof(T);                      // bytes per value: every shared-memory byte offset below is a multiple
     constexpr int W = 2 * RX * (S / 4);               // 32-bit TMEM words per knot point per lane: g(RX), v(RX)
@@ -496,10 +499,16 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 }
                 __syncwarp();
                 if (i < N - 2 && urow) sts1<32 * S>(a_myrt + o_rt, t_def);    // t_{i+1}: every lane has read r_{i+1} by now
+                if constexpr (S == 4) {      // four floats per 128-bit load
+                    lds4<0>(a_slot, pb[0], pb[1], pb[2], pb[3]);
+                    if constexpr (NX > 4) lds4<16>(a_slot, pb[4], pb[5], pb[6], pb[7]);
+                    if constexpr (NX > 8) lds4<32>(a_slot, pb[8], pb[9], pb[10], pb[11]);
+                } else {
                 lds2<0>(a_slot, pb[0], pb[1]);
                 if (NX > 2) lds2<2 * S>(a_slot, pb[2], pb[3]);
                 if (NX > 4) { lds2<4 * S>(a_slot, pb[4], pb[5]); lds2<6 * S>(a_slot, pb[6], pb[7]); }
                 if (NX > 8) { lds2<8 * S>(a_slot, pb[8], pb[9]); lds2<10 * S>(a_slot, pb[10], pb[11]); }
+                }
                 }
                 T rr[4];
                 lds2<0>(a_rt4 + o_rt, rr[0], rr[1]);
@@ -687,10 +696,16 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 __syncwarp();
                 if (i > 0 && urow) sts1<-32 * S>(a_myrt + o_rt, r_def);         // r_{i-1}: every lane has read t_{i-1} by now
                 T xb[NX];
+                if constexpr (S == 4) {      // four floats per 128-bit load
+                    lds4<0>(a_slot, xb[0], xb[1], xb[2], xb[3]);
+                    if constexpr (NX > 4) lds4<16>(a_slot, xb[4], xb[5], xb[6], xb[7]);
+                    if constexpr (NX > 8) lds4<32>(a_slot, xb[8], xb[9], xb[10], xb[11]);
+                } else {
                 lds2<0>(a_slot, xb[0], xb[1]);
                 if (NX > 2) lds2<2 * S>(a_slot, xb[2], xb[3]);
                 if (NX > 4) { lds2<4 * S>(a_slot, xb[4], xb[5]); lds2<6 * S>(a_slot, xb[6], xb[7]); }
                 if (NX > 8) { lds2<8 * S>(a_slot, xb[8], xb[9]); lds2<10 * S>(a_slot, xb[10], xb[11]); }
+                }
                 T tt[4], mq[4];
                 lds2<0>(a_rt4 + o_rt, tt[0], tt[1]);
                 lds2<16 * S>(a_rt4 + o_rt, tt[2], tt[3]);
@@ -843,7 +858,7 @@ struct QPlan { size_t smem_bytes; QuadParams qp; };
 
 template <class T, int NX, int NU>
 bool make_qplan(int N, int refs, QPlan& pl, bool pi = false) {
-    constexpr int XP = QPad<NX>::value;
+    constexpr int XP = QPad<NX, sizeof(T)>::value;
     constexpr int W = 2 * (NX / 4) * (sizeof(T) / 4);
     const int warps = pi ? QWarps<T, NX, true>::value : QWarps<T, NX, false>::value;
     if (N < 2 || N * W > (pi ? QTmemCols<T, NX, true>::value : QTmemCols<T, NX, false>::value)) return false;   // g, v of a lane must fit the warp's TMEM columns
@@ -853,10 +868,10 @@ bool make_qplan(int N, int refs, QPlan& pl, bool pi = false) {
     qp.off_consts = off; off += QConst<NX, NU>::size;
     qp.off_bounds = off; off += 2 * (nxN + nuN);
     qp.off_refs = off; if (refs == 1) off += nxN + nuN + NX;
-    off = (off + 1) / 2 * 2;
+    off = (off + 3) / 4 * 4;                                       // 16-byte aligned at either scalar
     qp.off_warp0 = off;
     int per_warp = (N - 1) * 96 + 2 * kQInst * XP;
-    per_warp = (per_warp + 1) / 2 * 2;
+    per_warp = (per_warp + 3) / 4 * 4;
     qp.off_pi = per_warp;
     if (pi) per_warp += 32 * 18;                                   // the lanes' private B / Quu_inv row slots
     qp.warp_stride = per_warp;

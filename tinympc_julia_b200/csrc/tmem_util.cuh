@@ -11,9 +11,12 @@ namespace tmu {
 
 constexpr unsigned kAll = 0xffffffffu;
 
-template <int NX>
-struct QPad {   // pitch of one instance's broadcast slot: an odd number of 16-byte chunks
-    static constexpr int value = ((NX / 2) % 2 == 1) ? NX : NX + 2;
+template <int NX, int BYTES = 8>
+struct QPad {   // pitch (values) of one instance's broadcast slot: an odd number of 16-byte chunks, so that the eight
+                // instances of a warp read their slots with 128-bit loads from disjoint banks
+    static constexpr int per_chunk = 16 / BYTES;
+    static constexpr int chunks = (NX + per_chunk - 1) / per_chunk;
+    static constexpr int value = (chunks % 2 == 1 ? chunks : chunks + 1) * per_chunk;
 };
 
 template <int NX, int NU>
@@ -207,6 +210,10 @@ __device__ __forceinline__ float shfl_dq(float v, int src_lane) {
 template <int OFF = 0>
 __device__ __forceinline__ void lds2(uint32_t a, float& x, float& y) {
     asm volatile("ld.shared.v2.f32 {%0, %1}, [%2+%3];" : "=f"(x), "=f"(y) : "r"(a), "n"(OFF));
+}
+template <int OFF = 0>
+__device__ __forceinline__ void lds4(uint32_t a, float& x, float& y, float& z, float& w) {
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+%5];" : "=f"(x), "=f"(y), "=f"(z), "=f"(w) : "r"(a), "n"(OFF));
 }
 template <int OFF = 0>
 __device__ __forceinline__ void sts1(uint32_t a, float x) {
