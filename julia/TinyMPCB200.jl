@@ -13,7 +13,7 @@ using Libdl
 
 export TinyMPCBatchSolver, setup_batch, set_x0, set_x_ref, set_u_ref, set_bound_constraints, set_linear_constraints,
        set_cone_constraints, set_cache_terms, update_settings, reset!, solve, get_solution, get_status,
-       set_kernel, set_precision, rollout!, solve_host, set_instance_dynamics, destroy!
+       set_kernel, set_precision, set_order, rollout!, solve_host, solve_host_u0, set_instance_dynamics, destroy!
 
 const lib_path = joinpath(dirname(@__DIR__), "lib", "libtinympc_jl." * Libdl.dlext)   # as reference src/TinyMPC.jl:12-13
 
@@ -166,6 +166,28 @@ function solve_host(s::TinyMPCBatchSolver, x0::Matrix{Float64}; cold::Bool = fal
     ret in (0, 1) || error("solve_host failed with status $ret")
     return ret, (states = X, controls = U), st, it
 end
+
+"""
+The same with only the first control of every instance (nu x B) and the status / iteration counts coming home: what an
+MPC loop reads from a solve (reference examples/cartpole_example_mpc.jl:41-42).  tmpc_batch_solve_host_select.
+"""
+function solve_host_u0(s::TinyMPCBatchSolver, x0::Matrix{Float64}; cold::Bool = false)
+    u0 = Array{Float64}(undef, s.nu, s.B)
+    st = Vector{Int32}(undef, s.B); it = Vector{Int32}(undef, s.B)
+    ret = ccall((:tmpc_batch_solve_host_select, lib_path), Int32,
+                (Ptr{Cvoid}, Ptr{Float64}, Int32, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}, Ptr{Int32}, Ptr{Int32}, Int32),
+                s.handle, x0, Int32(cold), C_NULL, C_NULL, u0, st, it, Int32(0))
+    ret in (0, 1) || error("solve_host_u0 failed with status $ret")
+    return ret, u0, st, it
+end
+
+"""
+Queue order of the persistent kernels: 0 natural, 1 longest-first (default), 2 `perm` (0-based permutation of 0..B-1).
+Results never depend on it (tmpc_batch_set_order).
+"""
+set_order(s::TinyMPCBatchSolver, mode::Integer; perm::Vector{Int32} = Int32[]) =
+    check(ccall((:tmpc_batch_set_order, lib_path), Int32, (Ptr{Cvoid}, Int32, Ptr{Int32}),
+                s.handle, mode, isempty(perm) ? C_NULL : pointer(perm)), "Failed to set the queue order")
 
 """
 Closed loop on the device: `nsteps` x (solve, apply controls[:, 1], x <- A x + B u + f), references sliding by one

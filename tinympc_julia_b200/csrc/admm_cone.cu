@@ -9,9 +9,10 @@
 //
 //   phase A  backward_pass_grad + forward_pass (admm.cpp:13-32): lane = matrix row.  10 lanes per instance, lanes 0-5
 //            own the state rows, 6-8 the input rows; the row a lane multiplies with is A / Kinf (forward) or AmBKt / B'
-//            (backward), so ONE 6-FMA chain per knot point serves both kinds of lane; vectors are all-gathered by
-//            shuffles.  Inputs q_i, r_i and outputs x_i, u_i go through a per-warp shared-memory exchange array of one
-//            80-byte record per knot point (x overwrites q, u overwrites the t = B'p + r + BPf that overwrote r).
+//            (backward), so ONE 6-FMA chain per knot point serves both kinds of lane.  Inputs q_i, r_i and outputs
+//            x_i, u_i go through a per-warp shared-memory exchange array of one 80-byte record per knot point (x
+//            overwrites q, u overwrites the t = B'p + r + BPf that overwrote r); the same records all-gather the
+//            vectors inside the sweeps (no shuffles).
 //   phase B  update_slack (box clamp, project_soc, sequential project_hyperplane), update_dual, update_linear_cost and
 //            the residual tests (admm.cpp:81-271): lane = knot point.  The 3 x N (instance, knot) tasks of the tile are
 //            dealt to the 32 lanes; a task holds its whole knot point in registers, so cone and half-space projections
@@ -20,8 +21,8 @@
 // Residency.  A task's state (g, v, gc, gl: 4 x 6; y, z, yc, yl: 4 x 3 doubles = 72 32-bit words) lives in the Tensor
 // Memory row of the lane that always processes it (tcgen05.ld/st .32x32b as lane-private scratch; 8 warps x 3 slots of
 // 72 columns = 96 tasks per warp), the remaining 3 N - 96 tasks element-major in shared memory: 24 instances per SM stay
-// on chip for the whole solve (221 KB shared + 216 of 256 TMEM columns per warp at N = 50), HBM is touched at install and
-// write-out only.  The thread-per-instance kernel streams 31 KB per instance-iteration through L2 / HBM instead.
+// on chip for the whole solve (226 KB shared + 216 of 256 TMEM columns per warp at N = 50), HBM is touched at install and
+// write-out only; shared references, knot-invariant bounds and the half-space rows are staged once per CTA.  The thread-per-instance kernel streams 31 KB per instance-iteration through L2 / HBM instead.
 //
 // Arithmetic: the same sequence of correctly rounded operations as admm_thread.cu (ascending-k FMA chains, explicitly
 // rounded elementwise updates, project_soc3 with the reference's float mu / norm), so both kernels agree bit for bit

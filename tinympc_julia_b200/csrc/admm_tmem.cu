@@ -23,6 +23,10 @@
 // Arithmetic is the same sequence of correctly rounded operations as admm_subwarp.cu / admm_thread.cu, so all
 // kernels agree bit for bit on the carried state (tests switch kernels in the middle of a closed loop).
 //
+// The kernel is generic in the scalar T = the reference's `tinytype` (types.hpp:15): double (default build) or float.
+// A value is two Tensor-Memory words as a double and one as a float, shared-memory byte offsets are multiples of
+// sizeof(T), arithmetic comes from Ar<T>; the float instantiation runs 12 warps per SM.
+//
 // Reference being reproduced: tinympc/TinyMPC/src/tinympc/admm.cpp:13-32 (Riccati sweeps), :81-98 (box slack),
 // :181-187 (dual), :214-247 (linear cost), :253-271 (termination), :274-389 (solve).
 #include <cuda_runtime.h>
