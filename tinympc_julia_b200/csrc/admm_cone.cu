@@ -41,13 +41,20 @@ namespace {
 
 using namespace tmu;
 
-constexpr int kCWarps = 8;          // warps per CTA, one CTA per SM: two per scheduler
-constexpr int kCInst = 3;           // instances per warp (a tile)
+#ifndef TMPC_CONE_WARPS
+#define TMPC_CONE_WARPS 8
+#endif
+#ifndef TMPC_CONE_INST
+#define TMPC_CONE_INST 3
+#endif
+constexpr int kCWarps = TMPC_CONE_WARPS;   // warps per CTA, one CTA per SM: two per scheduler
+constexpr int kCInst = TMPC_CONE_INST;     // instances per warp (a tile)
 constexpr int kCGroup = 10;         // lanes per instance in phase A
 constexpr int kRec = 10;            // doubles per knot record of the exchange array: [x | q (6)] [u | r | t (3)] [pad]
 constexpr int kTaskDoubles = 36;    // g v gc gl (4 x 6)  y z yc yl (4 x 3)
 constexpr int kTaskWords = 2 * kTaskDoubles;
-constexpr int kTmemSlots = 3;       // tasks per lane in Tensor Memory: 3 x 72 = 216 of the warp's 256 columns
+constexpr int kTmemCols = (512 / ((kCWarps + 3) / 4)) & ~1;   // Tensor-Memory columns of a warp (4 lane quarters)
+constexpr int kTmemSlots = kTmemCols / kTaskWords;            // tasks per lane in Tensor Memory: 3 x 72 = 216 of 256 columns at 8 warps
 constexpr int kTmemTasks = 32 * kTmemSlots;
 
 struct ConeParams {
@@ -204,7 +211,7 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     asm volatile("tcgen05.fence::after_thread_sync;");
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const uint32_t tbase = s_tmem_base + (static_cast<uint32_t>((warp & 3) * 32) << 16) + static_cast<uint32_t>((warp >> 2) * 256);
+    const uint32_t tbase = s_tmem_base + (static_cast<uint32_t>((warp & 3) * 32) << 16) + static_cast<uint32_t>((warp >> 2) * kTmemCols);
     double* ex = smem + cp.off_warp0 + static_cast<size_t>(warp) * cp.warp_stride;   // [T][kRec] knot records
     double* ss = ex + T * kRec;                                                       // [kTaskDoubles][smem_tasks] state of tasks >= 96
     const int TS = cp.smem_tasks;
@@ -247,6 +254,11 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
         if (b_first >= bv.B) break;
         int iter[kCInst], status[kCInst];
         bool live[kCInst];
+        // element gi of a per-instance register array, by selects (a dynamic index would go through local memory)
+        auto pick = [&](const auto& arr, int gi) { auto v = arr[0];
+#pragma unroll
+            for (int k = 1; k < kCInst; ++k) v = (gi == k) ? arr[k] : v;
+            return v; };
 #pragma unroll
         for (int k = 0; k < kCInst; ++k) { iter[k] = 0; status[k] = 1; live[k] = b_first + k < bv.B; }
 
@@ -303,7 +315,7 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
 
         // ================================================================= ADMM iterations of the tile
         for (;;) {
-            const bool glive = grp < kCInst && ((grp == 0 && live[0]) || (grp == 1 && live[1]) || (grp == 2 && live[2]));
+            const bool glive = grp < kCInst && pick(live, grp);
             // ------------------------------------------------- phase A: backward sweep (admm.cpp:13-20)
             // Vectors are all-gathered through the knot records themselves: the state lanes leave p_i in the q slot of
             // record i (q_i has just been consumed), everybody reads it back with three 16-byte loads one knot later.
@@ -363,16 +375,17 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             __syncwarp();
 
             // ------------------------------------------------- phase B: slack / dual / linear cost / residuals per knot point
-            unsigned okbits = 0x7u;
-            const bool tst0 = ((iter[0] + 1) % st.check_termination) == 0, tst1 = ((iter[1] + 1) % st.check_termination) == 0,
-                       tst2 = ((iter[2] + 1) % st.check_termination) == 0;
+            unsigned okbits = (1u << kCInst) - 1u;
+            bool tst[kCInst];
+#pragma unroll
+            for (int k = 0; k < kCInst; ++k) tst[k] = ((iter[k] + 1) % st.check_termination) == 0;
             for (int rd = 0; rd < rounds; ++rd) {
                 const int tau = rd * 32 + lane;
                 const bool in_tile = tau < T;
                 const int gi = in_tile ? tau / N : 0, i = in_tile ? tau - gi * N : 0;
                 const int b = b_first + gi;
-                const bool act = in_tile && ((gi == 0 && live[0]) || (gi == 1 && live[1]) || (gi == 2 && live[2]));
-                const bool testing = gi == 0 ? tst0 : (gi == 1 ? tst1 : tst2);
+                const bool act = in_tile && pick(live, gi);
+                const bool testing = pick(tst, gi);
                 const bool terminal = (i == N - 1);
                 uint32_t w[kTaskWords];
                 double s[kTaskDoubles];
@@ -543,7 +556,7 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             const int gi = in_tile ? tau / N : 0, i = in_tile ? tau - gi * N : 0;
             const int b = b_first + gi;
             const bool act = in_tile && b < bv.B;
-            const int st_k = gi == 0 ? status[0] : (gi == 1 ? status[1] : status[2]);
+            const int st_k = pick(status, gi);
             uint32_t w[kTaskWords];
             double s[kTaskDoubles];
             if (rd < kTmemSlots) {
@@ -581,7 +594,7 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                         bv.r[o] = rec[NX + r];
                     }
                 }
-                if (i == 0) { bv.status[b] = st_k; bv.iters[b] = gi == 0 ? iter[0] : (gi == 1 ? iter[1] : iter[2]); }
+                if (i == 0) { bv.status[b] = st_k; bv.iters[b] = pick(iter, gi); }
             }
         }
         __syncwarp();
