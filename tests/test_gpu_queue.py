@@ -145,6 +145,21 @@ def test_solve_host_output_selector():
     assert np.array_equal(s.states, X0) and np.array_equal(s.controls, U0) and np.array_equal(it, it0)
     r, s, st, it = sol.solve_host(c["x0"], cold=True, chunks=5, want_states=False, want_controls=False, want_u0=True)
     assert np.array_equal(s.controls, U0[:, 0, :]) and np.array_equal(it, it0)
+    # warm-started closed-loop shape on page-locked buffers: the kernel reads x0 from the mapped host buffer, the queue
+    # order comes from the previous iteration counts, one kernel writes u0 / status / iterations home; the device copy
+    # of x0 is refreshed beside the solve (a later plain solve must see it)
+    x1 = np.asfortranarray(c["x0"] * 0.8)
+    t.set_x0(ref, x1)
+    assert t.solve(ref) in (0, 1)
+    st1, it1 = ref.status()
+    X1, U1 = t.get_solution(ref)
+    r, s, st, it = sol.solve_host(x1, cold=False, want_states=False, want_controls=False, want_u0=True)
+    assert np.array_equal(st, st1) and np.array_equal(it, it1) and np.array_equal(s.controls, U1[:, 0, :])
+    assert t.solve(ref) in (0, 1) and t.solve(sol) in (0, 1)          # third solve, same (device-resident) x0 on both
+    st2, it2 = ref.status()
+    st3, it3 = sol.status()
+    assert np.array_equal(it2, it3) and np.array_equal(st2, st3)
+    assert np.array_equal(t.get_solution(ref).controls, t.get_solution(sol).controls)
 
 
 def test_rejected_settings():

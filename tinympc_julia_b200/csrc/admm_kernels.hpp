@@ -120,6 +120,9 @@ cudaError_t launch_plant_step_per_instance(const BatchView& bv, const PerInstanc
                                            cudaStream_t stream);
 cudaError_t launch_record_step(const BatchView& bv, int* status_out, int* iters_out, cudaStream_t stream);
 // out[nu x B] = Usol(:, 0, b): the first control of every instance, packed for one small device-to-host copy
-cudaError_t launch_gather_u0(const double* Usol, long long stride, int nu, int B, double* out, cudaStream_t stream);
+// with st_out / it_out: also copies the status / iteration words (all three destinations may be mapped host memory)
+cudaError_t launch_gather_u0(const double* Usol, long long stride, int nu, int B, double* out, cudaStream_t stream,
+                             const int* st_in = nullptr, const int* it_in = nullptr, int* st_out = nullptr,
+                             int* it_out = nullptr);
 
 }  // namespace tmpc

@@ -55,8 +55,16 @@ __global__ void record_step_kernel(const __grid_constant__ BatchView bv, int* __
 }
 
 // first control of every instance, packed nu x B: what a closed loop consumes from a solve (cartpole_example_mpc.jl:41-42)
-__global__ void gather_u0_kernel(const double* __restrict__ Usol, long long stride, int nu, int B, double* __restrict__ out) {
+// (optionally also the status / iteration words: with `out`, `st_out`, `it_out` in mapped pinned host memory this one
+// kernel is the whole device-to-host leg of a closed-loop step)
+__global__ void gather_u0_kernel(const double* __restrict__ Usol, long long stride, int nu, int B, double* __restrict__ out,
+                                 const int* __restrict__ st_in, const int* __restrict__ it_in, int* __restrict__ st_out,
+                                 int* __restrict__ it_out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < B) {
+        if (st_out) st_out[i] = st_in[i];
+        if (it_out) it_out[i] = it_in[i];
+    }
     if (i >= B * nu) return;
     const int b = i / nu, j = i - b * nu;
     out[i] = Usol[static_cast<size_t>(b) * stride + j];
@@ -64,10 +72,11 @@ __global__ void gather_u0_kernel(const double* __restrict__ Usol, long long stri
 
 }  // namespace
 
-cudaError_t launch_gather_u0(const double* Usol, long long stride, int nu, int B, double* out, cudaStream_t stream) {
+cudaError_t launch_gather_u0(const double* Usol, long long stride, int nu, int B, double* out, cudaStream_t stream,
+                             const int* st_in, const int* it_in, int* st_out, int* it_out) {
     if (B <= 0) return cudaSuccess;
     const int block = 256, grid = (B * nu + block - 1) / block;
-    gather_u0_kernel<<<grid, block, 0, stream>>>(Usol, stride, nu, B, out);
+    gather_u0_kernel<<<grid, block, 0, stream>>>(Usol, stride, nu, B, out, st_in, it_in, st_out, it_out);
     return cudaGetLastError();
 }
 
