@@ -7,7 +7,7 @@ import cases, oracle
 import tinympc_julia_b200 as t
 
 orc = oracle.load_oracle()
-KS = tuple(int(x) for x in os.environ.get('QONLY', '1,2,3,4').split(','))
+KS = tuple(int(x) for x in os.environ.get('QONLY', '1,2,3').split(','))
 FAST = os.environ.get('QONLY') is not None
 for name in () if FAST else ("cartpole_one_solve", "cartpole_test_basic_bounds", "cartpole_batch_64", "quadrotor_easy_64", "quadrotor_hard_64", "quadrotor_hover", "quadrotor_per_instance_32", "quadrotor_closed_loop_16x40", "rocket_julia_example", "random_5x2_16"):
     c = cases.GOLDEN_CASES[name]()
