@@ -98,7 +98,18 @@ class Workload:
         else:
             raise SystemExit(f"unknown workload {key}")
         self.nx, self.nu = self.sys.nx, self.sys.nu
-        self.flops = problems.flops_per_iteration(self.nx, self.nu, self.N)
+        self.flops = dict(problems.flops_per_iteration(self.nx, self.nu, self.N))
+        self.flops["box_only_F"] = self.flops["F"]
+        if self.cones is not None:
+            # SURVEY.md 8d, rocket row: + ~30 flop per cone per column, 2 (len + 1) per half-space row per column, 5 flop per
+            # element per extra slack / dual pair (cone and half-space pairs on both sides)
+            n, m, N = self.nx, self.nu, self.N
+            ncx, ncu = len(self.cones["Acu"]), len(self.cones["Acx"])          # Julia order: first triple -> state slots
+            nlx, nlu = (len(self.linear[1]), len(self.linear[3])) if self.linear is not None else (0, 0)
+            extra = 30 * (ncx * N + ncu * (N - 1)) + 2 * (n + 1) * nlx * N + 2 * (m + 1) * nlu * (N - 1)
+            pairs = (1 if ncx else 0) + (1 if nlx else 0), (1 if ncu else 0) + (1 if nlu else 0)
+            extra += 5 * (pairs[0] * n * N + pairs[1] * m * (N - 1))
+            self.flops["F"] += extra
 
     def seed(self, rank, k):
         return self.seed0 + NSEEDS * rank + (k % NSEEDS)
@@ -595,7 +606,7 @@ def run_gpu(args, rank, local_rank, world):
                      "peak_nominal_note": f"{nsm} SMs x {64 if f64 else 128} FMA/clk x 2 x {clk / 1e6:.0f} MHz (median SM clock sampled under load)",
                      "achieved_useful_fma": useful_tf, "frac_useful_fma": (useful_tf / peak) if peak else None,
                      "traffic": traffic, "traffic_source": traffic_src,
-                     "flop_per_iter": F, "fma_per_iter": wl.flops["M"], "kernel_ms": kern_ms,
+                     "flop_per_iter": F, "flop_per_iter_box_part": wl.flops["box_only_F"], "fma_per_iter": wl.flops["M"], "kernel_ms": kern_ms,
                      "peak_source": "FMA chains measured live on this GPU by tmpc_measure_fma_peak (MEASURED_PEAKS.json has no CUDA-core peak)",
                      "fp32_fma_peak_tflops": pk32.value},
         "roofline_hbm": {"bound": "hbm", "achieved": hbm_gbs, "peak": peaks_json.get("hbm_gbs"), "unit": "GB/s",
