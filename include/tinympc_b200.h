@@ -147,6 +147,10 @@ int tmpc_batch_create(tmpc_batch** out,
                       double rho, int nx, int nu, int N, int B, int device, int verbose);
 int tmpc_batch_destroy(tmpc_batch* h);
 
+/* Overwrites all settings (reference: src/bindings.cpp:336-376).  Rejected with TMPC_ERR_STATE: check_termination = 0 (the
+ * reference computes iter % 0) and max_iter <= 0.  adaptive_rho != 0 is accepted as a setting (tests/test_settings.jl:63-73
+ * only sets it up) and makes every later solve return TMPC_ERR_STATE with an explanation (through this API the reference
+ * crashes in that branch). */
 int tmpc_batch_update_settings(tmpc_batch* h, double abs_pri_tol, double abs_dua_tol, int max_iter,
                                int check_termination, int en_state_bound, int en_input_bound,
                                int en_state_soc, int en_input_soc, int en_state_linear, int en_input_linear,
@@ -156,11 +160,12 @@ int tmpc_batch_update_settings(tmpc_batch* h, double abs_pri_tol, double abs_dua
  * tinytype`, float being its other build).  bits = 32: the setup is redone as the float build does it (problem data and
  * rho rounded to float as in src/bindings.cpp:50-55, cache computed in float) and later solves run the float
  * instantiation of the kernel, inputs rounded on load as in bindings.cpp:82,105,128 and results widened as in :172,194;
- * the ABI stays double.  Only on a fresh / reset batch with shared dynamics; the float build runs the
- * shared-memory sub-warp kernel where the shape is compiled and the thread kernel otherwise (the TMEM kernels are 64-bit). */
+ * the ABI stays double.  Only on a fresh / reset batch with shared dynamics; the float build runs the float instantiation
+ * of the TMEM kernel where the shape is compiled (else the shared-memory sub-warp kernel, else the thread kernel); the cone
+ * kernel, per-instance dynamics and the device closed loop are 64-bit. */
 int tmpc_batch_set_precision(tmpc_batch* h, int bits);   /* 32 or 64 (default) */
 int tmpc_batch_get_precision(tmpc_batch* h);
-int tmpc_batch_set_kernel(tmpc_batch* h, int kernel);   /* TMPC_KERNEL_*; AUTO picks TMEM, then SUBWARP, where they apply */
+int tmpc_batch_set_kernel(tmpc_batch* h, int kernel);   /* TMPC_KERNEL_*; AUTO picks TMEM, then SUBWARP, then CONE, where they apply, else THREAD */
 int tmpc_batch_get_kernel(tmpc_batch* h);               /* kernel the next solve will run (resolved AUTO) */
 
 /* Queue order of the on-chip (persistent) kernels.  Iteration counts are data-dependent (admm.cpp:312-381), so an
