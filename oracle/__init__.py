@@ -49,6 +49,10 @@ class _CProblem(C.Structure):
         ("num_state_linear", C.c_int), ("Alin_x", _dp), ("blin_x", _dp),
         ("num_input_linear", C.c_int), ("Alin_u", _dp), ("blin_u", _dp),
         ("Kinf", _dp), ("Pinf", _dp), ("Quu_inv", _dp), ("AmBKt", _dp),
+        ("adaptive_rho", C.c_int), ("adaptive_rho_min", C.c_double), ("adaptive_rho_max", C.c_double),
+        ("adaptive_rho_enable_clipping", C.c_int),
+        ("dKinf_drho", _dp), ("dPinf_drho", _dp), ("dC1_drho", _dp), ("dC2_drho", _dp),
+        ("rho_final", _dp), ("Kinf_final", _dp), ("Pinf_final", _dp),
     ]
 
 
@@ -93,6 +97,11 @@ class Problem:
     Alin_u: Optional[np.ndarray] = None
     blin_u: Optional[np.ndarray] = None
     cache: Optional[dict] = None  # {"Kinf","Pinf","Quu_inv","AmBKt"} override (set_cache_terms semantics)
+    adaptive_rho: int = 0            # types.hpp:76-79; defaults as tiny_api.cpp:367-370
+    adaptive_rho_min: float = 1.0
+    adaptive_rho_max: float = 100.0
+    adaptive_rho_enable_clipping: int = 1
+    sensitivity: Optional[dict] = None   # {"dK","dP","dC1","dC2"}: what codegen_with_sensitivity stores (codegen.cpp:91-96)
     _keep: list = field(default_factory=list, repr=False)
 
     @property
@@ -150,6 +159,13 @@ class Problem:
         if self.cache is not None:
             c.Kinf, c.Pinf = dp(self.cache["Kinf"], (nu, nx)), dp(self.cache["Pinf"], (nx, nx))
             c.Quu_inv, c.AmBKt = dp(self.cache["Quu_inv"], (nu, nu)), dp(self.cache["AmBKt"], (nx, nx))
+        c.adaptive_rho = int(self.adaptive_rho)
+        c.adaptive_rho_min, c.adaptive_rho_max = float(self.adaptive_rho_min), float(self.adaptive_rho_max)
+        c.adaptive_rho_enable_clipping = int(self.adaptive_rho_enable_clipping)
+        if self.sensitivity is not None:
+            sv = self.sensitivity
+            c.dKinf_drho, c.dPinf_drho = dp(sv["dK"], (nu, nx)), dp(sv["dP"], (nx, nx))
+            c.dC1_drho, c.dC2_drho = dp(sv["dC1"], (nu, nu)), dp(sv["dC2"], (nx, nx))
         return c
 
 
@@ -192,13 +208,20 @@ class BatchLib:
         xr = None if Xref is None else _f(Xref)
         ur = None if Uref is None else _f(Uref)
         c = prob.to_c()
+        adapt = {}
+        if prob.adaptive_rho:
+            adapt = {"rho": np.zeros(B), "Kinf": np.zeros((nu, nx, B), order="F"), "Pinf": np.zeros((nx, nx, B), order="F")}
+            c.rho_final, c.Kinf_final, c.Pinf_final = (adapt[k].ctypes.data_as(_dp) for k in ("rho", "Kinf", "Pinf"))
         rc = self._run(C.byref(c), B, int(nsteps), x0.ctypes.data_as(_dp),
                        None if xr is None else xr.ctypes.data_as(_dp), None if ur is None else ur.ctypes.data_as(_dp),
                        int(ref_mode), int(nthreads), ret.ctypes.data_as(_ip), iters.ctypes.data_as(_ip),
                        X.ctypes.data_as(_dp), U.ctypes.data_as(_dp), xf.ctypes.data_as(_dp), C.byref(sec))
         if rc != 0:
             raise RuntimeError(f"{self.prefix}_batch_run rejected the problem (status {rc})")
-        return {"ret": ret, "iters": iters, "X": X, "U": U, "x_final": xf, "seconds": sec.value}
+        out = {"ret": ret, "iters": iters, "X": X, "U": U, "x_final": xf, "seconds": sec.value}
+        if adapt:
+            out["adapted"] = adapt
+        return out
 
 
 def build(ref: bool = True, quiet: bool = True) -> None:

@@ -53,6 +53,18 @@ typedef struct {
     /* optional cache override (set_cache_terms semantics, bindings.cpp:277-280): replaces
        Kinf (nu x nx), Pinf (nx x nx), Quu_inv (nu x nu), AmBKt (nx x nx) only. NULL => computed. */
     const double *Kinf, *Pinf, *Quu_inv, *AmBKt;
+
+    /* adaptive rho (admm.cpp:282-357, rho_benchmark.cpp:14-249): the four settings (types.hpp:76-79) and the sensitivity
+       matrices as `codegen_with_sensitivity` leaves them in the LIVE cache (codegen.cpp:91-96: the only loader of
+       arbitrary-shape matrices; tests/test_sensitivity.jl:40-53 is the call sequence).  adaptive_rho != 0 needs all
+       four (dKinf nu x nx, dPinf nx x nx, dC1 nu x nu, dC2 nx x nx); without them the reference adds 0 x 0 matrices
+       and crashes.  The adapted cache (rho, Kinf, Pinf, C1, C2) is solver state: it carries over the steps of ONE
+       instance and every instance starts from the cache tiny_setup computed. */
+    int adaptive_rho; double adaptive_rho_min, adaptive_rho_max; int adaptive_rho_enable_clipping;
+    const double *dKinf_drho, *dPinf_drho, *dC1_drho, *dC2_drho;
+    /* optional outputs of an adaptive run (NULL = not wanted): cache->rho [B], Kinf [nu*nx*B], Pinf [nx*nx*B] after the
+       instance's last step */
+    double *rho_final, *Kinf_final, *Pinf_final;
 } tmpc_problem;
 
 /* reference modes for batch_run */

@@ -88,7 +88,39 @@ TinySolver *make_solver(const tmpc_problem *P) {
     st->en_state_soc = P->en_state_soc; st->en_input_soc = P->en_input_soc;
     st->en_state_linear = P->en_state_linear; st->en_input_linear = P->en_input_linear;
     st->adaptive_rho = 0;
+    if (P->adaptive_rho) {
+        // What the Julia path does (tests/test_sensitivity.jl:40-53): update_settings switches the flag on
+        // (src/bindings.cpp:362-365), codegen_with_sensitivity then stores the four matrices in the live cache
+        // (codegen.cpp:91-96).  Only the stores are repeated here, not the code generation.
+        st->adaptive_rho = 1;
+        st->adaptive_rho_min = static_cast<tinytype>(P->adaptive_rho_min);
+        st->adaptive_rho_max = static_cast<tinytype>(P->adaptive_rho_max);
+        st->adaptive_rho_enable_clipping = P->adaptive_rho_enable_clipping;
+        s->cache->dKinf_drho = tt(MapMat(P->dKinf_drho, nu, nx));
+        s->cache->dPinf_drho = tt(MapMat(P->dPinf_drho, nx, nx));
+        s->cache->dC1_drho = tt(MapMat(P->dC1_drho, nu, nu));
+        s->cache->dC2_drho = tt(MapMat(P->dC2_drho, nx, nx));
+    }
     return s;
+}
+
+// The adapted cache is solver state (update_matrices_with_derivatives, rho_benchmark.cpp:197-211, writes rho, Kinf,
+// Pinf, C1, C2 in place): every instance of the batch starts from the cache tiny_setup computed.
+struct CacheSnapshot {
+    tinytype rho; tinyMatrix Kinf, Pinf, C1, C2;
+    void take(const TinyCache *c) { rho = c->rho; Kinf = c->Kinf; Pinf = c->Pinf; C1 = c->C1; C2 = c->C2; }
+    void restore(TinyCache *c) const { c->rho = rho; c->Kinf = Kinf; c->Pinf = Pinf; c->C1 = C1; c->C2 = C2; }
+};
+
+// solve() declares `RhoAdapter adapter;` (admm.cpp:282) and format_matrices reads
+// adapter->matrices_initialized (rho_benchmark.cpp:56) before anything wrote it.  The reference works when that stack
+// byte happens to be 0 (it is in a fresh process driving the Julia symbols: tools/ref_adaptive_rho_probe2.py) and
+// crashes otherwise.  The driver zeroes the stack region below its own frame before every adaptive solve, which is the
+// condition the reference needs, and changes nothing else.
+__attribute__((noinline)) void scrub_stack() {
+    volatile char buf[1 << 16];
+    std::memset(const_cast<char *>(buf), 0, sizeof buf);
+    asm volatile("" ::: "memory");
 }
 
 // Back to the state tiny_setup leaves (tiny_api.cpp:68-105), without redoing the Riccati cache.
@@ -110,6 +142,7 @@ extern "C" int REF_SYM(_batch_run)(const tmpc_problem *P, int B, int nsteps, con
                              double *Usol, double *x_final, double *seconds) {
     if (!P || B < 0 || nsteps < 1 || !x0) return 1;
     if (P->check_termination == 0) return 2;  // iter % 0 in admm.cpp:255 is a SIGFPE; refuse instead of crashing
+    if (P->adaptive_rho && !(P->dKinf_drho && P->dPinf_drho && P->dC1_drho && P->dC2_drho)) return 6;  // 0 x 0 sensitivities: the reference crashes
     const int nx = P->nx, nu = P->nu, N = P->N;
     if (nthreads < 1) nthreads = 1;
     if (nthreads > B && B > 0) nthreads = B;
@@ -125,10 +158,13 @@ extern "C" int REF_SYM(_batch_run)(const tmpc_problem *P, int B, int nsteps, con
 
     auto worker = [&](int t) {
         TinySolver *s = solvers[t];
+        CacheSnapshot snap;
+        if (P->adaptive_rho) snap.take(s->cache);
         const int lo = (int)((long long)B * t / nthreads), hi = (int)((long long)B * (t + 1) / nthreads);
         tinyVector x(nx);
         for (int b = lo; b < hi; ++b) {
             zero_workspace(s);
+            if (P->adaptive_rho) snap.restore(s->cache);
             if (P->x_min && P->bounds_per_instance) {
                 tiny_set_bound_constraints(s, tt(MapMat(P->x_min + sx * b, nx, N)), tt(MapMat(P->x_max + sx * b, nx, N)),
                                            tt(MapMat(P->u_min + su * b, nu, N - 1)), tt(MapMat(P->u_max + su * b, nu, N - 1)));
@@ -149,6 +185,7 @@ extern "C" int REF_SYM(_batch_run)(const tmpc_problem *P, int B, int nsteps, con
                     const size_t len = (size_t)nx * (N + nsteps - 1);
                     tiny_set_x_ref(s, tt(MapMat(Xref + len * b + (size_t)nx * k, nx, N)));
                 }
+                if (P->adaptive_rho) scrub_stack();
                 const int r = tiny_solve(s);
                 if (ret) ret[(size_t)k * B + b] = r;
                 if (iters) iters[(size_t)k * B + b] = s->solution->iter;
@@ -158,6 +195,11 @@ extern "C" int REF_SYM(_batch_run)(const tmpc_problem *P, int B, int nsteps, con
             if (Xsol) to_double(Xsol + sx * b, s->solution->x);
             if (Usol) to_double(Usol + su * b, s->solution->u);
             if (x_final) to_double(x_final + (size_t)nx * b, x);
+            if (P->adaptive_rho) {
+                if (P->rho_final) P->rho_final[b] = static_cast<double>(s->cache->rho);
+                if (P->Kinf_final) to_double(P->Kinf_final + (size_t)nu * nx * b, s->cache->Kinf);
+                if (P->Pinf_final) to_double(P->Pinf_final + (size_t)nx * nx * b, s->cache->Pinf);
+            }
         }
     };
 
