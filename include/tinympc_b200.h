@@ -57,10 +57,19 @@ int get_controls(double* controls_buffer, int* rows, int* cols);
 /* replaces src/bindings.cpp:205-208 (src/TinyMPC.jl:428-429) */
 void cleanup_solver(void);
 /* replaces src/bindings.cpp:210-225 and :298-331 — code generation for MCUs is outside the
- * accelerated path; the symbols exist and return a non-zero status. */
+ * accelerated path; the symbols exist and return a non-zero status.  codegen_with_sensitivity keeps the half of the
+ * reference call that belongs to the solve path: with adaptive_rho on it stores dK, dP, dC1, dC2 in the live solver
+ * (tinympc/TinyMPC/src/tinympc/codegen.cpp:90-97: the only loader the Julia package has, tests/test_sensitivity.jl:40-53)
+ * before it reports that no code was generated. */
 int codegen(const char* output_dir, int verbose);
 int codegen_with_sensitivity(const char* output_dir,
                              double* dK_data, int dK_rows, int dK_cols,
+                             double* dP_data, int dP_rows, int dP_cols,
+                             double* dC1_data, int dC1_rows, int dC1_cols,
+                             double* dC2_data, int dC2_rows, int dC2_cols, int verbose);
+/* NEW (no counterpart in src/bindings.cpp): the loader alone, returns 0.  dK nu x nx, dP nx x nx, dC1 nu x nu, dC2 nx x nx,
+ * column-major (what compute_sensitivity_autograd returns, src/TinyMPC.jl:301-323). */
+int set_sensitivity_matrices(double* dK_data, int dK_rows, int dK_cols,
                              double* dP_data, int dP_rows, int dP_cols,
                              double* dC1_data, int dC1_rows, int dC1_cols,
                              double* dC2_data, int dC2_rows, int dC2_cols, int verbose);
@@ -149,8 +158,7 @@ int tmpc_batch_destroy(tmpc_batch* h);
 
 /* Overwrites all settings (reference: src/bindings.cpp:336-376).  Rejected with TMPC_ERR_STATE: check_termination = 0 (the
  * reference computes iter % 0) and max_iter <= 0.  adaptive_rho != 0 is accepted as a setting (tests/test_settings.jl:63-73
- * only sets it up) and makes every later solve return TMPC_ERR_STATE with an explanation (through this API the reference
- * crashes in that branch). */
+ * only sets it up); solves with the flag on need tmpc_batch_set_sensitivity (below). */
 int tmpc_batch_update_settings(tmpc_batch* h, double abs_pri_tol, double abs_dua_tol, int max_iter,
                                int check_termination, int en_state_bound, int en_input_bound,
                                int en_state_soc, int en_input_soc, int en_state_linear, int en_input_linear,
@@ -215,8 +223,22 @@ int tmpc_batch_set_cache_terms(tmpc_batch* h, const double* Kinf, const double* 
 int tmpc_batch_get_cache_terms(tmpc_batch* h, double* Kinf, double* Pinf, double* Quu_inv, double* AmBKt,
                                double* APf, double* BPf);
 
-/* Back to the zero workspace (cold start): duals, slacks, linear cost terms and solution cleared;
- * x0, references, constraints and settings kept. */
+/* Adaptive rho (reference: solve, tinympc/TinyMPC/src/tinympc/admm.cpp:331-357; benchmark_rho_adaptation,
+ * rho_benchmark.cpp:213-249).  With adaptive_rho on (tmpc_batch_update_settings) every instance re-estimates rho after
+ * iterations 6, 11, 16, ... from the reference's residual ratio and applies the first-order update
+ * Kinf += d_rho * dKinf_drho, Pinf += d_rho * dPinf_drho to ITS OWN copy of the cache; like the reference's cache, the
+ * adapted rho / Kinf / Pinf stay with the instance over later solves (also after the flag is cleared) until
+ * tmpc_batch_reset.  The sensitivity matrices are shared (column-major dKinf nu x nx, dPinf nx x nx, dC1 nu x nu,
+ * dC2 nx x nx - the reference stores them with codegen_with_sensitivity, codegen.cpp:90-97); a solve with the flag on
+ * and no matrices returns TMPC_ERR_STATE (the reference crashes there).  64-bit build, shared dynamics, thread kernel
+ * (TMPC_KERNEL_AUTO selects it). */
+int tmpc_batch_set_sensitivity(tmpc_batch* h, const double* dKinf_drho, const double* dPinf_drho, const double* dC1_drho,
+                               const double* dC2_drho);
+/* The cache every instance currently solves with: rho [B], Kinf nu x nx x B, Pinf nx x nx x B (any may be NULL). */
+int tmpc_batch_get_adapted_cache(tmpc_batch* h, double* rho, double* Kinf, double* Pinf);
+
+/* Back to the zero workspace (cold start): duals, slacks, linear cost terms and solution cleared, every instance back
+ * on the cache the setup computed; x0, references, constraints and settings kept. */
 int tmpc_batch_reset(tmpc_batch* h);
 
 /* Solve all instances (warm-started from each instance's own carried state).  Returns 0 when every

@@ -218,6 +218,10 @@ extern "C" int REF_SYM(_batch_run)(const tmpc_problem *P, int B, int nsteps, con
     return 0;
 }
 
+// For tests that drive the reference's Julia-facing library (libtinympc_jl.so) with adaptive rho from Python: call this
+// right before solve_mpc on the same thread (Q12, see scrub_stack above).
+extern "C" void REF_SYM(_scrub_stack)(void) { scrub_stack(); }
+
 extern "C" int REF_SYM(_get_cache)(const tmpc_problem *P, double *Kinf, double *Pinf, double *Quu_inv, double *AmBKt,
                              double *APf, double *BPf) {
     TinySolver *s = make_solver(P);

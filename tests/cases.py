@@ -31,7 +31,7 @@ RTOL_F32, ATOL_F32 = 1e-4, 1e-5
 def _base(sys_, N, **kw):
     c = dict(sys=sys_, N=N, abs_pri_tol=1e-3, abs_dua_tol=1e-3, max_iter=100, check_termination=1,
              bounds=None, bounds_per_instance=False, cones=None, linear=None,
-             x0=None, Xref=None, Uref=None, ref_mode=oracle.REF_ZERO, nsteps=1, cache=None)
+             x0=None, Xref=None, Uref=None, ref_mode=oracle.REF_ZERO, nsteps=1, cache=None, adaptive=None)
     c.update(kw)
     return c
 
@@ -94,6 +94,17 @@ def quadrotor_closed_loop(B, nsteps, seed=5):
     return _base(s, N, bounds=s.bounds(N), x0=x0, Xref=Xlong, ref_mode=oracle.REF_SLIDING, nsteps=nsteps)
 
 
+def with_adaptive_rho(c, lo=0.1, hi=10.0, clip=True):
+    """the case solved with adaptive rho.  rho is kept inside [lo, hi] x the setup rho; the
+    sensitivity matrices are the Julia package's own finite differences (src/TinyMPC.jl:301-351), loaded the way
+    tests/test_sensitivity.jl:40-53 loads them (codegen_with_sensitivity stores them in the live cache)."""
+    from tinympc_julia_b200 import lqr_sensitivity
+    s = c["sys"]
+    dK, dP, dC1, dC2 = lqr_sensitivity(s.A, s.B, s.Q, s.R, s.rho)
+    c["adaptive"] = dict(rho_min=lo * s.rho, rho_max=hi * s.rho, clip=bool(clip), sens=dict(dK=dK, dP=dP, dC1=dC1, dC2=dC2))
+    return c
+
+
 def rocket(B, N=50, seed=4, linear=True, tol_pri=2e-3):
     """config 4: box + both cones (Julia argument order, so SURVEY.md Q1 applies) + synthetic half-spaces."""
     s = problems.rocket()
@@ -148,6 +159,10 @@ def to_oracle_problem(c) -> oracle.Problem:
     p = oracle.Problem(A=s.A, B=s.B, Q=s.Q, R=s.R, rho=s.rho, N=c["N"], f=s.f,
                        abs_pri_tol=c["abs_pri_tol"], abs_dua_tol=c["abs_dua_tol"], max_iter=c["max_iter"],
                        check_termination=c["check_termination"], cache=c["cache"])
+    if c.get("adaptive"):
+        ad = c["adaptive"]
+        p.adaptive_rho, p.adaptive_rho_min, p.adaptive_rho_max = 1, ad["rho_min"], ad["rho_max"]
+        p.adaptive_rho_enable_clipping, p.sensitivity = int(ad["clip"]), ad["sens"]
     if c["bounds"] is not None:
         p.with_bounds(*c["bounds"], per_instance=c["bounds_per_instance"])
     if c["cones"] is not None:
@@ -175,9 +190,15 @@ def make_cuda_solver(c, kernel=0, device=-1, precision=64):
     s = c["sys"]
     B = c["x0"].shape[1]
     sol = t.TinyMPCBatchSolver()
+    ad = c.get("adaptive")
+    adkw = dict(adaptive_rho=True, adaptive_rho_min=ad["rho_min"], adaptive_rho_max=ad["rho_max"],
+                adaptive_rho_clipping=ad["clip"]) if ad else {}
     t.setup(sol, s.A, s.B, s.f, s.Q, s.R, s.rho, s.nx, s.nu, c["N"], batch=B, device=device,
             abs_pri_tol=c["abs_pri_tol"], abs_dua_tol=c["abs_dua_tol"], max_iter=c["max_iter"],
-            check_termination=bool(c["check_termination"]))
+            check_termination=bool(c["check_termination"]), **adkw)
+    if ad:
+        v = ad["sens"]
+        t.set_sensitivity(sol, v["dK"], v["dP"], v["dC1"], v["dC2"])
     if precision != 64:
         sol.set_precision(precision)
     if c["cache"] is not None:
@@ -321,6 +342,13 @@ GOLDEN_CASES = {
     "rocket_soc_16_N20": lambda: rocket(16, N=20, linear=False),
     "random_5x2_16": lambda: random_system(5, 2, 8, 16),
     "random_9x3_16": lambda: random_system(9, 3, 12, 16, seed=9, with_linear=False),
+    # adaptive rho: fixtures also hold the adapted rho of every instance
+    "adaptive_quadrotor_easy_64": lambda: with_adaptive_rho(quadrotor_batch(64)),
+    "adaptive_quadrotor_hard_64": lambda: with_adaptive_rho(quadrotor_batch(64, hard=True)),
+    "adaptive_cartpole_64": lambda: with_adaptive_rho(cartpole_batch(64)),
+    "adaptive_quadrotor_closed_loop_16x12": lambda: with_adaptive_rho(quadrotor_closed_loop(16, 12)),
+    "adaptive_rocket_soc_linear_8": lambda: with_adaptive_rho(rocket(8, N=20)),
+    "adaptive_random_5x2_16": lambda: with_adaptive_rho(random_system(5, 2, 8, 16), clip=False),
 }
 
 # values quoted in SURVEY.md §8c / BASELINE.md §2 (captured from the compiled reference during the survey)

@@ -29,6 +29,9 @@ def digest(c):
     for a in (s.A, s.B, s.f, s.Q, s.R):
         h.update(np.ascontiguousarray(a).tobytes())
     h.update(repr((c["N"], c["max_iter"], c["abs_pri_tol"], c["abs_dua_tol"], c["nsteps"], c["ref_mode"])).encode())
+    if c.get("adaptive"):
+        ad = c["adaptive"]
+        h.update(repr((ad["rho_min"], ad["rho_max"], ad["clip"])).encode())
     return h.hexdigest()
 
 
@@ -36,11 +39,17 @@ def main():
     ref = oracle.load_ref()
     if ref is None:
         raise SystemExit("oracle/_ref is not built: run `make -C oracle ref` where /root/reference exists")
+    only = set(sys.argv[1:])        # optional: names of the fixtures to (re)generate; default all
     for name, make in cases.GOLDEN_CASES.items():
+        if only and name not in only:
+            continue
         c = make()
         out = cases.run_checker(c, ref)
+        extra = {}
+        if "adapted" in out:        # adaptive rho: the cache every instance ends with
+            extra = {"adapted_rho": out["adapted"]["rho"], "adapted_Kinf": out["adapted"]["Kinf"]}
         np.savez_compressed(os.path.join(HERE, name + ".npz"), ret=out["ret"], iters=out["iters"], X=out["X"], U=out["U"],
-                            x_final=out["x_final"], digest=np.array(digest(c)))
+                            x_final=out["x_final"], digest=np.array(digest(c)), **extra)
         print(f"{name:32s} B={c['x0'].shape[1]:4d} steps={c['nsteps']:3d} iters[min/max]={out['iters'].min()}/{out['iters'].max()} "
               f"solved={(out['ret'] == 0).mean():.2f}")
     # ---- float build of the reference (oracle/Makefile target ref32)
@@ -48,6 +57,8 @@ def main():
     if ref32 is None:
         raise SystemExit("oracle/_ref/libtinympc_refbatch32.so is not built: run `make -C oracle ref32`")
     for name in cases.GOLDEN_F32_CASES:
+        if only and ("f32_" + name) not in only:
+            continue
         c = cases.GOLDEN_CASES[name]()
         out = cases.run_checker(c, ref32)
         cache = ref32.get_cache(cases.to_oracle_problem(c))

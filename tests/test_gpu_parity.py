@@ -513,20 +513,3 @@ def test_float_build_warm_start_and_guards():
     back = cases.run_cuda(cases.GOLDEN_CASES["quadrotor_easy_64"](), sol=sol)
     cases.compare(back, cases.load_golden("quadrotor_easy_64"), what="double again after set_precision(64)")
 
-
-@pytest.mark.gpu
-def test_adaptive_rho_is_refused_not_imitated():
-    """SURVEY.md 8f rank 4 / DESIGN.md 8 item 4: through the reference's own symbols the adaptive-rho branch reads
-    0 x 0 sensitivity matrices (rho_benchmark.cpp:204-207 after src/bindings.cpp:362) and crashes.  The SETTING binds
-    (tests/test_settings.jl:63-73 only sets it up and never solves); a solve with it on is refused with a message
-    instead of imitating the crash; clearing the flag restores the solver."""
-    from tinympc_julia_b200 import _lib
-    c = cases.GOLDEN_CASES["quadrotor_easy_64"]()
-    sol = cases.make_cuda_solver(c, kernel=t.KERNEL_AUTO)
-    t.update_settings(sol, max_iter=100, en_state_bound=True, en_input_bound=True, adaptive_rho=True)
-    t.set_x0(sol, c["x0"])
-    assert t.solve(sol) not in (0, 1)
-    assert "adaptive_rho" in _lib.last_error()
-    t.update_settings(sol, max_iter=100, en_state_bound=True, en_input_bound=True, adaptive_rho=False)
-    out = cases.run_cuda(c, sol=sol)
-    cases.compare(out, cases.load_golden("quadrotor_easy_64"), what="after clearing adaptive_rho")

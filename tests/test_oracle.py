@@ -64,3 +64,55 @@ def test_reference_rejects_zero_check_termination(orc):
     c["check_termination"] = 0
     with pytest.raises(RuntimeError):
         cases.run_checker(c, orc)
+
+
+# ------------------------------------------------------------------ adaptive rho
+
+def test_sensitivity_matrices_like_the_julia_package():
+    """tests/test_sensitivity.jl:18-85 on the host-side mirror of compute_sensitivity_autograd (src/TinyMPC.jl:301-351):
+    shapes, finite, deterministic, different at another rho; and the forward difference is a derivative (it agrees with
+    a central difference of the same fixed point to first order in the step)."""
+    from tinympc_julia_b200 import lqr_sensitivity, problems
+    s = problems.cartpole()
+    A, B, Q, R = s.A, s.B.reshape(4, 1), s.Q, s.R
+    dK, dP, dC1, dC2 = lqr_sensitivity(A, B, Q, R, 1.0)
+    assert dK.shape == (1, 4) and dP.shape == (4, 4) and dC1.shape == (1, 1) and dC2.shape == (4, 4)
+    assert all(np.isfinite(m).all() for m in (dK, dP, dC1, dC2))
+    again = lqr_sensitivity(A, B, Q, R, 1.0)
+    assert all(np.array_equal(a, b) for a, b in zip((dK, dP, dC1, dC2), again))
+    other = lqr_sensitivity(A, B, Q, R, 2.0)
+    assert all(not np.allclose(a, b) for a, b in zip((dK, dP, dC1, dC2), other))
+    from tinympc_julia_b200.solver import _solve_lqr
+    h = 1e-4
+    central = [(y - x) / (2 * h) for x, y in zip(_solve_lqr(A, B, Q, R, 1.0 - h), _solve_lqr(A, B, Q, R, 1.0 + h))]
+    for a, b in zip((dK, dP, dC1, dC2), central):
+        np.testing.assert_allclose(a, b, rtol=2e-3, atol=1e-6 * max(1.0, np.abs(b).max()))
+
+
+def test_adaptive_branch_changes_rho_and_matches_reference_cache(orc, ref):
+    """The adapted cache (rho, Kinf, Pinf of every instance after the solve) of the oracle against the compiled reference's;
+    the branch is live (rho leaves its setup value) and stays inside the clip interval."""
+    c = cases.with_adaptive_rho(cases.quadrotor_batch(96, seed=17))
+    a = cases.run_checker(c, orc)
+    rho0 = c["sys"].rho
+    assert (a["adapted"]["rho"] != rho0).any()
+    assert a["adapted"]["rho"].min() >= 0.1 * rho0 - 1e-12 and a["adapted"]["rho"].max() <= 10 * rho0 + 1e-12
+    short = a["iters"][0] <= 5                                 # solves that stop before iteration 6 never adapt
+    assert np.all(a["adapted"]["rho"][short] == rho0)
+    if ref is None:
+        pytest.skip("oracle/_ref not built")
+    b = cases.run_checker(c, ref)
+    for k in ("rho", "Kinf", "Pinf"):
+        np.testing.assert_allclose(a["adapted"][k], b["adapted"][k], rtol=1e-9, atol=1e-11, err_msg=k)
+
+
+def test_adaptive_without_sensitivity_is_rejected(orc, ref):
+    """0 x 0 sensitivity matrices: the reference crashes (rho_benchmark.cpp:204-207); both checkers refuse instead."""
+    c = cases.with_adaptive_rho(cases.cartpole_batch(4))
+    p = cases.to_oracle_problem(c)
+    p.sensitivity = None
+    for lib in (orc, ref):
+        if lib is None:
+            continue
+        with pytest.raises(RuntimeError):
+            lib.batch_run(p, c["x0"])

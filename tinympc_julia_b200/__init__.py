@@ -9,6 +9,7 @@ from .solver import (  # noqa: F401
     Solution, TinyMPCBatchSolver, TinyMPCError, TinyMPCSolver, cleanup, codegen, get_solution, get_solve_info,
     print_problem_data, set_bound_constraints, set_cache_terms, set_cone_constraints, set_equality_constraints,
     set_instance_dynamics, set_linear_constraints, set_u_ref, set_x0, set_x_ref, setup, solve, update_settings,
+    codegen_with_sensitivity, compute_sensitivity_autograd, get_adapted_cache, lqr_sensitivity, set_sensitivity,
 )
 
 KERNEL_AUTO, KERNEL_THREAD, KERNEL_SUBWARP, KERNEL_TMEM, KERNEL_CONE = 0, 1, 2, 3, 4

@@ -32,6 +32,7 @@ SIGNATURES = {
     "cleanup_solver": (None, []),
     "codegen": (_I, [C.c_char_p, _I]),
     "codegen_with_sensitivity": (_I, [C.c_char_p] + _MAT * 4 + [_I]),
+    "set_sensitivity_matrices": (_I, _MAT * 4 + [_I]),
     "print_problem_data": (_I, [_I]),
     "set_cache_terms": (_I, _MAT * 4 + [_I]),
     "update_settings": (_I, [_D, _D, _I, _I, _I, _I, _I, _I, _I, _I, _I, _D, _D, _I, _I]),
@@ -61,6 +62,8 @@ SIGNATURES = {
     "tmpc_batch_get_settings": (_I, [_V, _P, _IP]),
     "tmpc_batch_set_cache_terms": (_I, [_V, _P, _P, _P, _P]),
     "tmpc_batch_get_cache_terms": (_I, [_V, _P, _P, _P, _P, _P, _P]),
+    "tmpc_batch_set_sensitivity": (_I, [_V, _P, _P, _P, _P]),
+    "tmpc_batch_get_adapted_cache": (_I, [_V, _P, _P, _P]),
     "tmpc_batch_reset": (_I, [_V]),
     "tmpc_batch_solve": (_I, [_V]),
     "tmpc_batch_solve_async": (_I, [_V, _V]),

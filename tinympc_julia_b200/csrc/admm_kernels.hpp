@@ -41,6 +41,29 @@ cudaError_t launch_admm_thread_per_instance(const BatchView& bv, const AdmmSetti
 cudaError_t launch_admm_thread(const BatchView& bv, const AdmmSettings& st, const HostMats& h, cudaStream_t stream,
                                int precision = 64);
 
+// ---- adaptive rho on the thread kernel (reference admm.cpp:331-357, rho_benchmark.cpp).  The
+// reference adapts rho, Kinf, Pinf (and C1, C2, which the solve never reads) in place in the solver's cache, so for a
+// batch they are per-instance carried state: element-major arrays [e][ld], broadcast from the shared cache by
+// launch_adaptive_init, updated by the solve, kept across solves.  dK / dP are the shared sensitivity matrices
+// (column-major nu x nx, nx x nx) that `codegen_with_sensitivity` stores in the reference's cache (codegen.cpp:91-96).
+struct AdaptiveRho {
+    int enabled;                 // settings->adaptive_rho; 0 = solve with the adapted cache as it stands (the reference keeps it
+                                 // after the flag is cleared)
+    int clip;                    // adaptive_rho_enable_clipping
+    double rho_min, rho_max;
+    double* rho;                 // [ld]
+    double* Kinf;                // [nu * nx][ld]
+    double* Pinf;                // [nx * nx][ld]
+    const double* dK;
+    const double* dP;
+};
+// keep_rho: only Kinf / Pinf are re-broadcast (set_cache_terms on an adapted batch: bindings.cpp:277-280 leaves cache->rho alone)
+cudaError_t launch_adaptive_init(const BatchView& bv, const AdaptiveRho& ad, cudaStream_t stream, bool keep_rho = false);
+cudaError_t launch_adaptive_gather(const BatchView& bv, const AdaptiveRho& ad, double* Kinf, double* Pinf,
+                                   cudaStream_t stream);
+cudaError_t launch_admm_thread_adaptive(const BatchView& bv, const AdmmSettings& st, const AdaptiveRho& ad,
+                                        cudaStream_t stream);
+
 // ---- one instance per 4-lane sub-warp, shared-memory resident (admm_subwarp.cu)
 // Applies to box-constrained problems (no cone / half-space flags) of a compiled-in shape.
 bool subwarp_kernel_supports(int nx, int nu, int N, const AdmmSettings& st, int precision = 64);

@@ -19,6 +19,11 @@
 //   solve                reference admm.cpp:274-389
 // The slack/dual/cost/residual updates are elementwise per knot point, so they are fused into the
 // forward sweep column by column; x, u and p never leave registers.
+//
+// Adaptive rho (reference admm.cpp:331-357 + rho_benchmark.cpp) runs here as well: the
+// MatsAdaptive operand provider gives every instance its own rho, Kinf and Pinf (the reference updates them in place
+// in the solver's cache, so in a batch they are per-instance carried state), and after every fifth iteration the
+// thread re-rolls its trajectory, forms the reference's residual ratio and applies the first-order update.
 #include <cuda_runtime.h>
 
 #include "admm_device.cuh"
@@ -41,6 +46,7 @@ template <class T, int NX, int NU>
 struct MatsConst {           // by-value kernel parameter -> constant bank
     static constexpr int kMaxNx = NX, kMaxNu = NU;
     static constexpr bool kStatic = true;
+    static constexpr bool kAdaptive = false;
     __device__ __forceinline__ const MatsConst& bound(int) const { return *this; }
     T A_[NX * NX], B_[NX * NU], Kinf_[NU * NX], AmBKt_[NX * NX], Quu_inv_[NU * NU], Pinf_[NX * NX];
     T f_[NX], APf_[NX], BPf_[NU], Qd_[NX], Rd_[NU];
@@ -62,6 +68,7 @@ struct MatsConst {           // by-value kernel parameter -> constant bank
 struct MatsGlobal {          // runtime dimensions: uniform loads through the read-only path
     static constexpr int kMaxNx = kThreadKernelMaxNx, kMaxNu = kThreadKernelMaxNu;
     static constexpr bool kStatic = false;
+    static constexpr bool kAdaptive = false;
     __device__ __forceinline__ const MatsGlobal& bound(int) const { return *this; }
     int nx_, nu_;
     const double *A_, *B_, *Kinf_, *AmBKt_, *Quu_inv_, *Pinf_, *f_, *APf_, *BPf_, *Qd_, *Rd_;
@@ -85,6 +92,7 @@ template <int NX, int NU>            // NX = 0: run-time dimensions (rolled loop
 struct MatsPerInstance {
     static constexpr int kMaxNx = NX ? NX : kPerInstanceMaxNx, kMaxNu = NX ? NU : kPerInstanceMaxNu;
     static constexpr bool kStatic = NX != 0;
+    static constexpr bool kAdaptive = false;
     int nx_, nu_;
     long long ld_;
     PerInstanceMats p_;
@@ -106,6 +114,33 @@ struct MatsPerInstance {
     __device__ __forceinline__ double Rd(int i) const { return at(p_.Rd, i); }
 };
 
+// adaptive rho: shared dynamics, but rho, Kinf and Pinf belong to the instance (element-major [e][ld], written by the
+// owning thread during the solve: plain loads, not the read-only path)
+template <int NX, int NU>            // NX = 0: run-time dimensions
+struct MatsAdaptive {
+    static constexpr int kMaxNx = NX ? NX : kThreadKernelMaxNx, kMaxNu = NX ? NU : kThreadKernelMaxNu;
+    static constexpr bool kStatic = NX != 0;
+    static constexpr bool kAdaptive = true;
+    int nx_, nu_;
+    long long ld_, b_;
+    const double *A_, *B_, *AmBKt_, *Quu_inv_, *f_, *APf_, *BPf_, *Qd_, *Rd_;
+    AdaptiveRho ad_;
+    __device__ __forceinline__ MatsAdaptive bound(int b) const { MatsAdaptive m = *this; m.b_ = b; return m; }
+    __device__ __forceinline__ int nx() const { return NX ? NX : nx_; }
+    __device__ __forceinline__ int nu() const { return NX ? NU : nu_; }
+    __device__ __forceinline__ double A(int i, int k) const { return __ldg(A_ + k * nx() + i); }
+    __device__ __forceinline__ double B(int i, int k) const { return __ldg(B_ + k * nx() + i); }
+    __device__ __forceinline__ double Kinf(int i, int k) const { return ad_.Kinf[(k * nu() + i) * ld_ + b_]; }
+    __device__ __forceinline__ double AmBKt(int i, int k) const { return __ldg(AmBKt_ + k * nx() + i); }
+    __device__ __forceinline__ double Quu_inv(int i, int k) const { return __ldg(Quu_inv_ + k * nu() + i); }
+    __device__ __forceinline__ double Pinf(int i, int k) const { return ad_.Pinf[(k * nx() + i) * ld_ + b_]; }
+    __device__ __forceinline__ double f(int i) const { return __ldg(f_ + i); }
+    __device__ __forceinline__ double APf(int i) const { return __ldg(APf_ + i); }
+    __device__ __forceinline__ double BPf(int i) const { return __ldg(BPf_ + i); }
+    __device__ __forceinline__ double Qd(int i) const { return __ldg(Qd_ + i); }
+    __device__ __forceinline__ double Rd(int i) const { return __ldg(Rd_ + i); }
+};
+
 template <class T, class M>
 __global__ void __launch_bounds__(kThreadKernelBlock)
 admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ BatchView bv,
@@ -118,7 +153,8 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
     const auto& mt = mt_param.bound(b);        // per-instance dynamics: operands of THIS instance; else the parameter itself
     const int nx = mt.nx(), nu = mt.nu(), N = bv.N;
     const size_t ld = static_cast<size_t>(bv.ld);
-    const T rho = static_cast<T>(bv.rho);                       // bindings.cpp:55
+    T rho = static_cast<T>(bv.rho);                             // bindings.cpp:55
+    if constexpr (M::kAdaptive) rho = static_cast<T>(mt.ad_.rho[b]);   // cache->rho of this instance (adapted by earlier solves)
     const T tol_pri = static_cast<T>(st.abs_pri_tol), tol_dua = static_cast<T>(st.abs_dua_tol);   // types.hpp:64-65
     // Carried state and scratch are the kernel's private format: element-major arrays of T.  The float instantiation
     // uses the first half of each (double-sized) allocation, which halves the bytes an iteration streams through L2 / HBM.
@@ -329,6 +365,114 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
         }
 
         iter += 1;
+
+        // ---------------- adaptive rho (reference admm.cpp:331-357): after iterations 6, 11, 16, ... and BEFORE the
+        // termination test, which then multiplies the dual residuals by the new rho.  benchmark_rho_adaptation
+        // (rho_benchmark.cpp:213-249) writes the horizon as one dense problem [x_0 u_0 x_1 ... x_{N-1}] with an identity
+        // row block per input and a row block [A B -I] per step; only the non-zero blocks are evaluated here, on a second
+        // roll-out of the trajectory (same operations as the forward sweep, so the same x and u).  Quirks kept: the
+        // dynamics rows carry no f and are compared with the SLACK vnew_{i+1} (:97-98, :158), the duals are the updated
+        // ones, q = Qd .* x at the terminal knot too (:135), Pinf enters before it is updated (:113).
+        if constexpr (M::kAdaptive) {
+            if (mt.ad_.enabled && it > 0 && it % 5 == 0) {
+                T pri_res = 0, max_Ax = 0, max_z = 0, dual_res = 0, max_Px = 0, max_ATy = 0, max_q = 0;
+#pragma unroll UNR
+                for (int j = 0; j < MX; ++j) if (j < nx) x[j] = bv.x0[static_cast<size_t>(b) * nx + j];
+                for (int i = 0; i < N; ++i) {
+                    const bool terminal = (i == N - 1);
+                    if (!terminal) {
+#pragma unroll UNR
+                        for (int j = 0; j < MU; ++j) if (j < nu) {
+                            T s = 0;
+#pragma unroll UNR
+                            for (int k = 0; k < MX; ++k) if (k < nx) s = R::fma(mt.Kinf(j, k), x[k], s);
+                            u[j] = R::sub(-s, ST(bv.d, i * nu + j));
+                            const T zj = ST(z_new, i * nu + j);               // input rows: (A x) = u_i, z = znew_i
+                            pri_res = R::max(pri_res, R::abs(R::sub(u[j], zj)));
+                            max_Ax = R::max(max_Ax, R::abs(u[j]));
+                            max_z = R::max(max_z, R::abs(zj));
+                        }
+#pragma unroll UNR
+                        for (int j = 0; j < MX; ++j) if (j < nx) acc[j] = ST(bv.g, (i + 1) * nx + j);     // g_{i+1}
+#pragma unroll UNR
+                        for (int j = 0; j < MX; ++j) if (j < nx) {
+                            T s1 = 0.0, s2 = 0.0;
+#pragma unroll UNR
+                            for (int k = 0; k < MX; ++k) if (k < nx) s1 = R::fma(mt.A(j, k), x[k], s1);
+#pragma unroll UNR
+                            for (int k = 0; k < MU; ++k) if (k < nu) s2 = R::fma(mt.B(j, k), u[k], s2);
+                            const T ab = R::add(s1, s2);
+                            tmp[j] = R::add(ab, mt.f(j));                       // x_{i+1} as the forward sweep computed it
+                            const T dyn = R::sub(ab, tmp[j]);                   // dynamics row: A x_i + B u_i - x_{i+1}
+                            const T vn = ST(v_new, (i + 1) * nx + j);           // ... against z = vnew_{i+1}
+                            pri_res = R::max(pri_res, R::abs(R::sub(dyn, vn)));
+                            max_Ax = R::max(max_Ax, R::abs(dyn));
+                            max_z = R::max(max_z, R::abs(vn));
+                        }
+#pragma unroll UNR
+                        for (int j = 0; j < MU; ++j) if (j < nu) {              // u_i block of P x + q + A' y
+                            const T Px = R::mul(mt.Rd(j), u[j]);                // = q (zero reference, :141-143)
+                            T aty = ST(bv.y, i * nu + j);
+#pragma unroll UNR
+                            for (int k = 0; k < MX; ++k) if (k < nx) aty = R::fma(mt.B(k, j), acc[k], aty);
+                            dual_res = R::max(dual_res, R::abs(R::add(R::add(Px, Px), aty)));
+                            max_Px = R::max(max_Px, R::abs(Px));
+                            max_q = R::max(max_q, R::abs(Px));
+                            max_ATy = R::max(max_ATy, R::abs(aty));
+                        }
+                    }
+#pragma unroll UNR
+                    for (int j = 0; j < MX; ++j) if (j < nx) {                  // x_i block
+                        const T qv = R::mul(mt.Qd(j), x[j]);
+                        T Px = qv;
+                        if (terminal) {
+                            Px = 0;
+#pragma unroll UNR
+                            for (int k = 0; k < MX; ++k) if (k < nx) Px = R::fma(mt.Pinf(j, k), x[k], Px);
+                        }
+                        T aty = 0;
+                        if (i >= 1) aty = -ST(bv.g, i * nx + j);                // -I of the previous dynamics block (y = g_i)
+                        if (!terminal) {
+#pragma unroll UNR
+                            for (int k = 0; k < MX; ++k) if (k < nx) aty = R::fma(mt.A(k, j), acc[k], aty);   // A' g_{i+1}
+                        }
+                        dual_res = R::max(dual_res, R::abs(R::add(R::add(Px, qv), aty)));
+                        max_Px = R::max(max_Px, R::abs(Px));
+                        max_q = R::max(max_q, R::abs(qv));
+                        max_ATy = R::max(max_ATy, R::abs(aty));
+                    }
+                    if (!terminal) {
+#pragma unroll UNR
+                        for (int j = 0; j < MX; ++j) if (j < nx) x[j] = tmp[j];
+                    }
+                }
+                // predict_rho (rho_benchmark.cpp:179-202)
+                const T eps = static_cast<T>(1e-10);
+                const T pri_norm = R::max(max_Ax, max_z);
+                const T dual_norm = R::max(R::max(max_Px, max_ATy), max_q);
+                const T n_pri = R::div(pri_res, R::add(pri_norm, eps));
+                const T n_dua = R::div(dual_res, R::add(dual_norm, eps));
+                T new_rho = R::mul(rho, R::sqrt(R::div(n_pri, R::add(n_dua, eps))));
+                if (mt.ad_.clip) {                                              // std::min(std::max(new_rho, lo), hi)
+                    const T lo = static_cast<T>(mt.ad_.rho_min), hi = static_cast<T>(mt.ad_.rho_max);
+                    new_rho = (new_rho < lo) ? lo : new_rho;
+                    new_rho = (hi < new_rho) ? hi : new_rho;
+                }
+                // update_matrices_with_derivatives (:204-218): first-order update of this instance's Kinf and Pinf.
+                // (C1 / C2 are updated there as well; nothing in the solve path reads them - the loop uses Quu_inv / AmBKt.)
+                const T delta = R::sub(new_rho, rho);
+                for (int e = 0; e < nu * nx; ++e) {
+                    double* p_ = mt.ad_.Kinf + static_cast<size_t>(e) * ld + b;
+                    *p_ = R::add(static_cast<T>(*p_), R::mul(delta, static_cast<T>(__ldg(mt.ad_.dK + e))));
+                }
+                for (int e = 0; e < nx * nx; ++e) {
+                    double* p_ = mt.ad_.Pinf + static_cast<size_t>(e) * ld + b;
+                    *p_ = R::add(static_cast<T>(*p_), R::mul(delta, static_cast<T>(__ldg(mt.ad_.dP + e))));
+                }
+                rho = new_rho;
+            }
+        }
+
         if (iter % st.check_termination == 0) {
             converged = pri_x < tol_pri && pri_u < tol_pri &&
                         R::mul(dua_x, rho) < tol_dua && R::mul(dua_u, rho) < tol_dua;
@@ -352,6 +496,7 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
     for (int j = 0; j < MX; ++j) if (j < nx) ST(bv.pN, j) = p[j];
     bv.status[b] = converged ? 0 : 1;
     bv.iters[b] = iter;
+    if constexpr (M::kAdaptive) mt.ad_.rho[b] = rho;
 #undef ST
 }
 
@@ -402,7 +547,57 @@ cudaError_t launch_per_instance(const BatchView& bv, const AdmmSettings& st, con
     return go(MatsPerInstance<0, 0>{});
 }
 
+// broadcast of the shared cache into the per-instance adaptive state (fresh / reset batch, new cache terms)
+__global__ void adaptive_init_kernel(AdaptiveRho ad, const double* __restrict__ Kinf, const double* __restrict__ Pinf,
+                                     double rho, int nkinf, int npinf, int B, long long ld, bool keep_rho) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    for (int e = 0; e < nkinf; ++e) ad.Kinf[e * ld + b] = __ldg(Kinf + e);
+    for (int e = 0; e < npinf; ++e) ad.Pinf[e * ld + b] = __ldg(Pinf + e);
+    if (!keep_rho) ad.rho[b] = rho;
+}
+
+// instance-major copies of the adapted cache for the getter: Kinf nu x nx x B, Pinf nx x nx x B
+__global__ void adaptive_gather_kernel(AdaptiveRho ad, double* __restrict__ Kinf, double* __restrict__ Pinf, int nkinf,
+                                       int npinf, int B, long long ld) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    if (Kinf) for (int e = 0; e < nkinf; ++e) Kinf[static_cast<size_t>(b) * nkinf + e] = ad.Kinf[e * ld + b];
+    if (Pinf) for (int e = 0; e < npinf; ++e) Pinf[static_cast<size_t>(b) * npinf + e] = ad.Pinf[e * ld + b];
+}
+
 }  // namespace
+
+cudaError_t launch_adaptive_init(const BatchView& bv, const AdaptiveRho& ad, cudaStream_t stream, bool keep_rho) {
+    if (bv.B <= 0) return cudaSuccess;
+    adaptive_init_kernel<<<(bv.B + 127) / 128, 128, 0, stream>>>(ad, bv.Kinf, bv.Pinf, bv.rho, bv.nu * bv.nx, bv.nx * bv.nx,
+                                                                 bv.B, bv.ld, keep_rho);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_adaptive_gather(const BatchView& bv, const AdaptiveRho& ad, double* Kinf, double* Pinf,
+                                   cudaStream_t stream) {
+    if (bv.B <= 0) return cudaSuccess;
+    adaptive_gather_kernel<<<(bv.B + 127) / 128, 128, 0, stream>>>(ad, Kinf, Pinf, bv.nu * bv.nx, bv.nx * bv.nx, bv.B, bv.ld);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_admm_thread_adaptive(const BatchView& bv, const AdmmSettings& st, const AdaptiveRho& ad,
+                                        cudaStream_t stream) {
+    if (bv.B <= 0) return cudaSuccess;
+    if (!thread_kernel_supports(bv.nx, bv.nu)) return cudaErrorInvalidValue;
+    const int grid = (bv.B + kThreadKernelBlock - 1) / kThreadKernelBlock;
+    auto go = [&](auto m) {
+        m.nx_ = bv.nx; m.nu_ = bv.nu; m.ld_ = bv.ld; m.b_ = 0; m.ad_ = ad;
+        m.A_ = bv.A; m.B_ = bv.Bm; m.AmBKt_ = bv.AmBKt; m.Quu_inv_ = bv.Quu_inv; m.f_ = bv.f; m.APf_ = bv.APf;
+        m.BPf_ = bv.BPf; m.Qd_ = bv.Qd; m.Rd_ = bv.Rd;
+        admm_thread_kernel<double, decltype(m)><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
+        return cudaGetLastError();
+    };
+    if (bv.nx == 12 && bv.nu == 4) return go(MatsAdaptive<12, 4>{});
+    if (bv.nx == 4 && bv.nu == 1) return go(MatsAdaptive<4, 1>{});
+    return go(MatsAdaptive<0, 0>{});
+}
 
 bool thread_kernel_supports(int nx, int nu) {
     return nx >= 1 && nu >= 1 && nx <= kThreadKernelMaxNx && nu <= kThreadKernelMaxNu;

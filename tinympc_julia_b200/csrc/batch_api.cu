@@ -84,7 +84,16 @@ struct tmpc_batch {
     int num_sms = 148;
     tmpc::HostMats hm;
     tmpc::AdmmSettings st{};
-    bool adaptive_rho = false;                // accepted as a setting, refused at solve time (see enqueue_solve)
+    // adaptive rho (reference admm.cpp:331-357, rho_benchmark.cpp): the settings, the shared
+    // sensitivity matrices (what codegen_with_sensitivity stores in the reference's cache, codegen.cpp:91-96) and the
+    // adapted cache - rho, Kinf, Pinf - which the reference updates in place and which is therefore per-instance carried
+    // state here: broadcast from the shared cache on a fresh / reset batch (ad_valid = false), then kept across solves.
+    bool adaptive_rho = false;
+    double adaptive_rho_min = 1.0, adaptive_rho_max = 100.0;   // tiny_api.cpp:368-369
+    bool adaptive_clip = true;
+    bool sens_set = false;
+    DevBuf<double> d_dK, d_dP, ad_rho, ad_Kinf, ad_Pinf;
+    bool ad_valid = false;
     int kernel_pref = TMPC_KERNEL_AUTO;
     bool rollout_fused = true;                // tmpc_batch_rollout_async: one fused launch where the TMEM kernel applies
     cudaStream_t stream = nullptr;
@@ -223,7 +232,32 @@ tmpc::PerInstanceMats per_instance_view(tmpc_batch* h) {
                                  h->piAPf.p, h->piBPf.p, h->piQd.p, h->piRd.p};
 }
 
+// The adapted cache is in use: the flag is on, or an earlier adaptive solve left per-instance rho / Kinf / Pinf behind
+// (the reference keeps solving with the adapted cache after the flag is cleared; only a new setup restores it - here:
+// reset, set_cache_terms, set_precision).
+bool adaptive_path(const tmpc_batch* h) { return h->adaptive_rho || h->ad_valid; }
+
+tmpc::AdaptiveRho adaptive_view(tmpc_batch* h) {
+    return tmpc::AdaptiveRho{h->adaptive_rho ? 1 : 0, h->adaptive_clip ? 1 : 0, h->adaptive_rho_min, h->adaptive_rho_max,
+                             h->ad_rho.p, h->ad_Kinf.p, h->ad_Pinf.p, h->d_dK.p, h->d_dP.p};
+}
+
+// nullptr = fine; else why a solve with adaptive rho cannot run
+const char* adaptive_refusal(const tmpc_batch* h) {
+    if (!adaptive_path(h)) return nullptr;
+    if (h->adaptive_rho && !h->sens_set)
+        return "adaptive_rho is set but no sensitivity matrices were given (tmpc_batch_set_sensitivity / codegen_with_sensitivity): "
+               "the reference then adds 0 x 0 matrices to its cache and crashes at the first rho update (admm.cpp:331-357, "
+               "rho_benchmark.cpp:204-207); the solve is refused instead";
+    if (h->precision == 32) return "adaptive rho runs in the 64-bit build only";
+    if (h->per_instance) return "adaptive rho needs shared dynamics (one set of sensitivity matrices)";
+    if (h->kernel_pref != TMPC_KERNEL_AUTO && h->kernel_pref != TMPC_KERNEL_THREAD)
+        return "adaptive rho runs on the thread kernel (TMPC_KERNEL_AUTO or TMPC_KERNEL_THREAD)";
+    return nullptr;
+}
+
 int resolve_kernel(tmpc_batch* h) {
+    if (adaptive_path(h)) return adaptive_refusal(h) ? -1 : TMPC_KERNEL_THREAD;
     if (h->precision == 32) {   // float build: the TMEM, sub-warp (shared-memory) and thread kernels are instantiated for float
         if (h->per_instance) return -1;
         const bool sub32 = tmpc::subwarp_kernel_supports(h->nx, h->nu, h->N, h->st, 32);
@@ -337,6 +371,20 @@ cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v_in, cuda
     else if (sub && k == TMPC_KERNEL_TMEM) e = tmpc::launch_admm_tmem(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s, order, h->precision);
     else if (sub && k == TMPC_KERNEL_CONE) e = tmpc::launch_admm_cone(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
     else if (sub) e = tmpc::launch_admm_subwarp(v, h->st, h->hm, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s, h->precision);
+    else if (adaptive_path(h)) {
+        if (!h->ad_rho.p) {
+            h->ad_rho.alloc(h->ld); h->ad_Kinf.alloc(static_cast<size_t>(h->nu) * h->nx * h->ld);
+            h->ad_Pinf.alloc(static_cast<size_t>(h->nx) * h->nx * h->ld);
+        }
+        const tmpc::AdaptiveRho ad = adaptive_view(h);
+        if (!h->ad_valid) {      // every instance starts from the cache the setup computed
+            e = tmpc::launch_adaptive_init(v, ad, s);
+            if (e != cudaSuccess) return e;
+            h->launches += 1;
+            h->ad_valid = true;
+        }
+        e = tmpc::launch_admm_thread_adaptive(v, h->st, ad, s);
+    }
     else if (h->per_instance) e = tmpc::launch_admm_thread_per_instance(v, h->st, per_instance_view(h), s, h->precision);
     else e = tmpc::launch_admm_thread(v, h->st, h->hm, s, h->precision);
     h->launches += 1;
@@ -348,7 +396,7 @@ cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v_in, cuda
 // stream when s is that stream; callers passing another stream order it themselves).
 int enqueue_solve(tmpc_batch* h, cudaStream_t s) {
     if (h->st.check_termination == 0) { set_error("check_termination = 0 is not supported (the reference divides by it)"); return TMPC_ERR_STATE; }
-    if (h->adaptive_rho) { set_error("adaptive_rho is set: through this API the reference reads unset (0 x 0) sensitivity matrices in that branch and crashes at its first rho update (admm.cpp:331-357, rho_benchmark.cpp:204-207; DESIGN.md 8); there is no reference behaviour to reproduce, so the solve is refused - clear the flag with update_settings"); return TMPC_ERR_STATE; }
+    if (const char* why = adaptive_refusal(h)) { set_error(why); return TMPC_ERR_STATE; }
     order_before_enqueue(h, s);
     ensure_aux_state(h, s);
     const int k = resolve_kernel(h);
@@ -513,7 +561,6 @@ int tmpc_batch_update_settings(tmpc_batch* h, double abs_pri_tol, double abs_dua
                                int check_termination, int en_state_bound, int en_input_bound, int en_state_soc,
                                int en_input_soc, int en_state_linear, int en_input_linear, int adaptive_rho,
                                double adaptive_rho_min, double adaptive_rho_max, int adaptive_rho_enable_clipping) {
-    (void)adaptive_rho_min; (void)adaptive_rho_max; (void)adaptive_rho_enable_clipping;
     return guarded([&]() -> int {
         if (!h) { set_error("update_settings: null handle"); return TMPC_ERR_DIM; }
         if (check_termination == 0) { set_error("update_settings: check_termination = 0 rejected (reference computes iter % 0)"); return TMPC_ERR_STATE; }
@@ -523,8 +570,10 @@ int tmpc_batch_update_settings(tmpc_batch* h, double abs_pri_tol, double abs_dua
         h->st.en_state_bound = en_state_bound != 0; h->st.en_input_bound = en_input_bound != 0;
         h->st.en_state_soc = en_state_soc != 0; h->st.en_input_soc = en_input_soc != 0;
         h->st.en_state_linear = en_state_linear != 0; h->st.en_input_linear = en_input_linear != 0;
-        // the BINDING is kept (tests/test_settings.jl "Adaptive Rho Settings" only sets it up); solves refuse while it is on
+        // src/bindings.cpp:362-365.  A solve with the flag on needs the sensitivity matrices (tmpc_batch_set_sensitivity)
         h->adaptive_rho = adaptive_rho != 0;
+        h->adaptive_rho_min = adaptive_rho_min; h->adaptive_rho_max = adaptive_rho_max;
+        h->adaptive_clip = adaptive_rho_enable_clipping != 0;
         return TMPC_OK;
     });
 }
@@ -827,6 +876,12 @@ int tmpc_batch_set_cache_terms(tmpc_batch* h, const double* Kinf, const double* 
                 for (double& x : *vec) x = static_cast<double>(static_cast<float>(x));
         sync_all(h);
         upload_mats(h);      // APf, BPf, rho deliberately untouched
+        if (h->ad_valid) {   // an adapted batch: the new Kinf / Pinf replace every instance's, cache->rho stays (bindings.cpp:277-280)
+            const cudaError_t e = tmpc::launch_adaptive_init(make_view(h), adaptive_view(h), h->stream, /*keep_rho=*/true);
+            if (e != cudaSuccess) throw CudaFail{e, "adapted-cache refresh"};
+            h->launches += 1;
+            h->own_pending = true;
+        }
         return TMPC_OK;
     });
 }
@@ -840,12 +895,61 @@ int tmpc_batch_get_cache_terms(tmpc_batch* h, double* Kinf, double* Pinf, double
     return TMPC_OK;
 }
 
+int tmpc_batch_set_sensitivity(tmpc_batch* h, const double* dKinf_drho, const double* dPinf_drho, const double* dC1_drho,
+                               const double* dC2_drho) {
+    return guarded([&]() -> int {
+        if (!h || !dKinf_drho || !dPinf_drho || !dC1_drho || !dC2_drho) { set_error("set_sensitivity: null argument"); return TMPC_ERR_DIM; }
+        const size_t n = h->nx, m = h->nu;
+        if (!finite_all(dKinf_drho, m * n) || !finite_all(dPinf_drho, n * n) || !finite_all(dC1_drho, m * m) || !finite_all(dC2_drho, n * n)) {
+            set_error("set_sensitivity: non-finite entry"); return TMPC_ERR_DIM;
+        }
+        h->use_device();
+        sync_all(h);
+        // dC1 / dC2 update C1 / C2 in the reference (rho_benchmark.cpp:206-207), which no part of the solve reads
+        // (SURVEY.md 8a a12): checked, not stored
+        h->d_dK.upload(dKinf_drho, m * n, h->stream);
+        h->d_dP.upload(dPinf_drho, n * n, h->stream);
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        h->sens_set = true;
+        return TMPC_OK;
+    });
+}
+
+int tmpc_batch_get_adapted_cache(tmpc_batch* h, double* rho, double* Kinf, double* Pinf) {
+    return guarded([&]() -> int {
+        if (!h) return TMPC_ERR_DIM;
+        h->use_device();
+        sync_all(h);
+        const size_t nk = static_cast<size_t>(h->nu) * h->nx, np = static_cast<size_t>(h->nx) * h->nx, B = h->B;
+        if (!h->ad_valid) {      // nothing adapted yet: every instance is on the shared cache
+            for (size_t b = 0; b < B; ++b) {
+                if (rho) rho[b] = h->rho;
+                if (Kinf) std::memcpy(Kinf + b * nk, h->hm.Kinf.data(), sizeof(double) * nk);
+                if (Pinf) std::memcpy(Pinf + b * np, h->hm.Pinf.data(), sizeof(double) * np);
+            }
+            return TMPC_OK;
+        }
+        DevBuf<double> tk, tp;
+        if (Kinf) tk.alloc(nk * B);
+        if (Pinf) tp.alloc(np * B);
+        const cudaError_t e = tmpc::launch_adaptive_gather(make_view(h), adaptive_view(h), tk.p, tp.p, h->stream);
+        if (e != cudaSuccess) throw CudaFail{e, "adapted-cache gather"};
+        h->launches += 1;
+        if (rho) CUDA_TRY(cudaMemcpyAsync(rho, h->ad_rho.p, sizeof(double) * B, cudaMemcpyDeviceToHost, h->stream));
+        if (Kinf) CUDA_TRY(cudaMemcpyAsync(Kinf, tk.p, sizeof(double) * nk * B, cudaMemcpyDeviceToHost, h->stream));
+        if (Pinf) CUDA_TRY(cudaMemcpyAsync(Pinf, tp.p, sizeof(double) * np * B, cudaMemcpyDeviceToHost, h->stream));
+        CUDA_TRY(cudaStreamSynchronize(h->stream));
+        return TMPC_OK;
+    });
+}
+
 int tmpc_batch_reset(tmpc_batch* h) {
     return guarded([&]() -> int {
         if (!h) return TMPC_ERR_DIM;
         h->use_device();
         h->state_zero = true;            // logical: physical zeroing is deferred to the first reader that needs it (stream-ordered there)
         h->order_built = false;
+        h->ad_valid = false;             // ... and every instance is back on the cache the setup computed
         return TMPC_OK;
     });
 }
@@ -898,12 +1002,12 @@ static int solve_host_impl(tmpc_batch* h, const double* x0, int cold, double* X,
         if (!h) return TMPC_ERR_DIM;
         h->use_device();
         if (h->st.check_termination == 0) { set_error("check_termination = 0 is not supported (the reference divides by it)"); return 100 + TMPC_ERR_STATE; }
-        if (h->adaptive_rho) { set_error("adaptive_rho is set: through this API the reference reads unset (0 x 0) sensitivity matrices in that branch and crashes at its first rho update (admm.cpp:331-357, rho_benchmark.cpp:204-207; DESIGN.md 8); there is no reference behaviour to reproduce, so the solve is refused - clear the flag with update_settings"); return 100 + TMPC_ERR_STATE; }
+        if (const char* why = adaptive_refusal(h)) { set_error(why); return 100 + TMPC_ERR_STATE; }
         if (x0) {   // copied below: whole before a single launch, else chunk by chunk in front of each chunk's launch
             h->ext_x0 = nullptr;
             if (h->x0.n < static_cast<size_t>(h->nx) * h->B) h->x0.alloc(static_cast<size_t>(h->nx) * h->B);
         }
-        if (cold) { h->state_zero = true; h->order_built = false; }
+        if (cold) { h->state_zero = true; h->order_built = false; h->ad_valid = false; }
         ensure_aux_state(h, h->stream);
         const int k = resolve_kernel(h);
         if (k < 0) { set_error("requested kernel does not support this problem"); return 100 + TMPC_ERR_STATE; }
@@ -1154,7 +1258,7 @@ int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_lo
             h->ext_x0 = nullptr;
         }
         if (h->st.check_termination == 0) { set_error("check_termination = 0 is not supported"); return TMPC_ERR_STATE; }
-        if (h->adaptive_rho) { set_error("adaptive_rho is set: through this API the reference reads unset (0 x 0) sensitivity matrices in that branch and crashes at its first rho update (admm.cpp:331-357, rho_benchmark.cpp:204-207; DESIGN.md 8); there is no reference behaviour to reproduce, so the solve is refused - clear the flag with update_settings"); return TMPC_ERR_STATE; }
+        if (const char* why = adaptive_refusal(h)) { set_error(why); return TMPC_ERR_STATE; }
         order_before_enqueue(h, s);
         ensure_aux_state(h, s);
         const int k = resolve_kernel(h);

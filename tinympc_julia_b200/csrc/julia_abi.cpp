@@ -22,6 +22,7 @@ struct Settings {
     double abs_pri_tol = 1e-3, abs_dua_tol = 1e-3;
     int max_iter = 1000, check_termination = 1;               // C++-side defaults, tiny_api_constants.hpp:5-14
     int en_state_bound = 1, en_input_bound = 1, en_state_soc = 0, en_input_soc = 0, en_state_linear = 0, en_input_linear = 0;
+    int adaptive_rho = 0; double adaptive_rho_min = 1.0, adaptive_rho_max = 100.0; int adaptive_rho_enable_clipping = 1;   // tiny_api.cpp:367-370
 } g_set;
 
 int fail(const char* fn, const char* why) {
@@ -33,7 +34,8 @@ int push_settings() {
     return tmpc_batch_update_settings(g_solver, g_set.abs_pri_tol, g_set.abs_dua_tol, g_set.max_iter,
                                       g_set.check_termination, g_set.en_state_bound, g_set.en_input_bound,
                                       g_set.en_state_soc, g_set.en_input_soc, g_set.en_state_linear,
-                                      g_set.en_input_linear, 0, 0.0, 0.0, 0);
+                                      g_set.en_input_linear, g_set.adaptive_rho, g_set.adaptive_rho_min,
+                                      g_set.adaptive_rho_max, g_set.adaptive_rho_enable_clipping);
 }
 
 }  // namespace
@@ -126,13 +128,47 @@ int codegen(const char* output_dir, int verbose) {
     return fail("codegen", "embedded code generation is not part of the CUDA library (use the reference library for codegen)");
 }
 
+namespace {
+int store_sensitivity(const char* fn, double* dK_data, int dK_rows, int dK_cols, double* dP_data, int dP_rows, int dP_cols,
+                      double* dC1_data, int dC1_rows, int dC1_cols, double* dC2_data, int dC2_rows, int dC2_cols) {
+    if (!dK_data || !dP_data || !dC1_data || !dC2_data) return fail(fn, "null sensitivity matrix");
+    if (dK_rows != g_nu || dK_cols != g_nx || dP_rows != g_nx || dP_cols != g_nx || dC1_rows != g_nu || dC1_cols != g_nu ||
+        dC2_rows != g_nx || dC2_cols != g_nx)
+        return fail(fn, "sensitivity matrices must be dK nu x nx, dP nx x nx, dC1 nu x nu, dC2 nx x nx");
+    if (tmpc_batch_set_sensitivity(g_solver, dK_data, dP_data, dC1_data, dC2_data) != 0) return fail(fn, tmpc_last_error());
+    return 0;
+}
+}  // namespace
+
+// The reference does two things here (codegen.cpp:82-100): with adaptive_rho on it first stores the four matrices in
+// the LIVE solver's cache - the only way the Julia package can load them (tests/test_sensitivity.jl:40-53) - and then
+// writes the MCU sources.  The first half is kept (later solve_mpc calls adapt rho with these matrices); the second is
+// outside this library, so the call still returns non-zero.
 int codegen_with_sensitivity(const char* output_dir, double* dK_data, int dK_rows, int dK_cols, double* dP_data,
                              int dP_rows, int dP_cols, double* dC1_data, int dC1_rows, int dC1_cols, double* dC2_data,
                              int dC2_rows, int dC2_cols, int verbose) {
-    (void)output_dir; (void)dK_data; (void)dK_rows; (void)dK_cols; (void)dP_data; (void)dP_rows; (void)dP_cols;
-    (void)dC1_data; (void)dC1_rows; (void)dC1_cols; (void)dC2_data; (void)dC2_rows; (void)dC2_cols; (void)verbose;
+    (void)output_dir; (void)verbose;
     if (!g_solver) return fail("codegen_with_sensitivity", "Solver not initialized");
-    return fail("codegen_with_sensitivity", "embedded code generation is not part of the CUDA library");
+    if (g_set.adaptive_rho) {     // "Only store sensitivity matrices if adaptive rho is enabled", codegen.cpp:90-97
+        const int rc = store_sensitivity("codegen_with_sensitivity", dK_data, dK_rows, dK_cols, dP_data, dP_rows, dP_cols,
+                                         dC1_data, dC1_rows, dC1_cols, dC2_data, dC2_rows, dC2_cols);
+        if (rc != 0) return rc;
+    }
+    return fail("codegen_with_sensitivity",
+                g_set.adaptive_rho ? "the sensitivity matrices are stored; embedded code generation is not part of the CUDA library"
+                                   : "embedded code generation is not part of the CUDA library");
+}
+
+// The loader on its own (no reference counterpart: there it only exists inside codegen_with_sensitivity).  Same
+// argument list minus the output directory; stores regardless of the adaptive_rho flag; returns 0.
+int set_sensitivity_matrices(double* dK_data, int dK_rows, int dK_cols, double* dP_data, int dP_rows, int dP_cols,
+                             double* dC1_data, int dC1_rows, int dC1_cols, double* dC2_data, int dC2_rows, int dC2_cols,
+                             int verbose) {
+    if (!g_solver) return fail("set_sensitivity_matrices", "Solver not initialized");
+    const int rc = store_sensitivity("set_sensitivity_matrices", dK_data, dK_rows, dK_cols, dP_data, dP_rows, dP_cols,
+                                     dC1_data, dC1_rows, dC1_cols, dC2_data, dC2_rows, dC2_cols);
+    if (rc == 0 && verbose) std::printf("Sensitivity matrices stored\n");
+    return rc;
 }
 
 int print_problem_data(int verbose) {
@@ -192,6 +228,8 @@ int update_settings(double abs_pri_tol, double abs_dua_tol, int max_iter, int ch
     g_set.en_state_bound = en_state_bound; g_set.en_input_bound = en_input_bound;
     g_set.en_state_soc = en_state_soc; g_set.en_input_soc = en_input_soc;
     g_set.en_state_linear = en_state_linear; g_set.en_input_linear = en_input_linear;
+    g_set.adaptive_rho = adaptive_rho; g_set.adaptive_rho_min = adaptive_rho_min; g_set.adaptive_rho_max = adaptive_rho_max;
+    g_set.adaptive_rho_enable_clipping = adaptive_rho_enable_clipping;
     if (verbose) std::printf("Updated settings with status: 0\n");
     return 0;
 }

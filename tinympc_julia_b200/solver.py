@@ -248,6 +248,7 @@ def setup(solver, A, B, f, Q, R, rho: float, nx: int, nu: int, N: int, *, batch:
         if status != 0:
             raise TinyMPCError(f"Setup failed with status: {status} ({_lib.last_error()})")
         solver._h, solver.B = h, int(batch)
+        solver.A_, solver.B_, solver.Q_, solver.R_ = A_.copy(), B_.copy(), Q_.copy(), R_.copy()
     else:
         solver.A, solver.B, solver.Q, solver.R = A_.copy(), B_.copy(), Q_.copy(), R_.copy()
         status = lib.setup_solver(_dp(A_), *A_.shape, _dp(B_), *B_.shape, _dp(f_), *f_.shape, _dp(Q_), *Q_.shape,
@@ -493,6 +494,90 @@ def print_problem_data(solver, *, verbose: bool = False) -> int:
               f"solved={int((st == 0).sum())}/{solver.B} iters[min/med/max]={it.min()}/{int(np.median(it))}/{it.max()}")
         return 0
     return int(_lib.load().print_problem_data(1 if verbose else 0))
+
+
+def _solve_lqr(A, B, Q, R, rho_val: float):
+    """reference src/TinyMPC.jl:328-351 (private helper of the Julia package): fixed-point Riccati iteration with the
+    rho-regularised costs, <= 5000 sweeps, stop when ||K - K_prev|| < 1e-10; returns K, P, C1 = Quu^-1, C2 = (A - B K)'."""
+    nx, nu = A.shape[0], B.shape[1]
+    Q_rho = Q + rho_val * np.eye(nx)
+    R_rho = R + rho_val * np.eye(nu)
+    P = Q_rho.copy()
+    K = np.zeros((nu, nx))
+    for it in range(5000):
+        K_prev = K.copy()
+        K = np.linalg.solve(R_rho + B.T @ P @ B + 1e-8 * np.eye(nu), B.T @ P @ A)
+        P = Q_rho + A.T @ P @ (A - B @ K)
+        if it > 0 and np.linalg.norm(K - K_prev) < 1e-10:
+            break
+    C1 = np.linalg.inv(R_rho + B.T @ P @ B)
+    C2 = (A - B @ K).T
+    return K, P, C1, C2
+
+
+def lqr_sensitivity(A, B, Q, R, rho: float, h: float = 1e-6):
+    """Forward differences of (K, P, C1, C2) in rho, step 1e-6: the arithmetic of compute_sensitivity_autograd
+    (reference src/TinyMPC.jl:301-323) on plain matrices.  Returns (dK, dP, dC1, dC2), column-major float64."""
+    A, B, Q, R = (np.asarray(m, dtype=np.float64) for m in (A, B, Q, R))
+    B = B.reshape(A.shape[0], -1)
+    a0 = _solve_lqr(A, B, Q, R, float(rho))
+    a1 = _solve_lqr(A, B, Q, R, float(rho) + h)
+    return tuple(np.asfortranarray((y - x) / h) for x, y in zip(a0, a1))
+
+
+def compute_sensitivity_autograd(solver):
+    """reference src/TinyMPC.jl:301-323 — numerical differentiation, the name notwithstanding."""
+    _need_setup(solver)
+    if isinstance(solver, TinyMPCBatchSolver):
+        return lqr_sensitivity(solver.A_, solver.B_, solver.Q_, solver.R_, solver.rho)
+    return lqr_sensitivity(solver.A, solver.B, solver.Q, solver.R, solver.rho)
+
+
+def set_sensitivity(solver, dK, dP, dC1, dC2, *, verbose: bool = False) -> int:
+    """Loads the sensitivity matrices of the adaptive-rho branch into the live solver: the half of the reference's
+    codegen_with_sensitivity (codegen.cpp:90-97) that the solve path needs, without the code generation."""
+    _need_setup(solver)
+    lib = _lib.load()
+    nx, nu = solver.nx, solver.nu
+    mats = [_mat(dK, (nu, nx)), _mat(dP, (nx, nx)), _mat(dC1, (nu, nu)), _mat(dC2, (nx, nx))]
+    if isinstance(solver, TinyMPCBatchSolver):
+        status = lib.tmpc_batch_set_sensitivity(solver._h, *[_dp(m) for m in mats])
+    else:
+        args = []
+        for m in mats:
+            args += [_dp(m), m.shape[0], m.shape[1]]
+        status = lib.set_sensitivity_matrices(*args, 1 if verbose else 0)
+    if status != 0:
+        raise TinyMPCError(f"Failed to set sensitivity matrices ({_lib.last_error()})")
+    return 0
+
+
+def get_adapted_cache(solver):
+    """rho [B], Kinf [nu, nx, B], Pinf [nx, nx, B] every instance of a batch currently solves with (adaptive rho)."""
+    _need_setup(solver)
+    nx, nu, B = solver.nx, solver.nu, solver.B
+    rho = np.zeros(B)
+    K = np.zeros((nu, nx, B), order="F")
+    P = np.zeros((nx, nx, B), order="F")
+    _chk(_lib.load().tmpc_batch_get_adapted_cache(solver._h, _dp(rho), _dp(K), _dp(P)), "get_adapted_cache")
+    return rho, K, P
+
+
+def codegen_with_sensitivity(solver, output_dir: str, dK, dP, dC1, dC2, *, verbose: bool = False) -> int:
+    """reference src/TinyMPC.jl:374-395.  The library stores the matrices when adaptive_rho is on (as the reference
+    does before it writes any file) and then reports that code generation is not part of it: raises like a failed
+    codegen, with the matrices in place."""
+    _need_setup(solver)
+    if isinstance(solver, TinyMPCBatchSolver):
+        raise TinyMPCError("Code generation with sensitivity failed (batch solvers: use set_sensitivity)")
+    nx, nu = solver.nx, solver.nu
+    args = []
+    for m in (_mat(dK, (nu, nx)), _mat(dP, (nx, nx)), _mat(dC1, (nu, nu)), _mat(dC2, (nx, nx))):
+        args += [_dp(m), m.shape[0], m.shape[1]]
+    status = _lib.load().codegen_with_sensitivity(str(output_dir).encode(), *args, 1 if verbose else 0)
+    if status != 0:
+        raise TinyMPCError("Code generation with sensitivity failed")
+    return status
 
 
 def codegen(solver, output_dir: str, *, verbose: bool = False) -> int:
