@@ -13,7 +13,8 @@ using Libdl
 
 export TinyMPCBatchSolver, setup_batch, set_x0, set_x_ref, set_u_ref, set_bound_constraints, set_linear_constraints,
        set_cone_constraints, set_cache_terms, update_settings, reset!, solve, get_solution, get_status,
-       set_kernel, set_precision, set_order, rollout!, solve_host, solve_host_u0, set_instance_dynamics, destroy!
+       set_kernel, set_precision, set_order, rollout!, solve_host, solve_host_u0, set_instance_dynamics, destroy!,
+       set_sensitivity, get_adapted_cache
 
 const lib_path = joinpath(dirname(@__DIR__), "lib", "libtinympc_jl." * Libdl.dlext)   # as reference src/TinyMPC.jl:12-13
 
@@ -179,6 +180,31 @@ function solve_host_u0(s::TinyMPCBatchSolver, x0::Matrix{Float64}; cold::Bool = 
                 s.handle, x0, Int32(cold), C_NULL, C_NULL, u0, st, it, Int32(0))
     ret in (0, 1) || error("solve_host_u0 failed with status $ret")
     return ret, u0, st, it
+end
+
+"""
+Adaptive rho (reference admm.cpp:331-357): loads the sensitivity matrices `compute_sensitivity_autograd` returns
+(reference src/TinyMPC.jl:301-323) into the batch - the part of the reference's `codegen_with_sensitivity`
+(codegen.cpp:90-97) that the solve path needs.  With `update_settings(s; adaptive_rho = true, ...)` every instance then
+adapts its own rho / Kinf / Pinf (tmpc_batch_set_sensitivity).  Single solver: `set_sensitivity_matrices` with the
+argument list of `codegen_with_sensitivity` minus the directory.
+"""
+function set_sensitivity(s::TinyMPCBatchSolver, dK::Matrix{Float64}, dP::Matrix{Float64}, dC1::Matrix{Float64},
+                         dC2::Matrix{Float64})
+    size(dK) == (s.nu, s.nx) && size(dP) == (s.nx, s.nx) && size(dC1) == (s.nu, s.nu) && size(dC2) == (s.nx, s.nx) ||
+        error("sensitivity matrices must be dK nu x nx, dP nx x nx, dC1 nu x nu, dC2 nx x nx")
+    check(ccall((:tmpc_batch_set_sensitivity, lib_path), Int32,
+                (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}), s.handle, dK, dP, dC1, dC2),
+          "Failed to set sensitivity matrices")
+end
+
+"rho (B), Kinf (nu x nx x B), Pinf (nx x nx x B) every instance currently solves with (tmpc_batch_get_adapted_cache)."
+function get_adapted_cache(s::TinyMPCBatchSolver)
+    rho = Vector{Float64}(undef, s.B)
+    K = Array{Float64}(undef, s.nu, s.nx, s.B); P = Array{Float64}(undef, s.nx, s.nx, s.B)
+    check(ccall((:tmpc_batch_get_adapted_cache, lib_path), Int32, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}),
+                s.handle, rho, K, P), "Failed to read the adapted cache")
+    return rho, K, P
 end
 
 """
