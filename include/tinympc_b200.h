@@ -292,6 +292,34 @@ int tmpc_batch_get_x0(tmpc_batch* h, void* dst, int device_dst);
 void* tmpc_host_alloc(size_t bytes);
 void tmpc_host_free(void* p);
 
+/* One batched cold solve that allocates nothing on the device.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  It is the thread-per-instance kernel with its working set (carried ADMM state + feed-forward scratch,
+ * (4 nx N + 5 nu (N-1) + nx) doubles per instance, instances rounded up to a multiple of 32) in a file-scope
+ * `static __device__` array of TMPC_NOALLOC_SCRATCH_BYTES, which every GPU that loads the library holds until the process
+ * exits.  A batch whose working set does not fit returns TMPC_ERR_DIM with the sizes in the message (quadrotor 12/4/20:
+ * B <= 3,072; cartpole 4/1/20: B <= 9,984): use tmpc_batch_create / tmpc_batch_solve for those.
+ *   host pointers   A nx x nx, Bdyn nx x nu, f nx, and Kinf .. Rd exactly as tmpc_compute_cache returns them (call it once);
+ *   device pointers d_x0 nx x B; d_x_ref nx x N and d_u_ref nu x (N-1) shared by all instances, or NULL (zeros);
+ *                   d_x_min / d_x_max nx x N and d_u_min / d_u_max nu x (N-1) shared, or NULL pairs (no box on that side);
+ *                   outputs d_states nx x N x B, d_controls nu x (N-1) x B, d_status B, d_iters B - all on the CURRENT device;
+ *   cuda_stream     the cudaStream_t everything is enqueued on (NULL = default stream); the call returns without waiting.
+ * Semantics = tmpc_batch_reset + tmpc_batch_solve on TMPC_KERNEL_THREAD with box constraints (results are identical).
+ * The calls it makes: cudaGetSymbolAddress (once per device), cudaMemsetAsync of the working set, one kernel launch; for
+ * shapes other than 12/4, 4/1, 6/3 also a cudaMemcpyAsync of the constants when they changed.  No cudaMalloc / cudaFree.
+ * The array is SHARED by every call and keeps the last call's contents (each call clears what it uses): calls that overlap
+ * on the GPU - other streams without ordering, other host threads - race.  errbuf (may be NULL) receives the message of a
+ * non-zero return. */
+#define TMPC_NOALLOC_SCRATCH_BYTES 33554432   /* 32 MiB */
+int tmpc_solve_noalloc(int nx, int nu, int N, int B, double rho, const double* A, const double* Bdyn, const double* f,
+                       const double* Kinf, const double* Pinf, const double* Quu_inv, const double* AmBKt,
+                       const double* APf, const double* BPf, const double* Qd, const double* Rd,
+                       const double* d_x0, const double* d_x_ref, const double* d_u_ref,
+                       const double* d_x_min, const double* d_x_max, const double* d_u_min, const double* d_u_max,
+                       double abs_pri_tol, double abs_dua_tol, int max_iter, int check_termination,
+                       double* d_states, double* d_controls, int* d_status, int* d_iters, void* cuda_stream,
+                       char* errbuf, size_t errbuf_len);
+
 /* Introspection */
 int tmpc_batch_dims(tmpc_batch* h, int* nx, int* nu, int* N, int* B);
 long long tmpc_batch_launch_count(tmpc_batch* h);   /* kernels launched by this handle so far */

@@ -65,6 +65,8 @@ SIGNATURES = {
     "tmpc_batch_set_sensitivity": (_I, [_V, _P, _P, _P, _P]),
     "tmpc_batch_get_adapted_cache": (_I, [_V, _P, _P, _P]),
     "tmpc_batch_reset": (_I, [_V]),
+    # no counterpart in the reference: device pointers are passed as integers
+    "tmpc_solve_noalloc": (_I, [_I, _I, _I, _I, _D] + [_P] * 11 + [_V] * 7 + [_D, _D, _I, _I] + [_V] * 5 + [C.c_char_p, C.c_size_t]),
     "tmpc_batch_solve": (_I, [_V]),
     "tmpc_batch_solve_async": (_I, [_V, _V]),
     "tmpc_batch_set_instance_dynamics": (_I, [_V, _P, _P, _P, _P, _P, _I]),
