@@ -47,6 +47,9 @@ using namespace tmu;
 #ifndef TMPC_CONE_INST
 #define TMPC_CONE_INST 3
 #endif
+#ifndef TMPC_CONE_SPEC
+#define TMPC_CONE_SPEC 1
+#endif
 constexpr int kCWarps = TMPC_CONE_WARPS;   // warps per CTA, one CTA per SM: two per scheduler
 constexpr int kCInst = TMPC_CONE_INST;     // instances per warp (a tile)
 constexpr int kCGroup = 10;         // lanes per instance in phase A
@@ -145,7 +148,10 @@ __device__ __forceinline__ void task_tm_store(uint32_t taddr, const uint32_t* w)
 
 __device__ __forceinline__ double shfl_d(double v, int src) { return shfl_dq(v, src); }
 
-template <int NX, int NU>
+// SPEC: the constraint set is fixed at compile time to the rocket-landing form - box on both sides with knot-invariant
+// bounds, shared references (both staged as tables), ONE cone per side starting at element 0, ONE half-space per side.
+// The run-time flags, cone loops and half-space loops then fold away and phase B becomes a few long basic blocks.
+template <int NX, int NU, bool SPEC>
 __global__ void __launch_bounds__(kCWarps * 32, 1)
 admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ AdmmSettings st,
                  const __grid_constant__ ConeParams cp) {
@@ -237,12 +243,15 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     const double cf = is_x ? sf[row] : 0.0;
     const double cb = is_x ? sAPf[row] : (is_u ? sBPf[jrow] : 0.0);
 
-    const bool box_x = st.en_state_bound && bv.x_min != nullptr;
-    const bool box_u = st.en_input_bound && bv.u_min != nullptr;
-    const bool soc_x = st.en_state_soc && bv.ncx > 0;
-    const bool soc_u = st.en_input_soc && bv.ncu > 0;
-    const bool lin_x = st.en_state_linear != 0;
-    const bool lin_u = st.en_input_linear != 0;
+    const bool box_x = SPEC || (st.en_state_bound && bv.x_min != nullptr);
+    const bool box_u = SPEC || (st.en_input_bound && bv.u_min != nullptr);
+    const bool soc_x = SPEC || (st.en_state_soc && bv.ncx > 0);
+    const bool soc_u = SPEC || (st.en_input_soc && bv.ncu > 0);
+    const bool lin_x = SPEC || st.en_state_linear != 0;
+    const bool lin_u = SPEC || st.en_input_linear != 0;
+    const bool tab_bounds = SPEC || cp.tab_bounds != 0;
+    const bool tab_refs = SPEC || cp.tab_refs != 0;
+    const int nlx = SPEC ? 1 : bv.nlx, nlu = SPEC ? 1 : bv.nlu;
     const int rounds = (T + 31) / 32;
 
     for (;;) {
@@ -417,19 +426,20 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                             const double yj = y[j];
                             const double t = dadd(u[j], yj);
                             double znew;
-                            if (cp.tab_bounds) znew = clampd(t, s_ub[2 * j], s_ub[2 * j + 1]);        // (-inf, inf) when the box is off
+                            if (tab_bounds) znew = clampd(t, s_ub[2 * j], s_ub[2 * j + 1]);           // (-inf, inf) when the box is off
                             else znew = box_u ? clampd(t, __ldg(umin + j), __ldg(umax + j)) : t;
                             const double ynew = dsub(t, znew);
                             zold[j] = z[j];
                             ok = ok && (fabs(dsub(u[j], znew)) < tol_pri) && (dmul(fabs(dsub(zold[j], znew)), rho) < tol_dua);
-                            double ra = cp.tab_refs ? s_cr[i * NU + j] : -dmul(uref ? __ldg(uref + j) : 0.0, sRd[j]);
+                            double ra = tab_refs ? s_cr[i * NU + j] : -dmul(uref ? __ldg(uref + j) : 0.0, sRd[j]);
                             ra = dsub(ra, dmul(rho, dsub(znew, ynew)));
                             y[j] = ynew; z[j] = znew; racc[j] = ra;
                         }
                         if (soc_u) {
 #pragma unroll
                             for (int j = 0; j < NU; ++j) vc[j] = dadd(u[j], yc[j]);
-                            { double v3[NU] = {vc[0], vc[1], vc[2]}; project_cones<NU>(v3, bv.ncu, bv.Acu, bv.cu); vc[0] = v3[0]; vc[1] = v3[1]; vc[2] = v3[2]; }
+                            if (SPEC) project_soc3(vc, bv.cu[0]);
+                            else { double v3[NU] = {vc[0], vc[1], vc[2]}; project_cones<NU>(v3, bv.ncu, bv.Acu, bv.cu); vc[0] = v3[0]; vc[1] = v3[1]; vc[2] = v3[2]; }
 #pragma unroll
                             for (int j = 0; j < NU; ++j) {
                                 const double ycn = dsub(dadd(yc[j], u[j]), vc[j]);
@@ -440,7 +450,7 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                         if (lin_u) {
 #pragma unroll
                             for (int j = 0; j < NU; ++j) vc[j] = dadd(u[j], yl[j]);
-                            { double v3[NU] = {vc[0], vc[1], vc[2]}; project_halfspaces_tab<NU>(v3, s_lu, bv.nlu); vc[0] = v3[0]; vc[1] = v3[1]; vc[2] = v3[2]; }
+                            { double v3[NU] = {vc[0], vc[1], vc[2]}; project_halfspaces_tab<NU>(v3, s_lu, nlu); vc[0] = v3[0]; vc[1] = v3[1]; vc[2] = v3[2]; }
 #pragma unroll
                             for (int j = 0; j < NU; ++j) {
                                 const double yln = dsub(dadd(yl[j], u[j]), vc[j]);
@@ -458,7 +468,7 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                             const double gj = g[j];
                             const double t = dadd(x[j], gj);
                             double vnew;
-                            if (cp.tab_bounds) vnew = clampd(t, s_xb[2 * j], s_xb[2 * j + 1]);
+                            if (tab_bounds) vnew = clampd(t, s_xb[2 * j], s_xb[2 * j + 1]);
                             else vnew = box_x ? clampd(t, __ldg(xmin + j), __ldg(xmax + j)) : t;
                             const double gnew = dsub(t, vnew);
                             vold[j] = v[j];
@@ -469,12 +479,12 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                         if (!terminal) {
 #pragma unroll
                             for (int j = 0; j < NX; ++j)
-                                acc[j] = dsub(cp.tab_refs ? s_cq[i * NX + j] : -dmul(xref ? __ldg(xref + j) : 0.0, sQd[j]), acc[j]);
+                                acc[j] = dsub(tab_refs ? s_cq[i * NX + j] : -dmul(xref ? __ldg(xref + j) : 0.0, sQd[j]), acc[j]);
                         } else {
 #pragma unroll
                             for (int j = 0; j < NX; ++j) {
                                 double sp = 0.0;
-                                if (cp.tab_refs) sp = s_tq[j];
+                                if (tab_refs) sp = s_tq[j];
                                 else if (xref) {
 #pragma unroll
                                     for (int k = 0; k < NX; ++k) sp = fma(__ldg(xref + k), sP[j * NX + k], sp);   // Xref_{N-1}' Pinf
@@ -485,7 +495,8 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                         if (soc_x) {
 #pragma unroll
                             for (int j = 0; j < NX; ++j) vc[j] = dadd(x[j], gc[j]);
-                            project_cones<NX>(vc, bv.ncx, bv.Acx, bv.cx);
+                            if (SPEC) project_soc3(vc, bv.cx[0]);       // the cone is elements 0..2
+                            else project_cones<NX>(vc, bv.ncx, bv.Acx, bv.cx);
 #pragma unroll
                             for (int j = 0; j < NX; ++j) {
                                 const double gcn = dsub(dadd(gc[j], x[j]), vc[j]);
@@ -496,7 +507,7 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                         if (lin_x) {
 #pragma unroll
                             for (int j = 0; j < NX; ++j) vc[j] = dadd(x[j], gl[j]);
-                            project_halfspaces_tab<NX>(vc, s_lx, bv.nlx);
+                            project_halfspaces_tab<NX>(vc, s_lx, nlx);
 #pragma unroll
                             for (int j = 0; j < NX; ++j) {
                                 const double gln = dsub(dadd(gl[j], x[j]), vc[j]);
@@ -656,7 +667,11 @@ cudaError_t launch_admm_cone(const BatchView& bv, const AdmmSettings& st, int co
     if (!cone_plan<6, 3>(bv, cp, bytes)) return cudaErrorInvalidConfiguration;
     cp.counter = counter;
     cp.cold = cold;
-    auto kern = admm_cone_kernel<6, 3>;
+    // the rocket-landing form of the constraint set runs the variant with everything folded at compile time
+    const bool spec = TMPC_CONE_SPEC && cp.tab_refs && cp.tab_bounds && st.en_state_bound && st.en_input_bound && bv.x_min && bv.u_min &&
+                      st.en_state_soc && st.en_input_soc && bv.ncx == 1 && bv.ncu == 1 && bv.Acx[0] == 0 && bv.Acu[0] == 0 &&
+                      st.en_state_linear && st.en_input_linear && bv.nlx == 1 && bv.nlu == 1;
+    auto kern = spec ? admm_cone_kernel<6, 3, true> : admm_cone_kernel<6, 3, false>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes));
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(counter, 0, sizeof(int), stream);
