@@ -56,6 +56,8 @@ constexpr int kCGroup = 10;         // lanes per instance in phase A
 constexpr int kRec = 10;            // doubles per knot record of the exchange array: [x | q (6)] [u | r | t (3)] [pad]
 constexpr int kTaskDoubles = 36;    // g v gc gl (4 x 6)  y z yc yl (4 x 3)
 constexpr int kTaskWords = 2 * kTaskDoubles;
+constexpr int kTaskPitch = kTaskDoubles + 1;   // doubles between consecutive tasks kept in shared memory: an odd pitch makes the
+                                               // 64-bit accesses of 16 consecutive lanes hit 16 different bank pairs
 constexpr int kTmemCols = (512 / ((kCWarps + 3) / 4)) & ~1;   // Tensor-Memory columns of a warp (4 lane quarters)
 constexpr int kTmemSlots = kTmemCols / kTaskWords;            // tasks per lane in Tensor Memory: 3 x 72 = 216 of 256 columns at 8 warps
 constexpr int kTmemTasks = 32 * kTmemSlots;
@@ -219,8 +221,7 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t tbase = s_tmem_base + (static_cast<uint32_t>((warp & 3) * 32) << 16) + static_cast<uint32_t>((warp >> 2) * kTmemCols);
     double* ex = smem + cp.off_warp0 + static_cast<size_t>(warp) * cp.warp_stride;   // [T][kRec] knot records
-    double* ss = ex + T * kRec;                                                       // [kTaskDoubles][smem_tasks] state of tasks >= 96
-    const int TS = cp.smem_tasks;
+    double* ss = ex + T * kRec;                                                       // [smem_tasks][kTaskPitch] state of tasks >= 96
 
     // ---------------- phase-A role of the lane
     const int grp = lane / kCGroup;                    // instance of the tile (3 = spare lanes 30, 31)
@@ -314,7 +315,7 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 task_tm_store(tbase + rd * kTaskWords, w);
             } else if (act) {
 #pragma unroll
-                for (int e = 0; e < kTaskDoubles; ++e) ss[e * TS + (tau - kTmemTasks)] = s[e];
+                for (int e = 0; e < kTaskDoubles; ++e) ss[(tau - kTmemTasks) * kTaskPitch + e] = s[e];
             }
         }
         tm_wait_st();
@@ -336,7 +337,7 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                     rec -= kRec;
                     ld2(rec + NX, rr[0], rr[1]); rr[2] = rec[NX + 2];                                   // r_i
                     const double q_own = is_x ? rec[row] : 0.0;
-                    const double r_own = is_u ? rr[jrow == 0 ? 0 : (jrow == 1 ? 1 : 2)] : 0.0;
+                    const double r_own = is_u ? rec[NX + jrow] : 0.0;
                     double c1 = 0.0, c2 = 0.0;
 #pragma unroll
                     for (int k = 0; k < NX; ++k) c1 = fma(Wb[k], pb[k], c1);
@@ -388,24 +389,15 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             bool tst[kCInst];
 #pragma unroll
             for (int k = 0; k < kCInst; ++k) tst[k] = ((iter[k] + 1) % st.check_termination) == 0;
-            for (int rd = 0; rd < rounds; ++rd) {
-                const int tau = rd * 32 + lane;
-                const bool in_tile = tau < T;
+            // One task: the whole knot point of one instance in registers.  The body is instantiated twice - for the rounds whose
+            // state sits in Tensor Memory and for those in shared memory - so that neither path has to move its registers
+            // to where the other one expects them.
+            auto task = [&](double (&s)[kTaskDoubles], const int tau, const bool in_tile) {
                 const int gi = in_tile ? tau / N : 0, i = in_tile ? tau - gi * N : 0;
                 const int b = b_first + gi;
                 const bool act = in_tile && pick(live, gi);
                 const bool testing = pick(tst, gi);
                 const bool terminal = (i == N - 1);
-                uint32_t w[kTaskWords];
-                double s[kTaskDoubles];
-                if (rd < kTmemSlots) {
-                    task_tm_load(tbase + rd * kTaskWords, w);
-#pragma unroll
-                    for (int e = 0; e < kTaskDoubles; ++e) s[e] = mk_double(w[2 * e], w[2 * e + 1]);
-                } else {
-#pragma unroll
-                    for (int e = 0; e < kTaskDoubles; ++e) s[e] = in_tile ? ss[e * TS + (tau - kTmemTasks)] : 0.0;
-                }
                 if (act) {
                     double* rec = ex + static_cast<size_t>(tau) * kRec;
                     double x[NX], u[NU], acc[NX], racc[NU], vc[NX];
@@ -532,13 +524,31 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                     }
                     if (!(testing && ok)) okbits &= ~(1u << gi);
                 }
-                if (rd < kTmemSlots) {
+                return act;
+            };
+            const int rounds_tm = rounds < kTmemSlots ? rounds : kTmemSlots;
+            for (int rd = 0; rd < rounds_tm; ++rd) {
+                const int tau = rd * 32 + lane;
+                uint32_t w[kTaskWords];
+                double s[kTaskDoubles];
+                task_tm_load(tbase + rd * kTaskWords, w);
 #pragma unroll
-                    for (int e = 0; e < kTaskDoubles; ++e) { w[2 * e] = lo32(s[e]); w[2 * e + 1] = hi32(s[e]); }
-                    task_tm_store(tbase + rd * kTaskWords, w);
-                } else if (act) {
+                for (int e = 0; e < kTaskDoubles; ++e) s[e] = mk_double(w[2 * e], w[2 * e + 1]);
+                task(s, tau, tau < T);
 #pragma unroll
-                    for (int e = 0; e < kTaskDoubles; ++e) ss[e * TS + (tau - kTmemTasks)] = s[e];
+                for (int e = 0; e < kTaskDoubles; ++e) { w[2 * e] = lo32(s[e]); w[2 * e + 1] = hi32(s[e]); }
+                task_tm_store(tbase + rd * kTaskWords, w);
+            }
+            for (int rd = kTmemSlots; rd < rounds; ++rd) {
+                const int tau = rd * 32 + lane;
+                const bool in_tile = tau < T;
+                double* sp = ss + (in_tile ? tau - kTmemTasks : 0) * kTaskPitch;
+                double s[kTaskDoubles];
+#pragma unroll
+                for (int e = 0; e < kTaskDoubles; ++e) s[e] = sp[e];
+                if (task(s, tau, in_tile)) {
+#pragma unroll
+                    for (int e = 0; e < kTaskDoubles; ++e) sp[e] = s[e];
                 }
             }
             tm_wait_st();
@@ -576,7 +586,7 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 for (int e = 0; e < kTaskDoubles; ++e) s[e] = mk_double(w[2 * e], w[2 * e + 1]);
             } else {
 #pragma unroll
-                for (int e = 0; e < kTaskDoubles; ++e) s[e] = in_tile ? ss[e * TS + (tau - kTmemTasks)] : 0.0;
+                for (int e = 0; e < kTaskDoubles; ++e) s[e] = in_tile ? ss[(tau - kTmemTasks) * kTaskPitch + e] : 0.0;
             }
             if (act) {
                 const double* rec = ex + static_cast<size_t>(tau) * kRec;
@@ -626,7 +636,7 @@ bool cone_plan(const BatchView& bv, ConeParams& cp, size_t& smem_bytes) {
     if (bv.nlx > kMaxLinear || bv.nlu > kMaxLinear) return false;
     constexpr size_t kLimit = 227 * 1024 - 64;
     cp.smem_tasks = T > kTmemTasks ? T - kTmemTasks : 0;
-    int per_warp = T * kRec + kTaskDoubles * cp.smem_tasks;
+    int per_warp = T * kRec + kTaskPitch * cp.smem_tasks;
     per_warp = (per_warp + 1) / 2 * 2;
     cp.warp_stride = per_warp;
     const bool shared_refs = (bv.Xref == nullptr || bv.xref_stride == 0) && (bv.Uref == nullptr || bv.uref_stride == 0);
