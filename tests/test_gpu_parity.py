@@ -50,6 +50,46 @@ def test_cuda_matches_oracle_seeded(orc, make, B):
         cases.compare(got, want, what=f"cuda[kernel {k}] vs oracle")
 
 
+def test_cone_kernel_every_compiled_form(orc):
+    """admm_cone.cu compiles the rocket shape three times: cones only (the reference's rocket example), cones + one
+    half-space per side (config 4), and the general form with run-time flags.  Each against the oracle and, bit for bit,
+    against the thread kernel; the general form with constraint sets the fixed forms do not cover (cone on one side only,
+    a cone that does not start at element 0, two half-spaces, per-instance references, no box)."""
+    from tinympc_julia_b200 import problems
+    e = problems.rocket().extra
+    variants = []
+    variants.append(("cones only", cases.rocket(150, N=30, linear=False)))
+    variants.append(("cones + one half-space per side", cases.rocket(150, N=50)))
+    c = cases.rocket(150, N=30, linear=False)
+    c["cones"] = dict(Acu=e["Acu"], qcu=e["qcu"], cu=e["cu"], Acx=[], qcx=[], cx=[])       # Julia order: lands on the state side only (Q1)
+    variants.append(("cone on one side", c))
+    c = cases.rocket(150, N=30, linear=False)
+    c["cones"] = dict(Acu=[3], qcu=[3], cu=[0.4], Acx=e["Acx"], qcx=e["qcx"], cx=e["cx"])  # state-side cone on elements 3..5
+    variants.append(("cone at element 3", c))
+    c = cases.rocket(150, N=30)
+    Ax, bx, Au, bu = c["linear"]
+    c["linear"] = (np.asfortranarray(np.vstack([Ax, -0.5 * Ax + 0.1])), np.array([bx[0], 40.0]), Au, bu)
+    variants.append(("two state half-spaces", c))
+    c = cases.rocket(150, N=30)
+    rng = np.random.default_rng(2)
+    c["Xref"] = np.asfortranarray(c["Xref"][:, :, None] + 0.05 * rng.standard_normal((6, 30, 150)))
+    c["Uref"] = np.asfortranarray(np.repeat(c["Uref"][:, :, None], 150, axis=2))
+    c["ref_mode"] = cases.oracle.REF_PER_INSTANCE
+    variants.append(("per-instance references", c))
+    c = cases.rocket(150, N=30)
+    c["bounds"] = None
+    variants.append(("no box", c))
+    for what, c in variants:
+        c["max_iter"] = 40
+        want = cases.run_checker(c, orc, nthreads=8)
+        a = cases.run_cuda(c, kernel=CONE)
+        assert a["solver"].kernel == CONE, what
+        b = cases.run_cuda(c, kernel=THREAD)
+        cases.compare(a, want, what=f"cone kernel, {what}")
+        for k in ("ret", "iters", "X", "U"):
+            assert np.array_equal(a[k], b[k]), f"{what}: {k} differs between the cone and the thread kernel"
+
+
 def test_cuda_ragged_batch_sizes(orc):
     """B not a multiple of the tile (8) / warp (32) / block: tail lanes must stay inert."""
     for B in (1, 2, 7, 9, 31, 33, 130):

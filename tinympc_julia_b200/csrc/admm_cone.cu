@@ -150,10 +150,13 @@ __device__ __forceinline__ void task_tm_store(uint32_t taddr, const uint32_t* w)
 
 __device__ __forceinline__ double shfl_d(double v, int src) { return shfl_dq(v, src); }
 
-// SPEC: the constraint set is fixed at compile time to the rocket-landing form - box on both sides with knot-invariant
-// bounds, shared references (both staged as tables), ONE cone per side starting at element 0, ONE half-space per side.
-// The run-time flags, cone loops and half-space loops then fold away and phase B becomes a few long basic blocks.
-template <int NX, int NU, bool SPEC>
+// SPEC >= 0: the constraint set is fixed at compile time - the box on both sides through the staged bound table (a side
+// without a box holds (-inf, inf)), shared references staged as tables, and per bit of SPEC
+//   1: ONE cone per side, starting at element 0 (the reference's rocket-landing example, rocket_landing_mpc.cpp:59-94)
+//   2: ONE half-space per side.
+// The run-time flags, cone loops and half-space loops then fold away and phase B becomes a few long basic blocks, which
+// is what its instruction-level parallelism needs (config 4: 50.0 -> 33.3 ms).  SPEC = -1 is the general form.
+template <int NX, int NU, int SPEC>
 __global__ void __launch_bounds__(kCWarps * 32, 1)
 admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ AdmmSettings st,
                  const __grid_constant__ ConeParams cp) {
@@ -244,15 +247,16 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     const double cf = is_x ? sf[row] : 0.0;
     const double cb = is_x ? sAPf[row] : (is_u ? sBPf[jrow] : 0.0);
 
-    const bool box_x = SPEC || (st.en_state_bound && bv.x_min != nullptr);
-    const bool box_u = SPEC || (st.en_input_bound && bv.u_min != nullptr);
-    const bool soc_x = SPEC || (st.en_state_soc && bv.ncx > 0);
-    const bool soc_u = SPEC || (st.en_input_soc && bv.ncu > 0);
-    const bool lin_x = SPEC || st.en_state_linear != 0;
-    const bool lin_u = SPEC || st.en_input_linear != 0;
-    const bool tab_bounds = SPEC || cp.tab_bounds != 0;
-    const bool tab_refs = SPEC || cp.tab_refs != 0;
-    const int nlx = SPEC ? 1 : bv.nlx, nlu = SPEC ? 1 : bv.nlu;
+    constexpr bool FIX = SPEC >= 0, FIX_SOC = FIX && (SPEC & 1), FIX_LIN = FIX && (SPEC & 2);
+    const bool box_x = FIX || (st.en_state_bound && bv.x_min != nullptr);
+    const bool box_u = FIX || (st.en_input_bound && bv.u_min != nullptr);
+    const bool soc_x = FIX ? FIX_SOC : (st.en_state_soc && bv.ncx > 0);
+    const bool soc_u = FIX ? FIX_SOC : (st.en_input_soc && bv.ncu > 0);
+    const bool lin_x = FIX ? FIX_LIN : st.en_state_linear != 0;
+    const bool lin_u = FIX ? FIX_LIN : st.en_input_linear != 0;
+    const bool tab_bounds = FIX || cp.tab_bounds != 0;
+    const bool tab_refs = FIX || cp.tab_refs != 0;
+    const int nlx = FIX ? 1 : bv.nlx, nlu = FIX ? 1 : bv.nlu;
     const int rounds = (T + 31) / 32;
 
     for (;;) {
@@ -430,7 +434,7 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                         if (soc_u) {
 #pragma unroll
                             for (int j = 0; j < NU; ++j) vc[j] = dadd(u[j], yc[j]);
-                            if (SPEC) project_soc3(vc, bv.cu[0]);
+                            if (FIX) project_soc3(vc, bv.cu[0]);
                             else { double v3[NU] = {vc[0], vc[1], vc[2]}; project_cones<NU>(v3, bv.ncu, bv.Acu, bv.cu); vc[0] = v3[0]; vc[1] = v3[1]; vc[2] = v3[2]; }
 #pragma unroll
                             for (int j = 0; j < NU; ++j) {
@@ -487,7 +491,7 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                         if (soc_x) {
 #pragma unroll
                             for (int j = 0; j < NX; ++j) vc[j] = dadd(x[j], gc[j]);
-                            if (SPEC) project_soc3(vc, bv.cx[0]);       // the cone is elements 0..2
+                            if (FIX) project_soc3(vc, bv.cx[0]);        // the cone is elements 0..2
                             else project_cones<NX>(vc, bv.ncx, bv.Acx, bv.cx);
 #pragma unroll
                             for (int j = 0; j < NX; ++j) {
@@ -677,11 +681,15 @@ cudaError_t launch_admm_cone(const BatchView& bv, const AdmmSettings& st, int co
     if (!cone_plan<6, 3>(bv, cp, bytes)) return cudaErrorInvalidConfiguration;
     cp.counter = counter;
     cp.cold = cold;
-    // the rocket-landing form of the constraint set runs the variant with everything folded at compile time
-    const bool spec = TMPC_CONE_SPEC && cp.tab_refs && cp.tab_bounds && st.en_state_bound && st.en_input_bound && bv.x_min && bv.u_min &&
-                      st.en_state_soc && st.en_input_soc && bv.ncx == 1 && bv.ncu == 1 && bv.Acx[0] == 0 && bv.Acu[0] == 0 &&
-                      st.en_state_linear && st.en_input_linear && bv.nlx == 1 && bv.nlu == 1;
-    auto kern = spec ? admm_cone_kernel<6, 3, true> : admm_cone_kernel<6, 3, false>;
+    // constraint sets of the forms listed at the kernel run the variant with everything folded at compile time
+    const bool no_soc = !(st.en_state_soc && bv.ncx > 0) && !(st.en_input_soc && bv.ncu > 0);
+    const bool one_soc = st.en_state_soc && st.en_input_soc && bv.ncx == 1 && bv.ncu == 1 && bv.Acx[0] == 0 && bv.Acu[0] == 0;
+    const bool no_lin = !st.en_state_linear && !st.en_input_linear;
+    const bool one_lin = st.en_state_linear && st.en_input_linear && bv.nlx == 1 && bv.nlu == 1;
+    int spec = -1;
+    if (TMPC_CONE_SPEC && cp.tab_refs && cp.tab_bounds && one_soc && (no_lin || one_lin)) spec = 1 | (one_lin ? 2 : 0);
+    (void)no_soc;
+    auto kern = spec == 3 ? admm_cone_kernel<6, 3, 3> : (spec == 1 ? admm_cone_kernel<6, 3, 1> : admm_cone_kernel<6, 3, -1>);
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes));
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(counter, 0, sizeof(int), stream);
