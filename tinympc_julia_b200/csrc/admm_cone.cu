@@ -269,6 +269,11 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
         int iter[kCInst], status[kCInst];
         bool live[kCInst];
         // element gi of a per-instance register array, by selects (a dynamic index would go through local memory)
+        // instance of the tile that task tau belongs to (tau / N without the integer division: kCInst - 1 compares)
+        auto inst_of = [&](int tau) { int gi = 0;
+#pragma unroll
+            for (int k = 1; k < kCInst; ++k) gi += (tau >= k * N) ? 1 : 0;
+            return gi; };
         auto pick = [&](const auto& arr, int gi) { auto v = arr[0];
 #pragma unroll
             for (int k = 1; k < kCInst; ++k) v = (gi == k) ? arr[k] : v;
@@ -280,7 +285,7 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
         for (int rd = 0; rd < rounds; ++rd) {
             const int tau = rd * 32 + lane;
             const bool act = tau < T;
-            const int gi = act ? tau / N : 0, i = act ? tau - gi * N : 0;
+            const int gi = act ? inst_of(tau) : 0, i = act ? tau - gi * N : 0;
             const int b = b_first + gi;
             const bool ldst = act && b < bv.B && !cp.cold;
             uint32_t w[kTaskWords];
@@ -397,7 +402,7 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             // state sits in Tensor Memory and for those in shared memory - so that neither path has to move its registers
             // to where the other one expects them.
             auto task = [&](double (&s)[kTaskDoubles], const int tau, const bool in_tile) {
-                const int gi = in_tile ? tau / N : 0, i = in_tile ? tau - gi * N : 0;
+                const int gi = in_tile ? inst_of(tau) : 0, i = in_tile ? tau - gi * N : 0;
                 const int b = b_first + gi;
                 const bool act = in_tile && pick(live, gi);
                 const bool testing = pick(tst, gi);
@@ -578,7 +583,7 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
         for (int rd = 0; rd < rounds; ++rd) {
             const int tau = rd * 32 + lane;
             const bool in_tile = tau < T;
-            const int gi = in_tile ? tau / N : 0, i = in_tile ? tau - gi * N : 0;
+            const int gi = in_tile ? inst_of(tau) : 0, i = in_tile ? tau - gi * N : 0;
             const int b = b_first + gi;
             const bool act = in_tile && b < bv.B;
             const int st_k = pick(status, gi);
