@@ -51,14 +51,20 @@ def test_cuda_matches_oracle_seeded(orc, make, B):
 
 
 def test_cone_kernel_every_compiled_form(orc):
-    """admm_cone.cu compiles the rocket shape three times: cones only (the reference's rocket example), cones + one
-    half-space per side (config 4), and the general form with run-time flags.  Each against the oracle and, bit for bit,
+    """admm_cone.cu compiles the rocket shape five times: box only, cones only (the reference's rocket example), one half-space
+    per side, cones + one half-space per side (config 4), and the general form with run-time flags.  Each against the oracle and, bit for bit,
     against the thread kernel; the general form with constraint sets the fixed forms do not cover (cone on one side only,
     a cone that does not start at element 0, two half-spaces, per-instance references, no box)."""
     from tinympc_julia_b200 import problems
     e = problems.rocket().extra
     variants = []
     variants.append(("cones only", cases.rocket(150, N=30, linear=False)))
+    c = cases.rocket(150, N=30, linear=False)
+    c["cones"] = None
+    variants.append(("box only", c))
+    c = cases.rocket(150, N=30)
+    c["cones"] = None
+    variants.append(("one half-space per side, no cones", c))
     variants.append(("cones + one half-space per side", cases.rocket(150, N=50)))
     c = cases.rocket(150, N=30, linear=False)
     c["cones"] = dict(Acu=e["Acu"], qcu=e["qcu"], cu=e["cu"], Acx=[], qcx=[], cx=[])       # Julia order: lands on the state side only (Q1)

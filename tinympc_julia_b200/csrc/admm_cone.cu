@@ -155,7 +155,7 @@ __device__ __forceinline__ double shfl_d(double v, int src) { return shfl_dq(v, 
 //   1: ONE cone per side, starting at element 0 (the reference's rocket-landing example, rocket_landing_mpc.cpp:59-94)
 //   2: ONE half-space per side.
 // The run-time flags, cone loops and half-space loops then fold away and phase B becomes a few long basic blocks, which
-// is what its instruction-level parallelism needs (config 4: 50.0 -> 33.3 ms).  SPEC = -1 is the general form.
+// is what its instruction-level parallelism needs (config 4: 50.0 -> 32.9 ms).  SPEC = -1 is the general form.
 template <int NX, int NU, int SPEC>
 __global__ void __launch_bounds__(kCWarps * 32, 1)
 admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ AdmmSettings st,
@@ -692,9 +692,12 @@ cudaError_t launch_admm_cone(const BatchView& bv, const AdmmSettings& st, int co
     const bool no_lin = !st.en_state_linear && !st.en_input_linear;
     const bool one_lin = st.en_state_linear && st.en_input_linear && bv.nlx == 1 && bv.nlu == 1;
     int spec = -1;
-    if (TMPC_CONE_SPEC && cp.tab_refs && cp.tab_bounds && one_soc && (no_lin || one_lin)) spec = 1 | (one_lin ? 2 : 0);
-    (void)no_soc;
-    auto kern = spec == 3 ? admm_cone_kernel<6, 3, 3> : (spec == 1 ? admm_cone_kernel<6, 3, 1> : admm_cone_kernel<6, 3, -1>);
+    if (TMPC_CONE_SPEC && cp.tab_refs && cp.tab_bounds && (no_soc || one_soc) && (no_lin || one_lin)) spec = (one_soc ? 1 : 0) | (one_lin ? 2 : 0);
+    auto kern = admm_cone_kernel<6, 3, -1>;
+    if (spec == 0) kern = admm_cone_kernel<6, 3, 0>;
+    if (spec == 1) kern = admm_cone_kernel<6, 3, 1>;
+    if (spec == 2) kern = admm_cone_kernel<6, 3, 2>;
+    if (spec == 3) kern = admm_cone_kernel<6, 3, 3>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes));
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(counter, 0, sizeof(int), stream);
