@@ -153,10 +153,11 @@ __device__ __forceinline__ double shfl_d(double v, int src) { return shfl_dq(v, 
 // SPEC >= 0: the constraint set is fixed at compile time - the box on both sides through the staged bound table (a side
 // without a box holds (-inf, inf)), shared references staged as tables, and per bit of SPEC
 //   1: ONE cone per side, starting at element 0 (the reference's rocket-landing example, rocket_landing_mpc.cpp:59-94)
-//   2: ONE half-space per side.
+//   2: ONE half-space per side;
+// RTAB says whether the references are shared (staged as tables) or per instance (read through the read-only path).
 // The run-time flags, cone loops and half-space loops then fold away and phase B becomes a few long basic blocks, which
 // is what its instruction-level parallelism needs (config 4: 50.0 -> 32.9 ms).  SPEC = -1 is the general form.
-template <int NX, int NU, int SPEC>
+template <int NX, int NU, int SPEC, bool RTAB = true>
 __global__ void __launch_bounds__(kCWarps * 32, 1)
 admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ AdmmSettings st,
                  const __grid_constant__ ConeParams cp) {
@@ -255,7 +256,7 @@ admm_cone_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     const bool lin_x = FIX ? FIX_LIN : st.en_state_linear != 0;
     const bool lin_u = FIX ? FIX_LIN : st.en_input_linear != 0;
     const bool tab_bounds = FIX || cp.tab_bounds != 0;
-    const bool tab_refs = FIX || cp.tab_refs != 0;
+    const bool tab_refs = FIX ? RTAB : cp.tab_refs != 0;      // RTAB = false: per-instance references through the read-only path
     const int nlx = FIX ? 1 : bv.nlx, nlu = FIX ? 1 : bv.nlu;
     const int rounds = (T + 31) / 32;
 
@@ -692,12 +693,19 @@ cudaError_t launch_admm_cone(const BatchView& bv, const AdmmSettings& st, int co
     const bool no_lin = !st.en_state_linear && !st.en_input_linear;
     const bool one_lin = st.en_state_linear && st.en_input_linear && bv.nlx == 1 && bv.nlu == 1;
     int spec = -1;
-    if (TMPC_CONE_SPEC && cp.tab_refs && cp.tab_bounds && (no_soc || one_soc) && (no_lin || one_lin)) spec = (one_soc ? 1 : 0) | (one_lin ? 2 : 0);
+    if (TMPC_CONE_SPEC && cp.tab_bounds && (no_soc || one_soc) && (no_lin || one_lin)) spec = (one_soc ? 1 : 0) | (one_lin ? 2 : 0);
     auto kern = admm_cone_kernel<6, 3, -1>;
-    if (spec == 0) kern = admm_cone_kernel<6, 3, 0>;
-    if (spec == 1) kern = admm_cone_kernel<6, 3, 1>;
-    if (spec == 2) kern = admm_cone_kernel<6, 3, 2>;
-    if (spec == 3) kern = admm_cone_kernel<6, 3, 3>;
+    if (cp.tab_refs) {
+        if (spec == 0) kern = admm_cone_kernel<6, 3, 0, true>;
+        if (spec == 1) kern = admm_cone_kernel<6, 3, 1, true>;
+        if (spec == 2) kern = admm_cone_kernel<6, 3, 2, true>;
+        if (spec == 3) kern = admm_cone_kernel<6, 3, 3, true>;
+    } else {
+        if (spec == 0) kern = admm_cone_kernel<6, 3, 0, false>;
+        if (spec == 1) kern = admm_cone_kernel<6, 3, 1, false>;
+        if (spec == 2) kern = admm_cone_kernel<6, 3, 2, false>;
+        if (spec == 3) kern = admm_cone_kernel<6, 3, 3, false>;
+    }
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(bytes));
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(counter, 0, sizeof(int), stream);
