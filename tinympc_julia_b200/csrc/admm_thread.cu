@@ -41,12 +41,24 @@ namespace {
 // and the C ABI stay double; the carried state, which only this kernel reads in float mode, is stored as T.
 // (the traits class Ar<T> lives in admm_device.cuh)
 
+// Blocks per SM the register allocation aims at (M::kMinBlocks).  The kernel streams its state through L2 / HBM and hides
+// that latency with resident warps only: with the compiled-in shapes at one block per 242 registers (8 warps per SM) the
+// quadrotor batch runs 80 ms on the hard workload, at four blocks (128 registers, ~0.7 KB of L1-resident spills per
+// thread) 49 ms; five and more lose again.  The adaptive-rho provider keeps one: its run time is the tail of the few
+// instances that never converge, i.e. the latency of single warps, which the spills lengthen.
+#ifndef TMPC_THREAD_MINBLOCKS
+#define TMPC_THREAD_MINBLOCKS 4
+#endif
+#ifndef TMPC_THREAD_MINBLOCKS_PI
+#define TMPC_THREAD_MINBLOCKS_PI 0
+#endif
 // ---------------------------------------------------------------- matrix operand providers
 template <class T, int NX, int NU>
 struct MatsConst {           // by-value kernel parameter -> constant bank
     static constexpr int kMaxNx = NX, kMaxNu = NU;
     static constexpr bool kStatic = true;
     static constexpr bool kAdaptive = false;
+    static constexpr int kMinBlocks = TMPC_THREAD_MINBLOCKS;
     __device__ __forceinline__ const MatsConst& bound(int) const { return *this; }
     T A_[NX * NX], B_[NX * NU], Kinf_[NU * NX], AmBKt_[NX * NX], Quu_inv_[NU * NU], Pinf_[NX * NX];
     T f_[NX], APf_[NX], BPf_[NU], Qd_[NX], Rd_[NU];
@@ -69,6 +81,7 @@ struct MatsGlobal {          // runtime dimensions: uniform loads through the re
     static constexpr int kMaxNx = kThreadKernelMaxNx, kMaxNu = kThreadKernelMaxNu;
     static constexpr bool kStatic = false;
     static constexpr bool kAdaptive = false;
+    static constexpr int kMinBlocks = 0;        // unspecified (rolled loops: 56-64 registers)
     __device__ __forceinline__ const MatsGlobal& bound(int) const { return *this; }
     int nx_, nu_;
     const double *A_, *B_, *Kinf_, *AmBKt_, *Quu_inv_, *Pinf_, *f_, *APf_, *BPf_, *Qd_, *Rd_;
@@ -93,6 +106,7 @@ struct MatsPerInstance {
     static constexpr int kMaxNx = NX ? NX : kPerInstanceMaxNx, kMaxNu = NX ? NU : kPerInstanceMaxNu;
     static constexpr bool kStatic = NX != 0;
     static constexpr bool kAdaptive = false;
+    static constexpr int kMinBlocks = NX ? TMPC_THREAD_MINBLOCKS_PI : 0;
     int nx_, nu_;
     long long ld_;
     PerInstanceMats p_;
@@ -121,6 +135,7 @@ struct MatsAdaptive {
     static constexpr int kMaxNx = NX ? NX : kThreadKernelMaxNx, kMaxNu = NX ? NU : kThreadKernelMaxNu;
     static constexpr bool kStatic = NX != 0;
     static constexpr bool kAdaptive = true;
+    static constexpr int kMinBlocks = 0;
     int nx_, nu_;
     long long ld_, b_;
     const double *A_, *B_, *AmBKt_, *Quu_inv_, *f_, *APf_, *BPf_, *Qd_, *Rd_;
@@ -142,7 +157,7 @@ struct MatsAdaptive {
 };
 
 template <class T, class M>
-__global__ void __launch_bounds__(kThreadKernelBlock)
+__global__ void __launch_bounds__(kThreadKernelBlock, M::kMinBlocks)
 admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ BatchView bv,
                    const __grid_constant__ AdmmSettings st) {
     using R = Ar<T>;

@@ -10,7 +10,7 @@ import tinympc_julia_b200 as t
 
 B = int(os.environ.get("QB", 65536))
 c = cases.rocket(B, N=50)
-sol = cases.make_cuda_solver(c, kernel=t.KERNEL_CONE)
+sol = cases.make_cuda_solver(c, kernel=int(os.environ.get('QK', t.KERNEL_CONE)))
 t.set_x_ref(sol, c["Xref"]); t.set_u_ref(sol, c["Uref"]); t.set_x0(sol, c["x0"])
 stream = torch.cuda.Stream()
 ts = []
