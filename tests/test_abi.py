@@ -118,3 +118,26 @@ def test_host_lqr_cache_rejects_singular():
     none = C.cast(None, _lib.c_double_p)
     rc = lib.tmpc_compute_cache(P(z), P(z), P(f), P(z), P(z), 0.0, 2, 2, *([none] * 8))
     assert rc != 0
+
+
+def test_noalloc_entry_point_validates_before_touching_the_device():
+    """tmpc_solve_noalloc (no counterpart in the reference; operators' request): argument and size checks come before any
+    CUDA call, so they can be exercised here.  A working set beyond the static array is refused with the sizes named."""
+    lib = _lib.load()
+    s = problems.quadrotor()
+    n, m, N = 12, 4, 20
+    A, B, f, Q, R = (np.asfortranarray(np.asarray(a, dtype=np.float64)) for a in (s.A, s.B, s.f.reshape(n), s.Q, s.R))
+    P = lambda a: a.ctypes.data_as(_lib.c_double_p)
+    cache = [np.zeros(k) for k in (m * n, n * n, m * m, n * n, n, m, n, m)]
+    assert lib.tmpc_compute_cache(P(A), P(B), P(f), P(Q), P(R), float(s.rho), n, m, *[P(c) for c in cache]) == 0
+    err = C.create_string_buffer(512)
+    fake = C.c_void_p(0x1000)                       # never dereferenced: the call must fail before reaching the device
+
+    def call(B_, max_iter=100, x0=fake):
+        return lib.tmpc_solve_noalloc(n, m, N, B_, float(s.rho), P(A), P(B), P(f), *[P(c) for c in cache], x0, None, None, None, None,
+                                      None, None, 1e-3, 1e-3, max_iter, 1, fake, fake, fake, fake, None, err, len(err))
+    assert call(3073) == 1 and b"too large" in err.value and b"tmpc_batch_create" in err.value
+    assert call(1 << 20) == 1 and b"too large" in err.value
+    assert call(64, max_iter=0) == 2 and b"max_iter" in err.value
+    assert call(64, x0=None) == 1 and b"null device pointer" in err.value
+    assert call(0) == 1
