@@ -211,9 +211,26 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
         double* __restrict__ z_new = bv.z[cur ^ 1];
 
         // ---------------- backward pass: d_i, p_i for i = N-2 .. 0
-        for (int i = N - 2; i >= 0; --i) {
+        // r_i and q_i do not depend on the recursion: they are requested one knot point ahead, BEFORE this knot's store of
+        // d_i (the compiler must assume the store may alias them and would otherwise start every load after it - a lone
+        // warp then pays one HBM round trip per group of loads, ~10 per knot point)
+        T qn[MX], rn[MU];
 #pragma unroll UNR
-            for (int j = 0; j < MU; ++j) if (j < nu) rr[j] = ST(bv.r, i * nu + j);
+        for (int j = 0; j < MU; ++j) if (j < nu) rn[j] = ST(bv.r, (N - 2) * nu + j);
+#pragma unroll UNR
+        for (int j = 0; j < MX; ++j) if (j < nx) qn[j] = ST(bv.q, (N - 2) * nx + j);
+        for (int i = N - 2; i >= 0; --i) {
+            T qi[MX];
+#pragma unroll UNR
+            for (int j = 0; j < MU; ++j) if (j < nu) rr[j] = rn[j];
+#pragma unroll UNR
+            for (int j = 0; j < MX; ++j) if (j < nx) qi[j] = qn[j];
+            if (i > 0) {
+#pragma unroll UNR
+                for (int j = 0; j < MU; ++j) if (j < nu) rn[j] = ST(bv.r, (i - 1) * nu + j);
+#pragma unroll UNR
+                for (int j = 0; j < MX; ++j) if (j < nx) qn[j] = ST(bv.q, (i - 1) * nx + j);
+            }
 #pragma unroll UNR
             for (int j = 0; j < MU; ++j) if (j < nu) {
                 T s = 0;
@@ -235,7 +252,7 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
                 for (int k = 0; k < MX; ++k) if (k < nx) s1 = R::fma(mt.AmBKt(j, k), p[k], s1);
 #pragma unroll UNR
                 for (int k = 0; k < MU; ++k) if (k < nu) s2 = R::fma(mt.Kinf(k, j), rr[k], s2);
-                tmp[j] = R::add(R::sub(R::add(ST(bv.q, i * nx + j), s1), s2), mt.APf(j));
+                tmp[j] = R::add(R::sub(R::add(qi[j], s1), s2), mt.APf(j));
             }
 #pragma unroll UNR
             for (int j = 0; j < MX; ++j) if (j < nx) p[j] = tmp[j];
@@ -248,6 +265,17 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
 
         for (int i = 0; i < N; ++i) {
             const bool terminal = (i == N - 1);
+            // everything this knot point reads of the box-constrained state is requested here, before its first store
+            // (see the backward pass): d_i, y_i, z_i (previous), g_i, v_i (previous)
+            T dk[MU], yk[MU], zo[MU], gk[MX], vo[MX];
+            if (!terminal) {
+#pragma unroll UNR
+                for (int j = 0; j < MU; ++j) if (j < nu) {
+                    dk[j] = ST(bv.d, i * nu + j); yk[j] = ST(bv.y, i * nu + j); zo[j] = ST(z_old, i * nu + j);
+                }
+            }
+#pragma unroll UNR
+            for (int j = 0; j < MX; ++j) if (j < nx) { gk[j] = ST(bv.g, i * nx + j); vo[j] = ST(v_old, i * nx + j); }
             if (!terminal) {
                 // u_i = -Kinf x_i - d_i
 #pragma unroll UNR
@@ -255,19 +283,19 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
                     T s = 0;
 #pragma unroll UNR
                     for (int k = 0; k < MX; ++k) if (k < nx) s = R::fma(mt.Kinf(j, k), x[k], s);
-                    u[j] = R::sub(-s, ST(bv.d, i * nu + j));
+                    u[j] = R::sub(-s, dk[j]);
                 }
                 // ---- input column i
 #pragma unroll UNR
                 for (int j = 0; j < MU; ++j) if (j < nu) {
                     const int e = i * nu + j;
-                    const T yj = ST(bv.y, e);
+                    const T yj = yk[j];
                     T znew = R::add(u[j], yj);
-                    if (box_u) znew = R::clamp(znew, umin[e], umax[e]);
+                    if (box_u) znew = R::clamp(znew, __ldg(umin + e), __ldg(umax + e));
                     const T ynew = R::sub(R::add(yj, u[j]), znew);
                     pri_u = R::max(pri_u, R::abs(R::sub(u[j], znew)));
-                    dua_u = R::max(dua_u, R::abs(R::sub(ST(z_old, e), znew)));
-                    T racc = -R::mul(uref ? uref[e] : 0.0, mt.Rd(j));
+                    dua_u = R::max(dua_u, R::abs(R::sub(zo[j], znew)));
+                    T racc = -R::mul(uref ? __ldg(uref + e) : 0.0, mt.Rd(j));
                     racc = R::sub(racc, R::mul(rho, R::sub(znew, ynew)));
                     ST(bv.y, e) = ynew;
                     ST(z_new, e) = znew;
@@ -306,12 +334,12 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
 #pragma unroll UNR
             for (int j = 0; j < MX; ++j) if (j < nx) {
                 const int e = i * nx + j;
-                const T gj = ST(bv.g, e);
+                const T gj = gk[j];
                 T vnew = R::add(x[j], gj);
-                if (box_x) vnew = R::clamp(vnew, xmin[e], xmax[e]);
+                if (box_x) vnew = R::clamp(vnew, __ldg(xmin + e), __ldg(xmax + e));
                 const T gnew = R::sub(R::add(gj, x[j]), vnew);
                 pri_x = R::max(pri_x, R::abs(R::sub(x[j], vnew)));
-                dua_x = R::max(dua_x, R::abs(R::sub(ST(v_old, e), vnew)));
+                dua_x = R::max(dua_x, R::abs(R::sub(vo[j], vnew)));
                 ST(bv.g, e) = gnew;
                 ST(v_new, e) = vnew;
                 acc[j] = R::mul(rho, R::sub(vnew, gnew));       // rho * (vnew - g)
@@ -321,14 +349,14 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
             if (!terminal) {
 #pragma unroll UNR
                 for (int j = 0; j < MX; ++j) if (j < nx)
-                    acc[j] = R::sub(-R::mul(xref ? xref[i * nx + j] : 0.0, mt.Qd(j)), acc[j]);
+                    acc[j] = R::sub(-R::mul(xref ? __ldg(xref + i * nx + j) : 0.0, mt.Qd(j)), acc[j]);
             } else {
 #pragma unroll UNR
                 for (int j = 0; j < MX; ++j) if (j < nx) {
                     T s = 0;
                     if (xref) {
 #pragma unroll UNR
-                        for (int k = 0; k < MX; ++k) if (k < nx) s = R::fma(xref[i * nx + k], mt.Pinf(k, j), s);
+                        for (int k = 0; k < MX; ++k) if (k < nx) s = R::fma(__ldg(xref + i * nx + k), mt.Pinf(k, j), s);
                     }
                     acc[j] = R::sub(-s, acc[j]);
                 }
