@@ -156,7 +156,9 @@ struct MatsAdaptive {
     __device__ __forceinline__ double Rd(int i) const { return __ldg(Rd_ + i); }
 };
 
-template <class T, class M>
+// EXTRA = false: box constraints only - the cone / half-space code and the registers of its slack columns are compiled out
+// (the launchers pick the instantiation from the settings).
+template <class T, class M, bool EXTRA>
 __global__ void __launch_bounds__(kThreadKernelBlock, M::kMinBlocks)
 admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ BatchView bv,
                    const __grid_constant__ AdmmSettings st) {
@@ -182,10 +184,10 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
 
     const bool box_x = st.en_state_bound && bv.x_min != nullptr;
     const bool box_u = st.en_input_bound && bv.u_min != nullptr;
-    const bool soc_x = st.en_state_soc && bv.ncx > 0;
-    const bool soc_u = st.en_input_soc && bv.ncu > 0;
-    const bool lin_x = st.en_state_linear != 0;
-    const bool lin_u = st.en_input_linear != 0;
+    const bool soc_x = EXTRA && st.en_state_soc && bv.ncx > 0;
+    const bool soc_u = EXTRA && st.en_input_soc && bv.ncu > 0;
+    const bool lin_x = EXTRA && st.en_state_linear != 0;
+    const bool lin_u = EXTRA && st.en_input_linear != 0;
 
     const double* xref = bv.Xref ? bv.Xref + static_cast<size_t>(b) * bv.xref_stride : nullptr;
     const double* uref = bv.Uref ? bv.Uref + static_cast<size_t>(b) * bv.uref_stride : nullptr;
@@ -276,6 +278,23 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
             }
 #pragma unroll UNR
             for (int j = 0; j < MX; ++j) if (j < nx) { gk[j] = ST(bv.g, i * nx + j); vo[j] = ST(v_old, i * nx + j); }
+            T gck[MX], glk[MX], yck[MU], ylk[MU];          // cone / half-space duals of the knot point, likewise
+            if (soc_u && !terminal) {
+#pragma unroll UNR
+                for (int j = 0; j < MU; ++j) if (j < nu) yck[j] = ST(bv.yc, i * nu + j);
+            }
+            if (lin_u && !terminal) {
+#pragma unroll UNR
+                for (int j = 0; j < MU; ++j) if (j < nu) ylk[j] = ST(bv.yl, i * nu + j);
+            }
+            if (soc_x) {
+#pragma unroll UNR
+                for (int j = 0; j < MX; ++j) if (j < nx) gck[j] = ST(bv.gc, i * nx + j);
+            }
+            if (lin_x) {
+#pragma unroll UNR
+                for (int j = 0; j < MX; ++j) if (j < nx) glk[j] = ST(bv.gl, i * nx + j);
+            }
             if (!terminal) {
                 // u_i = -Kinf x_i - d_i
 #pragma unroll UNR
@@ -303,25 +322,25 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
                 }
                 if (soc_u) {
 #pragma unroll UNR
-                    for (int j = 0; j < MU; ++j) if (j < nu) vc[j] = R::add(u[j], ST(bv.yc, i * nu + j));
+                    for (int j = 0; j < MU; ++j) if (j < nu) vc[j] = R::add(u[j], yck[j]);
                     if (st.en_input_soc)
                         for (int k = 0; k < bv.ncu; ++k) project_soc3(vc + bv.Acu[k], bv.cu[k]);
 #pragma unroll UNR
                     for (int j = 0; j < MU; ++j) if (j < nu) {
                         const int e = i * nu + j;
-                        const T ycn = R::sub(R::add(ST(bv.yc, e), u[j]), vc[j]);
+                        const T ycn = R::sub(R::add(yck[j], u[j]), vc[j]);
                         t[j] = R::sub(t[j], R::mul(rho, R::sub(vc[j], ycn)));
                         ST(bv.yc, e) = ycn;
                     }
                 }
                 if (lin_u) {
 #pragma unroll UNR
-                    for (int j = 0; j < MU; ++j) if (j < nu) vc[j] = R::add(u[j], ST(bv.yl, i * nu + j));
+                    for (int j = 0; j < MU; ++j) if (j < nu) vc[j] = R::add(u[j], ylk[j]);
                     project_halfspaces(vc, nu, bv.Alin_u, bv.blin_u, bv.nlu);
 #pragma unroll UNR
                     for (int j = 0; j < MU; ++j) if (j < nu) {
                         const int e = i * nu + j;
-                        const T yln = R::sub(R::add(ST(bv.yl, e), u[j]), vc[j]);
+                        const T yln = R::sub(R::add(ylk[j], u[j]), vc[j]);
                         t[j] = R::sub(t[j], R::mul(rho, R::sub(vc[j], yln)));
                         ST(bv.yl, e) = yln;
                     }
@@ -363,25 +382,25 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
             }
             if (soc_x) {
 #pragma unroll UNR
-                for (int j = 0; j < MX; ++j) if (j < nx) vc[j] = R::add(x[j], ST(bv.gc, i * nx + j));
+                for (int j = 0; j < MX; ++j) if (j < nx) vc[j] = R::add(x[j], gck[j]);
                 if (st.en_state_soc)
                     for (int k = 0; k < bv.ncx; ++k) project_soc3(vc + bv.Acx[k], bv.cx[k]);
 #pragma unroll UNR
                 for (int j = 0; j < MX; ++j) if (j < nx) {
                     const int e = i * nx + j;
-                    const T gcn = R::sub(R::add(ST(bv.gc, e), x[j]), vc[j]);
+                    const T gcn = R::sub(R::add(gck[j], x[j]), vc[j]);
                     acc[j] = R::sub(acc[j], R::mul(rho, R::sub(vc[j], gcn)));
                     ST(bv.gc, e) = gcn;
                 }
             }
             if (lin_x) {
 #pragma unroll UNR
-                for (int j = 0; j < MX; ++j) if (j < nx) vc[j] = R::add(x[j], ST(bv.gl, i * nx + j));
+                for (int j = 0; j < MX; ++j) if (j < nx) vc[j] = R::add(x[j], glk[j]);
                 project_halfspaces(vc, nx, bv.Alin_x, bv.blin_x, bv.nlx);
 #pragma unroll UNR
                 for (int j = 0; j < MX; ++j) if (j < nx) {
                     const int e = i * nx + j;
-                    const T gln = R::sub(R::add(ST(bv.gl, e), x[j]), vc[j]);
+                    const T gln = R::sub(R::add(glk[j], x[j]), vc[j]);
                     acc[j] = R::sub(acc[j], R::mul(rho, R::sub(vc[j], gln)));
                     ST(bv.gl, e) = gln;
                 }
@@ -529,11 +548,35 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
     const int nxN = nx * N, nuN = nu * (N - 1);
     double* Xs = bv.Xsol + static_cast<size_t>(b) * nxN;
     double* Us = bv.Usol + static_cast<size_t>(b) * nuN;
-    for (int e = 0; e < nxN; ++e) Xs[e] = ST(bv.v[sol], e);
-    for (int e = 0; e < nuN; ++e) Us[e] = ST(bv.z[sol], e);
+    // copies in groups of eight loads, then eight stores (a load behind a store that may alias it would wait for nothing less
+    // than the previous round trip)
+    auto copy_out = [&](double* dst, const double* src_arr, int n) {            // dst[e] = element e of the thread's column
+        int e = 0;
+        for (; e + 8 <= n; e += 8) {
+            T w[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) w[k] = reinterpret_cast<const T*>(src_arr)[static_cast<size_t>(e + k) * ld + b];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) dst[e + k] = w[k];
+        }
+        for (; e < n; ++e) dst[e] = reinterpret_cast<const T*>(src_arr)[static_cast<size_t>(e) * ld + b];
+    };
+    auto copy_col = [&](double* dst_arr, const double* src_arr, int n) {        // element-major to element-major
+        int e = 0;
+        for (; e + 8 <= n; e += 8) {
+            T w[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) w[k] = reinterpret_cast<const T*>(src_arr)[static_cast<size_t>(e + k) * ld + b];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) reinterpret_cast<T*>(dst_arr)[static_cast<size_t>(e + k) * ld + b] = w[k];
+        }
+        for (; e < n; ++e) reinterpret_cast<T*>(dst_arr)[static_cast<size_t>(e) * ld + b] = reinterpret_cast<const T*>(src_arr)[static_cast<size_t>(e) * ld + b];
+    };
+    copy_out(Xs, bv.v[sol], nxN);
+    copy_out(Us, bv.z[sol], nuN);
     if (cur == 1) {   // the carried previous-slack pair must end up in buffer 0
-        for (int e = 0; e < nxN; ++e) ST(bv.v[0], e) = ST(bv.v[1], e);
-        for (int e = 0; e < nuN; ++e) ST(bv.z[0], e) = ST(bv.z[1], e);
+        copy_col(bv.v[0], bv.v[1], nxN);
+        copy_col(bv.z[0], bv.z[1], nuN);
     }
 #pragma unroll UNR
     for (int j = 0; j < MX; ++j) if (j < nx) ST(bv.pN, j) = p[j];
@@ -541,6 +584,11 @@ admm_thread_kernel(const __grid_constant__ M mt_param, const __grid_constant__ B
     bv.iters[b] = iter;
     if constexpr (M::kAdaptive) mt.ad_.rho[b] = rho;
 #undef ST
+}
+
+// any cone or half-space active? (same conditions as in the kernel)
+inline bool needs_extra(const BatchView& bv, const AdmmSettings& st) {
+    return (st.en_state_soc && bv.ncx > 0) || (st.en_input_soc && bv.ncu > 0) || st.en_state_linear != 0 || st.en_input_linear != 0;
 }
 
 template <class T, int NX, int NU>
@@ -555,7 +603,8 @@ cudaError_t launch_const(const BatchView& bv, const AdmmSettings& st, const Host
     MatsConst<T, NX, NU> m;
     fill_const(m, h);
     const int grid = (bv.B + kThreadKernelBlock - 1) / kThreadKernelBlock;
-    admm_thread_kernel<T, MatsConst<T, NX, NU>><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
+    if (needs_extra(bv, st)) admm_thread_kernel<T, MatsConst<T, NX, NU>, true><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
+    else admm_thread_kernel<T, MatsConst<T, NX, NU>, false><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
     return cudaGetLastError();
 }
 
@@ -570,7 +619,8 @@ cudaError_t launch_shared(const BatchView& bv, const AdmmSettings& st, const Hos
     m.A_ = bv.A; m.B_ = bv.Bm; m.Kinf_ = bv.Kinf; m.AmBKt_ = bv.AmBKt; m.Quu_inv_ = bv.Quu_inv; m.Pinf_ = bv.Pinf;
     m.f_ = bv.f; m.APf_ = bv.APf; m.BPf_ = bv.BPf; m.Qd_ = bv.Qd; m.Rd_ = bv.Rd;
     const int grid = (bv.B + kThreadKernelBlock - 1) / kThreadKernelBlock;
-    admm_thread_kernel<T, MatsGlobal><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
+    if (needs_extra(bv, st)) admm_thread_kernel<T, MatsGlobal, true><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
+    else admm_thread_kernel<T, MatsGlobal, false><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
     return cudaGetLastError();
 }
 
@@ -582,7 +632,8 @@ cudaError_t launch_per_instance(const BatchView& bv, const AdmmSettings& st, con
     const int grid = (bv.B + kThreadKernelBlock - 1) / kThreadKernelBlock;
     auto go = [&](auto m) {
         m.nx_ = bv.nx; m.nu_ = bv.nu; m.ld_ = bv.ld; m.p_ = pm; m.b_ = 0;
-        admm_thread_kernel<T, decltype(m)><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
+        if (needs_extra(bv, st)) admm_thread_kernel<T, decltype(m), true><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
+        else admm_thread_kernel<T, decltype(m), false><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
         return cudaGetLastError();
     };
     if (bv.nx == 12 && bv.nu == 4) return go(MatsPerInstance<12, 4>{});
@@ -634,7 +685,8 @@ cudaError_t launch_admm_thread_adaptive(const BatchView& bv, const AdmmSettings&
         m.nx_ = bv.nx; m.nu_ = bv.nu; m.ld_ = bv.ld; m.b_ = 0; m.ad_ = ad;
         m.A_ = bv.A; m.B_ = bv.Bm; m.AmBKt_ = bv.AmBKt; m.Quu_inv_ = bv.Quu_inv; m.f_ = bv.f; m.APf_ = bv.APf;
         m.BPf_ = bv.BPf; m.Qd_ = bv.Qd; m.Rd_ = bv.Rd;
-        admm_thread_kernel<double, decltype(m)><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
+        if (needs_extra(bv, st)) admm_thread_kernel<double, decltype(m), true><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
+        else admm_thread_kernel<double, decltype(m), false><<<grid, kThreadKernelBlock, 0, stream>>>(m, bv, st);
         return cudaGetLastError();
     };
     if (bv.nx == 12 && bv.nu == 4) return go(MatsAdaptive<12, 4>{});
