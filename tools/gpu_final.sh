@@ -11,15 +11,15 @@ print("  value %.4e ms %.4f frac %s iters/s %.4e"%(d["value"], d["ms_per_step"],
 e=d["e2e"]; print("  e2e %.4e u0 %s"%(e["value"], e.get("u0_only",{}).get("value")), d.get("single_solve",{}).get("gpu"))
 PY
 }
-run r02_j_bench_quadrotor_easy
-run r02_j_bench_quadrotor_easy_natural_order --order 0 --no-cpu
-run r02_j_bench_quadrotor_hard --workload quadrotor_hard --steps 16
-run r02_j_bench_cartpole --workload cartpole
-run r02_j_bench_rocket --workload rocket
-run r02_j_bench_rollout --workload rollout
-run r02_j_bench_float_easy --precision 32
-run r02_j_bench_float_hard --precision 32 --workload quadrotor_hard --steps 16 --no-cpu
-run r02_j_bench_float_cartpole --precision 32 --workload cartpole --no-cpu
-run r02_j_bench_reference_arm --impl reference --steps 5 --warmup 1
-run r02_j_bench_reference_arm_rocket --impl reference --workload rocket
-run r02_j_bench_reference_arm_rollout --impl reference --workload rollout
+run r02_m_bench_quadrotor_easy
+run r02_m_bench_quadrotor_easy_natural_order --order 0 --no-cpu
+run r02_m_bench_quadrotor_hard --workload quadrotor_hard --steps 16
+run r02_m_bench_cartpole --workload cartpole
+run r02_m_bench_rocket --workload rocket
+run r02_m_bench_rollout --workload rollout
+run r02_m_bench_float_easy --precision 32
+run r02_m_bench_float_hard --precision 32 --workload quadrotor_hard --steps 16 --no-cpu
+run r02_m_bench_float_cartpole --precision 32 --workload cartpole --no-cpu
+run r02_m_bench_reference_arm --impl reference --steps 5 --warmup 1
+run r02_m_bench_reference_arm_rocket --impl reference --workload rocket
+run r02_m_bench_reference_arm_rollout --impl reference --workload rollout
