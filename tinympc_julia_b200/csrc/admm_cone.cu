@@ -20,9 +20,10 @@
 //
 // Residency.  A task's state (g, v, gc, gl: 4 x 6; y, z, yc, yl: 4 x 3 doubles = 72 32-bit words) lives in the Tensor
 // Memory row of the lane that always processes it (tcgen05.ld/st .32x32b as lane-private scratch; 8 warps x 3 slots of
-// 72 columns = 96 tasks per warp), the remaining 3 N - 96 tasks element-major in shared memory: 24 instances per SM stay
-// on chip for the whole solve (226 KB shared + 216 of 256 TMEM columns per warp at N = 50), HBM is touched at install and
-// write-out only; shared references, knot-invariant bounds and the half-space rows are staged once per CTA.  The thread-per-instance kernel streams 31 KB per instance-iteration through L2 / HBM instead.
+// 72 columns = 96 tasks per warp), the remaining 3 N - 96 tasks in shared memory (37-double pitch): 24 instances per SM stay
+// on chip for the whole solve (224 KB shared + 216 of 256 TMEM columns per warp at N = 50), HBM is touched at install and
+// write-out only; shared references, knot-invariant bounds and the half-space rows are staged once per CTA.  The
+// thread-per-instance kernel streams 31 KB per instance-iteration through L2 / HBM instead.
 //
 // Arithmetic: the same sequence of correctly rounded operations as admm_thread.cu (ascending-k FMA chains, explicitly
 // rounded elementwise updates, project_soc3 with the reference's float mu / norm), so both kernels agree bit for bit
