@@ -129,7 +129,7 @@ enum {
     TMPC_KERNEL_THREAD = 1,   /* one thread per instance, state streamed through L2/HBM each iteration; any nx, nu */
     TMPC_KERNEL_SUBWARP = 2,  /* one instance per 4-lane sub-warp, state resident in shared memory (box constraints) */
     TMPC_KERNEL_TMEM = 3,     /* 4-lane sub-warp, state rows in Tensor Memory + input rows in shared memory, 8 warps/SM,
-                                 per-instance refill (box constraints with shared bounds, nx=12 nu=4, N <= 21) */
+                                 per-instance refill (box constraints with shared bounds; nx=12 nu=4 with N <= 42, nx=4 nu=1) */
     TMPC_KERNEL_CONE = 4      /* box + second-order cones + half-spaces on chip: 3 instances per warp, recursions with a lane
                                  per matrix row, projections with a lane per knot point (nx=6 nu=3, N <= 50) */
 };

@@ -50,6 +50,41 @@ def test_cuda_matches_oracle_seeded(orc, make, B):
         cases.compare(got, want, what=f"cuda[kernel {k}] vs oracle")
 
 
+def test_tmem_kernel_long_horizon_form(orc):
+    """Horizons 22 .. 42 of the quadrotor shape run the four-warp form of the TMEM kernel (all 512 Tensor-Memory columns of a
+    lane quarter per warp): cold and warm solves against the oracle and, bit for bit, the thread kernel; the device closed
+    loop on such a horizon (launch sequence, not the fused kernel); N = 43 is beyond it."""
+    import torch
+    for N in (22, 30, 42):
+        c = cases.quadrotor_batch(700, hard=True, seed=40 + N, N=N, max_iter=30)
+        c["nsteps"] = 2                                        # second step = warm start from the carried state
+        want = cases.run_checker(c, orc, nthreads=8)
+        a = cases.run_cuda(c, kernel=t.KERNEL_AUTO)
+        assert a["solver"].kernel == TMEM, N
+        b = cases.run_cuda(c, kernel=THREAD)
+        cases.compare(a, want, what=f"long-horizon TMEM form, N = {N}")
+        for k in ("ret", "iters", "X", "U"):
+            assert np.array_equal(a[k], b[k]), f"N = {N}: {k} differs between the TMEM and the thread kernel"
+    c = cases.quadrotor_closed_loop(200, 5)                    # per-instance sliding references
+    c["N"] = 20
+    # same closed loop on a 30-knot horizon: references of that length
+    x0, Xlong = problems_mod.quadrotor_line_refs(200, 30, 5, 7)
+    c = cases.quadrotor_batch(200, N=30)
+    c.update(x0=x0, Xref=Xlong, ref_mode=cases.oracle.REF_SLIDING, nsteps=5)
+    want = cases.run_checker(c, orc, nthreads=8)
+    sol = cases.make_cuda_solver(c)
+    assert sol.kernel == TMEM
+    t.set_x0(sol, c["x0"])
+    st, it, xf = _device_rollout(sol, 5, xlong=c["Xref"])
+    assert np.array_equal(it, want["iters"]) and np.array_equal(st, want["ret"])
+    np.testing.assert_allclose(xf, want["x_final"], rtol=1e-5, atol=1e-6)
+    c = cases.quadrotor_batch(64, N=43)
+    sol = cases.make_cuda_solver(c)
+    assert sol.kernel != TMEM
+    sol.set_kernel(TMEM)
+    assert sol.kernel == -1
+
+
 def test_cone_kernel_every_compiled_form(orc):
     """admm_cone.cu compiles the rocket shape five times: box only, cones only (the reference's rocket example), one half-space
     per side, cones + one half-space per side (config 4), and the general form with run-time flags.  Each against the oracle and, bit for bit,

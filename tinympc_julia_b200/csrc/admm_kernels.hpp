@@ -78,6 +78,9 @@ cudaError_t launch_admm_subwarp(const BatchView& bv, const AdmmSettings& st, con
 // the natural order.
 // `precision` = 32: the float instantiation (tinytype = float: 16 warps per SM, carried state as float blocks).
 bool tmem_kernel_supports(const BatchView& bv, const AdmmSettings& st, int precision = 64);
+// the default form of the kernel applies (what the fused closed loop needs; tmem_kernel_supports also accepts the long-horizon
+// form: quadrotor shape in double, N = 22 .. 42, four warps per SM)
+bool tmem_kernel_fused_supports(const BatchView& bv, const AdmmSettings& st, int precision = 64);
 cudaError_t launch_admm_tmem(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms,
                              cudaStream_t stream, const int* order = nullptr, int precision = 64);
 

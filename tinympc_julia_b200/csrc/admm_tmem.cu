@@ -101,8 +101,11 @@ struct QuadParams {
 
 // REFS: 0 = no references (Xref = Uref = 0), 1 = references shared by all instances (staged in shared memory as
 // the products the linear cost needs), 2 = per-instance references read through the read-only path.
-template <class T, int NX, int NU, bool COLD, int REFS, bool ROLL = false, bool PI = false>
-__global__ void __launch_bounds__(QWarps<T, NX, PI>::value * 32, 1)
+// WARPS != 0 overrides the warps per CTA of the shape (QWarps): the long-horizon form runs FOUR warps per SM, each with all
+// 512 Tensor-Memory columns of its lane quarter, which takes the horizon of the quadrotor shape from N <= 21 to N <= 42 at
+// one warp per scheduler.
+template <class T, int NX, int NU, bool COLD, int REFS, bool ROLL = false, bool PI = false, int WARPS = 0>
+__global__ void __launch_bounds__((WARPS ? WARPS : QWarps<T, NX, PI>::value) * 32, 1)
 admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ AdmmSettings st,
                  const __grid_constant__ QuadParams qp) {
     // A global access in uniform control flow before anything else: ptxas then keeps the global-memory descriptor in a
@@ -214,7 +217,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     const bool urow = (NU == 4) || (sub < NU);        // this lane owns an input row
     const int usub = urow ? sub : 0;
     const uint32_t tbase = s_tmem_base + (static_cast<uint32_t>((warp & 3) * 32) << 16) +
-                           static_cast<uint32_t>((warp >> 2) * QTmemCols<T, NX, PI>::value);
+                           static_cast<uint32_t>((warp >> 2) * (WARPS ? ((512 / ((WARPS + 3) / 4)) & ~1) : QTmemCols<T, NX, PI>::value));
     T* wbase = smem + qp.off_warp0 + static_cast<size_t>(warp) * qp.warp_stride;
     T* s_yz = wbase;                             // [N-1][32 lanes][2] : (y, z) of the lane's input row
     T* s_rt = s_yz + (N - 1) * 64;               // [N-1][2 halves][8 inst][2] : r_i (after a forward sweep) / t_i (after a
@@ -860,12 +863,15 @@ T dual_threshold_q(T rho, T tol) {
 
 struct QPlan { size_t smem_bytes; QuadParams qp; };
 
+constexpr int kQLongWarps = 4;       // the long-horizon form (kernel template parameter WARPS)
+
 template <class T, int NX, int NU>
-bool make_qplan(int N, int refs, QPlan& pl, bool pi = false) {
+bool make_qplan(int N, int refs, QPlan& pl, bool pi = false, int warps_override = 0) {
     constexpr int XP = QPad<NX, sizeof(T)>::value;
     constexpr int W = 2 * (NX / 4) * (sizeof(T) / 4);
-    const int warps = pi ? QWarps<T, NX, true>::value : QWarps<T, NX, false>::value;
-    if (N < 2 || N * W > (pi ? QTmemCols<T, NX, true>::value : QTmemCols<T, NX, false>::value)) return false;   // g, v of a lane must fit the warp's TMEM columns
+    const int warps = warps_override ? warps_override : (pi ? QWarps<T, NX, true>::value : QWarps<T, NX, false>::value);
+    const int cols = warps_override ? ((512 / ((warps_override + 3) / 4)) & ~1) : (pi ? QTmemCols<T, NX, true>::value : QTmemCols<T, NX, false>::value);
+    if (N < 2 || N * W > cols) return false;   // g, v of a lane must fit the warp's TMEM columns
     const int nxN = NX * N, nuN = NU * (N - 1);
     QuadParams qp{};
     int off = 0;
@@ -890,30 +896,50 @@ int refs_mode(const BatchView& bv) {
     return (xs && us) ? 1 : 2;
 }
 
-template <class T, int NX, int NU, bool COLD, int REFS, bool ROLL = false, bool PI = false>
+template <class T, int NX, int NU, bool COLD, int REFS, bool ROLL = false, bool PI = false, int WARPS = 0>
 cudaError_t launch_q(const BatchView& bv, const AdmmSettings& st, const QPlan& pl, int num_sms, cudaStream_t stream) {
-    auto kern = admm_tmem_kernel<T, NX, NU, COLD, REFS, ROLL, PI>;
+    auto kern = admm_tmem_kernel<T, NX, NU, COLD, REFS, ROLL, PI, WARPS>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(pl.smem_bytes));
     if (e != cudaSuccess) return e;
-    const int per_cta = QWarps<T, NX, PI>::value * kQInst;
+    constexpr int NW = WARPS ? WARPS : QWarps<T, NX, PI>::value;
+    const int per_cta = NW * kQInst;
     int grid = (bv.B + per_cta - 1) / per_cta;
     if (grid > num_sms) grid = num_sms;            // persistent: one CTA per SM, sub-warps pull instances from the queue
-    kern<<<grid, QWarps<T, NX, PI>::value * 32, pl.smem_bytes, stream>>>(bv, st, pl.qp);
+    kern<<<grid, NW * 32, pl.smem_bytes, stream>>>(bv, st, pl.qp);
     return cudaGetLastError();
 }
+
+// shapes that have the long-horizon form compiled: the quadrotor shape in double (N = 22 .. 42)
+template <class T, int NX> constexpr bool long_horizon_shape() { return sizeof(T) == 8 && NX == 12; }
 
 template <class T, int NX, int NU>
 cudaError_t launch_shape(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms,
                          cudaStream_t stream, const int* order) {
     QPlan pl;
     const int refs = refs_mode(bv);
-    if (!make_qplan<T, NX, NU>(bv.N, refs, pl)) return cudaErrorInvalidConfiguration;
+    bool long_form = false;
+    if (!make_qplan<T, NX, NU>(bv.N, refs, pl)) {
+        if (!long_horizon_shape<T, NX>() || !make_qplan<T, NX, NU>(bv.N, refs, pl, false, kQLongWarps)) return cudaErrorInvalidConfiguration;
+        long_form = true;
+    }
     pl.qp.counter = counter;
     pl.qp.order = order;
     pl.qp.pri_thresh = static_cast<T>(st.abs_pri_tol);                                   // types.hpp:64-65: tolerances are tinytype
     pl.qp.dua_thresh = dual_threshold_q<T>(static_cast<T>(bv.rho), static_cast<T>(st.abs_dua_tol));
     cudaError_t e = cudaMemsetAsync(counter, 0, sizeof(int), stream);
     if (e != cudaSuccess) return e;
+    if constexpr (long_horizon_shape<T, NX>()) {
+        if (long_form) {
+            if (cold) {
+                if (refs == 0) return launch_q<T, NX, NU, true, 0, false, false, kQLongWarps>(bv, st, pl, num_sms, stream);
+                if (refs == 1) return launch_q<T, NX, NU, true, 1, false, false, kQLongWarps>(bv, st, pl, num_sms, stream);
+                return launch_q<T, NX, NU, true, 2, false, false, kQLongWarps>(bv, st, pl, num_sms, stream);
+            }
+            if (refs == 0) return launch_q<T, NX, NU, false, 0, false, false, kQLongWarps>(bv, st, pl, num_sms, stream);
+            if (refs == 1) return launch_q<T, NX, NU, false, 1, false, false, kQLongWarps>(bv, st, pl, num_sms, stream);
+            return launch_q<T, NX, NU, false, 2, false, false, kQLongWarps>(bv, st, pl, num_sms, stream);
+        }
+    }
     if (cold) {
         if (refs == 0) return launch_q<T, NX, NU, true, 0>(bv, st, pl, num_sms, stream);
         if (refs == 1) return launch_q<T, NX, NU, true, 1>(bv, st, pl, num_sms, stream);
@@ -1050,7 +1076,7 @@ bool tmem_pi_kernel_supports(const BatchView& bv, const AdmmSettings& st) {
     return false;
 }
 
-bool tmem_kernel_supports(const BatchView& bv, const AdmmSettings& st, int precision) {
+bool tmem_kernel_fused_supports(const BatchView& bv, const AdmmSettings& st, int precision) {
     if (st.en_state_soc || st.en_input_soc || st.en_state_linear || st.en_input_linear) return false;
     if (st.max_iter <= 0 || !(bv.rho > 0.0)) return false;
     if (bv.x_min != nullptr && (bv.xb_stride != 0 || bv.ub_stride != 0)) return false;   // per-instance bounds: other kernels
@@ -1063,6 +1089,17 @@ bool tmem_kernel_supports(const BatchView& bv, const AdmmSettings& st, int preci
     if (bv.nx == 12 && bv.nu == 4) return make_qplan<double, 12, 4>(bv.N, refs_mode(bv), pl);
     if (bv.nx == 4 && bv.nu == 1) return make_qplan<double, 4, 1>(bv.N, refs_mode(bv), pl);
     return false;
+}
+
+// ... or the long-horizon form (plain solves only: the fused closed loop and per-instance dynamics keep the default form)
+bool tmem_kernel_supports(const BatchView& bv, const AdmmSettings& st, int precision) {
+    if (tmem_kernel_fused_supports(bv, st, precision)) return true;
+    if (precision != 64 || bv.nx != 12 || bv.nu != 4) return false;
+    if (st.en_state_soc || st.en_input_soc || st.en_state_linear || st.en_input_linear) return false;
+    if (st.max_iter <= 0 || !(bv.rho > 0.0)) return false;
+    if (bv.x_min != nullptr && (bv.xb_stride != 0 || bv.ub_stride != 0)) return false;
+    QPlan pl;
+    return make_qplan<double, 12, 4>(bv.N, refs_mode(bv), pl, false, kQLongWarps);
 }
 
 cudaError_t launch_admm_tmem(const BatchView& bv, const AdmmSettings& st, int cold, int* counter, int num_sms,

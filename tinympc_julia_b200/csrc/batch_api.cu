@@ -1268,7 +1268,7 @@ int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_lo
             // one launch: every instance runs all its steps on the sub-warp that owns it (admm_tmem.cu, ROLL)
             tmpc::BatchView v = make_view(h);
             if (d_x_ref_long) { v.Xref = d_x_ref_long; v.xref_stride = ref_len; }
-            if (h->per_instance ? tmpc::tmem_pi_kernel_supports(v, h->st) : tmpc::tmem_kernel_supports(v, h->st)) {
+            if (h->per_instance ? tmpc::tmem_pi_kernel_supports(v, h->st) : tmpc::tmem_kernel_fused_supports(v, h->st)) {
                 if (!h->state_im.p) { h->state_im.alloc(static_cast<size_t>(v.state_im_stride) * h->B); v.state_im = h->state_im.p; }
                 if (!h->state_zero && !h->state_in_im) {
                     cudaError_t ce = tmpc::launch_state_convert(v, true, s);
