@@ -50,6 +50,19 @@ def test_cuda_matches_oracle_seeded(orc, make, B):
         cases.compare(got, want, what=f"cuda[kernel {k}] vs oracle")
 
 
+@pytest.mark.parametrize("nx,nu,N,lin", [(20, 8, 12, True), (32, 16, 6, False), (1, 1, 5, False), (3, 2, 40, True)])
+def test_thread_kernel_shape_limits(orc, nx, nu, N, lin):
+    """The general kernel at and near its limits (nx <= 32, nu <= 16; run-time dimensions, rolled loops), with and without
+    half-spaces, cold and warm, against the oracle."""
+    c = cases.random_system(nx, nu, N, 96, seed=100 + nx, with_linear=lin)
+    c["nsteps"] = 2
+    want = cases.run_checker(c, orc, nthreads=8)
+    got = cases.run_cuda(c)
+    assert got["solver"].kernel == THREAD
+    cases.compare(got, want, what=f"thread kernel {nx}x{nu}, N = {N}")
+    np.testing.assert_allclose(got["x_final"], want["x_final"], rtol=1e-5, atol=1e-6)
+
+
 def test_tmem_kernel_long_horizon_form(orc):
     """Horizons 22 .. 42 of the quadrotor shape run the four-warp form of the TMEM kernel (all 512 Tensor-Memory columns of a
     lane quarter per warp): cold and warm solves against the oracle and, bit for bit, the thread kernel; the device closed
