@@ -137,7 +137,48 @@ struct OrderArgs {
 cudaError_t launch_build_order(const OrderArgs& a, cudaStream_t stream);
 
 // ---- carried-state formats (state_layout.cu): element-major [e][ld] arrays <-> instance-major blocks
-inline long long state_im_doubles(int nx, int nu, int N) { return 3LL * nx * N + 3LL * nu * (N - 1) + nx; }
+// The instance-major block, in VALUES (doubles, or floats in the float build).  A lane of the TMEM kernel owns the state
+// rows 4 r + sub (r < rx) and the input row sub of its instance.  It stores 8 bytes at a time: one double, or a chunk of
+// vw = 2 floats (measured: 128-bit stores of double pairs are 1.2 % slower than 64-bit ones on config 3, 64-bit stores of
+// float pairs 6 % faster than 32-bit ones); the chunks of the 4 lanes are interleaved so that one store of the sub-warp
+// fills whole sectors:
+//   knot i < N      at xk i        : chunk c of lane sub at (4 c + sub) vw; a lane's sequence is g_0..g_{rx-1},
+//                                    q_0..q_{rx-1} (written together), padded to whole chunks, then v_0..v_{rx-1}
+//                                    (written only when v = vnew happened), padded likewise
+//   knot i < N - 1  at ib + uk i   : vw = 1: y_j at j, r_j at nu + j, z_j at 2 nu + j
+//                                    vw = 2: (y_j, r_j) at 2 j, z_j at 2 nu + j;  uk = 3 nu rounded up to even
+//   terminal p      at pb + row
+#if defined(__CUDACC__)
+#define TMPC_HD __host__ __device__
+#else
+#define TMPC_HD
+#endif
+struct ImLayout {
+    int rx, nu, vw, gc, xk, uk, ib, pb;
+    long long size;
+    TMPC_HD ImLayout(int nx, int nu_, int N, int vw_) {
+        rx = (nx + 3) / 4; nu = nu_; vw = vw_;
+        gc = (2 * rx + vw - 1) / vw;                      // chunks of the (g, q) sequence
+        xk = (gc + (rx + vw - 1) / vw) * 4 * vw;
+        uk = vw == 1 ? 3 * nu : ((3 * nu + 1) & ~1);
+        ib = xk * N; pb = ib + uk * (N - 1);
+        size = pb + 4 * rx;
+    }
+    // field f: 0 g, 1 v, 2 q
+    TMPC_HD int x_off(int f, int i, int row) const {
+        const int r = row / 4, sub = row % 4, s = (f == 0 ? 0 : f == 2 ? rx : gc * vw) + r;
+        return xk * i + ((s / vw) * 4 + sub) * vw + s % vw;
+    }
+    // field f: 0 y, 1 z, 2 r
+    TMPC_HD int u_off(int f, int i, int j) const {
+        if (vw == 1) return ib + uk * i + (f == 0 ? 0 : f == 2 ? nu : 2 * nu) + j;
+        return ib + uk * i + (f == 1 ? 2 * nu + j : 2 * j + (f == 2 ? 1 : 0));
+    }
+    TMPC_HD int p_off(int row) const { return pb + row; }
+};
+// values per instance block at the given precision (64: doubles, 32: floats); an allocation of state_im_values(.., 64) doubles
+// per instance holds either
+inline long long state_im_values(int nx, int nu, int N, int precision) { return ImLayout(nx, nu, N, precision == 32 ? 2 : 1).size; }
 cudaError_t launch_state_convert(const BatchView& bv, bool to_instance_major, cudaStream_t stream, int precision = 64);
 
 // ---- closed-loop plant step (rollout.cu): x0 <- A x0 + B Usol(:,0) + f, optional reference slide

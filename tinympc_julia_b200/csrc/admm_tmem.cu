@@ -265,12 +265,20 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
     T x0r[RX], p_term[RX];
 #pragma unroll
     for (int r = 0; r < RX; ++r) { x0r[r] = T(0); p_term[r] = T(0); }
-    // carried state of an instance: one contiguous block (instance-major):
-    //   knot i < N    : + 3 NX i : g(NX), v(NX), q(NX)
-    //   knot i < N - 1: IB + 3 NU i : y(NU), z(NU), r(NU)          PB: terminal p (NX)
-    const int IB = 3 * NX * N, PB = IB + 3 * NU * (N - 1);
+    // carried state of an instance: one contiguous block (instance-major, ImLayout in admm_kernels.hpp).
+    // A lane stores 8-byte chunks of VW values (one double, two floats), the chunks of the 4 lanes of an instance
+    // interleaved so that a store of the sub-warp fills whole sectors.  Lane pointers carry + VW sub:
+    //   knot i < N    : + XK i : chunk c at + CS c; chunks 0..GC-1 = g_0..g_{RX-1}, q_0..q_{RX-1}; chunks GC..GC+VC-1 = v
+    //   knot i < N - 1: IB + UK i : y, r (+ NU), z (+ 2 NU) of the lane's input row as doubles; as floats the chunk (y, r)
+    //                   and z at + 2 NU - sub                                    PB + 4 r - (VW - 1) sub: terminal p
+    constexpr int VW = 8 / S, CS = 4 * VW;
+    constexpr int GC = (2 * RX + VW - 1) / VW, VC = (RX + VW - 1) / VW, XK = (GC + VC) * CS;
+    constexpr int UK = VW == 1 ? 3 * NU : ((3 * NU + 1) & ~1);
+    const int IB = XK * N, PB = IB + UK * (N - 1);
     T* const state_im = reinterpret_cast<T*>(bv.state_im);
-    T* sblk = state_im + sub;                    // block of the lane's instance, + sub
+    T* sblk = state_im + VW * sub;               // block of the lane's instance, + VW sub
+    const int zo = 2 * NU - (VW - 1) * sub;      // z of the lane's input row, from its (y, r)
+    const int po = PB - (VW - 1) * sub;          // terminal p of the lane's row r: + 4 r
     const double* xref_g = nullptr;              // REFS == 2 only
     const double* uref_g = nullptr;
     // fused closed loop (ROLL): MPC step of the lane's instance; cont = the instance carries on from its previous
@@ -334,23 +342,23 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             const bool wr = fin && valid;                 // results to write
             const bool unconv = (status != 0);
             const size_t bb = wr ? static_cast<size_t>(b) : 0;
-            T* const ob = sblk;                      // block of the finished instance (+ sub)
+            T* const ob = sblk;                      // block of the finished instance (+ VW sub)
             if (wr && urow) {
                 double* Us = bv.Usol + bb * nuN + sub;
-                T* ou = ob + IB;                     // knot i: + 3 NU i ; y +0, z +NU, r +2 NU
+                T* ou = ob + IB;                     // knot i: + UK i
                 for (int i = 0; i < N - 1; ++i) {
                     T yy, zz;
                     ld2(s_yz + (i * 32 + lane) * 2, yy, zz);
                     *Us = static_cast<double>(zz);                // solution = znew of the last iteration (admm.cpp:371,387)
-                    ou[0] = yy;
-                    if (unconv) ou[NU] = zz;                      // z = znew happened (admm.cpp:380); else the lagging copy is there
-                    ou[2 * NU] = my_rt[i * 32];                   // r as update_linear_cost left it (admm.cpp:228-233)
-                    Us += NU; ou += 3 * NU;
+                    if constexpr (VW == 2) st2(ou, yy, my_rt[i * 32]);   // r as update_linear_cost left it (admm.cpp:228-233)
+                    else { ou[0] = yy; ou[NU] = my_rt[i * 32]; }
+                    if (unconv) ou[zo] = zz;                      // z = znew happened (admm.cpp:380); else the lagging copy is there
+                    Us += NU; ou += UK;
                 }
             }
             if (wr) {
 #pragma unroll
-                for (int r = 0; r < RX; ++r) ob[PB + r * 4] = p_term[r];
+                for (int r = 0; r < RX; ++r) ob[po + r * 4] = p_term[r];
                 if (sub == 0) { bv.status[b] = status; bv.iters[b] = iter; }
             }
             // next instance for every finished sub-warp (the atomic was issued at the top of the pass); the ticket
@@ -360,60 +368,74 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             const bool nvalid = fin && nb < bv.B;
             const size_t nbb = nvalid ? static_cast<size_t>(nb) : 0;
             const bool warm = !COLD && nvalid && !(ROLL && qp.cold_install);
-            T* const nblk = state_im + nbb * static_cast<size_t>(bv.state_im_stride) + sub;
+            T* const nblk = state_im + nbb * static_cast<size_t>(bv.state_im_stride) + VW * sub;
 
             double* Xs = bv.Xsol + bb * nxN + sub;
             const double* xr_old = ROLL ? xref_g : ((REFS == 2 && bv.Xref) ? bv.Xref + bb * bv.xref_stride + sub : nullptr);
-            T* op = ob;                              // knot i of the old / new instance: + 3 NX i ; g +0, v +NX, q +2 NX
+            T* op = ob;                              // knot i of the old / new instance: + XK i ; chunks (g, q) +0, v + CS GC
             const T* np = nblk;
             const bool wr_v = wr && unconv;
+            auto walk = [&](auto anyv) {
+            constexpr bool ANYV = decltype(anyv)::value;
             for (int i = 0; i < N; ++i) {
                 uint32_t w[W];
                 tm_load<W>(tbase + i * W, w);
-                T gn[RX], vn[RX];
+                T gn[VW * VC], vn[VW * VC];              // the new instance's g (head of its (g, q) sequence) and v
 #pragma unroll
-                for (int r = 0; r < RX; ++r) { gn[r] = T(0); vn[r] = T(0); }
+                for (int r = 0; r < VW * VC; ++r) { gn[r] = T(0); vn[r] = T(0); }
                 if (warm) {
 #pragma unroll
-                    for (int r = 0; r < RX; ++r) { gn[r] = np[r * 4]; vn[r] = np[NX + r * 4]; }
+                    for (int c = 0; c < VC; ++c) { ldc<VW>(np + CS * c, gn + VW * c); ldc<VW>(np + CS * (GC + c), vn + VW * c); }
                 }
                 tm_wait_ld<W>(w);
-                const bool wr_q = wr && (i < N - 1);
+                T sq[VW * GC], sv[VW * VC];              // the finished instance's (g, q) sequence and v
+                sq[VW * GC - 1] = T(0); sv[VW * VC - 1] = T(0);
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
                     // branch-free: every lane forms the values, the stores are predicated
                     const T gg = tm_get(w, r, T());
                     const T vv = tm_get(w, RX + r, T());
                     stg_if(Xs + r * 4, static_cast<double>(vv), wr);   // solution = vnew of the last iteration (admm.cpp:370,386)
-                    stg_if(op + r * 4, gg, wr);
-                    stg_if(op + NX + r * 4, vv, wr_v);            // v = vnew happened (admm.cpp:379); else the lagging copy is there
-                    T q;                                     // q as update_linear_cost left it (admm.cpp:218-219)
+                    T q;                                     // q as update_linear_cost left it (admm.cpp:218-219), all N columns
                     if (REFS == 0) q = R::mul(nrho, R::sub(vv, gg));
                     else {
-                        const T cq = (REFS == 1) ? s_cq[(i < N - 1 ? i : 0) * NX + r * 4 + sub]
-                                                      : -R::mul(static_cast<T>((xr_old && wr_q) ? __ldg(xr_old + i * NX + r * 4) : 0.0), fr_Qd[r]);
+                        const T cq = (REFS == 1) ? s_cq[i * NX + r * 4 + sub]
+                                                      : -R::mul(static_cast<T>((xr_old && wr) ? __ldg(xr_old + i * NX + r * 4) : 0.0), fr_Qd[r]);
                         q = R::sub(cq, R::mul(rho, R::sub(vv, gg)));
                     }
-                    stg_if(op + 2 * NX + r * 4, q, wr_q);
+                    sq[r] = gg; sq[RX + r] = q; sv[r] = vv;
                     tm_put_if(w, r, gn[r], fin);
                     tm_put_if(w, RX + r, vn[r], fin);
                 }
+#pragma unroll
+                for (int c = 0; c < GC; ++c) stgc_if<VW>(op + CS * c, sq + VW * c, wr);
+                if (ANYV) {                                  // v = vnew happened (admm.cpp:379); else the lagging copy is there
+#pragma unroll
+                    for (int c = 0; c < VC; ++c) stgc_if<VW>(op + CS * (GC + c), sv + VW * c, wr_v);
+                }
                 tm_store<W>(tbase + i * W, w);
-                Xs += NX; op += 3 * NX; np += 3 * NX;
+                Xs += NX; op += XK; np += XK;
             }
+            };
+            // the v stores exist only in the variant that has an unconverged instance to write (none in a batch that converges:
+            // a predicated-off store still costs its issue slot, 3 of the 12 per knot point)
+            if (__any_sync(kAll, wr_v)) walk(std::true_type{}); else walk(std::false_type{});
             if (fin) {
                 const T* nu_p = nblk + IB;
                 for (int i = 0; i < N - 1; ++i) {
                     T yy = T(0), zz = T(0), rr = T(0);
-                    if (warm && urow) { yy = nu_p[0]; zz = nu_p[NU]; rr = nu_p[2 * NU]; }
+                    if (warm && urow) {
+                        if constexpr (VW == 2) ld2(nu_p, yy, rr); else { yy = nu_p[0]; rr = nu_p[NU]; }
+                        zz = nu_p[zo];
+                    }
                     st2(s_yz + (i * 32 + lane) * 2, yy, zz);
                     my_rt[i * 32] = rr;
-                    nu_p += 3 * NU;
+                    nu_p += UK;
                 }
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
                     x0r[r] = nvalid ? static_cast<T>(bv.x0[nbb * NX + r * 4 + sub]) : T(0);
-                    p_term[r] = warm ? nblk[PB + r * 4] : T(0);
+                    p_term[r] = warm ? nblk[po + r * 4] : T(0);
                 }
                 b = nvalid ? nb : 0;
                 sblk = nblk;
@@ -474,11 +496,15 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             // previous step, i.e. built from the slacks and duals in Tensor Memory and the PREVIOUS reference window
             const bool usecar = first && !(ROLL && cont);
             const double* xref_b = (ROLL && REFS == 2 && cont && first && qp.slide && xref_g) ? xref_g - NX : xref_g;
-            const T* qp_g = sblk + 2 * NX + (N - 2) * 3 * NX;          // q of knot N-2; row r: + 4 r
-            if (ldq) {
+            const T* qp_g = sblk + (N - 2) * XK;                       // knot N-2; q = the second half of the (g, q) sequence
+            auto load_q = [&]() {
+                T sq[VW * GC];
 #pragma unroll
-                for (int r = 0; r < RX; ++r) qcar[r] = qp_g[r * 4];
-            }
+                for (int c = RX / VW; c < GC; ++c) ldc<VW>(qp_g + CS * c, sq + VW * c);
+#pragma unroll
+                for (int r = 0; r < RX; ++r) qcar[r] = sq[RX + r];
+            };
+            if (ldq) load_q();
             T t_def = T(0);
             uint32_t o_rt = (N - 2) * 32 * S;                // byte offset of knot i in the r/t array
             uint32_t o_cq = (N - 2) * NX * S;
@@ -541,11 +567,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 }
                 if (i > 0) {
                     tm_load<W>(tbase + (i - 1) * W, w);
-                    if (ldq) {
-                        qp_g -= 3 * NX;
-#pragma unroll
-                        for (int r = 0; r < RX; ++r) qcar[r] = qp_g[r * 4];
-                    }
+                    if (ldq) { qp_g -= XK; load_q(); }
                 }
 
                 // own row of B' p_{i+1} and the lane's rows of AmBKt p_{i+1}: RX + 1 independent chains, interleaved
@@ -578,24 +600,26 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
         // the last sweep parked in its block (admm.cpp:375 returns before :379-380).  The backward sweep above
         // was the last reader of vnew; put v_old / z_old in place for the dual residual of this solve's first iteration.
         if (ROLL && __any_sync(kAll, fix)) {
-            const T* vl = sblk + NX;                 // v of knot i: + 3 NX i ; row r: + 4 r
+            const T* vl = sblk + CS * GC;            // v chunks of knot i: + XK i
             for (int i = 0; i < N; ++i) {
                 uint32_t w[W];
                 tm_load<W>(tbase + i * W, w);
-                T vo[RX];
+                T vo[VW * VC];
 #pragma unroll
-                for (int r = 0; r < RX; ++r) vo[r] = fix ? vl[r * 4] : T(0);
+                for (int r = 0; r < VW * VC; ++r) vo[r] = T(0);
+#pragma unroll
+                for (int c = 0; c < VC; ++c) { if (fix) ldc<VW>(vl + CS * c, vo + VW * c); }
                 tm_wait_ld<W>(w);
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
                     tm_put_if(w, RX + r, vo[r], fix);
                 }
                 tm_store<W>(tbase + i * W, w);
-                vl += 3 * NX;
+                vl += XK;
             }
             if (fix && urow) {
-                const T* zl = sblk + IB + NU;        // z of knot i: + 3 NU i
-                for (int i = 0; i < N - 1; ++i) { s_yz[(i * 32 + lane) * 2 + 1] = *zl; zl += 3 * NU; }
+                const T* zl = sblk + IB + zo;             // z of knot i: + UK i
+                for (int i = 0; i < N - 1; ++i) { s_yz[(i * 32 + lane) * 2 + 1] = *zl; zl += UK; }
             }
             fix = false;
             tm_wait_st();
@@ -642,8 +666,8 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
             // (admm.cpp:375 returns before :379-380): while this sweep can still end in convergence the lane parks
             // them in the instance's carried-state block in HBM ([pointer + immediate] stores, whole 32-byte sectors)
             const bool lag = valid && ((iter + 1) % st.check_termination == 0);
-            T* vlag = sblk + NX;                                         // v of knot i: + 3 NX i ; row r: + 4 r
-            T* zlag = sblk + IB + NU;                                    // z of knot i: + 3 NU i
+            T* vlag = sblk + CS * GC;                                    // v chunks of knot i: + XK i
+            T* zlag = sblk + IB + zo;                                    // z of knot i: + UK i
             T r_def = T(0);
             T vg[RX];
             uint32_t o_xb = 0;                                                // byte offset of knot i in the state-bound table
@@ -666,6 +690,8 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                 }
                 tm_wait_ld<W>(w);
                 uint32_t wn[W];
+                T vol[VW * VC];                              // previous slacks of the lane's rows, parked chunk by chunk
+                vol[VW * VC - 1] = T(0);
 #pragma unroll
                 for (int r = 0; r < RX; ++r) {
                     const T gold = tm_get(w, r, T());
@@ -677,7 +703,8 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                         const bool p1 = R::abs(R::sub(x[r], vnew)) < pri_thresh;
                         const bool p2 = R::abs(R::sub(vold, vnew)) <= dua_thresh;
                         ok = ok & p1 & p2;
-                        if (lag & ok) vlag[r * 4] = vold;
+                        vol[r] = vold;
+                        if ((r + 1) % VW == 0 || r == RX - 1) { if (lag & ok) stc<VW>(vlag + CS * (r / VW), vol + (r / VW) * VW); }
                     }
                     tm_put(wn, r, gnew);
                     tm_put(wn, RX + r, vnew);
@@ -802,7 +829,7 @@ admm_tmem_kernel(const __grid_constant__ BatchView bv, const __grid_constant__ A
                     for (int k = 0; k < NU; ++k) s2 = R::fma(mb[r][k], ub[k], s2);
                     x[r] = R::add(R::add(s1[r], s2), fr_f[r]);
                 }
-                vlag += 3 * NX; zlag += 3 * NU;
+                vlag += XK; zlag += UK;
                 o_rt += 32 * S; o_yz += 64 * S; o_ub += NU * 2 * S; o_cr += NU * S; o_xb += NX * 2 * S;
             };
 

@@ -223,7 +223,7 @@ tmpc::BatchView make_view(tmpc_batch* h) {
     v.q = h->q.p; v.r = h->r.p; v.pN = h->pN.p; v.d = h->d.p;
     v.gc = h->gc.p; v.yc = h->yc.p; v.gl = h->gl.p; v.yl = h->yl.p;
     v.Xsol = h->Xsol.p; v.Usol = h->Usol.p; v.status = h->status.p; v.iters = h->iters.p;
-    v.state_im = h->state_im.p; v.state_im_stride = tmpc::state_im_doubles(h->nx, h->nu, h->N);
+    v.state_im = h->state_im.p; v.state_im_stride = tmpc::state_im_values(h->nx, h->nu, h->N, h->precision);
     return v;
 }
 
@@ -351,7 +351,7 @@ cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v_in, cuda
     tmpc::BatchView v = v_in;
     const bool wants_im = sub && tm;
     if (wants_im && !h->state_im.p) {
-        h->state_im.alloc(static_cast<size_t>(v.state_im_stride) * h->B);
+        h->state_im.alloc(static_cast<size_t>(tmpc::state_im_values(h->nx, h->nu, h->N, 64)) * h->B);
         v.state_im = h->state_im.p;
     }
     if (!h->state_zero && wants_im != h->state_in_im) {      // the previous solve left the other format: convert on `s`
@@ -1063,7 +1063,7 @@ static int solve_host_impl(tmpc_batch* h, const double* x0, int cold, double* X,
         };
         if (nch > 1) {
             const bool was_cold = h->state_zero;
-            if (!h->state_im.p) { h->state_im.alloc(static_cast<size_t>(v.state_im_stride) * h->B); v.state_im = h->state_im.p; }
+            if (!h->state_im.p) { h->state_im.alloc(static_cast<size_t>(tmpc::state_im_values(h->nx, h->nu, h->N, 64)) * h->B); v.state_im = h->state_im.p; }
             if (!was_cold && !h->state_in_im) {
                 cudaError_t ce = tmpc::launch_state_convert(v, true, h->stream, h->precision);
                 if (ce != cudaSuccess) throw CudaFail{ce, "state conversion"};
@@ -1269,7 +1269,7 @@ int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_lo
             tmpc::BatchView v = make_view(h);
             if (d_x_ref_long) { v.Xref = d_x_ref_long; v.xref_stride = ref_len; }
             if (h->per_instance ? tmpc::tmem_pi_kernel_supports(v, h->st) : tmpc::tmem_kernel_fused_supports(v, h->st)) {
-                if (!h->state_im.p) { h->state_im.alloc(static_cast<size_t>(v.state_im_stride) * h->B); v.state_im = h->state_im.p; }
+                if (!h->state_im.p) { h->state_im.alloc(static_cast<size_t>(tmpc::state_im_values(h->nx, h->nu, h->N, 64)) * h->B); v.state_im = h->state_im.p; }
                 if (!h->state_zero && !h->state_in_im) {
                     cudaError_t ce = tmpc::launch_state_convert(v, true, s);
                     if (ce != cudaSuccess) throw CudaFail{ce, "state conversion"};

@@ -179,6 +179,11 @@ __device__ __forceinline__ void stg_if(double* p, double v, bool pred) {
                  :: "l"(p), "d"(v), "r"(static_cast<int>(pred)) : "memory");
 }
 
+__device__ __forceinline__ void stg2_if(double* p, double a, double b, bool pred) {
+    asm volatile("{ .reg .pred p; setp.ne.s32 p, %3, 0; @p st.global.v2.f64 [%0], {%1, %2}; }"
+                 :: "l"(p), "d"(a), "d"(b), "r"(static_cast<int>(pred)) : "memory");
+}
+
 template <int W> __device__ __forceinline__ void tm_wait_ld(uint32_t* w);
 template <> __device__ __forceinline__ void tm_wait_ld<12>(uint32_t* w) { tm_wait_ld12(w); }
 template <> __device__ __forceinline__ void tm_wait_ld<4>(uint32_t* w) { tm_wait_ld4(w); }
@@ -233,9 +238,24 @@ __device__ __forceinline__ T lds1t(uint32_t a) {
         return x;
     }
 }
+__device__ __forceinline__ void stg2_if(float* p, float a, float b, bool pred) {
+    asm volatile("{ .reg .pred p; setp.ne.s32 p, %3, 0; @p st.global.v2.f32 [%0], {%1, %2}; }"
+                 :: "l"(p), "f"(a), "f"(b), "r"(static_cast<int>(pred)) : "memory");
+}
 __device__ __forceinline__ void stg_if(float* p, float v, bool pred) {
     asm volatile("{ .reg .pred p; setp.ne.s32 p, %2, 0; @p st.global.f32 [%0], %1; }"
                  :: "l"(p), "f"(v), "r"(static_cast<int>(pred)) : "memory");
+}
+
+// a chunk of VW values (one double, or two floats: 8 bytes either way) of the instance-major carried state
+template <int VW, class T> __device__ __forceinline__ void ldc(const T* p, T* v) {
+    if constexpr (VW == 1) v[0] = *p; else ld2(p, v[0], v[1]);
+}
+template <int VW, class T> __device__ __forceinline__ void stc(T* p, const T* v) {
+    if constexpr (VW == 1) *p = v[0]; else st2(p, v[0], v[1]);
+}
+template <int VW, class T> __device__ __forceinline__ void stgc_if(T* p, const T* v, bool pred) {
+    if constexpr (VW == 1) stg_if(p, v[0], pred); else stg2_if(p, v[0], v[1], pred);
 }
 
 }  // namespace tmu
