@@ -130,8 +130,10 @@ enum {
     TMPC_KERNEL_SUBWARP = 2,  /* one instance per 4-lane sub-warp, state resident in shared memory (box constraints) */
     TMPC_KERNEL_TMEM = 3,     /* 4-lane sub-warp, state rows in Tensor Memory + input rows in shared memory, 8 warps/SM,
                                  per-instance refill (box constraints with shared bounds; nx=12 nu=4 with N <= 42, nx=4 nu=1) */
-    TMPC_KERNEL_CONE = 4      /* box + second-order cones + half-spaces on chip: 3 instances per warp, recursions with a lane
+    TMPC_KERNEL_CONE = 4,     /* box + second-order cones + half-spaces on chip: 3 instances per warp, recursions with a lane
                                  per matrix row, projections with a lane per knot point (nx=6 nu=3, N <= 50) */
+    TMPC_KERNEL_WARP = 5      /* one warp per instance, built for latency: what AUTO picks for B <= 2048 (the single solve
+                                 behind the reference's own symbols first of all); box constraints, nx=12 nu=4 / nx=4 nu=1 */
 };
 
 /* Host-only: the infinite-horizon LQR cache the solve loop reads (replaces tiny_precompute_and_set_cache,
@@ -173,7 +175,7 @@ int tmpc_batch_update_settings(tmpc_batch* h, double abs_pri_tol, double abs_dua
  * kernel, per-instance dynamics and the device closed loop are 64-bit. */
 int tmpc_batch_set_precision(tmpc_batch* h, int bits);   /* 32 or 64 (default) */
 int tmpc_batch_get_precision(tmpc_batch* h);
-int tmpc_batch_set_kernel(tmpc_batch* h, int kernel);   /* TMPC_KERNEL_*; AUTO picks TMEM, then SUBWARP, then CONE, where they apply, else THREAD */
+int tmpc_batch_set_kernel(tmpc_batch* h, int kernel);   /* TMPC_KERNEL_*; AUTO picks WARP for small batches, else TMEM, then SUBWARP, then CONE, where they apply, else THREAD */
 int tmpc_batch_get_kernel(tmpc_batch* h);               /* kernel the next solve will run (resolved AUTO) */
 
 /* Queue order of the on-chip (persistent) kernels.  Iteration counts are data-dependent (admm.cpp:312-381), so an

@@ -18,7 +18,7 @@ export TinyMPCBatchSolver, setup_batch, set_x0, set_x_ref, set_u_ref, set_bound_
 
 const lib_path = joinpath(dirname(@__DIR__), "lib", "libtinympc_jl." * Libdl.dlext)   # as reference src/TinyMPC.jl:12-13
 
-const KERNEL_AUTO, KERNEL_THREAD, KERNEL_SUBWARP, KERNEL_TMEM, KERNEL_CONE = Int32(0), Int32(1), Int32(2), Int32(3), Int32(4)
+const KERNEL_AUTO, KERNEL_THREAD, KERNEL_SUBWARP, KERNEL_TMEM, KERNEL_CONE, KERNEL_WARP = Int32(0), Int32(1), Int32(2), Int32(3), Int32(4), Int32(5)
 
 mutable struct TinyMPCBatchSolver
     handle::Ptr{Cvoid}

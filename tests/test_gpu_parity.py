@@ -13,14 +13,14 @@ from tinympc_julia_b200 import problems as problems_mod
 
 pytestmark = pytest.mark.gpu
 
-THREAD, SUBWARP, TMEM, CONE = t.KERNEL_THREAD, t.KERNEL_SUBWARP, t.KERNEL_TMEM, t.KERNEL_CONE
+THREAD, SUBWARP, TMEM, CONE, WARP = t.KERNEL_THREAD, t.KERNEL_SUBWARP, t.KERNEL_TMEM, t.KERNEL_CONE, t.KERNEL_WARP
 
 
 def kernels_for(c):
     """Kernels able to run a case: the thread kernel always; the on-chip kernels where they apply."""
     ks = [THREAD]
     sol = cases.make_cuda_solver(c, kernel=t.KERNEL_AUTO)
-    for k in (SUBWARP, TMEM, CONE):
+    for k in (SUBWARP, TMEM, CONE, WARP):
         sol.set_kernel(k)
         if sol.kernel == k:
             ks.append(k)
@@ -72,7 +72,7 @@ def test_tmem_kernel_long_horizon_form(orc):
         c = cases.quadrotor_batch(700, hard=True, seed=40 + N, N=N, max_iter=30)
         c["nsteps"] = 2                                        # second step = warm start from the carried state
         want = cases.run_checker(c, orc, nthreads=8)
-        a = cases.run_cuda(c, kernel=t.KERNEL_AUTO)
+        a = cases.run_cuda(c, kernel=TMEM)
         assert a["solver"].kernel == TMEM, N
         b = cases.run_cuda(c, kernel=THREAD)
         cases.compare(a, want, what=f"long-horizon TMEM form, N = {N}")
@@ -85,7 +85,7 @@ def test_tmem_kernel_long_horizon_form(orc):
     c = cases.quadrotor_batch(200, N=30)
     c.update(x0=x0, Xref=Xlong, ref_mode=cases.oracle.REF_SLIDING, nsteps=5)
     want = cases.run_checker(c, orc, nthreads=8)
-    sol = cases.make_cuda_solver(c)
+    sol = cases.make_cuda_solver(c, kernel=TMEM)
     assert sol.kernel == TMEM
     t.set_x0(sol, c["x0"])
     st, it, xf = _device_rollout(sol, 5, xlong=c["Xref"])
@@ -142,6 +142,21 @@ def test_cone_kernel_every_compiled_form(orc):
         cases.compare(a, want, what=f"cone kernel, {what}")
         for k in ("ret", "iters", "X", "U"):
             assert np.array_equal(a[k], b[k]), f"{what}: {k} differs between the cone and the thread kernel"
+
+
+def test_warp_kernel_is_what_small_batches_run_on(orc):
+    """TMPC_KERNEL_AUTO: the latency kernel (one warp per instance) up to 2048 instances, the throughput kernels beyond; a
+    long horizon (shared memory sized by N), per-instance bounds and references, and a warm-started sequence on it."""
+    for B, want_k in ((1, WARP), (2048, WARP), (2049, TMEM)):
+        sol = cases.make_cuda_solver(cases.quadrotor_batch(B), kernel=t.KERNEL_AUTO)
+        assert sol.kernel == want_k, (B, sol.kernel)
+    sol = cases.make_cuda_solver(cases.rocket(4, N=10), kernel=t.KERNEL_AUTO)      # cones: not this kernel
+    assert sol.kernel != WARP
+    for N in (2, 3, 45, 120):
+        c = cases.quadrotor_batch(40, hard=True, seed=N, N=N, max_iter=30)
+        cases.compare(cases.run_cuda(c, kernel=WARP), cases.run_checker(c, orc), what=f"warp kernel N={N}")
+    c = cases.quadrotor_per_instance(37)
+    cases.compare(cases.run_cuda(c, kernel=WARP), cases.run_checker(c, orc), what="warp kernel, per-instance bounds and references")
 
 
 def test_cuda_ragged_batch_sizes(orc):

@@ -12,4 +12,4 @@ from .solver import (  # noqa: F401
     codegen_with_sensitivity, compute_sensitivity_autograd, get_adapted_cache, lqr_sensitivity, set_sensitivity,
 )
 
-KERNEL_AUTO, KERNEL_THREAD, KERNEL_SUBWARP, KERNEL_TMEM, KERNEL_CONE = 0, 1, 2, 3, 4
+KERNEL_AUTO, KERNEL_THREAD, KERNEL_SUBWARP, KERNEL_TMEM, KERNEL_CONE, KERNEL_WARP = 0, 1, 2, 3, 4, 5

@@ -72,6 +72,15 @@ bool subwarp_kernel_supports(int nx, int nu, int N, const AdmmSettings& st, int 
 cudaError_t launch_admm_subwarp(const BatchView& bv, const AdmmSettings& st, const HostMats& h, int cold,
                                 int* counter, int num_sms, cudaStream_t stream, int precision = 64);
 
+// ---- one warp per instance, built for latency (admm_warp.cu): the recursions with a lane per matrix row, everything else
+// over all knot points at once, state in shared memory for the whole solve.  Box-constrained problems of a compiled-in shape,
+// double build, shared dynamics; element-major carried state (interchangeable with the thread kernel).  TMPC_KERNEL_AUTO
+// picks it for batches of at most kWarpKernelAutoMaxB instances (the B = 1 singleton behind the reference's symbols first
+// of all), where the throughput kernels would leave the GPU empty.
+constexpr int kWarpKernelAutoMaxB = 2048;
+bool warp_kernel_supports(const BatchView& bv, const AdmmSettings& st);
+cudaError_t launch_admm_warp(const BatchView& bv, const AdmmSettings& st, int cold, cudaStream_t stream);
+
 // ---- one instance per 4-lane sub-warp, state rows in Tensor Memory + input rows in shared memory, per-instance
 // refill from a global queue (admm_tmem.cu).  Box-constrained (or unconstrained) problems with shared bounds.
 // `order` (all TMEM launchers): device permutation of 0..B-1 the queue tickets index (queue_order.cu), or nullptr for

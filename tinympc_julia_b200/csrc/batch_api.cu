@@ -278,10 +278,14 @@ int resolve_kernel(tmpc_batch* h) {
     const bool sub_ok = tmpc::subwarp_kernel_supports(h->nx, h->nu, h->N, h->st);
     const bool tm_ok = tmpc::tmem_kernel_supports(make_view(h), h->st);
     const bool cone_ok = tmpc::cone_kernel_supports(make_view(h), h->st);
+    const bool warp_ok = tmpc::warp_kernel_supports(make_view(h), h->st);
+    if (h->kernel_pref == TMPC_KERNEL_WARP) return warp_ok ? TMPC_KERNEL_WARP : -1;
     if (h->kernel_pref == TMPC_KERNEL_CONE) return cone_ok ? TMPC_KERNEL_CONE : -1;
     if (h->kernel_pref == TMPC_KERNEL_TMEM) return tm_ok ? TMPC_KERNEL_TMEM : -1;
     if (h->kernel_pref == TMPC_KERNEL_SUBWARP) return sub_ok ? TMPC_KERNEL_SUBWARP : -1;
     if (h->kernel_pref == TMPC_KERNEL_THREAD) return TMPC_KERNEL_THREAD;
+    if (h->kernel_pref != TMPC_KERNEL_AUTO) return -1;
+    if (warp_ok && h->B <= tmpc::kWarpKernelAutoMaxB) return TMPC_KERNEL_WARP;       // small batch: latency first
     return tm_ok ? TMPC_KERNEL_TMEM : (sub_ok ? TMPC_KERNEL_SUBWARP : (cone_ok ? TMPC_KERNEL_CONE : TMPC_KERNEL_THREAD));
 }
 
@@ -347,7 +351,7 @@ T* mapped_alias(T* p) {
 // caller stream may still be running, and memsets on another stream would race with it.
 cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v_in, cudaStream_t s, bool ordered = true) {
     const bool tm = (k == TMPC_KERNEL_TMEM);
-    const bool sub = (k == TMPC_KERNEL_SUBWARP || k == TMPC_KERNEL_CONE || tm) && h->st.max_iter > 0 && h->rho > 0.0;
+    const bool sub = (k == TMPC_KERNEL_SUBWARP || k == TMPC_KERNEL_CONE || k == TMPC_KERNEL_WARP || tm) && h->st.max_iter > 0 && h->rho > 0.0;
     tmpc::BatchView v = v_in;
     const bool wants_im = sub && tm;
     if (wants_im && !h->state_im.p) {
@@ -369,6 +373,7 @@ cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v_in, cuda
     if (sub && k == TMPC_KERNEL_TMEM && h->per_instance)
         e = tmpc::launch_admm_tmem_pi(v, h->st, h->state_zero ? 1 : 0, h->pi_blocks.p, h->counter.p, h->num_sms, s, order);
     else if (sub && k == TMPC_KERNEL_TMEM) e = tmpc::launch_admm_tmem(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s, order, h->precision);
+    else if (sub && k == TMPC_KERNEL_WARP) e = tmpc::launch_admm_warp(v, h->st, h->state_zero ? 1 : 0, s);
     else if (sub && k == TMPC_KERNEL_CONE) e = tmpc::launch_admm_cone(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
     else if (sub) e = tmpc::launch_admm_subwarp(v, h->st, h->hm, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s, h->precision);
     else if (adaptive_path(h)) {
@@ -616,7 +621,7 @@ int tmpc_batch_set_precision(tmpc_batch* h, int bits) {
 int tmpc_batch_get_precision(tmpc_batch* h) { return h ? h->precision : -1; }
 
 int tmpc_batch_set_kernel(tmpc_batch* h, int kernel) {
-    if (!h || kernel < TMPC_KERNEL_AUTO || kernel > TMPC_KERNEL_CONE) return TMPC_ERR_DIM;
+    if (!h || kernel < TMPC_KERNEL_AUTO || kernel > TMPC_KERNEL_WARP) return TMPC_ERR_DIM;
     h->kernel_pref = kernel;
     return TMPC_OK;
 }
@@ -1261,8 +1266,11 @@ int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_lo
         if (const char* why = adaptive_refusal(h)) { set_error(why); return TMPC_ERR_STATE; }
         order_before_enqueue(h, s);
         ensure_aux_state(h, s);
-        const int k = resolve_kernel(h);
+        int k = resolve_kernel(h);
         if (k < 0) { set_error("requested kernel does not support this problem"); return TMPC_ERR_STATE; }
+        // a small batch left to AUTO: the closed loop in ONE launch (TMEM kernel) rather than three launches per step
+        if (k == TMPC_KERNEL_WARP && h->kernel_pref == TMPC_KERNEL_AUTO && h->rollout_fused &&
+            tmpc::tmem_kernel_fused_supports(make_view(h), h->st)) k = TMPC_KERNEL_TMEM;
         const long long ref_len = static_cast<long long>(h->nx) * (h->N + nsteps - 1);
         if (k == TMPC_KERNEL_TMEM && h->st.max_iter > 0 && h->rho > 0.0 && h->rollout_fused) {
             // one launch: every instance runs all its steps on the sub-warp that owns it (admm_tmem.cu, ROLL)
