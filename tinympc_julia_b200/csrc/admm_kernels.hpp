@@ -79,7 +79,7 @@ cudaError_t launch_admm_subwarp(const BatchView& bv, const AdmmSettings& st, con
 // of all), where the throughput kernels would leave the GPU empty.
 constexpr int kWarpKernelAutoMaxB = 2048;
 bool warp_kernel_supports(const BatchView& bv, const AdmmSettings& st);
-cudaError_t launch_admm_warp(const BatchView& bv, const AdmmSettings& st, int cold, cudaStream_t stream);
+cudaError_t launch_admm_warp(const BatchView& bv, const AdmmSettings& st, int cold, int num_sms, cudaStream_t stream);
 
 // ---- one instance per 4-lane sub-warp, state rows in Tensor Memory + input rows in shared memory, per-instance
 // refill from a global queue (admm_tmem.cu).  Box-constrained (or unconstrained) problems with shared bounds.

@@ -113,6 +113,7 @@ struct tmpc_batch {
     bool results_mapped = false;              // Xsol / Usol / status / iters live in mapped pinned host memory (tiny batch)
     double* x0_stage = nullptr;               // pinned staging of x0 for tiny batches: set_x0 returns without a stream sync
     cudaEvent_t x0_staged = nullptr;
+    bool x0_lazy = false;                     // the current x0 is in the staging buffer only; kernels read it there (mapped)
     long long launches = 0;
     bool state_zero = true;   // carried state is LOGICALLY zero (fresh or reset) ...
     bool mem_zero = true;     // ... and the device buffers physically hold those zeros.  tmpc_batch_reset only flips
@@ -199,11 +200,21 @@ void sync_all(tmpc_batch* h) {
     h->own_pending = false;
 }
 
+// Tiny batch: bring an x0 that lives in the staging buffer only into the device buffer, before something other than a
+// solve kernel (which reads the mapped staging buffer directly) needs it there.
+void flush_x0(tmpc_batch* h, cudaStream_t s) {
+    if (!h->x0_lazy) return;
+    CUDA_TRY(cudaMemcpyAsync(h->x0.p, h->x0_stage, sizeof(double) * h->nx * h->B, cudaMemcpyHostToDevice, s));
+    CUDA_TRY(cudaEventRecord(h->x0_staged, s));
+    h->x0_lazy = false;
+    mark_enqueued(h, s);
+}
+
 tmpc::BatchView make_view(tmpc_batch* h) {
     tmpc::BatchView v{};
     v.B = h->B; v.ld = h->ld; v.nx = h->nx; v.nu = h->nu; v.N = h->N; v.rho = h->rho;
     const long long sxN = static_cast<long long>(h->nx) * h->N, suN = static_cast<long long>(h->nu) * (h->N - 1);
-    v.x0 = h->ext_x0 ? h->ext_x0 : h->x0.p;
+    v.x0 = h->ext_x0 ? h->ext_x0 : (h->x0_lazy ? h->x0_stage : h->x0.p);
     if (h->ext_xref) { v.Xref = h->ext_xref; v.xref_stride = h->ext_xref_batch > 1 ? sxN : 0; }
     else if (h->xref_batch) { v.Xref = h->Xref.p; v.xref_stride = h->xref_batch > 1 ? sxN : 0; }
     if (h->ext_uref) { v.Uref = h->ext_uref; v.uref_stride = h->ext_uref_batch > 1 ? suN : 0; }
@@ -373,7 +384,7 @@ cudaError_t launch_solve(tmpc_batch* h, int k, const tmpc::BatchView& v_in, cuda
     if (sub && k == TMPC_KERNEL_TMEM && h->per_instance)
         e = tmpc::launch_admm_tmem_pi(v, h->st, h->state_zero ? 1 : 0, h->pi_blocks.p, h->counter.p, h->num_sms, s, order);
     else if (sub && k == TMPC_KERNEL_TMEM) e = tmpc::launch_admm_tmem(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s, order, h->precision);
-    else if (sub && k == TMPC_KERNEL_WARP) e = tmpc::launch_admm_warp(v, h->st, h->state_zero ? 1 : 0, s);
+    else if (sub && k == TMPC_KERNEL_WARP) e = tmpc::launch_admm_warp(v, h->st, h->state_zero ? 1 : 0, h->num_sms, s);
     else if (sub && k == TMPC_KERNEL_CONE) e = tmpc::launch_admm_cone(v, h->st, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s);
     else if (sub) e = tmpc::launch_admm_subwarp(v, h->st, h->hm, h->state_zero ? 1 : 0, h->counter.p, h->num_sms, s, h->precision);
     else if (adaptive_path(h)) {
@@ -530,7 +541,7 @@ int tmpc_batch_create(tmpc_batch** out, const double* A, const double* Bdyn, con
         if (h->results_mapped) {
             h->Xsol.alloc_mapped(static_cast<size_t>(nx) * N * B); h->Usol.alloc_mapped(static_cast<size_t>(nu) * (N - 1) * B);
             h->status.alloc_mapped(B); h->iters.alloc_mapped(B);
-            CUDA_TRY(cudaHostAlloc(reinterpret_cast<void**>(&h->x0_stage), sizeof(double) * nx * B, cudaHostAllocDefault));
+            CUDA_TRY(cudaHostAlloc(reinterpret_cast<void**>(&h->x0_stage), sizeof(double) * nx * B, cudaHostAllocMapped));
             CUDA_TRY(cudaEventCreateWithFlags(&h->x0_staged, cudaEventDisableTiming));
         } else {
             h->Xsol.alloc(static_cast<size_t>(nx) * N * B); h->Usol.alloc(static_cast<size_t>(nu) * (N - 1) * B);
@@ -666,7 +677,16 @@ int tmpc_batch_set_x0(tmpc_batch* h, const double* x0, int rows, int batch) {
         if (rows != h->nx || batch != h->B) { set_error("set_x0: expected nx x B"); return TMPC_ERR_DIM; }
         h->use_device();
         h->ext_x0 = nullptr;
+        if (h->x0_stage && !h->own_pending && !h->foreign_pending) {
+            // tiny batch with nothing in flight (set_x0 -> solve -> get_controls): x0 goes into the mapped staging buffer and the
+            // solve kernel reads it there - no CUDA call here, no copy in front of the kernel
+            CUDA_TRY(cudaEventSynchronize(h->x0_staged));      // an upload from the staging buffer, if any, has left it
+            std::memcpy(h->x0_stage, x0, sizeof(double) * h->nx * h->B);
+            h->x0_lazy = true;
+            return TMPC_OK;
+        }
         if (h->x0_stage) {      // tiny batch: copy into the pinned staging buffer and return; the upload is stream-ordered
+            h->x0_lazy = false;
             CUDA_TRY(cudaEventSynchronize(h->x0_staged));      // the previous upload has left the staging buffer
             std::memcpy(h->x0_stage, x0, sizeof(double) * h->nx * h->B);
             CUDA_TRY(cudaMemcpyAsync(h->x0.p, h->x0_stage, sizeof(double) * h->nx * h->B, cudaMemcpyHostToDevice, h->stream));
@@ -674,6 +694,7 @@ int tmpc_batch_set_x0(tmpc_batch* h, const double* x0, int rows, int batch) {
             h->own_pending = true;
             return TMPC_OK;
         }
+        h->x0_lazy = false;
         h->x0.upload(x0, static_cast<size_t>(h->nx) * h->B, h->stream);
         sync_all(h);
         return TMPC_OK;
@@ -1010,6 +1031,7 @@ static int solve_host_impl(tmpc_batch* h, const double* x0, int cold, double* X,
         if (const char* why = adaptive_refusal(h)) { set_error(why); return 100 + TMPC_ERR_STATE; }
         if (x0) {   // copied below: whole before a single launch, else chunk by chunk in front of each chunk's launch
             h->ext_x0 = nullptr;
+            h->x0_lazy = false;
             if (h->x0.n < static_cast<size_t>(h->nx) * h->B) h->x0.alloc(static_cast<size_t>(h->nx) * h->B);
         }
         if (cold) { h->state_zero = true; h->order_built = false; h->ad_valid = false; }
@@ -1246,7 +1268,7 @@ void* tmpc_batch_device_ptr(tmpc_batch* h, int which) {
         case 1: return h->Usol.p;
         case 2: return h->status.p;
         case 3: return h->iters.p;
-        case 4: return h->x0.p;
+        case 4: try { h->use_device(); flush_x0(h, h->stream); } catch (...) { return nullptr; } return h->x0.p;
         default: return nullptr;
     }
 }
@@ -1258,6 +1280,7 @@ int tmpc_batch_rollout_async(tmpc_batch* h, int nsteps, const double* d_x_ref_lo
         if (h->precision == 32) { set_error("rollout: the device closed loop is built for 64-bit only"); return TMPC_ERR_STATE; }
         h->use_device();
         cudaStream_t s = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : h->stream;
+        flush_x0(h, s);
         if (h->ext_x0) {   // the plant state is advanced in place: work on the internal copy
             CUDA_TRY(cudaMemcpyAsync(h->x0.p, h->ext_x0, sizeof(double) * h->nx * h->B, cudaMemcpyDeviceToDevice, s));
             h->ext_x0 = nullptr;
@@ -1325,6 +1348,7 @@ int tmpc_batch_get_x0(tmpc_batch* h, void* dst, int device_dst) {
     return guarded([&]() -> int {
         if (!h || !dst) return TMPC_ERR_DIM;
         h->use_device();
+        flush_x0(h, h->stream);
         const double* src = h->ext_x0 ? h->ext_x0 : h->x0.p;
         CUDA_TRY(cudaMemcpyAsync(dst, src, sizeof(double) * h->nx * h->B,
                                  device_dst ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, h->stream));
