@@ -9,7 +9,7 @@ import tinympc_julia_b200 as t
 
 st = torch.cuda.Stream()
 for hard in (False, True):
-    for B in (1, 64, 444, 445, 1024, 2048):
+    for B in (1, 64, 296, 297, 1024, 2048, 4096):
         c = cases.quadrotor_batch(B, hard=hard, seed=3)
         row = {"B": B, "x0": "hard" if hard else "easy"}
         for name, k in (("warp", t.KERNEL_WARP), ("tmem", t.KERNEL_TMEM)):
