@@ -108,7 +108,9 @@ def test_caller_stream_is_ordered_against_getters(orc):
     first cone / half-space solve on a caller stream (the duals are zeroed on that stream)."""
     import torch
     stream = torch.cuda.Stream()
-    for c in (cases.quadrotor_batch(WAVE + 500, hard=True, max_iter=40), cases.rocket(300, N=50)):
+    # the third case is a tiny batch: results in mapped host memory, x0 read by the latency kernel from its staging buffer
+    for c in (cases.quadrotor_batch(WAVE + 500, hard=True, max_iter=40), cases.rocket(300, N=50),
+              cases.quadrotor_batch(20, hard=True, max_iter=100)):
         want = cases.run_cuda(c)                                    # blocking path
         sol = cases.make_cuda_solver(c)
         if c["Xref"] is not None:

@@ -686,6 +686,7 @@ int tmpc_batch_set_x0(tmpc_batch* h, const double* x0, int rows, int batch) {
             return TMPC_OK;
         }
         if (h->x0_stage) {      // tiny batch: copy into the pinned staging buffer and return; the upload is stream-ordered
+            if (h->x0_lazy) sync_all(h);      // a solve still in flight reads the staging buffer itself (use_device() chained caller-stream work)
             h->x0_lazy = false;
             CUDA_TRY(cudaEventSynchronize(h->x0_staged));      // the previous upload has left the staging buffer
             std::memcpy(h->x0_stage, x0, sizeof(double) * h->nx * h->B);
