@@ -132,7 +132,7 @@ enum {
                                  per-instance refill (box constraints with shared bounds; nx=12 nu=4 with N <= 42, nx=4 nu=1) */
     TMPC_KERNEL_CONE = 4,     /* box + second-order cones + half-spaces on chip: 3 instances per warp, recursions with a lane
                                  per matrix row, projections with a lane per knot point (nx=6 nu=3, N <= 50) */
-    TMPC_KERNEL_WARP = 5      /* one warp per instance, built for latency: what AUTO picks for B <= 2048 (the single solve
+    TMPC_KERNEL_WARP = 5      /* one warp per instance, built for latency: what AUTO picks for B <= 2048 (nx=4: 4096) (the single solve
                                  behind the reference's own symbols first of all); box constraints, nx=12 nu=4 / nx=4 nu=1 */
 };
 

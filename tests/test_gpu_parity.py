@@ -150,6 +150,9 @@ def test_warp_kernel_is_what_small_batches_run_on(orc):
     for B, want_k in ((1, WARP), (2048, WARP), (2049, TMEM)):
         sol = cases.make_cuda_solver(cases.quadrotor_batch(B), kernel=t.KERNEL_AUTO)
         assert sol.kernel == want_k, (B, sol.kernel)
+    for B, want_k in ((4096, WARP), (4097, TMEM)):                                  # cartpole shape: light blocks, higher limit
+        sol = cases.make_cuda_solver(cases.cartpole_batch(B), kernel=t.KERNEL_AUTO)
+        assert sol.kernel == want_k, (B, sol.kernel)
     sol = cases.make_cuda_solver(cases.rocket(4, N=10), kernel=t.KERNEL_AUTO)      # cones: not this kernel
     assert sol.kernel != WARP
     for N in (2, 3, 45, 120):

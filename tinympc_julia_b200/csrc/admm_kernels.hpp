@@ -75,9 +75,11 @@ cudaError_t launch_admm_subwarp(const BatchView& bv, const AdmmSettings& st, con
 // ---- one warp per instance, built for latency (admm_warp.cu): the recursions with a lane per matrix row, everything else
 // over all knot points at once, state in shared memory for the whole solve.  Box-constrained problems of a compiled-in shape,
 // double build, shared dynamics; element-major carried state (interchangeable with the thread kernel).  TMPC_KERNEL_AUTO
-// picks it for batches of at most kWarpKernelAutoMaxB instances (the B = 1 singleton behind the reference's symbols first
+// picks it for batches of at most warp_kernel_auto_max_b(nx) instances (the B = 1 singleton behind the reference's symbols first
 // of all), where the throughput kernels would leave the GPU empty.
-constexpr int kWarpKernelAutoMaxB = 2048;
+constexpr int kWarpKernelAutoMaxB = 2048;            // quadrotor shape: 118 us against 138 on the TMEM kernel at 2,048, 215 against 138 at 4,096
+constexpr int kWarpKernelAutoMaxBSmall = 4096;       // cartpole shape (96 registers, 5 KB of shared memory per block): 196 us against 332 at 4,096
+inline int warp_kernel_auto_max_b(int nx) { return nx <= 4 ? kWarpKernelAutoMaxBSmall : kWarpKernelAutoMaxB; }
 bool warp_kernel_supports(const BatchView& bv, const AdmmSettings& st);
 cudaError_t launch_admm_warp(const BatchView& bv, const AdmmSettings& st, int cold, int num_sms, cudaStream_t stream);
 

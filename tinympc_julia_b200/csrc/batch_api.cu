@@ -296,7 +296,7 @@ int resolve_kernel(tmpc_batch* h) {
     if (h->kernel_pref == TMPC_KERNEL_SUBWARP) return sub_ok ? TMPC_KERNEL_SUBWARP : -1;
     if (h->kernel_pref == TMPC_KERNEL_THREAD) return TMPC_KERNEL_THREAD;
     if (h->kernel_pref != TMPC_KERNEL_AUTO) return -1;
-    if (warp_ok && h->B <= tmpc::kWarpKernelAutoMaxB) return TMPC_KERNEL_WARP;       // small batch: latency first
+    if (warp_ok && h->B <= tmpc::warp_kernel_auto_max_b(h->nx)) return TMPC_KERNEL_WARP;       // small batch: latency first
     return tm_ok ? TMPC_KERNEL_TMEM : (sub_ok ? TMPC_KERNEL_SUBWARP : (cone_ok ? TMPC_KERNEL_CONE : TMPC_KERNEL_THREAD));
 }
 

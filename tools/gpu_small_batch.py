@@ -1,4 +1,4 @@
-"""Small batches: device time of one cold solve of B quadrotor instances on the latency kernel (one warp per instance) and on
+"""Small batches: device time of one cold solve of B quadrotor (easy / hard x0) or cartpole instances on the latency kernel (one warp per instance) and on
 the throughput kernel (TMEM), CUDA events on the launching stream, median of 30 after 10; plus the B = 1 path through the
 reference's own symbols (tools/gpu_b1.py prints its split).  One JSON line per B."""
 import sys, json
@@ -8,10 +8,10 @@ import cases
 import tinympc_julia_b200 as t
 
 st = torch.cuda.Stream()
-for hard in (False, True):
+for wl in ("easy", "hard", "cartpole"):
     for B in (1, 64, 296, 297, 1024, 2048, 4096):
-        c = cases.quadrotor_batch(B, hard=hard, seed=3)
-        row = {"B": B, "x0": "hard" if hard else "easy"}
+        c = cases.cartpole_batch(B, seed=3) if wl == "cartpole" else cases.quadrotor_batch(B, hard=(wl == "hard"), seed=3)
+        row = {"B": B, "x0": wl}
         for name, k in (("warp", t.KERNEL_WARP), ("tmem", t.KERNEL_TMEM)):
             sol = cases.make_cuda_solver(c, kernel=k)
             t.set_x0(sol, c["x0"])
