@@ -8,7 +8,8 @@
  * entry points of the reference glue (reference: src/bindings.cpp) so that the unmodified
  * `src/TinyMPC.jl` drives the CUDA solver through its existing `ccall`s.  They operate on one
  * process-wide solver (reference: src/bindings.cpp:15) which here is a batch of B = 1 living
- * on the current CUDA device.
+ * on the current CUDA device (box-constrained quadrotor / cartpole shapes: on the latency kernel,
+ * TMPC_KERNEL_WARP, a block of four warps for the one instance).
  *
  * PART 2 adds the batched, handle-based variants (B independent problem instances that share
  * dynamics, cost and cache) and device-pointer variants for callers that keep their data in HBM.
@@ -132,8 +133,10 @@ enum {
                                  per-instance refill (box constraints with shared bounds; nx=12 nu=4 with N <= 42, nx=4 nu=1) */
     TMPC_KERNEL_CONE = 4,     /* box + second-order cones + half-spaces on chip: 3 instances per warp, recursions with a lane
                                  per matrix row, projections with a lane per knot point (nx=6 nu=3, N <= 50) */
-    TMPC_KERNEL_WARP = 5      /* one warp per instance, built for latency: what AUTO picks for B <= 2048 (nx=4: 4096) (the single solve
-                                 behind the reference's own symbols first of all); box constraints, nx=12 nu=4 / nx=4 nu=1 */
+    TMPC_KERNEL_WARP = 5      /* a block per instance, built for latency (recursions on one warp, the rest of an iteration over all knot
+                                 points at once on four; one warp per instance beyond 296 instances): what AUTO picks for
+                                 B <= 2048 (nx=4: 4096), the single solve behind the reference's own symbols first of all;
+                                 box constraints, nx=12 nu=4 / nx=4 nu=1, double build, shared dynamics */
 };
 
 /* Host-only: the infinite-horizon LQR cache the solve loop reads (replaces tiny_precompute_and_set_cache,
